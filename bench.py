@@ -1,0 +1,328 @@
+"""bench.py -- YOLOv1 head hot path: images/s on N B200s (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the whole head over one synthetic batch of 65,536 images
+(BASELINE.json configs[1], S=7 B=2 C=20) through the package's public API:
+    YOLOLoss forward + backward      (fused loss kernel)
+    mAPMetric.reset/update/compute   (decode + per-class NMS + TP/FP + AP reduce)
+`value` times it with the batch resident in HBM; `e2e` repeats it with the batch in
+pinned host memory (H2D inside the timed region, results read back).  Inputs (770 MB)
+exceed the 126 MB L2, so no explicit flush is needed between iterations.
+
+`--impl reference` times the CPU oracle port of the same path (oracle/, the reference
+itself is pure Python and cannot travel to the GPU box) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+S, B, C, D = 7, 2, 20, 30
+IMG_BYTES = S * S * D * 4  # 5,880
+METRIC = "head images/sec (loss fwd+bwd; decode+NMS+mAP)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--images", type=int, default=65536, help="images per GPU per step")
+    ap.add_argument("--profile", default="uniform", choices=["uniform", "realistic", "correlated", "ties"])
+    ap.add_argument("--conf", type=float, default=0.3)
+    ap.add_argument("--nms", type=float, default=0.4)
+    ap.add_argument("--cpu-sample", type=int, default=4096, help="images in the bounded CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def make_batch(n, profile, seed):
+    from yolo_v1_b200 import synth
+
+    tgt = synth.make_targets(n, seed=seed, p_obj=0.055, size_mix=True)
+    pred = synth.make_preds(n, profile, seed=seed, targets=tgt)
+    return pred, tgt
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clock / throttle reasons with NVML while the timed region runs."""
+
+    BAD = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown"}
+    NOTE = {0x4: "sw_power_cap"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                r = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in {**self.BAD, **self.NOTE}.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+
+    def summary(self):
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------ CPU baseline (oracle port)
+def cpu_pass(pred, tgt, conf, nms, threads):
+    """One pass of the head on the host: torch-CPU loss fwd+bwd + C oracle update/compute."""
+    from oracle import c_oracle, loss_oracle
+
+    loss_oracle.yolo_loss_and_grad(pred, tgt)
+    st = c_oracle.update_batch(pred.numpy(), tgt.numpy(), conf, nms, n_threads=threads)
+    c_oracle.compute(st, [0.5 + 0.05 * i for i in range(10)], n_threads=threads)
+
+
+def cpu_baseline(args, repeats=3):
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    n = args.cpu_sample
+    pred, tgt = make_batch(n, args.profile, 1234)
+    cpu_pass(pred[:256], tgt[:256], args.conf, args.nms, threads)  # warm
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        cpu_pass(pred, tgt, args.conf, args.nms, threads)
+        best = min(best, time.perf_counter() - t0)
+    return {"value": n / best, "unit": "images/s", "cores": threads, "kind": "port",
+            "sample": f"{n} images of the same workload ({args.profile}); torch-CPU loss fwd+bwd + "
+                      f"oracle/yolo_oracle.c decode/NMS/TP-FP/AP with {threads} OpenMP threads; best of {repeats}"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    n = args.cpu_sample
+    pred, tgt = make_batch(n, args.profile, 1234)
+    for _ in range(max(args.warmup, 1)):
+        cpu_pass(pred, tgt, args.conf, args.nms, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_pass(pred, tgt, args.conf, args.nms, threads)
+    dt = (time.perf_counter() - t0) / args.steps
+    v = n / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32 loss / f64 geometry", "data": "synthetic",
+        "config": workload_config(args, n),
+        "cpu_baseline": {"value": v, "unit": "images/s", "cores": threads, "kind": "port",
+                         "sample": f"each step = {n} images of the workload on the host: torch-CPU loss fwd+bwd + "
+                                   f"oracle/yolo_oracle.c with {threads} threads"},
+        "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, images_per_gpu):
+    return {"workload": f"YOLOv1 head: loss fwd+bwd + decode/per-class NMS (conf {args.conf}, IoU {args.nms}) + "
+                        f"TP/FP + mAP@50:95 on {images_per_gpu} synthetic images per GPU (S=7,B=2,C=20)",
+            "profile": args.profile, "images_per_gpu": images_per_gpu,
+            "l2": "inputs (770 MB at 65,536 images) exceed the 126 MB L2; no explicit flush"}
+
+
+# ------------------------------------------------------------------ our arm
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch.distributed as dist
+
+    from yolo_v1_b200 import YOLOLoss, _lib, head, mAPMetric
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.images
+    pred_h, tgt_h = make_batch(n, args.profile, 1234 + rank)
+    pred_h, tgt_h = pred_h.pin_memory(), tgt_h.pin_memory()
+    pred_d, tgt_d = pred_h.to(dev), tgt_h.to(dev)
+    crit = YOLOLoss()
+    metric = mAPMetric(num_classes=C, conf_threshold=args.conf, nms_threshold=args.nms)
+    if world > 1:
+        from yolo_v1_b200.distributed import DistributedMAP
+
+        metric = DistributedMAP(metric)
+
+    def step(p, t):
+        p = p.requires_grad_(True)
+        total, parts = crit(p, t)
+        total.backward()
+        metric.reset()
+        metric.update(p.detach(), t)
+        res = metric.compute()
+        return parts, res
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, out
+
+    # ---- device-resident throughput
+    for _ in range(max(args.warmup, 3)):
+        step(pred_d.detach(), tgt_d)
+    l0 = _lib.lib().yh_launch_count()
+    with ClockSampler(local) as clk:
+        ms, (parts, res) = timed(lambda: step(pred_d.detach(), tgt_d), args.steps)
+    launches = (_lib.lib().yh_launch_count() - l0) // args.steps
+    value = world * n / (ms * 1e-3)
+
+    # ---- end to end: host buffers in, results out
+    def e2e_step():
+        p = pred_h.to(dev, non_blocking=True)
+        t = tgt_h.to(dev, non_blocking=True)
+        parts, res = step(p, t)
+        return float(parts["total"]), float(res["mAP50:95"])
+
+    e2e_step()
+    e2e_ms, _ = timed(e2e_step, max(2, args.steps // 2))
+    e2e = {"value": world * n / (e2e_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": 2 * n * IMG_BYTES,
+           "d2h_bytes_per_step": 5 * 4 + 4 * C * 10 * 8 + 16 + 4 * C * 4, "ms_per_step": e2e_ms}
+
+    # ---- per-stage kernels, timed alone with CUDA events on the launching stream
+    stages = {}
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+
+    def time_call(fn, reps=10):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    from yolo_v1_b200.loss import loss_fwd_bwd
+
+    t_loss = time_call(lambda: loss_fwd_bwd(pred_d, tgt_d, S, B, C, 5.0, 0.5, True))
+    stages["loss_fwd_bwd"] = {"ms": t_loss, "bytes_per_image": 3 * IMG_BYTES,
+                              "gbs": 3 * IMG_BYTES * n / (t_loss * 1e-3) / 1e9}
+    gt_count = torch.zeros(4 * C, dtype=torch.int32, device=dev)
+    thr = [0.5 + 0.05 * i for i in range(10)]
+    t_upd = time_call(lambda: head.map_update(pred_d, tgt_d, args.conf, args.nms, thr, gt_count))
+    chunk = head.map_update(pred_d, tgt_d, args.conf, args.nms, thr, gt_count.zero_())
+    kbar = float(chunk.n_keep.float().mean().item())
+    upd_bytes = 2 * IMG_BYTES + 8 + kbar * (8 + 8 + 1 + 1 + 32) + 2.7 * 33
+    stages["map_update"] = {"ms": t_upd, "bytes_per_image": upd_bytes, "kept_per_image": kbar,
+                            "gbs": upd_bytes * n / (t_upd * 1e-3) / 1e9}
+    t_dec = time_call(lambda: head.decode_nms(pred_d, args.conf, args.nms, head.IOU_INFER, head.ORDER_GLOBAL_CONF,
+                                              want_boxes=False))
+    stages["decode_nms_infer"] = {"ms": t_dec, "bytes_per_image": IMG_BYTES + 128,
+                                  "gbs": (IMG_BYTES + 128) * n / (t_dec * 1e-3) / 1e9}
+    key, flg, off = head.compact_records(chunk)
+    M = int(off[-1].item())
+
+    def ap_only():
+        k2, f2 = key[:M].clone(), flg[:M].clone()
+        head.ap_reduce(k2, f2, M, gt_count, C, 10)
+
+    t_clone = time_call(lambda: (key[:M].clone(), flg[:M].clone()))
+    t_ap = time_call(ap_only) - t_clone
+    ap_bytes = M * 16 * (1 + 2 * 9 + 2)  # histogram read + 9 passes r+w + two flag sweeps
+    stages["ap_reduce"] = {"ms": t_ap, "records": M, "bytes": ap_bytes, "gbs": ap_bytes / (t_ap * 1e-3) / 1e9}
+    t_cmp = time_call(lambda: head.compact_records(chunk))
+    stages["compact_records"] = {"ms": t_cmp}
+
+    dom = max(("loss_fwd_bwd", "map_update"), key=lambda k: stages[k]["ms"])
+    roof = {"bound": "hbm", "kernel": {"loss_fwd_bwd": "loss_kernel<float>", "map_update": "map_update_kernel"}[dom],
+            "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": stages[dom]["gbs"] / peak,
+            "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": stages[dom]["bytes_per_image"] * n,
+            "all": {k: {"gbs": v.get("gbs"), "frac": (v["gbs"] / peak) if v.get("gbs") else None, "ms": v["ms"]}
+                    for k, v in stages.items()}}
+
+    if rank == 0:
+        cpu = None
+        if not args.no_cpu_baseline and world == 1:
+            cpu = cpu_baseline(args)
+        line = {
+            "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 loss / f64 geometry", "data": "synthetic",
+            "config": workload_config(args, n), "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cpu, "stages": stages,
+            "result_check": {"loss_total": float(parts["total"]), "mAP50:95": float(res["mAP50:95"])},
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,175 @@
+/*
+ * yolohead.h -- C ABI of libyolohead.so, the B200 (sm_100a) implementation of the
+ * YOLOv1 detection-head hot path of mattiaskvist/yolo-v1.
+ *
+ * The reference is pure Python; its "FFI" for this path is the Python call surface
+ * of src/yolo/loss.py, src/yolo/metrics.py and src/yolo/inference.py.  Each entry
+ * point below names the reference code it replaces (paths relative to the
+ * reference checkout).  The Python host in yolo_v1_b200/ binds these with ctypes,
+ * passing tensor.data_ptr() and torch.cuda.current_stream().cuda_stream.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - nothing is allocated or freed here: the caller owns all buffers, including
+ *     the workspace whose size the matching *_workspace_bytes() call returns;
+ *   - all work is enqueued on `stream` (a cudaStream_t); no call synchronises;
+ *   - return value: 0 = ok, < 0 = YH_ERR_*, > 0 = a cudaError_t from a launch;
+ *     yh_last_error() gives a message for the calling thread's last failure;
+ *   - thread-safe for calls on distinct streams with distinct buffers.
+ *   - layout constants: one image = S*S cells of D = B*5+C floats
+ *     [x0,y0,w0,h0,c0, x1,...,c1, p0..pC-1]; candidate k = (row*S + col)*B + b.
+ *     This build is specialised for S=7, B=2, C=20 (anything else returns
+ *     YH_ERR_UNSUPPORTED; the Python host raises NotImplementedError).
+ */
+#ifndef YOLOHEAD_H
+#define YOLOHEAD_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YH_VERSION 100
+
+#define YH_ERR_BAD_ARG (-1)
+#define YH_ERR_UNSUPPORTED (-2)
+#define YH_ERR_WORKSPACE (-3)
+#define YH_ERR_ALIGNMENT (-4)
+
+/* pred_dtype */
+#define YH_F32 0
+#define YH_F16 1
+#define YH_BF16 2
+
+/* iou_mode: which of the reference's IoU definitions NMS uses */
+#define YH_IOU_METRICS 0 /* metrics.py:298-341: inter/union, union == 0 -> 0            */
+#define YH_IOU_INFER 1   /* inference.py:212-249: inter/(a1 + a2 - inter + 1e-6)        */
+
+/* order of the kept list */
+#define YH_ORDER_CLASS_GROUPED 0 /* metrics.py:277-296: class groups by first appearance */
+#define YH_ORDER_GLOBAL_CONF 1   /* inference.py:302-317: global confidence order        */
+
+#define YH_MAX_THRESHOLDS 13 /* 4 subsets * T + 1 overall bit + 8 class bits fit 64 */
+
+int yh_version(void);
+const char *yh_last_error(void);
+/* kernels this library has launched in this process so far (all threads) */
+long long yh_launch_count(void);
+
+/* ---------------------------------------------------------------- loss ----
+ * Replaces YOLOLoss.forward + compute_iou + their autograd backward
+ * (src/yolo/loss.py:55-172, 174-212).
+ * parts[5] (device, fp32) = {total, coord, conf_obj, conf_noobj, class}, each
+ * already divided by N (loss.py:162-170).  grad_pred (same dtype and shape as
+ * pred; NULL = forward only) receives d total / d pred for an upstream gradient
+ * of 1.  One fused pass: 17,640 B of HBM traffic per image in fp32. */
+size_t yh_loss_workspace_bytes(int N, int S, int B, int C);
+int yh_loss_fwd_bwd(const void *pred, int pred_dtype, const float *tgt, int N, int S, int B, int C,
+                    float lambda_coord, float lambda_noobj, float *parts, void *grad_pred,
+                    void *workspace, size_t workspace_bytes, void *stream);
+
+/* grad[i] *= *scale (device scalar; the autograd upstream gradient, e.g. the
+ * GradScaler factor at training/trainer.py:75).  Every CTA returns at once when
+ * *scale == 1, so the plain fp32 training path costs no extra traffic. */
+int yh_scale_inplace(void *grad, int dtype, size_t n_elems, const float *scale, void *stream);
+
+/* ------------------------------------------------------- decode + NMS ----
+ * Replaces mAPMetric._parse_predictions + _apply_nms (metrics.py:173-218,
+ * 258-296) and YOLOInference.parse_predictions + non_max_suppression
+ * (inference.py:141-210, 251-317) for a batch of N images, one warp per image.
+ * Outputs, per image n (K = S*S*B slots each):
+ *   n_keep[n]          number of kept detections
+ *   keep_k[n*K + q]    candidate index of the q-th kept detection, in `order`
+ *   keep_cls[n*K + q]  its class;   keep_conf[n*K + q]  its confidence (fp64)
+ *   keep_box[(n*K + q)*4 ..]  (x_abs, y_abs, w, h) in fp64 as the reference builds them
+ *   n_cand[n]          candidates above conf_thr before NMS (nullable)
+ *   bad_range[n]       nonzero if any candidate above conf_thr has x,y,w,h or
+ *                      confidence outside [0,1] -- where the reference's pydantic
+ *                      schema raises (schemas.py:9-16,88) (nullable)
+ * keep_cls / keep_conf / keep_box are nullable. */
+int yh_decode_nms(const float *pred, int N, int S, int B, int C, double conf_thr, double nms_thr,
+                  int iou_mode, int order, int32_t *n_keep, uint8_t *keep_k, uint8_t *keep_cls,
+                  double *keep_conf, double *keep_box, int32_t *n_cand, uint8_t *bad_range,
+                  void *stream);
+
+/* ------------------------------------------- mAP update (fused, records) ----
+ * Replaces mAPMetric.update (metrics.py:78-100) AND the per-detection part of
+ * compute(): best-IoU ground truth, greedy TP/FP at every threshold for the four
+ * ground-truth subsets (all / small / medium / large, metrics.py:343-413,
+ * 444-491, 493-633).  Matching is image-local, so each image emits final flags.
+ * Per image n, for its q-th kept detection in (class asc, confidence desc,
+ * candidate asc) order:
+ *   rec_key[n*K+q]   = ~orderable(conf): ascending key order = confidence descending
+ *                      (orderable() maps a double to a uint64 with the same order)
+ *   rec_flags[n*K+q] = class << 56
+ *                      | bit s*T+t: TP for subset s at thresholds[t]
+ *                      | bit 4*T:   TP in the overall pass at IoU 0.5
+ *   rec_k[n*K+q]     = candidate index;  rec_pos[n*K+q] = position of this
+ *                      detection in the reference's all_predictions[n] list
+ *   rec_box[(n*K+q)*4..] = its (x_abs, y_abs, w, h) in fp64 (nullable)
+ *   n_keep[n], n_gt[n]; gt_count[s*C + c] += ground truths (atomic; zero it first)
+ *   gt_cls[n*S*S+g], gt_box[(n*S*S+g)*4..]: ground truths in the reference's list
+ *                      order and fp64 form (both nullable)
+ * thresholds_host: T doubles on the HOST (copied into the launch parameters). */
+int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int C, double conf_thr,
+                  double nms_thr, const double *thresholds_host, int T, int32_t *n_keep,
+                  uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k, uint8_t *rec_pos,
+                  double *rec_box, int32_t *n_gt, uint8_t *gt_cls, double *gt_box,
+                  int32_t *gt_count, void *stream);
+
+/* Ground truths of a batch in the reference's list form (metrics.py:220-256):
+ * gt_cls[n*S*S + g], gt_box[(n*S*S + g)*4] fp64, n_gt[n]. */
+int yh_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t *n_gt, uint8_t *gt_cls,
+                double *gt_box, void *stream);
+
+/* Compacts the fixed-stride records of yh_map_update into dense arrays in image
+ * order: offsets[n] = exclusive prefix of n_keep (offsets[N] = total).  Uses
+ * `workspace` of yh_compact_workspace_bytes(N). */
+size_t yh_compact_workspace_bytes(int N);
+int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key, const uint64_t *rec_flags,
+                       int N, int K, int64_t *offsets, uint64_t *out_key, uint64_t *out_flags,
+                       void *workspace, size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------ AP reduce ----
+ * Replaces the sort / cumsum / 11-point interpolation of
+ * mAPMetric._calculate_ap_for_class and _calculate_ap_for_size_class
+ * (metrics.py:382, 415-436, 606, 635-649) over M compact records.
+ * key/flags are scratch afterwards (the stable LSD radix sort ping-pongs between
+ * them and the workspace; ties keep image order then per-image order -- the
+ * reference's stable sorted()).  The class is read from flags >> 56.
+ *   ap[(s*C + c)*T + t]  fp64, bit-exact with the reference's arithmetic
+ *   totals[0] = overall TP (bit 4*T), totals[1] = M  (int64)
+ * gt_count[4*C] as produced by yh_map_update. */
+size_t yh_ap_workspace_bytes(int64_t M, int C, int T);
+int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int32_t *gt_count, int C, int T,
+                 double *ap, int64_t *totals, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------- list-form entry points ----
+ * The reference's helpers also accept arbitrary Python lists (tests call
+ * _apply_nms / non_max_suppression / _calculate_iou / iou on hand-built boxes,
+ * and compute() runs on whatever all_predictions holds).  These take CSR lists
+ * of fp64 boxes (x, y, w, h): list i owns [off[i], off[i+1]). */
+int yh_iou_pairs(const double *box_a, const double *box_b, int64_t n, int iou_mode, double *out,
+                 void *stream);
+/* keep_idx[off[i] + q] = index (within list i) of the q-th kept box; n_keep[i].
+ * max_len = longest list (host-known); at most 1024 boxes per list in this build. */
+int yh_nms_lists(const int64_t *off, int n_lists, const int32_t *cls, const double *conf,
+                 const double *box, double nms_thr, int iou_mode, int order, int32_t *n_keep,
+                 int32_t *keep_idx, int max_len, void *stream);
+/* TP flags for list-form detections / ground truths of the same n_lists images.
+ * Detections may be in any per-image order: "earlier" is decided as the global
+ * stable sort does (higher confidence, or equal confidence and earlier in the
+ * list).  Emits the same rec_key / rec_flags as yh_map_update (dense, CSR order)
+ * and adds to gt_count[4*C].  max_dets = most detections in one image (<= 1024). */
+int yh_match_lists(const int64_t *det_off, const int32_t *det_cls, const double *det_conf,
+                   const double *det_box, const int64_t *gt_off, const int32_t *gt_cls,
+                   const double *gt_box, int n_lists, int C, const double *thresholds_host, int T,
+                   uint64_t *rec_key, uint64_t *rec_flags, int32_t *gt_count, int max_dets,
+                   void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YOLOHEAD_H */

@@ -1,0 +1,15 @@
+"""yolo_v1_b200 -- B200-native (sm_100a) implementation of the YOLOv1 detection-head hot path.
+
+Drop-in counterparts of the reference's loss / metrics / inference modules
+(mattiaskvist/yolo-v1, src/yolo/{loss,metrics,inference,schemas}.py) over
+hand-written CUDA kernels behind a C ABI (include/yolohead.h, libyolohead.so).
+The conv backbone stays stock PyTorch/cuDNN and is not part of this package.
+"""
+from .inference import YOLOInference
+from .loss import YOLOLoss
+from .metrics import evaluate_model, mAPMetric
+from .schemas import BoundingBox, Detection
+
+__version__ = "0.1.0"
+
+__all__ = ["BoundingBox", "Detection", "YOLOInference", "YOLOLoss", "evaluate_model", "mAPMetric"]

@@ -1,0 +1,98 @@
+"""ctypes binding of libyolohead.so (include/yolohead.h).
+
+There is no fallback: if the library is missing or a call fails, the caller gets
+an exception.  Nothing here touches oracle/.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libyolohead.so")
+
+F32, F16, BF16 = 0, 1, 2
+IOU_METRICS, IOU_INFER = 0, 1
+ORDER_CLASS_GROUPED, ORDER_GLOBAL_CONF = 0, 1
+MAX_THRESHOLDS = 13
+
+_DTYPES = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
+
+_vp, _i, _d, _f, _sz, _i64 = C.c_void_p, C.c_int, C.c_double, C.c_float, C.c_size_t, C.c_int64
+
+# name -> (restype, argtypes); must list every symbol include/yolohead.h declares
+SIGNATURES = {
+    "yh_version": (_i, []),
+    "yh_last_error": (C.c_char_p, []),
+    "yh_launch_count": (C.c_longlong, []),
+    "yh_loss_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "yh_loss_fwd_bwd": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _f, _f, _vp, _vp, _vp, _sz, _vp]),
+    "yh_scale_inplace": (_i, [_vp, _i, _sz, _vp, _vp]),
+    "yh_decode_nms": (_i, [_vp, _i, _i, _i, _i, _d, _d, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "yh_map_update": (_i, [_vp, _vp, _i, _i, _i, _i, _d, _d, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "yh_parse_gt": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "yh_compact_workspace_bytes": (_sz, [_i]),
+    "yh_compact_records": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "yh_ap_workspace_bytes": (_sz, [_i64, _i, _i]),
+    "yh_ap_reduce": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "yh_iou_pairs": (_i, [_vp, _vp, _i64, _i, _vp, _vp]),
+    "yh_nms_lists": (_i, [_vp, _i, _vp, _vp, _vp, _d, _i, _i, _vp, _vp, _i, _vp]),
+    "yh_match_lists": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp]),
+}
+
+_lib = None
+
+
+class YoloHeadError(RuntimeError):
+    pass
+
+
+def lib():
+    """The loaded library; raises if it has not been built (no CPU fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise YoloHeadError(
+                f"{LIB_PATH} not found: build it with `python -m yolo_v1_b200.build` "
+                "(the head hot path has no CPU or PyTorch fallback)")
+        h = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = h
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().yh_last_error().decode("utf-8", "replace")
+        kind = {-1: "bad argument", -2: "unsupported shape", -3: "workspace too small", -4: "misaligned pointer"}.get(
+            rc, f"CUDA error {rc}" if rc > 0 else f"error {rc}")
+        if rc == -2:
+            raise NotImplementedError(f"{what}: {msg}")
+        raise YoloHeadError(f"{what}: {kind}: {msg}")
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported prediction dtype {t.dtype}; use float32, float16 or bfloat16") from None
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise YoloHeadError(
+            f"{name} is on {t.device}: the YOLOv1 head kernels run on CUDA only (no CPU fallback). "
+            "Move the tensor to the GPU first.")
+
+
+def stream_ptr(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()

@@ -1,0 +1,203 @@
+// ap_emit.cuh -- included at the end of ap_reduce.cu: cumulative TP counts over
+// the class-sorted records and the 11-point AP (metrics.py:415-436, 635-649).
+#pragma once
+
+namespace yh {
+
+struct ApCtl {                        // zeroed per call, follows SortCtl in the workspace
+    unsigned bit_total[kMaxBits];     // set bits per flag position over all records
+    unsigned seg_bits[32][kMaxBits];  // set bits at positions before the start of class c
+    unsigned long long binmax[1];     // [4*C*T*kLevels] best precision per recall bucket (flex)
+};
+
+// Per-tile population count of each flag bit.  Lane (b & 31) accumulates bit b.
+__device__ __forceinline__ void count_bits_round(uint64_t flags, bool ok, int nbits, int lane,
+                                                 unsigned acc[2]) {
+    const unsigned lo = ok ? (unsigned)flags : 0u, hi = ok ? (unsigned)(flags >> 32) : 0u;
+    unsigned ulo = __reduce_or_sync(0xffffffffu, lo), uhi = __reduce_or_sync(0xffffffffu, hi);
+    if (nbits < 32) ulo &= (1u << nbits) - 1u;
+    uhi &= nbits >= 64 ? 0xffffffffu : (nbits > 32 ? (1u << (nbits - 32)) - 1u : 0u);
+    while (ulo) {
+        const int b = __ffs(ulo) - 1;
+        ulo &= ulo - 1;
+        const unsigned m = __ballot_sync(0xffffffffu, (lo >> b) & 1u);
+        if (lane == b) acc[0] += __popc(m);
+    }
+    while (uhi) {
+        const int b = __ffs(uhi) - 1;
+        uhi &= uhi - 1;
+        const unsigned m = __ballot_sync(0xffffffffu, (hi >> b) & 1u);
+        if (lane == b) acc[1] += __popc(m);
+    }
+}
+
+// tile_bits[tile][b] = set bits b inside the tile (records in sorted order)
+__global__ void __launch_bounds__(kSortThreads)
+tile_bit_counts(const uint64_t *__restrict__ val, int64_t M, int nbits, unsigned *__restrict__ tile_bits) {
+    __shared__ unsigned s_acc[kSortWarps][kMaxBits];
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const int64_t first = (int64_t)blockIdx.x * kSortTile + wp * kWarpSpan + lane;
+    unsigned acc[2] = {0, 0};
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i) {
+        const int64_t idx = first + 32 * i;
+        const bool ok = idx < M;
+        const uint64_t f = ok ? __ldg(val + idx) : 0;
+        count_bits_round(f, ok, nbits, lane, acc);
+    }
+    s_acc[wp][lane] = acc[0];
+    s_acc[wp][lane + 32] = acc[1];
+    __syncthreads();
+    if (tid < kMaxBits) {
+        unsigned t = 0;
+#pragma unroll
+        for (int q = 0; q < kSortWarps; ++q) t += s_acc[q][tid];
+        tile_bits[(size_t)blockIdx.x * kMaxBits + tid] = t;
+    }
+}
+
+// exclusive scan over tiles, one thread per bit (tiles are few thousand at most)
+__global__ void __launch_bounds__(kMaxBits)
+scan_tile_bits(unsigned *__restrict__ tile_bits, int ntiles, ApCtl *__restrict__ ap) {
+    const int b = threadIdx.x;
+    unsigned run = 0;
+    for (int t = 0; t < ntiles; ++t) {
+        const unsigned c = tile_bits[(size_t)t * kMaxBits + b];
+        tile_bits[(size_t)t * kMaxBits + b] = run;
+        run += c;
+    }
+    ap->bit_total[b] = run;
+}
+
+// seg_bits[c][b] = set bits b at sorted positions < start of class c (one CTA per class)
+__global__ void __launch_bounds__(kSortThreads)
+class_start_bits(const uint64_t *__restrict__ val, int64_t M, int nbits, const SortCtl *__restrict__ ctl,
+                 const unsigned *__restrict__ tile_bits, ApCtl *__restrict__ ap) {
+    __shared__ unsigned s_acc[kSortWarps][kMaxBits];
+    const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const int64_t start = ctl->hist[8][c];  // records whose class is < c
+    const int64_t tile = start / kSortTile, tile0 = tile * kSortTile;
+    unsigned acc[2] = {0, 0};
+    // count inside [tile0, start); warp-strided rounds of 32 records
+    for (int64_t base = tile0 + wp * 32; base < start; base += kSortThreads) {
+        const int64_t idx = base + lane;
+        const bool ok = idx < start && idx < M;
+        const uint64_t f = ok ? __ldg(val + idx) : 0;
+        count_bits_round(f, ok, nbits, lane, acc);
+    }
+    s_acc[wp][lane] = acc[0];
+    s_acc[wp][lane + 32] = acc[1];
+    __syncthreads();
+    if (tid < kMaxBits) {
+        unsigned t = 0;
+#pragma unroll
+        for (int q = 0; q < kSortWarps; ++q) t += s_acc[q][tid];
+        const unsigned before = (start < M) ? tile_bits[(size_t)tile * kMaxBits + tid] : ap->bit_total[tid] - t;
+        ap->seg_bits[c][tid] = before + t;
+    }
+}
+
+// For every TP: ordinal within its class, rank within its class -> precision, recall
+// -> atomicMax into the highest recall level it reaches.
+__global__ void __launch_bounds__(kSortThreads)
+emit_precisions(const uint64_t *__restrict__ val, int64_t M, int C, int T, const SortCtl *__restrict__ ctl,
+                const unsigned *__restrict__ tile_bits, const int32_t *__restrict__ gt_count,
+                ApCtl *__restrict__ ap) {
+    __shared__ unsigned s_acc[kSortWarps][kMaxBits];
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const int nbits = 4 * T;  // the overall bit (4*T) only needs its total
+    const int64_t first = (int64_t)blockIdx.x * kSortTile + wp * kWarpSpan + lane;
+    uint64_t f[kSortItems];
+    unsigned acc[2] = {0, 0};
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i) {
+        const int64_t idx = first + 32 * i;
+        const bool ok = idx < M;
+        f[i] = ok ? __ldg(val + idx) : 0;
+        count_bits_round(f[i], ok, nbits, lane, acc);
+    }
+    s_acc[wp][lane] = acc[0];
+    s_acc[wp][lane + 32] = acc[1];
+    __syncthreads();
+    // running[b] for this warp = tile prefix + earlier warps of the tile; lane (b&31) holds bit b
+    unsigned run[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int b = lane + 32 * h;
+        unsigned r = tile_bits[(size_t)blockIdx.x * kMaxBits + b];
+        for (int q = 0; q < wp; ++q) r += s_acc[q][b];
+        run[h] = r;
+    }
+    const unsigned le = (lane == 31) ? 0xffffffffu : ((2u << lane) - 1u);
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i) {
+        const int64_t idx = first + 32 * i;
+        const bool ok = idx < M;
+        const unsigned lo = ok ? (unsigned)f[i] : 0u, hi = ok ? (unsigned)(f[i] >> 32) : 0u;
+        const int c = (int)(f[i] >> 56);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const unsigned mine = h ? hi : lo;
+            unsigned u = __reduce_or_sync(0xffffffffu, mine);
+            const int lim = nbits - 32 * h;
+            u &= lim >= 32 ? 0xffffffffu : (lim > 0 ? (1u << lim) - 1u : 0u);
+            while (u) {
+                const int bb = __ffs(u) - 1;
+                u &= u - 1;
+                const unsigned m = __ballot_sync(0xffffffffu, (mine >> bb) & 1u);
+                const unsigned before = __shfl_sync(0xffffffffu, run[h], bb);
+                if (lane == bb) run[h] += __popc(m);
+                if ((mine >> bb) & 1u) {
+                    const int b = bb + 32 * h, s = b / T, t = b % T;
+                    const unsigned ordinal = before + __popc(m & le) - ap->seg_bits[c][b];
+                    const int64_t rank = idx - (int64_t)ctl->hist[8][c];  // 0-based within class
+                    const int ngt = gt_count[s * C + c];
+                    const double prec = __ddiv_rn((double)ordinal, __dadd_rn((double)(rank + 1), 1e-6));
+                    const double rec = __ddiv_rn((double)ordinal, (double)ngt);
+                    int lvl = 0;
+#pragma unroll
+                    for (int r = kLevels - 1; r >= 1; --r) {
+                        const double level = (r == kLevels - 1) ? 1.0 : __dmul_rn((double)r, 0.1);
+                        if (lvl == 0 && rec >= level) lvl = r;
+                    }
+                    atomicMax(&ap->binmax[(((size_t)s * C + c) * T + t) * kLevels + lvl],
+                              (unsigned long long)__double_as_longlong(prec));
+                }
+            }
+        }
+    }
+}
+
+// ap[(s*C+c)*T+t]; totals[0] = TP of the overall pass, totals[1] = M
+__global__ void finalize_ap(int C, int T, int64_t M, const SortCtl *__restrict__ ctl,
+                            const int32_t *__restrict__ gt_count, const ApCtl *__restrict__ apc,
+                            double *__restrict__ ap, int64_t *__restrict__ totals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        totals[0] = apc->bit_total[4 * T];
+        totals[1] = M;
+    }
+    if (i >= 4 * C * T) return;
+    const int c = (i / T) % C, s = i / (T * C);
+    const unsigned n_pred = ((c + 1 < 256) ? ctl->hist[8][c + 1] : (unsigned)M) - ctl->hist[8][c];
+    const int ngt = gt_count[s * C + c];
+    if (ngt == 0 || n_pred == 0) {  // metrics.py:375-379, 592-603
+        ap[i] = 0.0;
+        return;
+    }
+    double p[kLevels];
+    double best = 0.0;
+#pragma unroll
+    for (int r = kLevels - 1; r >= 1; --r) {
+        const double v = __longlong_as_double((long long)apc->binmax[(size_t)i * kLevels + r]);
+        best = v > best ? v : best;
+        p[r] = best;
+    }
+    p[0] = 1.0;  // recall >= 0 always includes the (precision 1, recall 0) sentinel
+    double a = 0.0;
+#pragma unroll
+    for (int r = 0; r < kLevels; ++r) a = __dadd_rn(a, __ddiv_rn(p[r], 11.0));
+    ap[i] = a;
+}
+
+}  // namespace yh

@@ -1,0 +1,383 @@
+// ap_reduce.cu -- record compaction, stable 64-bit radix sort, and the
+// cumulative-TP / 11-point-AP reduction (sm_100a).
+//
+// Replaces the global half of mAPMetric.compute(): sorted(class_predictions,
+// key=conf, reverse=True) (metrics.py:382, 606), np.cumsum of tp/fp, the
+// precision/recall arrays and the 11-point interpolation (metrics.py:415-436,
+// 635-649), for all classes x thresholds x ground-truth subsets at once.
+//
+// Pipeline (every step a bandwidth-bound streaming kernel over M records):
+//   compact   fixed-stride per-image records -> dense arrays in image order
+//   sort      LSD radix, 8-bit digits, one kernel per digit: tiles take dynamic
+//             ids and publish per-digit counts; later tiles look back (chained
+//             scan), so each pass reads and writes every record exactly once.
+//             Stable, therefore equal confidences keep (image, per-image) order,
+//             which is what Python's stable sorted() leaves.  Last pass = class.
+//   bits      per-tile population count of every TP flag bit, scanned over tiles
+//   emit      for every TP: ordinal m (cumulative TP in its class), rank i ->
+//             precision m/(i+1+1e-6), recall m/n_gt; atomicMax into the recall
+//             bucket it reaches
+//   final     suffix-max over the 11 buckets, ap = sum(p_interp/11)
+#include "common.cuh"
+
+namespace yh {
+
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 8;
+constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 records per tile
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kWarpSpan = 32 * kSortItems;            // records a warp owns inside a tile
+constexpr int kPasses = 9;                             // 8 key digits + the class digit
+constexpr int kMaxBits = 64;
+constexpr int kLevels = 11;                            // np.linspace(0, 1, 11)
+constexpr unsigned kFlagAgg = 1u << 30, kFlagIncl = 2u << 30, kValMask = (1u << 30) - 1u;
+
+// ------------------------------------------------------------------ compaction
+__global__ void __launch_bounds__(1024)
+scan_counts_local(const int32_t *__restrict__ cnt, int N, int64_t *__restrict__ off,
+                  int64_t *__restrict__ block_tot) {
+    __shared__ int64_t s_w[32];
+    const int i = blockIdx.x * 1024 + threadIdx.x, lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    int64_t v = (i < N) ? cnt[i] : 0, inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int64_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_w[wp] = inc;
+    __syncthreads();
+    if (wp == 0) {
+        int64_t x = s_w[lane], xi = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int64_t t = __shfl_up_sync(0xffffffffu, xi, o);
+            if (lane >= o) xi += t;
+        }
+        s_w[lane] = xi - x;
+        if (lane == 31) block_tot[blockIdx.x] = xi;
+    }
+    __syncthreads();
+    if (i < N) off[i] = s_w[wp] + inc - v;
+}
+
+__global__ void __launch_bounds__(1024)
+scan_block_totals(int64_t *__restrict__ block_tot, int nb, int64_t *__restrict__ total_out) {
+    // single CTA; sequential chunks of 1024 with a running carry
+    __shared__ int64_t s_w[32];
+    __shared__ int64_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    for (int base = 0; base < nb; base += 1024) {
+        const int i = base + threadIdx.x;
+        int64_t v = (i < nb) ? block_tot[i] : 0, inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int64_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_w[wp] = inc;
+        __syncthreads();
+        if (wp == 0) {
+            int64_t x = s_w[lane], xi = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int64_t t = __shfl_up_sync(0xffffffffu, xi, o);
+                if (lane >= o) xi += t;
+            }
+            s_w[lane] = xi - x;
+        }
+        __syncthreads();
+        const int64_t carry = s_carry;
+        if (i < nb) block_tot[i] = carry + s_w[wp] + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = carry + s_w[wp] + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total_out = s_carry;
+}
+
+// one warp per image: add the block base to its offset and copy its records
+__global__ void __launch_bounds__(256)
+gather_records(const int32_t *__restrict__ cnt, const uint64_t *__restrict__ rec_key,
+               const uint64_t *__restrict__ rec_flags, int N, int K, int64_t *__restrict__ off,
+               const int64_t *__restrict__ block_base, uint64_t *__restrict__ out_key,
+               uint64_t *__restrict__ out_flags) {
+    const int img = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (img >= N) return;
+    const int64_t o = off[img] + block_base[img >> 10];
+    const int n = cnt[img];
+    __syncwarp();
+    if (lane == 0) off[img] = o;
+    for (int q = lane; q < n; q += 32) {
+        out_key[o + q] = __ldg(rec_key + (size_t)img * K + q);
+        out_flags[o + q] = __ldg(rec_flags + (size_t)img * K + q);
+    }
+}
+
+}  // namespace yh
+
+using namespace yh;
+
+extern "C" size_t yh_compact_workspace_bytes(int N) {
+    if (N < 0) return 0;
+    return 256 + sizeof(int64_t) * ((size_t)(N + 1023) / 1024 + 1);
+}
+
+extern "C" int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key,
+                                  const uint64_t *rec_flags, int N, int K, int64_t *offsets,
+                                  uint64_t *out_key, uint64_t *out_flags, void *workspace,
+                                  size_t workspace_bytes, void *stream) {
+    if (N < 0 || K <= 0 || !n_keep || !rec_key || !rec_flags || !offsets || !out_key || !out_flags ||
+        !workspace) {
+        set_error("yh_compact_records: bad argument");
+        return YH_ERR_BAD_ARG;
+    }
+    if (workspace_bytes < yh_compact_workspace_bytes(N)) {
+        set_error("yh_compact_records: workspace too small");
+        return YH_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t *block_tot = (int64_t *)((char *)workspace + 256);
+    const int nb = (N + 1023) / 1024;
+    if (N == 0) {
+        cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
+        return check_launch("yh_compact_records");
+    }
+    scan_counts_local<<<nb, 1024, 0, st>>>(n_keep, N, offsets, block_tot);
+    scan_block_totals<<<1, 1024, 0, st>>>(block_tot, nb, offsets + N);
+    gather_records<<<(N + 7) / 8, 256, 0, st>>>(n_keep, rec_key, rec_flags, N, K, offsets, block_tot,
+                                                out_key, out_flags);
+    return check_launch("yh_compact_records", 3);
+}
+
+// ======================================================================= sort
+namespace yh {
+
+struct SortCtl {                 // lives at the head of the workspace, zeroed per call
+    unsigned tile_counter[16];   // dynamic tile ids, one counter per pass
+    unsigned err;                // set if a look-back spin gave up (never expected)
+    unsigned pad[15];
+    unsigned hist[kPasses][256];  // global digit histograms -> exclusive digit offsets
+};
+
+__device__ __forceinline__ unsigned digit_of(uint64_t key, uint64_t val, int pass) {
+    return pass < 8 ? (unsigned)((key >> (8 * pass)) & 0xff) : (unsigned)(val >> 56);
+}
+
+// all nine digit histograms in one read of the records
+__global__ void __launch_bounds__(256)
+digit_histograms(const uint64_t *__restrict__ key, const uint64_t *__restrict__ val, int64_t M,
+                 SortCtl *__restrict__ ctl) {
+    __shared__ unsigned s_h[kPasses][256];
+    for (int i = threadIdx.x; i < kPasses * 256; i += 256) (&s_h[0][0])[i] = 0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < M; i += (int64_t)gridDim.x * 256) {
+        const uint64_t k = __ldg(key + i), v = __ldg(val + i);
+#pragma unroll
+        for (int p = 0; p < kPasses; ++p) atomicAdd(&s_h[p][digit_of(k, v, p)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < kPasses * 256; i += 256) {
+        const unsigned c = (&s_h[0][0])[i];
+        if (c) atomicAdd(&ctl->hist[0][0] + i, c);
+    }
+}
+
+// hist[p][d] -> number of records whose digit is < d  (one CTA per pass)
+__global__ void __launch_bounds__(256) digit_offsets(SortCtl *__restrict__ ctl) {
+    __shared__ unsigned s_w[8];
+    const int p = blockIdx.x, d = threadIdx.x, lane = d & 31, wp = d >> 5;
+    const unsigned v = ctl->hist[p][d];
+    unsigned inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_w[wp] = inc;
+    __syncthreads();
+    unsigned base = 0;
+    for (int q = 0; q < wp; ++q) base += s_w[q];
+    ctl->hist[p][d] = base + inc - v;
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+radix_pass(const uint64_t *__restrict__ kin, const uint64_t *__restrict__ vin,
+           uint64_t *__restrict__ kout, uint64_t *__restrict__ vout, int64_t M, int pass,
+           SortCtl *__restrict__ ctl, unsigned *__restrict__ status) {
+    __shared__ unsigned s_hist[kSortWarps][256];
+    __shared__ unsigned s_base[256];
+    __shared__ unsigned s_tile;
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(&ctl->tile_counter[pass], 1u);
+    for (int i = tid; i < kSortWarps * 256; i += kSortThreads) (&s_hist[0][0])[i] = 0;
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const int64_t first = (int64_t)tile * kSortTile + wp * kWarpSpan + lane;
+
+    uint64_t k[kSortItems], v[kSortItems];
+    unsigned dg[kSortItems], rk[kSortItems];
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i) {
+        const int64_t idx = first + 32 * i;
+        const bool ok = idx < M;
+        k[i] = ok ? __ldg(kin + idx) : 0;
+        v[i] = ok ? __ldg(vin + idx) : 0;
+    }
+    // stable rank of every record among the records of its warp with the same digit
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i) {
+        const bool ok = (first + 32 * i) < M;
+        dg[i] = digit_of(k[i], v[i], pass);
+        const unsigned act = __ballot_sync(0xffffffffu, ok);
+        unsigned peers = 0, pre = 0;
+        if (ok) {
+            peers = __match_any_sync(act, dg[i]);
+            pre = s_hist[wp][dg[i]];
+        }
+        __syncwarp();
+        if (ok) {
+            rk[i] = pre + __popc(peers & lt);
+            if ((peers & lt) == 0) s_hist[wp][dg[i]] = pre + __popc(peers);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // thread d owns digit d: warp offsets inside the tile, then the chained scan
+        const int d = tid;
+        unsigned tot = 0;
+#pragma unroll
+        for (int q = 0; q < kSortWarps; ++q) {
+            const unsigned c = s_hist[q][d];
+            s_hist[q][d] = tot;
+            tot += c;
+        }
+        volatile unsigned *st = status;
+        unsigned excl = 0;
+        if (tile == 0) {
+            st[(size_t)tile * 256 + d] = kFlagIncl | tot;
+        } else {
+            st[(size_t)tile * 256 + d] = kFlagAgg | tot;
+            for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+                unsigned s = st[(size_t)t * 256 + d];
+                unsigned spins = 0;
+                while ((s >> 30) == 0) {
+                    __nanosleep(32);
+                    s = st[(size_t)t * 256 + d];
+                    if (++spins > (1u << 22)) {
+                        atomicExch(&ctl->err, 1u);
+                        break;
+                    }
+                }
+                excl += s & kValMask;
+                if ((s >> 30) == 2 || (s >> 30) == 0) break;
+            }
+            st[(size_t)tile * 256 + d] = kFlagIncl | (excl + tot);
+        }
+        s_base[d] = ctl->hist[pass][d] + excl;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i) {
+        if ((first + 32 * i) < M) {
+            const unsigned pos = s_base[dg[i]] + s_hist[wp][dg[i]] + rk[i];
+            kout[pos] = k[i];
+            vout[pos] = v[i];
+        }
+    }
+}
+
+}  // namespace yh
+
+#include "ap_emit.cuh"
+
+namespace yh {
+
+struct ApLayout {
+    size_t ctl, apc, status, zero_end, tile_bits, key_alt, val_alt, total;
+    int ntiles;
+};
+
+static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static ApLayout ap_layout(int64_t M, int C, int T) {
+    ApLayout L;
+    L.ntiles = (int)((M + kSortTile - 1) / kSortTile);
+    if (L.ntiles < 1) L.ntiles = 1;
+    size_t o = 0;
+    L.ctl = o; o = up256(o + sizeof(SortCtl));
+    L.apc = o; o = up256(o + sizeof(ApCtl) + sizeof(unsigned long long) * (size_t)4 * C * T * kLevels);
+    L.status = o; o = up256(o + sizeof(unsigned) * (size_t)kPasses * L.ntiles * 256);
+    L.zero_end = o;
+    L.tile_bits = o; o = up256(o + sizeof(unsigned) * (size_t)L.ntiles * kMaxBits);
+    L.key_alt = o; o = up256(o + sizeof(uint64_t) * (size_t)(M > 0 ? M : 1));
+    L.val_alt = o; o = up256(o + sizeof(uint64_t) * (size_t)(M > 0 ? M : 1));
+    L.total = o;
+    return L;
+}
+
+}  // namespace yh
+
+extern "C" size_t yh_ap_workspace_bytes(int64_t M, int C, int T) {
+    if (M < 0 || C < 1 || C > 32 || T < 1 || T > YH_MAX_THRESHOLDS) return 0;
+    return ap_layout(M, C, T).total;
+}
+
+extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int32_t *gt_count, int C,
+                            int T, double *ap, int64_t *totals, void *workspace,
+                            size_t workspace_bytes, void *stream) {
+    if (C < 1 || C > 32 || T < 1 || T > YH_MAX_THRESHOLDS) {
+        set_error("yh_ap_reduce: C=%d / T=%d outside what this build carries (C<=32, T<=%d)", C, T,
+                  YH_MAX_THRESHOLDS);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (M < 0 || M >= (1ll << 30) || (M > 0 && (!key || !flags)) || !gt_count || !ap || !totals || !workspace) {
+        set_error("yh_ap_reduce: bad argument (M=%lld)", (long long)M);
+        return YH_ERR_BAD_ARG;
+    }
+    const ApLayout L = ap_layout(M, C, T);
+    if (workspace_bytes < L.total) {
+        set_error("yh_ap_reduce: workspace too small (%zu < %zu)", workspace_bytes, L.total);
+        return YH_ERR_WORKSPACE;
+    }
+    if ((uintptr_t)workspace % 256) {
+        set_error("yh_ap_reduce: workspace must be 256-byte aligned");
+        return YH_ERR_ALIGNMENT;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    char *ws = (char *)workspace;
+    SortCtl *ctl = (SortCtl *)(ws + L.ctl);
+    ApCtl *apc = (ApCtl *)(ws + L.apc);
+    unsigned *status = (unsigned *)(ws + L.status);
+    unsigned *tile_bits = (unsigned *)(ws + L.tile_bits);
+    uint64_t *kb = (uint64_t *)(ws + L.key_alt), *vb = (uint64_t *)(ws + L.val_alt);
+    cudaError_t e = cudaMemsetAsync(ws, 0, L.zero_end, st);
+    if (e != cudaSuccess) {
+        set_error("yh_ap_reduce: memset: %s", cudaGetErrorString(e));
+        return (int)e;
+    }
+    const uint64_t *sorted_val = flags;
+    if (M > 0) {
+        int hb = (int)((M + 256 * 16 - 1) / (256 * 16));
+        if (hb > 148 * 8) hb = 148 * 8;
+        digit_histograms<<<hb, 256, 0, st>>>(key, flags, M, ctl);
+        digit_offsets<<<kPasses, 256, 0, st>>>(ctl);
+        uint64_t *ki = key, *vi = flags, *ko = kb, *vo = vb;
+        for (int p = 0; p < kPasses; ++p) {
+            radix_pass<<<L.ntiles, kSortThreads, 0, st>>>(ki, vi, ko, vo, M, p, ctl,
+                                                          status + (size_t)p * L.ntiles * 256);
+            uint64_t *t = ki; ki = ko; ko = t;
+            t = vi; vi = vo; vo = t;
+        }
+        sorted_val = vi;  // nine passes: the sorted records sit in the workspace copies
+        const int nbits = 4 * T + 1;
+        tile_bit_counts<<<L.ntiles, kSortThreads, 0, st>>>(sorted_val, M, nbits, tile_bits);
+        scan_tile_bits<<<1, kMaxBits, 0, st>>>(tile_bits, L.ntiles, apc);
+        class_start_bits<<<C, kSortThreads, 0, st>>>(sorted_val, M, nbits, ctl, tile_bits, apc);
+        emit_precisions<<<L.ntiles, kSortThreads, 0, st>>>(sorted_val, M, C, T, ctl, tile_bits, gt_count, apc);
+    }
+    finalize_ap<<<(4 * C * T + 127) / 128, 128, 0, st>>>(C, T, M, ctl, gt_count, apc, ap, totals);
+    return check_launch("yh_ap_reduce", M > 0 ? 2 + kPasses + 4 + 1 : 1);
+}

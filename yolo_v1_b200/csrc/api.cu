@@ -1,0 +1,34 @@
+// api.cu -- version / error plumbing of libyolohead.so.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "common.cuh"
+
+namespace yh {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_launch(const char *what, int kernels_launched) {
+    g_launches.fetch_add(kernels_launched, std::memory_order_relaxed);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return (int)e;
+    }
+    return 0;
+}
+
+}  // namespace yh
+
+extern "C" int yh_version(void) { return YH_VERSION; }
+extern "C" const char *yh_last_error(void) { return yh::g_err; }
+extern "C" long long yh_launch_count(void) { return yh::g_launches.load(std::memory_order_relaxed); }

@@ -1,0 +1,124 @@
+// common.cuh -- shared helpers for libyolohead.so (sm_100a only).
+//
+// Arithmetic rules (SURVEY.md section 7 "hard parts"): the reference computes the
+// decode / NMS / matching geometry in Python doubles, one rounding per operator.
+// Every TU is compiled with -fmad=false and the fp64 helpers below use the
+// explicit round-to-nearest intrinsics, so no multiply-add is ever contracted.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/yolohead.h"
+
+namespace yh {
+
+constexpr int kS = 7;
+constexpr int kB = 2;
+constexpr int kC = 20;
+constexpr int kD = kB * 5 + kC;       // 30 floats per cell
+constexpr int kCells = kS * kS;       // 49
+constexpr int kCand = kCells * kB;    // 98 candidates per image
+constexpr int kImgFloats = kCells * kD;  // 1470 floats = 5880 B per image
+
+void set_error(const char *fmt, ...);
+int check_launch(const char *what, int kernels_launched = 1);
+
+inline bool shape_ok(int S, int B, int C) { return S == kS && B == kB && C == kC; }
+
+// ---- Python float semantics -------------------------------------------------
+// builtin max(a, b) / min(a, b): first argument unless the second is strictly
+// greater / smaller (so a NaN second argument never wins).
+__device__ __forceinline__ double py_max(double a, double b) { return (b > a) ? b : a; }
+__device__ __forceinline__ double py_min(double a, double b) { return (b < a) ? b : a; }
+
+struct Corners {
+    double x1, y1, x2, y2, area;
+};
+
+// (x, y, w, h) -> corners and area exactly as metrics.py:317-320,333-334 and
+// schemas.py:25-28,55 build them (x - w / 2 etc., w * h).
+__device__ __forceinline__ Corners corners_of(double x, double y, double w, double h) {
+    Corners c;
+    double hw = __dmul_rn(w, 0.5), hh = __dmul_rn(h, 0.5);  // w / 2 is exact either way
+    c.x1 = __dsub_rn(x, hw);
+    c.y1 = __dsub_rn(y, hh);
+    c.x2 = __dadd_rn(x, hw);
+    c.y2 = __dadd_rn(y, hh);
+    c.area = __dmul_rn(w, h);
+    return c;
+}
+
+// Intersection area, argument order as the reference (first box = a).
+__device__ __forceinline__ double inter_area(const Corners &a, const Corners &b) {
+    double ix1 = py_max(a.x1, b.x1), iy1 = py_max(a.y1, b.y1);
+    double ix2 = py_min(a.x2, b.x2), iy2 = py_min(a.y2, b.y2);
+    double dx = py_max(0.0, __dsub_rn(ix2, ix1));
+    double dy = py_max(0.0, __dsub_rn(iy2, iy1));
+    return __dmul_rn(dx, dy);
+}
+
+// Denominator of the IoU: metrics.py:335 (a1 + a2 - inter) or inference.py:248
+// (a1 + a2 - inter + 1e-6).
+template <int MODE>
+__device__ __forceinline__ double iou_denominator(const Corners &a, const Corners &b, double inter) {
+    double u = __dsub_rn(__dadd_rn(a.area, b.area), inter);
+    if (MODE == YH_IOU_INFER) u = __dadd_rn(u, 1e-6);
+    return u;
+}
+
+template <int MODE>
+__device__ __forceinline__ double iou_exact(const Corners &a, const Corners &b) {
+    double inter = inter_area(a, b);
+    double u = iou_denominator<MODE>(a, b, inter);
+    if (MODE == YH_IOU_METRICS && u == 0.0) return 0.0;
+    return __ddiv_rn(inter, u);
+}
+
+// "is IoU(a, b) < thr" -- the keep test of NMS (metrics.py:293, inference.py:314).
+// Decides without the division whenever inter and thr*denominator are further
+// apart than any rounding could bridge; falls back to the exact quotient
+// otherwise, so the outcome is always the reference's.
+template <int MODE>
+__device__ __forceinline__ bool iou_below(const Corners &a, const Corners &b, double thr) {
+    double inter = inter_area(a, b);
+    double u = iou_denominator<MODE>(a, b, inter);
+    if (MODE == YH_IOU_METRICS && u == 0.0) return 0.0 < thr;
+    if (u > 0.0 && thr > 0.0 && inter >= 0.0 && u < 1e300 && inter < 1e300) {
+        double t = __dmul_rn(thr, u);
+        if (t > 1e-280) {
+            double slack = __dmul_rn(t, 1e-12);
+            if (inter < __dsub_rn(t, slack)) return true;
+            if (inter > __dadd_rn(t, slack)) return false;
+        }
+    }
+    return __ddiv_rn(inter, u) < thr;
+}
+
+// Monotone map double -> uint64 (ascending).  -0.0 sorts just below +0.0.
+__device__ __forceinline__ uint64_t orderable(double v) {
+    uint64_t b = (uint64_t)__double_as_longlong(v);
+    return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double from_orderable(uint64_t k) {
+    uint64_t b = (k & 0x8000000000000000ull) ? (k & 0x7fffffffffffffffull) : ~k;
+    return __longlong_as_double((long long)b);
+}
+
+// torch.argmax over the C class scores of one cell: first maximum, NaN maximal.
+__device__ __forceinline__ int argmax_first(const float *v, int n, float &best_v) {
+    int best = 0;
+    float bv = v[0];
+#pragma unroll
+    for (int i = 1; i < n; ++i) {
+        float x = v[i];
+        if ((x > bv) || (x != x && bv == bv)) {
+            best = i;
+            bv = x;
+        }
+    }
+    best_v = bv;
+    return best;
+}
+
+}  // namespace yh

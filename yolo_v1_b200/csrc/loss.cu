@@ -1,0 +1,365 @@
+// loss.cu -- fused YOLOv1 loss forward + backward (sm_100a).
+//
+// Replaces YOLOLoss.forward / compute_iou and their autograd backward
+// (reference src/yolo/loss.py:55-172, 174-212).  One pass over the batch reads
+// pred and target once and writes d(total)/d(pred) once: 17,640 B per image.
+//
+// Mapping: a CTA owns a tile of kTile consecutive cells (a cell = 30 floats).
+// The tile is staged through shared memory with coalesced 8-byte accesses
+// (a cell is 120 B, so 8 B is the widest alignment every cell start has); each
+// thread then owns one cell, reads it with conflict-free LDS.64 (cell stride =
+// 15 x 8 B, odd), and writes its gradient back in place for the coalesced store.
+// Loss terms are reduced warp -> CTA -> (fp64) global partials; the last CTA to
+// finish folds the partials in a fixed order, so results are deterministic.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace yh {
+
+constexpr int kTile = 128;              // cells per CTA == threads per CTA
+constexpr int kPairs = kD / 2;          // 15 two-element pairs per cell
+constexpr int kTilePairs = kTile * kPairs;
+
+// ---- element-pair global I/O for the three prediction dtypes ----------------
+template <typename T> struct Pair;
+template <> struct Pair<float> {
+    using G = float2;
+    static __device__ __forceinline__ float2 load(const G *p) { return __ldg(p); }
+    static __device__ __forceinline__ G store(float2 v) { return v; }
+};
+template <> struct Pair<__half> {
+    using G = __half2;
+    static __device__ __forceinline__ float2 load(const G *p) { return __half22float2(*p); }
+    static __device__ __forceinline__ G store(float2 v) { return __float22half2_rn(v); }
+};
+template <> struct Pair<__nv_bfloat16> {
+    using G = __nv_bfloat162;
+    static __device__ __forceinline__ float2 load(const G *p) { return __bfloat1622float2(*p); }
+    static __device__ __forceinline__ G store(float2 v) { return __float22bfloat162_rn(v); }
+};
+
+// torch.maximum / torch.minimum / clamp(min=0): NaN propagates.
+__device__ __forceinline__ float t_max(float a, float b) { return (a > b || a != a) ? a : b; }
+__device__ __forceinline__ float t_min(float a, float b) { return (a < b || a != a) ? a : b; }
+__device__ __forceinline__ float t_relu(float v) { return (v < 0.f) ? 0.f : v; }
+
+struct IouCtx {  // forward values the backward needs
+    float iou, inter, U, iw, ih, rawx, rawy;
+    float px1, px2, py1, py2;
+};
+
+// loss.py:191-212 in fp32, one rounding per operator (-fmad=false).
+__device__ __forceinline__ IouCtx iou_fwd(float x, float y, float w, float h, float tx1, float tx2,
+                                          float ty1, float ty2, float tarea) {
+    IouCtx c;
+    float hw = w * 0.5f, hh = h * 0.5f;
+    c.px1 = x - hw; c.px2 = x + hw;
+    c.py1 = y - hh; c.py2 = y + hh;
+    c.rawx = t_min(c.px2, tx2) - t_max(c.px1, tx1);
+    c.rawy = t_min(c.py2, ty2) - t_max(c.py1, ty1);
+    c.iw = t_relu(c.rawx);
+    c.ih = t_relu(c.rawy);
+    c.inter = c.iw * c.ih;
+    float uni = (w * h + tarea) - c.inter;
+    c.U = uni + 1e-6f;
+    c.iou = c.inter / c.U;
+    return c;
+}
+
+// gradient of torch.maximum(self, other) w.r.t. self: 1, 1/2 at equality, 0.
+__device__ __forceinline__ float max_mask(float self, float other) {
+    return (self < other) ? 0.f : ((self == other) ? 0.5f : 1.f);
+}
+__device__ __forceinline__ float min_mask(float self, float other) {
+    return (self > other) ? 0.f : ((self == other) ? 0.5f : 1.f);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kTile)
+loss_kernel(const typename Pair<T>::G *__restrict__ pred, const float2 *__restrict__ tgt,
+            typename Pair<T>::G *__restrict__ grad, long long n_cells, float lambda_coord,
+            float lambda_noobj, float inv_n, double *__restrict__ partials,
+            unsigned int *__restrict__ ticket, float *__restrict__ parts) {
+    __shared__ float2 s_pred[kTilePairs];
+    __shared__ float2 s_tgt[kTilePairs];
+    __shared__ double s_red[kTile / 32][4];
+    __shared__ bool s_last;
+
+    const int tid = threadIdx.x;
+    const long long cell0 = (long long)blockIdx.x * kTile;
+    const int cells_here = (int)min((long long)kTile, n_cells - cell0);
+    const int pairs_here = cells_here * kPairs;
+    const long long pair0 = cell0 * kPairs;
+
+    // stage the tile: 15 independent 8-byte loads per thread per tensor
+#pragma unroll
+    for (int i = 0; i < kPairs; ++i) {
+        int p = tid + i * kTile;
+        if (p < pairs_here) {
+            s_pred[p] = Pair<T>::load(pred + pair0 + p);
+            s_tgt[p] = __ldg(tgt + pair0 + p);
+        }
+    }
+    __syncthreads();
+
+    float acc_coord = 0.f, acc_obj = 0.f, acc_noobj = 0.f, acc_cls = 0.f;
+    if (tid < cells_here) {
+        float p[kD], t[kD];
+#pragma unroll
+        for (int i = 0; i < kPairs; ++i) {
+            float2 a = s_pred[tid * kPairs + i], b = s_tgt[tid * kPairs + i];
+            p[2 * i] = a.x; p[2 * i + 1] = a.y;
+            t[2 * i] = b.x; t[2 * i + 1] = b.y;
+        }
+        float g[kD];
+#pragma unroll
+        for (int i = 0; i < kD; ++i) g[i] = 0.f;
+
+        const bool has0 = t[4] > 0.f, has1 = t[9] > 0.f;
+        const bool obj = has0 || has1;                    // loss.py:98-99
+        const int slot = (!has0 && has1) ? 1 : 0;         // loss.py:102 (first filled slot)
+        const float gn = inv_n * lambda_noobj;
+        if (!obj) {
+            // no-object cell: both confidences are "noobj" terms (loss.py:150-153)
+            acc_noobj = p[4] * p[4] + p[9] * p[9];
+            g[4] = gn * (2.f * p[4]);
+            g[9] = gn * (2.f * p[9]);
+        } else {
+            const float tx = slot ? t[5] : t[0], ty = slot ? t[6] : t[1];
+            const float tw = slot ? t[7] : t[2], th = slot ? t[8] : t[3];
+            const float thw = tw * 0.5f, thh = th * 0.5f;
+            const float tx1 = tx - thw, tx2 = tx + thw, ty1 = ty - thh, ty2 = ty + thh;
+            const float tarea = tw * th;
+            IouCtx c0 = iou_fwd(p[0], p[1], p[2], p[3], tx1, tx2, ty1, ty2, tarea);
+            IouCtx c1 = iou_fwd(p[5], p[6], p[7], p[8], tx1, tx2, ty1, ty2, tarea);
+            // argmax over B=2 (loss.py:110): first maximum, NaN counts as maximal
+            const bool pick1 = (c1.iou > c0.iou) || (c1.iou != c1.iou && c0.iou == c0.iou);
+            const IouCtx c = pick1 ? c1 : c0;
+            // responsible box (x, y, w, h, conf) and the other box's confidence, by select
+            // (no runtime-indexed register arrays)
+            const float x = pick1 ? p[5] : p[0], y = pick1 ? p[6] : p[1];
+            const float w = pick1 ? p[7] : p[2], h = pick1 ? p[8] : p[3];
+            const float cf = pick1 ? p[9] : p[4], co = pick1 ? p[4] : p[9];
+
+            // --- coordinate term (loss.py:126-137)
+            const float dx = x - tx, dy = y - ty;
+            const float wc = t_max(w, 1e-6f), hc = t_max(h, 1e-6f);
+            const float sw = sqrtf(wc), sh = sqrtf(hc);
+            const float dw = sw - sqrtf(t_max(tw, 1e-6f)), dh = sh - sqrtf(t_max(th, 1e-6f));
+            acc_coord = (dx * dx + dy * dy) + (dw * dw + dh * dh);
+            // --- confidence terms (loss.py:142-153); IoU target is not detached
+            const float dc = cf - c.iou;
+            acc_obj = dc * dc;
+            acc_noobj = co * co;
+            // --- class term (loss.py:156-157)
+            float cs = 0.f;
+#pragma unroll
+            for (int k = kB * 5; k < kD; ++k) {
+                float d = p[k] - t[k];
+                cs += d * d;
+                g[k] = inv_n * (2.f * d);
+            }
+            acc_cls = cs;
+
+            // --- backward
+            const float gc = inv_n * lambda_coord;
+            const float g_other = gn * (2.f * co);
+            const float g_resp = inv_n * (2.f * dc);
+            float gx = gc * (2.f * dx), gy = gc * (2.f * dy);
+            // sqrt'(v) = 1/(2 sqrt v); clamp(min) passes the gradient where w >= 1e-6
+            float gw = (w >= 1e-6f) ? (gc * (2.f * dw)) / (2.f * sw) : 0.f;
+            float gh = (h >= 1e-6f) ? (gc * (2.f * dh)) / (2.f * sh) : 0.f;
+            // through the IoU (d conf_obj / d iou = -2 dc)
+            const float gi = -(inv_n * (2.f * dc));
+            const float g_union = -gi * c.inter / (c.U * c.U);
+            const float g_inter = gi / c.U - g_union;
+            gw += g_union * h;
+            gh += g_union * w;
+            const float g_rawx = (c.rawx >= 0.f) ? g_inter * c.ih : 0.f;
+            const float g_rawy = (c.rawy >= 0.f) ? g_inter * c.iw : 0.f;
+            const float gpx2 = g_rawx * min_mask(c.px2, tx2), gpx1 = -g_rawx * max_mask(c.px1, tx1);
+            const float gpy2 = g_rawy * min_mask(c.py2, ty2), gpy1 = -g_rawy * max_mask(c.py1, ty1);
+            gx += gpx1 + gpx2;
+            gy += gpy1 + gpy2;
+            gw += (gpx2 - gpx1) * 0.5f;
+            gh += (gpy2 - gpy1) * 0.5f;
+            g[0] = pick1 ? 0.f : gx; g[1] = pick1 ? 0.f : gy;
+            g[2] = pick1 ? 0.f : gw; g[3] = pick1 ? 0.f : gh;
+            g[4] = pick1 ? g_other : g_resp;
+            g[5] = pick1 ? gx : 0.f; g[6] = pick1 ? gy : 0.f;
+            g[7] = pick1 ? gw : 0.f; g[8] = pick1 ? gh : 0.f;
+            g[9] = pick1 ? g_resp : g_other;
+        }
+        if (grad != nullptr) {
+#pragma unroll
+            for (int i = 0; i < kPairs; ++i)
+                s_pred[tid * kPairs + i] = make_float2(g[2 * i], g[2 * i + 1]);
+        }
+    }
+
+    // CTA reduction of the four terms
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        acc_coord += __shfl_down_sync(0xffffffffu, acc_coord, off);
+        acc_obj += __shfl_down_sync(0xffffffffu, acc_obj, off);
+        acc_noobj += __shfl_down_sync(0xffffffffu, acc_noobj, off);
+        acc_cls += __shfl_down_sync(0xffffffffu, acc_cls, off);
+    }
+    if ((tid & 31) == 0) {
+        s_red[tid >> 5][0] = acc_coord; s_red[tid >> 5][1] = acc_obj;
+        s_red[tid >> 5][2] = acc_noobj; s_red[tid >> 5][3] = acc_cls;
+    }
+    __syncthreads();
+
+    if (grad != nullptr) {
+#pragma unroll
+        for (int i = 0; i < kPairs; ++i) {
+            int q = tid + i * kTile;
+            if (q < pairs_here) grad[pair0 + q] = Pair<T>::store(s_pred[q]);
+        }
+    }
+
+    if (tid < 4) {
+        double s = 0.0;
+#pragma unroll
+        for (int wdx = 0; wdx < kTile / 32; ++wdx) s += s_red[wdx][tid];
+        partials[(size_t)blockIdx.x * 4 + tid] = s;
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (!s_last) return;
+
+    // last CTA: fold all partials in a fixed order (deterministic)
+    __threadfence();
+    double a[4] = {0.0, 0.0, 0.0, 0.0};
+    for (unsigned b = tid; b < gridDim.x; b += kTile) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[k] += __ldcg(partials + (size_t)b * 4 + k);
+    }
+    __shared__ double s_fin[kTile][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s_fin[tid][k] = a[k];
+    __syncthreads();
+    for (int st = kTile / 2; st > 0; st >>= 1) {
+        if (tid < st) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_fin[tid][k] += s_fin[tid + st][k];
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        double coord = (double)lambda_coord * s_fin[0][0];
+        double cobj = s_fin[0][1];
+        double noobj = (double)lambda_noobj * s_fin[0][2];
+        double cls = s_fin[0][3];
+        double invn = (double)inv_n;
+        parts[0] = (float)((coord + cobj + noobj + cls) * invn);
+        parts[1] = (float)(coord * invn);
+        parts[2] = (float)(cobj * invn);
+        parts[3] = (float)(noobj * invn);
+        parts[4] = (float)(cls * invn);
+        *ticket = 0u;  // leave the workspace ready for the next call
+    }
+}
+
+template <typename T>
+__global__ void scale_kernel(T *__restrict__ g, size_t n, const float *__restrict__ scale) {
+    const float s = __ldg(scale);
+    if (s == 1.0f) return;  // plain fp32 training: upstream gradient is exactly 1
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (size_t)gridDim.x * blockDim.x)
+        g[i] = (T)((float)g[i] * s);
+}
+
+}  // namespace yh
+
+using namespace yh;
+
+extern "C" size_t yh_loss_workspace_bytes(int N, int S, int B, int C) {
+    if (N < 0 || !shape_ok(S, B, C)) return 0;
+    size_t cells = (size_t)N * kCells;
+    size_t blocks = (cells + kTile - 1) / kTile;
+    return 256 + blocks * 4 * sizeof(double);
+}
+
+extern "C" int yh_loss_fwd_bwd(const void *pred, int pred_dtype, const float *tgt, int N, int S,
+                               int B, int C, float lambda_coord, float lambda_noobj, float *parts,
+                               void *grad_pred, void *workspace, size_t workspace_bytes,
+                               void *stream) {
+    if (!shape_ok(S, B, C)) {
+        set_error("yh_loss_fwd_bwd: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (N <= 0 || !pred || !tgt || !parts || !workspace) {
+        set_error("yh_loss_fwd_bwd: bad argument (N=%d)", N);
+        return YH_ERR_BAD_ARG;
+    }
+    if (workspace_bytes < yh_loss_workspace_bytes(N, S, B, C)) {
+        set_error("yh_loss_fwd_bwd: workspace too small");
+        return YH_ERR_WORKSPACE;
+    }
+    const size_t esz = (pred_dtype == YH_F32) ? 4 : 2;
+    if (((uintptr_t)pred % (2 * esz)) || ((uintptr_t)tgt % 8) || ((uintptr_t)grad_pred % (2 * esz)) ||
+        ((uintptr_t)workspace % 256)) {
+        set_error("yh_loss_fwd_bwd: pointers must be aligned to one element pair (workspace: 256 B)");
+        return YH_ERR_ALIGNMENT;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    long long cells = (long long)N * kCells;
+    unsigned blocks = (unsigned)((cells + kTile - 1) / kTile);
+    unsigned int *ticket = (unsigned int *)workspace;
+    double *partials = (double *)((char *)workspace + 256);
+    cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st);
+    if (e != cudaSuccess) {
+        set_error("yh_loss_fwd_bwd: memset: %s", cudaGetErrorString(e));
+        return (int)e;
+    }
+    const float inv_n = 1.0f / (float)N;
+    switch (pred_dtype) {
+        case YH_F32:
+            loss_kernel<float><<<blocks, kTile, 0, st>>>((const float2 *)pred, (const float2 *)tgt,
+                                                         (float2 *)grad_pred, cells, lambda_coord,
+                                                         lambda_noobj, inv_n, partials, ticket, parts);
+            break;
+        case YH_F16:
+            loss_kernel<__half><<<blocks, kTile, 0, st>>>((const __half2 *)pred, (const float2 *)tgt,
+                                                          (__half2 *)grad_pred, cells, lambda_coord,
+                                                          lambda_noobj, inv_n, partials, ticket, parts);
+            break;
+        case YH_BF16:
+            loss_kernel<__nv_bfloat16><<<blocks, kTile, 0, st>>>(
+                (const __nv_bfloat162 *)pred, (const float2 *)tgt, (__nv_bfloat162 *)grad_pred, cells,
+                lambda_coord, lambda_noobj, inv_n, partials, ticket, parts);
+            break;
+        default:
+            set_error("yh_loss_fwd_bwd: unknown pred_dtype %d", pred_dtype);
+            return YH_ERR_BAD_ARG;
+    }
+    return check_launch("yh_loss_fwd_bwd");
+}
+
+extern "C" int yh_scale_inplace(void *grad, int dtype, size_t n_elems, const float *scale,
+                                void *stream) {
+    if (!grad || !scale) {
+        set_error("yh_scale_inplace: null pointer");
+        return YH_ERR_BAD_ARG;
+    }
+    if (n_elems == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned blocks = (unsigned)min((size_t)148 * 16, (n_elems + 255) / 256);
+    switch (dtype) {
+        case YH_F32: scale_kernel<float><<<blocks, 256, 0, st>>>((float *)grad, n_elems, scale); break;
+        case YH_F16: scale_kernel<__half><<<blocks, 256, 0, st>>>((__half *)grad, n_elems, scale); break;
+        case YH_BF16:
+            scale_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((__nv_bfloat16 *)grad, n_elems, scale);
+            break;
+        default:
+            set_error("yh_scale_inplace: unknown dtype %d", dtype);
+            return YH_ERR_BAD_ARG;
+    }
+    return check_launch("yh_scale_inplace");
+}

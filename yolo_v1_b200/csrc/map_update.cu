@@ -1,0 +1,288 @@
+// map_update.cu -- yh_map_update: decode + NMS + ground-truth parse + TP/FP matching
+// fused into one pass over (pred, target), one warp per image; plus yh_parse_gt.
+//
+// Replaces mAPMetric.update (metrics.py:78-100) and the per-detection half of
+// compute(): best-IoU ground truth and greedy TP/FP marking for every IoU
+// threshold and every ground-truth subset (metrics.py:391-413, 465-486, 613-633).
+// The reference does that matching after a global sort, but a detection only ever
+// meets ground truths and rival detections of its own image and class, and their
+// relative order in the global stable sort equals their per-image order, so the
+// flags can be finalised here (verified against the
+// reference's tp arrays in tests/golden/map_small.npz).
+#include "head_image.cuh"
+
+namespace yh {
+
+constexpr int kWarpsPerCtaM = 4;
+
+struct Thresholds {
+    double t[YH_MAX_THRESHOLDS];
+    int n;
+};
+
+// Ground truths of one target image -> MatchOverlay (compact, in cell order).
+// Returns the number of ground truths.  gt_hist (shared, 4*kC ints) accumulates
+// the per-(subset, class) counts of this CTA.
+__device__ __forceinline__ int parse_targets(WarpWindow &w, int lane, int *gt_hist,
+                                             uint8_t *__restrict__ out_cls, double *__restrict__ out_box) {
+    const float *st = reinterpret_cast<const float *>(w.stage);
+    bool is_gt[2];
+    int cls[2];
+    float x[2], y[2], bw[2], bh[2];
+#pragma unroll
+    for (int cs = 0; cs < 2; ++cs) {
+        const int cell = lane + 32 * cs;
+        const bool live = cell < kCells;
+        const float *c = st + (live ? cell : 0) * kD;
+        is_gt[cs] = live && (c[4] > 0.f);  // slot-0 confidence only (metrics.py:239)
+        x[cs] = c[0]; y[cs] = c[1]; bw[cs] = c[2]; bh[cs] = c[3];
+        float cls_p[kC];
+#pragma unroll
+        for (int i = 0; i < kC / 2; ++i) {
+            float2 v = *reinterpret_cast<const float2 *>(c + kB * 5 + 2 * i);
+            cls_p[2 * i] = v.x;
+            cls_p[2 * i + 1] = v.y;
+        }
+        float pv;
+        cls[cs] = argmax_first(cls_p, kC, pv);
+    }
+    const unsigned m0 = __ballot_sync(kFull, is_gt[0]), m1 = __ballot_sync(kFull, is_gt[1]);
+    const unsigned lt = (1u << lane) - 1u;
+    __syncwarp();  // all lanes hold their cells; `stage` may be overwritten now
+    MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
+    const double small_a = __dmul_rn(__ddiv_rn(32.0, 448.0), __ddiv_rn(32.0, 448.0));   // metrics.py:511
+    const double medium_a = __dmul_rn(__ddiv_rn(96.0, 448.0), __ddiv_rn(96.0, 448.0));  // metrics.py:512
+#pragma unroll
+    for (int cs = 0; cs < 2; ++cs)
+        if (is_gt[cs]) {
+            const int g = cs ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
+            const int cell = lane + 32 * cs;
+            const double xa = abs_coord(cell % kS, x[cs]), ya = abs_coord(cell / kS, y[cs]);
+            const Corners cr = corners_of(xa, ya, (double)bw[cs], (double)bh[cs]);
+            mo.gx1[g] = cr.x1; mo.gy1[g] = cr.y1; mo.gx2[g] = cr.x2; mo.gy2[g] = cr.y2;
+            mo.garea[g] = cr.area;
+            mo.gcls[g] = (uint8_t)cls[cs];
+            const int bucket = (cr.area < small_a) ? 1 : ((cr.area < medium_a) ? 2 : 3);
+            mo.gbucket[g] = (uint8_t)bucket;
+            if (out_cls != nullptr) out_cls[g] = (uint8_t)cls[cs];
+            if (out_box != nullptr) {  // the reference's (x, y, w, h) tuple, metrics.py:254
+                out_box[4 * g + 0] = xa; out_box[4 * g + 1] = ya;
+                out_box[4 * g + 2] = (double)bw[cs]; out_box[4 * g + 3] = (double)bh[cs];
+            }
+            atomicAdd(&gt_hist[cls[cs]], 1);
+            atomicAdd(&gt_hist[bucket * kC + cls[cs]], 1);
+        }
+    __syncwarp();
+    return __popc(m0) + __popc(m1);
+}
+
+__global__ void __launch_bounds__(kWarpsPerCtaM * 32)
+map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt, int N,
+                  double conf_thr, double nms_thr, Thresholds thr, int32_t *__restrict__ n_keep,
+                  uint64_t *__restrict__ rec_key, uint64_t *__restrict__ rec_flags,
+                  uint8_t *__restrict__ rec_k, uint8_t *__restrict__ rec_pos,
+                  double *__restrict__ rec_box, int32_t *__restrict__ n_gt,
+                  uint8_t *__restrict__ gt_cls, double *__restrict__ gt_box,
+                  int32_t *__restrict__ gt_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    WarpWindow *windows = reinterpret_cast<WarpWindow *>(smem_raw);
+    __shared__ int gt_hist[4 * kC];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    WarpWindow &w = windows[wib];
+    const int warps_total = gridDim.x * kWarpsPerCtaM;
+    for (int i = threadIdx.x; i < 4 * kC; i += blockDim.x) gt_hist[i] = 0;
+    __syncthreads();
+
+    for (int img = blockIdx.x * kWarpsPerCtaM + wib; img < N; img += warps_total) {
+        // ---- predictions: decode, order, NMS
+        stage_image(w, pred + (size_t)img * kImgFloats, lane);
+        LaneCands lc;
+        decode_cells(w, lane, conf_thr, lc);
+        const int n = order_candidates(w, lc, lane);
+        const Mask128 keep = nms_rounds<YH_IOU_METRICS>(w, n, nms_thr, lane);
+        const int total = count_below(keep, kCand + 30);
+        class_group_offsets(w, keep, lane);
+
+        // ---- targets: parse into the overlay
+        stage_image(w, tgt + (size_t)img * kImgFloats, lane);
+        const int ngt = parse_targets(w, lane, gt_hist, gt_cls ? gt_cls + (size_t)img * kCells : nullptr,
+                                      gt_box ? gt_box + (size_t)img * kCells * 4 : nullptr);
+        MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
+        if (lane == 0) {
+            n_keep[img] = total;
+            n_gt[img] = ngt;
+        }
+
+        // ---- best ground truth of every kept detection, per subset
+        // subset 0 = all ground truths, 1/2/3 = small/medium/large only
+#pragma unroll
+        for (int s = 0; s < kSlots; ++s) {
+            const int p = lane + 32 * s;
+            if (!((keep.w[s] >> lane) & 1u)) continue;
+            const int c = w.scls[p];
+            const Corners d = load_corners(w, p);
+            double bi[4] = {0.0, 0.0, 0.0, 0.0};
+            int bg[4] = {255, 255, 255, 255};
+            for (int g = 0; g < ngt; ++g) {
+                if (mo.gcls[g] != c) continue;
+                Corners gc;
+                gc.x1 = mo.gx1[g]; gc.y1 = mo.gy1[g]; gc.x2 = mo.gx2[g]; gc.y2 = mo.gy2[g];
+                gc.area = mo.garea[g];
+                const double iou = iou_exact<YH_IOU_METRICS>(d, gc);
+                const int b = mo.gbucket[g];
+                if (iou > bi[0]) { bi[0] = iou; bg[0] = g; }  // strict: first GT wins ties
+#pragma unroll
+                for (int q = 1; q < 4; ++q)
+                    if (b == q && iou > bi[q]) { bi[q] = iou; bg[q] = g; }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                mo.biou[q][p] = bi[q];
+                mo.bgt[q][p] = (uint8_t)bg[q];
+            }
+        }
+        __syncwarp();
+
+        // ---- greedy TP/FP: a detection is a TP at threshold t iff its best IoU >= t
+        // and no earlier detection of its class claimed the same ground truth with
+        // IoU >= t (metrics.py:406-413).  "Earlier" = lower sorted position.
+#pragma unroll
+        for (int s = 0; s < kSlots; ++s) {
+            const int p = lane + 32 * s;
+            if (!((keep.w[s] >> lane) & 1u)) continue;
+            const int c = w.scls[p];
+            const int lo = w.cls_start[c];
+            uint64_t flags = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int g = mo.bgt[q][p];
+                if (g == 255) continue;
+                const double mine = mo.biou[q][p];
+                double rival = 0.0;  // best IoU an earlier detection brought to the same GT
+                for (int e = lo; e < p; ++e) {
+                    if (!test_bit(keep, e)) continue;
+                    if (mo.bgt[q][e] == g) rival = fmax(rival, mo.biou[q][e]);
+                }
+                for (int t = 0; t < thr.n; ++t)
+                    if (mine >= thr.t[t] && !(rival >= thr.t[t])) flags |= 1ull << (q * thr.n + t);
+                if (q == 0 && mine >= 0.5 && !(rival >= 0.5)) flags |= 1ull << (4 * thr.n);
+            }
+            const int j = count_below(keep, p);  // emission slot: sorted order among the kept
+            const size_t o = (size_t)img * kCand + j;
+            rec_key[o] = ~orderable(w.sconf[p] == 0.0 ? 0.0 : w.sconf[p]);
+            rec_flags[o] = flags | ((uint64_t)c << 56);
+            rec_k[o] = w.sk[p];
+            rec_pos[o] = (uint8_t)(w.cls_off[c] + j - count_below(keep, lo));
+            if (rec_box != nullptr) {  // the reference's (x, y, w, h) tuple, metrics.py:214-216
+                const int k = w.sk[p], cell = k / kB, b = k % kB;
+                const float *raw = pred + (size_t)img * kImgFloats + cell * kD + b * 5;
+                rec_box[4 * o + 0] = abs_coord(cell % kS, __ldg(raw + 0));
+                rec_box[4 * o + 1] = abs_coord(cell / kS, __ldg(raw + 1));
+                rec_box[4 * o + 2] = (double)__ldg(raw + 2);
+                rec_box[4 * o + 3] = (double)__ldg(raw + 3);
+            }
+        }
+        __syncwarp();
+    }
+
+    __syncthreads();
+    for (int i = threadIdx.x; i < 4 * kC; i += blockDim.x)
+        if (gt_hist[i]) atomicAdd(&gt_count[i], gt_hist[i]);
+}
+
+// Ground truths in list form (metrics.py:220-256), one warp per image.
+__global__ void __launch_bounds__(128)
+parse_gt_kernel(const float *__restrict__ tgt, int N, int32_t *__restrict__ n_gt,
+                uint8_t *__restrict__ gt_cls, double *__restrict__ gt_box) {
+    const int lane = threadIdx.x & 31;
+    const int img = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (img >= N) return;
+    const float *base = tgt + (size_t)img * kImgFloats;
+    bool is_gt[2];
+#pragma unroll
+    for (int cs = 0; cs < 2; ++cs) {
+        const int cell = lane + 32 * cs;
+        is_gt[cs] = cell < kCells && __ldg(base + cell * kD + 4) > 0.f;
+    }
+    const unsigned m0 = __ballot_sync(kFull, is_gt[0]), m1 = __ballot_sync(kFull, is_gt[1]);
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int cs = 0; cs < 2; ++cs)
+        if (is_gt[cs]) {
+            const int cell = lane + 32 * cs;
+            const float *c = base + cell * kD;
+            float cls_p[kC];
+#pragma unroll
+            for (int i = 0; i < kC; ++i) cls_p[i] = __ldg(c + kB * 5 + i);
+            float pv;
+            const int cls = argmax_first(cls_p, kC, pv);
+            const int g = cs ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
+            const size_t o = (size_t)img * kCells + g;
+            gt_cls[o] = (uint8_t)cls;
+            gt_box[4 * o + 0] = abs_coord(cell % kS, __ldg(c + 0));
+            gt_box[4 * o + 1] = abs_coord(cell / kS, __ldg(c + 1));
+            gt_box[4 * o + 2] = (double)__ldg(c + 2);
+            gt_box[4 * o + 3] = (double)__ldg(c + 3);
+        }
+    if (lane == 0) n_gt[img] = __popc(m0) + __popc(m1);
+}
+
+}  // namespace yh
+
+using namespace yh;
+
+extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int C,
+                             double conf_thr, double nms_thr, const double *thresholds_host, int T,
+                             int32_t *n_keep, uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k,
+                             uint8_t *rec_pos, double *rec_box, int32_t *n_gt, uint8_t *gt_cls,
+                             double *gt_box, int32_t *gt_count, void *stream) {
+    if (!shape_ok(S, B, C)) {
+        set_error("yh_map_update: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (T < 1 || T > YH_MAX_THRESHOLDS) {
+        set_error("yh_map_update: T=%d thresholds; this build carries 1..%d", T, YH_MAX_THRESHOLDS);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (N < 0 || !pred || !tgt || !thresholds_host || !n_keep || !rec_key || !rec_flags || !rec_k ||
+        !rec_pos || !n_gt || !gt_count) {
+        set_error("yh_map_update: bad argument");
+        return YH_ERR_BAD_ARG;
+    }
+    if (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8)) {
+        set_error("yh_map_update: pred/tgt must be 8-byte aligned");
+        return YH_ERR_ALIGNMENT;
+    }
+    if (N == 0) return 0;
+    Thresholds th;
+    th.n = T;
+    for (int i = 0; i < YH_MAX_THRESHOLDS; ++i) th.t[i] = i < T ? thresholds_host[i] : 2.0;
+    const size_t smem = sizeof(WarpWindow) * kWarpsPerCtaM;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(map_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_done = true;
+    }
+    int ctas = (N + kWarpsPerCtaM - 1) / kWarpsPerCtaM;
+    const int cap = 148 * 5;
+    if (ctas > cap) ctas = cap;
+    map_update_kernel<<<ctas, kWarpsPerCtaM * 32, smem, (cudaStream_t)stream>>>(
+        pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, rec_pos, rec_box, n_gt, gt_cls,
+        gt_box, gt_count);
+    return check_launch("yh_map_update");
+}
+
+extern "C" int yh_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t *n_gt,
+                           uint8_t *gt_cls, double *gt_box, void *stream) {
+    if (!shape_ok(S, B, C)) {
+        set_error("yh_parse_gt: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (N < 0 || !tgt || !n_gt || !gt_cls || !gt_box) {
+        set_error("yh_parse_gt: bad argument");
+        return YH_ERR_BAD_ARG;
+    }
+    if (N == 0) return 0;
+    parse_gt_kernel<<<(N + 3) / 4, 128, 0, (cudaStream_t)stream>>>(tgt, N, n_gt, gt_cls, gt_box);
+    return check_launch("yh_parse_gt");
+}

@@ -1,0 +1,214 @@
+"""Functional wrappers over the C ABI (include/yolohead.h): tensors in, tensors out.
+
+Everything here enqueues CUDA kernels on the current stream of the input's device
+and returns device tensors; nothing synchronises unless the caller reads a result.
+No CPU or PyTorch fallback exists: a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+from ._lib import IOU_INFER, IOU_METRICS, ORDER_CLASS_GROUPED, ORDER_GLOBAL_CONF  # noqa: F401
+
+S_, B_, C_ = 7, 2, 20
+
+
+def _check_pred(t: torch.Tensor, name: str, S: int, B: int, Cn: int) -> torch.Tensor:
+    _lib.require_cuda(t, name)
+    D = B * 5 + Cn
+    if t.dim() == 3:
+        t = t.unsqueeze(0)
+    if t.dim() != 4 or tuple(t.shape[1:]) != (S, S, D):
+        raise ValueError(f"{name}: expected shape (N,{S},{S},{D}), got {tuple(t.shape)}")
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    t = t.contiguous()
+    if t.data_ptr() % 8:
+        t = t.clone()
+    return t
+
+
+def _thr_array(thresholds):
+    thr = [float(t) for t in thresholds]
+    if not 1 <= len(thr) <= _lib.MAX_THRESHOLDS:
+        raise NotImplementedError(
+            f"{len(thr)} IoU thresholds: the matching kernel carries 1..{_lib.MAX_THRESHOLDS} "
+            "(4 ground-truth subsets x T + 1 flag bits per detection)")
+    return thr, (C.c_double * len(thr))(*thr)
+
+
+@dataclass
+class DecodeResult:
+    n_keep: torch.Tensor      # (N,) int32
+    keep_k: torch.Tensor      # (N,K) uint8 candidate indices, ordered
+    keep_cls: torch.Tensor    # (N,K) uint8
+    keep_conf: torch.Tensor   # (N,K) float64
+    keep_box: torch.Tensor    # (N,K,4) float64 (x_abs, y_abs, w, h)
+    n_cand: torch.Tensor      # (N,) int32 candidates above conf_thr
+    bad_range: torch.Tensor   # (N,) uint8
+
+
+def decode_nms(pred: torch.Tensor, conf_thr: float, nms_thr: float, iou_mode: int = IOU_METRICS,
+               order: int = ORDER_CLASS_GROUPED, S: int = S_, B: int = B_, Cn: int = C_,
+               want_boxes: bool = True) -> DecodeResult:
+    """yh_decode_nms over a batch (or a single (S,S,D) image)."""
+    p = _check_pred(pred, "predictions", S, B, Cn)
+    N, K, dev = p.shape[0], S * S * B, p.device
+    n_keep = torch.zeros(N, dtype=torch.int32, device=dev)
+    n_cand = torch.zeros(N, dtype=torch.int32, device=dev)
+    bad = torch.zeros(N, dtype=torch.uint8, device=dev)
+    keep_k = torch.empty(N, K, dtype=torch.uint8, device=dev)
+    keep_cls = torch.empty(N, K, dtype=torch.uint8, device=dev)
+    keep_conf = torch.empty(N, K, dtype=torch.float64, device=dev)
+    keep_box = torch.empty(N, K, 4, dtype=torch.float64, device=dev) if want_boxes else None
+    with torch.cuda.device(dev):
+        rc = _lib.lib().yh_decode_nms(p.data_ptr(), N, S, B, Cn, float(conf_thr), float(nms_thr), int(iou_mode),
+                                      int(order), n_keep.data_ptr(), keep_k.data_ptr(), keep_cls.data_ptr(),
+                                      keep_conf.data_ptr(), _lib.ptr(keep_box), n_cand.data_ptr(),
+                                      bad.data_ptr(), _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_decode_nms")
+    return DecodeResult(n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad)
+
+
+@dataclass
+class UpdateChunk:
+    """Device-resident result of one mAPMetric.update() batch."""
+    n: int
+    n_keep: torch.Tensor     # (N,) int32
+    rec_key: torch.Tensor    # (N,K) uint64-as-int64: ~orderable(conf)
+    rec_flags: torch.Tensor  # (N,K) int64: class << 56 | TP bits
+    rec_k: torch.Tensor      # (N,K) uint8
+    rec_pos: torch.Tensor    # (N,K) uint8 position in the reference's per-image list
+    rec_box: torch.Tensor | None  # (N,K,4) float64
+    n_gt: torch.Tensor       # (N,) int32
+    gt_cls: torch.Tensor | None   # (N,S*S) uint8
+    gt_box: torch.Tensor | None   # (N,S*S,4) float64
+
+
+def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: float, thresholds,
+               gt_count: torch.Tensor, S: int = S_, B: int = B_, Cn: int = C_,
+               want_lists: bool = True) -> UpdateChunk:
+    """yh_map_update: fused decode + NMS + GT parse + TP/FP flags; adds into gt_count (4*C int32)."""
+    p = _check_pred(pred, "predictions", S, B, Cn)
+    t = _check_pred(tgt, "targets", S, B, Cn)
+    if p.shape != t.shape:
+        raise ValueError(f"predictions {tuple(p.shape)} and targets {tuple(t.shape)} differ in shape")
+    _, thr_c = _thr_array(thresholds)
+    N, K, G, dev = p.shape[0], S * S * B, S * S, p.device
+    i64 = dict(dtype=torch.int64, device=dev)
+    u8 = dict(dtype=torch.uint8, device=dev)
+    n_keep = torch.zeros(N, dtype=torch.int32, device=dev)
+    n_gt = torch.zeros(N, dtype=torch.int32, device=dev)
+    rec_key = torch.empty(N, K, **i64)
+    rec_flags = torch.empty(N, K, **i64)
+    rec_k = torch.empty(N, K, **u8)
+    rec_pos = torch.empty(N, K, **u8)
+    rec_box = torch.empty(N, K, 4, dtype=torch.float64, device=dev) if want_lists else None
+    gt_cls = torch.empty(N, G, **u8) if want_lists else None
+    gt_box = torch.empty(N, G, 4, dtype=torch.float64, device=dev) if want_lists else None
+    with torch.cuda.device(dev):
+        rc = _lib.lib().yh_map_update(p.data_ptr(), t.data_ptr(), N, S, B, Cn, float(conf_thr), float(nms_thr),
+                                      thr_c, len(thr_c), n_keep.data_ptr(), rec_key.data_ptr(),
+                                      rec_flags.data_ptr(), rec_k.data_ptr(), rec_pos.data_ptr(),
+                                      _lib.ptr(rec_box), n_gt.data_ptr(), _lib.ptr(gt_cls), _lib.ptr(gt_box),
+                                      gt_count.data_ptr(), _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_map_update")
+    return UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, rec_pos, rec_box, n_gt, gt_cls, gt_box)
+
+
+def compact_records(chunk: UpdateChunk):
+    """Dense (key, flags) arrays of a chunk in image order; capacity N*K, `total` valid (device scalar).
+
+    Returns (key, flags, offsets) with offsets[N] = number of records."""
+    N, K = chunk.rec_key.shape
+    dev = chunk.rec_key.device
+    lib = _lib.lib()
+    offsets = torch.empty(N + 1, dtype=torch.int64, device=dev)
+    out_key = torch.empty(N * K, dtype=torch.int64, device=dev)
+    out_flags = torch.empty(N * K, dtype=torch.int64, device=dev)
+    ws = torch.empty(lib.yh_compact_workspace_bytes(N), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.yh_compact_records(chunk.n_keep.data_ptr(), chunk.rec_key.data_ptr(), chunk.rec_flags.data_ptr(),
+                                    N, K, offsets.data_ptr(), out_key.data_ptr(), out_flags.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_compact_records")
+    return out_key, out_flags, offsets
+
+
+def ap_reduce(key: torch.Tensor, flags: torch.Tensor, M: int, gt_count: torch.Tensor, Cn: int, T: int):
+    """yh_ap_reduce over the first M records.  key/flags are clobbered.
+
+    Returns (ap (4,C,T) float64 device tensor, totals (2,) int64 device tensor)."""
+    dev = gt_count.device
+    lib = _lib.lib()
+    nbytes = lib.yh_ap_workspace_bytes(int(M), Cn, T)
+    if nbytes == 0:
+        raise NotImplementedError(f"yh_ap_reduce: C={Cn}, T={T} outside this build")
+    ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
+    pad = (-ws.data_ptr()) % 256
+    ap = torch.empty(4, Cn, T, dtype=torch.float64, device=dev)
+    totals = torch.empty(2, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.yh_ap_reduce(key.data_ptr() if M else None, flags.data_ptr() if M else None, int(M),
+                              gt_count.data_ptr(), Cn, T, ap.data_ptr(), totals.data_ptr(),
+                              ws.data_ptr() + pad, nbytes, _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_ap_reduce")
+    return ap, totals
+
+
+def iou_pairs(box_a, box_b, iou_mode: int, device) -> torch.Tensor:
+    a = torch.as_tensor(box_a, dtype=torch.float64).reshape(-1, 4).to(device)
+    b = torch.as_tensor(box_b, dtype=torch.float64).reshape(-1, 4).to(device)
+    _lib.require_cuda(a, "boxes")
+    out = torch.empty(a.shape[0], dtype=torch.float64, device=a.device)
+    with torch.cuda.device(a.device):
+        rc = _lib.lib().yh_iou_pairs(a.data_ptr(), b.data_ptr(), a.shape[0], int(iou_mode), out.data_ptr(),
+                                     _lib.stream_ptr(a.device))
+    _lib.check(rc, "yh_iou_pairs")
+    return out
+
+
+def nms_lists(offsets, cls, conf, box, nms_thr: float, iou_mode: int, order: int, device):
+    """Greedy NMS over CSR lists (host sequences in, device tensors out: n_keep, keep_idx)."""
+    off = torch.as_tensor(offsets, dtype=torch.int64)
+    n_lists = off.numel() - 1
+    max_len = int((off[1:] - off[:-1]).max()) if n_lists > 0 else 0
+    off_d = off.to(device)
+    _lib.require_cuda(off_d, "lists")
+    cls_d = torch.as_tensor(cls, dtype=torch.int32).to(device)
+    conf_d = torch.as_tensor(conf, dtype=torch.float64).to(device)
+    box_d = torch.as_tensor(box, dtype=torch.float64).reshape(-1, 4).to(device)
+    n_keep = torch.zeros(max(n_lists, 1), dtype=torch.int32, device=device)
+    keep_idx = torch.zeros(max(cls_d.numel(), 1), dtype=torch.int32, device=device)
+    with torch.cuda.device(off_d.device):
+        rc = _lib.lib().yh_nms_lists(off_d.data_ptr(), n_lists, cls_d.data_ptr(), conf_d.data_ptr(),
+                                     box_d.data_ptr(), float(nms_thr), int(iou_mode), int(order),
+                                     n_keep.data_ptr(), keep_idx.data_ptr(), max_len,
+                                     _lib.stream_ptr(off_d.device))
+    _lib.check(rc, "yh_nms_lists")
+    return n_keep[:n_lists], keep_idx
+
+
+def match_lists(det_off, det_cls, det_conf, det_box, gt_off, gt_cls, gt_box, Cn: int, thresholds,
+                gt_count: torch.Tensor):
+    """yh_match_lists; all list arguments are device tensors.  Returns (rec_key, rec_flags)."""
+    _, thr_c = _thr_array(thresholds)
+    dev = gt_count.device
+    n_lists = det_off.numel() - 1
+    M = det_cls.numel()
+    max_dets = int((det_off[1:] - det_off[:-1]).max()) if n_lists > 0 else 0
+    rec_key = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
+    rec_flags = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().yh_match_lists(det_off.data_ptr(), det_cls.data_ptr(), det_conf.data_ptr(),
+                                       det_box.data_ptr(), gt_off.data_ptr(), gt_cls.data_ptr(),
+                                       gt_box.data_ptr(), n_lists, Cn, thr_c, len(thr_c), rec_key.data_ptr(),
+                                       rec_flags.data_ptr(), gt_count.data_ptr(), max_dets,
+                                       _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_match_lists")
+    return rec_key, rec_flags

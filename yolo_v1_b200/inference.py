@@ -1,0 +1,139 @@
+"""YOLOInference -- drop-in for the reference's inference engine, post-processing on CUDA.
+
+Constructor, ``predict`` / ``parse_predictions`` / ``iou`` / ``non_max_suppression``
+signatures, defaults, the DeprecationWarning for ``iou_threshold=`` and the
+pydantic validation behaviour follow /root/reference/src/yolo/inference.py:12-317.
+Decode and NMS run in yh_decode_nms (one warp per image); ``predict_batch`` is the
+batched form the kernel is built for.
+"""
+from __future__ import annotations
+
+import warnings
+
+import torch
+import torch.nn as nn
+
+from . import _lib, head
+from .schemas import BoundingBox, Detection
+
+EPSILON = 1e-6
+
+
+def _default_device() -> str:
+    if torch.cuda.is_available():
+        return "cuda"
+    raise _lib.YoloHeadError("no CUDA device: YOLOInference post-processing has no CPU fallback")
+
+
+class YOLOInference:
+    """Image -> list[Detection]: load, preprocess, model forward, decode, NMS."""
+
+    def __init__(self, model: nn.Module, device: str | None = None) -> None:
+        self.device = device if device is not None else _default_device()
+        self.model = model.to(self.device)
+        self.model.eval()
+        from torchvision import transforms
+
+        self.transform = transforms.Compose([
+            transforms.Resize((448, 448)),
+            transforms.ToTensor(),
+            transforms.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225]),
+        ])
+
+    # ---------------------------------------------------------------- image I/O (unchanged path)
+    def load_image(self, image_path: str):
+        from PIL import Image
+
+        return Image.open(image_path).convert("RGB")
+
+    def preprocess_image(self, image) -> torch.Tensor:
+        return self.transform(image).unsqueeze(0).to(self.device)
+
+    # ---------------------------------------------------------------- pipeline
+    def predict(self, image_path: str, conf_threshold: float = 0.5, nms_threshold: float = 0.4,
+                class_names: list[str] | None = None) -> list[Detection]:
+        image = self.load_image(image_path)
+        batch = self.preprocess_image(image)
+        with torch.no_grad():
+            out = self.model(batch)
+        return self.predict_batch(out[:1], conf_threshold, nms_threshold, class_names)[0]
+
+    def predict_batch(self, predictions: torch.Tensor, conf_threshold: float = 0.5, nms_threshold: float = 0.4,
+                      class_names: list[str] | None = None) -> list[list[Detection]]:
+        """Decode + NMS for a whole (N,S,S,B*5+C) batch in one launch; one list per image.
+
+        Same result per image as parse_predictions() followed by non_max_suppression()."""
+        S, B = self.model.S, self.model.B
+        Cn = predictions.shape[-1] - B * 5
+        r = head.decode_nms(self._on_cuda(predictions), conf_threshold, nms_threshold, head.IOU_INFER,
+                            head.ORDER_GLOBAL_CONF, S, B, Cn)
+        return self._build(r, class_names)
+
+    def parse_predictions(self, pred: torch.Tensor, conf_threshold: float,
+                          class_names: list[str] | None = None) -> list[Detection]:
+        """(S,S,B*5+C) tensor -> every candidate above the threshold, in cell/box order
+        (inference.py:141-210).  Raises pydantic's ValidationError when a kept candidate
+        is outside [0,1], as the reference's schema does."""
+        S, B = self.model.S, self.model.B
+        Cn = pred.shape[-1] - B * 5
+        r = head.decode_nms(self._on_cuda(pred), conf_threshold, float("nan"), head.IOU_INFER,
+                            head.ORDER_GLOBAL_CONF, S, B, Cn)
+        dets = self._build(r, class_names, sort_by_candidate=True)
+        return dets[0]
+
+    def iou(self, bbox1: BoundingBox, bbox2: BoundingBox) -> float:
+        """IoU with +1e-6 in the denominator (inference.py:212-249)."""
+        a = (bbox1.x, bbox1.y, bbox1.width, bbox1.height)
+        b = (bbox2.x, bbox2.y, bbox2.width, bbox2.height)
+        return float(head.iou_pairs([a], [b], head.IOU_INFER, self._cuda_device()).item())
+
+    def non_max_suppression(self, detections: list[Detection], nms_threshold: float = None,
+                            iou_threshold: float = None) -> list[Detection]:
+        """Greedy same-class NMS in confidence order (inference.py:251-317)."""
+        if iou_threshold is not None:
+            warnings.warn("Parameter 'iou_threshold' is deprecated, use 'nms_threshold' instead.",
+                          DeprecationWarning, stacklevel=2)
+            threshold = iou_threshold
+        elif nms_threshold is not None:
+            threshold = nms_threshold
+        else:
+            threshold = 0.4
+        if len(detections) == 0:
+            return []
+        n_keep, keep_idx = head.nms_lists(
+            [0, len(detections)], [d.class_id for d in detections], [d.confidence for d in detections],
+            [(d.bbox.x, d.bbox.y, d.bbox.width, d.bbox.height) for d in detections], threshold,
+            head.IOU_INFER, head.ORDER_GLOBAL_CONF, self._cuda_device())
+        n = int(n_keep[0].item())
+        return [detections[i] for i in keep_idx[:n].cpu().tolist()]
+
+    # ---------------------------------------------------------------- internals
+    def _cuda_device(self) -> torch.device:
+        d = torch.device(self.device)
+        if d.type != "cuda":
+            if not torch.cuda.is_available():
+                raise _lib.YoloHeadError("no CUDA device: YOLOInference post-processing has no CPU fallback")
+            d = torch.device("cuda", torch.cuda.current_device())
+        return d
+
+    def _on_cuda(self, t: torch.Tensor) -> torch.Tensor:
+        return t if t.is_cuda else t.to(self._cuda_device())
+
+    @staticmethod
+    def _build(r: head.DecodeResult, class_names, sort_by_candidate: bool = False) -> list[list[Detection]]:
+        n_keep = r.n_keep.cpu().tolist()
+        k, cls = r.keep_k.cpu(), r.keep_cls.cpu()
+        conf, box = r.keep_conf.cpu(), r.keep_box.cpu()
+        out = []
+        for i, n in enumerate(n_keep):
+            ks, cs = k[i, :n].tolist(), cls[i, :n].tolist()
+            fs, bs = conf[i, :n].tolist(), box[i, :n].tolist()
+            order = sorted(range(n), key=ks.__getitem__) if sort_by_candidate else range(n)
+            dets = []
+            for q in order:
+                cid = int(cs[q])
+                name = class_names[cid] if class_names else f"class_{cid}"
+                dets.append(Detection(class_id=cid, class_name=name, confidence=fs[q],
+                                      bbox=BoundingBox(x=bs[q][0], y=bs[q][1], width=bs[q][2], height=bs[q][3])))
+            out.append(dets)
+        return out

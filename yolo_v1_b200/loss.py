@@ -1,0 +1,119 @@
+"""YOLOLoss -- drop-in for the reference's loss module, computed by one fused CUDA kernel.
+
+Same constructor, attributes, return value and loss_dict keys as
+/root/reference/src/yolo/loss.py:7-172 (``YOLOLoss(S, B, C, lambda_coord,
+lambda_noobj)``; ``forward(predictions, targets) -> (total, dict)``;
+``compute_iou`` static method, loss.py:174-212).  forward + backward are a single
+pass of ``yh_loss_fwd_bwd`` (csrc/loss.cu); the autograd backward only multiplies
+the saved gradient by the upstream scalar (``yh_scale_inplace``, which exits
+immediately when that scalar is 1).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+_KEYS = ("total", "coord", "conf_obj", "conf_noobj", "class")
+
+
+class _Workspace:
+    """Per-device scratch for the loss kernel, grown on demand, reused across calls."""
+
+    def __init__(self):
+        self.buf = {}
+
+    def get(self, device, nbytes: int) -> torch.Tensor:
+        b = self.buf.get(device)
+        if b is None or b.numel() < nbytes:
+            b = torch.zeros(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
+            self.buf[device] = b
+        return b
+
+
+_WS = _Workspace()
+
+
+def loss_fwd_bwd(pred: torch.Tensor, tgt: torch.Tensor, S: int, B: int, C: int, lambda_coord: float,
+                 lambda_noobj: float, want_grad: bool = True):
+    """Raw kernel call: returns (parts[5] fp32 device tensor, grad or None)."""
+    _lib.require_cuda(pred, "predictions")
+    _lib.require_cuda(tgt, "targets")
+    D = B * 5 + C
+    if pred.dim() != 4 or tuple(pred.shape[1:]) != (S, S, D) or pred.shape != tgt.shape:
+        raise ValueError(f"expected predictions and targets of shape (N,{S},{S},{D}); got "
+                         f"{tuple(pred.shape)} and {tuple(tgt.shape)}")
+    N = pred.shape[0]
+    if N == 0:
+        raise ValueError("empty batch")
+    p = pred.detach().contiguous()
+    t = tgt.detach().to(torch.float32).contiguous()
+    lib = _lib.lib()
+    parts = torch.empty(5, dtype=torch.float32, device=p.device)
+    grad = torch.empty_like(p) if want_grad else None
+    nbytes = lib.yh_loss_workspace_bytes(N, S, B, C)
+    if nbytes == 0:
+        raise NotImplementedError(f"YOLOLoss kernels are built for S=7,B=2,C=20 only (got {S},{B},{C})")
+    ws = _WS.get(p.device, nbytes)
+    with torch.cuda.device(p.device):
+        rc = lib.yh_loss_fwd_bwd(p.data_ptr(), _lib.dtype_code(p), t.data_ptr(), N, S, B, C,
+                                 float(lambda_coord), float(lambda_noobj), parts.data_ptr(), _lib.ptr(grad),
+                                 ws.data_ptr(), ws.numel(), _lib.stream_ptr(p.device))
+    _lib.check(rc, "yh_loss_fwd_bwd")
+    return parts, grad
+
+
+class _YoloLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, tgt, S, B, C, lc, ln):
+        need = pred.requires_grad
+        parts, grad = loss_fwd_bwd(pred, tgt, S, B, C, lc, ln, want_grad=need)
+        ctx.saved_grad = grad
+        ctx.mark_non_differentiable(parts)
+        return parts[0].clone(), parts
+
+    @staticmethod
+    def backward(ctx, g_total, _g_parts):
+        grad = ctx.saved_grad
+        if grad is None:
+            return (None,) * 7
+        ctx.saved_grad = None
+        scale = g_total.detach().to(torch.float32).reshape(1).contiguous()
+        with torch.cuda.device(grad.device):
+            rc = _lib.lib().yh_scale_inplace(grad.data_ptr(), _lib.dtype_code(grad), grad.numel(),
+                                             scale.data_ptr(), _lib.stream_ptr(grad.device))
+        _lib.check(rc, "yh_scale_inplace")
+        return (grad, None, None, None, None, None, None)
+
+
+class YOLOLoss(nn.Module):
+    """YOLO v1 loss (reference: src/yolo/loss.py:7-53 for the constructor contract)."""
+
+    def __init__(self, S: int = 7, B: int = 2, C: int = 20, lambda_coord: float = 5.0,
+                 lambda_noobj: float = 0.5):
+        super().__init__()
+        self.S, self.B, self.C = S, B, C
+        self.lambda_coord = lambda_coord
+        self.lambda_noobj = lambda_noobj
+
+    def forward(self, predictions: torch.Tensor, targets: torch.Tensor) -> tuple[torch.Tensor, dict[str, float]]:
+        total, parts = _YoloLossFn.apply(predictions, targets, self.S, self.B, self.C, self.lambda_coord,
+                                         self.lambda_noobj)
+        vals = parts.tolist()  # the one device->host read the loss_dict API requires (loss.py:164-170)
+        return total, dict(zip(_KEYS, vals))
+
+    @staticmethod
+    def compute_iou(boxes1: torch.Tensor, boxes2: torch.Tensor) -> torch.Tensor:
+        """IoU of (…,B,4) vs (…,1,4) centre-format boxes, +1e-6 in the denominator
+        (loss.py:174-212).  Public helper of the reference; the fused kernel computes the
+        same quantity internally, this stays as plain tensor ops for API parity."""
+        b1x1, b1x2 = boxes1[..., 0] - boxes1[..., 2] / 2, boxes1[..., 0] + boxes1[..., 2] / 2
+        b1y1, b1y2 = boxes1[..., 1] - boxes1[..., 3] / 2, boxes1[..., 1] + boxes1[..., 3] / 2
+        b2x1, b2x2 = boxes2[..., 0] - boxes2[..., 2] / 2, boxes2[..., 0] + boxes2[..., 2] / 2
+        b2y1, b2y2 = boxes2[..., 1] - boxes2[..., 3] / 2, boxes2[..., 1] + boxes2[..., 3] / 2
+        iw = torch.clamp(torch.minimum(b1x2, b2x2) - torch.maximum(b1x1, b2x1), min=0)
+        ih = torch.clamp(torch.minimum(b1y2, b2y2) - torch.maximum(b1y1, b2y1), min=0)
+        inter = iw * ih
+        union = boxes1[..., 2] * boxes1[..., 3] + boxes2[..., 2] * boxes2[..., 3] - inter
+        return inter / (union + 1e-6)
