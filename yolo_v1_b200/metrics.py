@@ -156,7 +156,7 @@ class mAPMetric:
             ap, tp_total, n_pred, gt_count, n_gt_total = self._reduce_lists()
         else:
             ap, tp_total, n_pred, gt_count = self._reduce_chunks()
-            n_gt_total = int(gt_count[0].sum())
+            n_gt_total = int(gt_count.reshape(4, C)[0].sum())
         return self._results(ap, tp_total, n_pred, gt_count.reshape(4, C), n_gt_total, T, C)
 
     def _reduce_chunks(self):
