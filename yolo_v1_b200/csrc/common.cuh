@@ -75,6 +75,11 @@ __device__ __forceinline__ double iou_exact(const Corners &a, const Corners &b) 
     return __ddiv_rn(inter, u);
 }
 
+// the rare exact path of iou_below, kept out of line (code size)
+static __device__ __noinline__ bool quotient_below(double inter, double u, double thr) {
+    return __ddiv_rn(inter, u) < thr;
+}
+
 // "is IoU(a, b) < thr" -- the keep test of NMS (metrics.py:293, inference.py:314).
 // Decides without the division whenever inter and thr*denominator are further
 // apart than any rounding could bridge; falls back to the exact quotient
@@ -92,7 +97,7 @@ __device__ __forceinline__ bool iou_below(const Corners &a, const Corners &b, do
             if (inter > __dadd_rn(t, slack)) return false;
         }
     }
-    return __ddiv_rn(inter, u) < thr;
+    return quotient_below(inter, u, thr);
 }
 
 // Monotone map double -> uint64 (ascending).  -0.0 sorts just below +0.0.

@@ -2,16 +2,16 @@
 //
 // Replaces mAPMetric._parse_predictions + _apply_nms (metrics.py:173-218, 258-296)
 // and YOLOInference.parse_predictions + non_max_suppression (inference.py:141-210,
-// 251-317).  Building blocks in head_image.cuh.
-#include "head_image.cuh"
+// 251-317).  Building blocks in head_image.cuh / head_nms.cuh.
+#include "head_nms.cuh"
 
 namespace yh {
 
 constexpr int kWarpsPerCta = 4;
 
-template <int MODE, int ORDER>
+template <int MODE>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
-decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double nms_thr,
+decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double nms_thr, int order,
                   int32_t *__restrict__ n_keep, uint8_t *__restrict__ keep_k,
                   uint8_t *__restrict__ keep_cls, double *__restrict__ keep_conf,
                   double *__restrict__ keep_box, int32_t *__restrict__ n_cand,
@@ -24,62 +24,46 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
 
     for (int img = blockIdx.x * kWarpsPerCta + wib; img < N; img += warps_total) {
         stage_image(w, pred + (size_t)img * kImgFloats, lane);
-        LaneCands lc;
-        decode_cells(w, lane, conf_thr, lc);
-
+        bool bad = false;
+        const Mask128 valid = decode_image(w, lane, conf_thr, &bad);
         if (bad_range != nullptr) {
-            // where the reference's pydantic schema raises (schemas.py:9-16,88): a
-            // candidate above the threshold with x,y,w,h or confidence outside [0,1]
-            bool bad = false;
-#pragma unroll
-            for (int s = 0; s < kSlots; ++s)
-                if ((lc.valid >> s) & 1u) {
-                    const int cell = lane + 32 * (s >> 1);
-                    const double xa = abs_coord(cell % kS, lc.x[s]), ya = abs_coord(cell / kS, lc.y[s]);
-                    const double ww = (double)lc.w[s], hh = (double)lc.h[s], cf = lc.conf[s];
-                    bad |= !(xa >= 0.0 && xa <= 1.0 && ya >= 0.0 && ya <= 1.0 && ww >= 0.0 &&
-                             ww <= 1.0 && hh >= 0.0 && hh <= 1.0 && cf >= 0.0 && cf <= 1.0);
-                }
             const unsigned anybad = __ballot_sync(kFull, bad);
             if (lane == 0) bad_range[img] = anybad ? 1 : 0;
         }
-
-        const int n = order_candidates(w, lc, lane);
+        const int n = order_candidates(w, valid, lane);
         const Mask128 keep = nms_rounds<MODE>(w, n, nms_thr, lane);
-        const int total = count_below(keep, kCand + 30);
         if (lane == 0) {
-            n_keep[img] = total;
+            n_keep[img] = keep.count();
             if (n_cand != nullptr) n_cand[img] = n;
         }
-        if (ORDER == YH_ORDER_CLASS_GROUPED) class_group_offsets(w, keep, lane);
+        if (order == YH_ORDER_CLASS_GROUPED) class_group_offsets(w, keep, lane);
 
-#pragma unroll
+#pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
             const int p = lane + 32 * s;
-            if (!((keep.w[s] >> lane) & 1u)) continue;
+            if (!((keep.word(s) >> lane) & 1u)) continue;
+            const int k = w.order[p], c = w.cand.cls[k];
             int pos;
-            if (ORDER == YH_ORDER_CLASS_GROUPED) {
-                const int c = w.scls[p];
+            if (order == YH_ORDER_CLASS_GROUPED) {
                 pos = w.cls_off[c] + count_below(keep, p) - count_below(keep, w.cls_start[c]);
             } else {
                 // global (confidence desc, candidate asc) rank among the kept
-                const double mine = w.sconf[p];
-                const int mi = w.sidx[p];
+                const double mine = w.cand.conf[k];
                 pos = 0;
                 for (int q = 0; q < n; ++q) {
-                    if (!test_bit(keep, q)) continue;
-                    const double oc = w.sconf[q];
-                    pos += (oc > mine) || (oc == mine && w.sidx[q] < mi);
+                    if (!keep.test(q)) continue;
+                    const int ok = w.order[q];
+                    const double oc = w.cand.conf[ok];
+                    pos += (oc > mine) || (oc == mine && ok < k);
                 }
             }
             const size_t o = (size_t)img * kCand + pos;
-            keep_k[o] = w.sk[p];
-            if (keep_cls != nullptr) keep_cls[o] = w.scls[p];
-            if (keep_conf != nullptr) keep_conf[o] = w.sconf[p];
+            keep_k[o] = (uint8_t)k;
+            if (keep_cls != nullptr) keep_cls[o] = (uint8_t)c;
+            if (keep_conf != nullptr) keep_conf[o] = w.cand.conf[k];
             if (keep_box != nullptr) {
-                // (x, y, w, h) as the reference stores them; x = (x1 + x2)/2 would round
-                // differently, so rebuild from the raw cell values
-                const int k = w.sk[p], cell = k / kB, b = k % kB;
+                // (x, y, w, h) as the reference stores them, rebuilt from the raw cell values
+                const int cell = k / kB, b = k % kB;
                 const float *raw = pred + (size_t)img * kImgFloats + cell * kD + b * 5;
                 keep_box[4 * o + 0] = abs_coord(cell % kS, __ldg(raw + 0));
                 keep_box[4 * o + 1] = abs_coord(cell / kS, __ldg(raw + 1));
@@ -91,22 +75,21 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
     }
 }
 
-template <int MODE, int ORDER>
-static int launch(const float *pred, int N, double conf_thr, double nms_thr, int32_t *n_keep,
+template <int MODE>
+static int launch(const float *pred, int N, double conf_thr, double nms_thr, int order, int32_t *n_keep,
                   uint8_t *keep_k, uint8_t *keep_cls, double *keep_conf, double *keep_box,
                   int32_t *n_cand, uint8_t *bad_range, cudaStream_t st) {
     const size_t smem = sizeof(WarpWindow) * kWarpsPerCta;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(decode_nms_kernel<MODE, ORDER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)smem);
+        cudaFuncSetAttribute(decode_nms_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         attr_done = true;
     }
     int ctas = (N + kWarpsPerCta - 1) / kWarpsPerCta;
-    const int cap = 148 * 5 * 4;
+    const int cap = 148 * 5;
     if (ctas > cap) ctas = cap;
-    decode_nms_kernel<MODE, ORDER><<<ctas, kWarpsPerCta * 32, smem, st>>>(
-        pred, N, conf_thr, nms_thr, n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad_range);
+    decode_nms_kernel<MODE><<<ctas, kWarpsPerCta * 32, smem, st>>>(
+        pred, N, conf_thr, nms_thr, order, n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad_range);
     return check_launch("yh_decode_nms");
 }
 
@@ -130,15 +113,18 @@ extern "C" int yh_decode_nms(const float *pred, int N, int S, int B, int C, doub
         set_error("yh_decode_nms: pred must be 8-byte aligned");
         return YH_ERR_ALIGNMENT;
     }
+    if (order != YH_ORDER_CLASS_GROUPED && order != YH_ORDER_GLOBAL_CONF) {
+        set_error("yh_decode_nms: unknown order %d", order);
+        return YH_ERR_BAD_ARG;
+    }
     if (N == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-#define YH_GO(M, O) \
-    return launch<M, O>(pred, N, conf_thr, nms_thr, n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad_range, st)
-    if (iou_mode == YH_IOU_METRICS && order == YH_ORDER_CLASS_GROUPED) YH_GO(YH_IOU_METRICS, YH_ORDER_CLASS_GROUPED);
-    if (iou_mode == YH_IOU_METRICS && order == YH_ORDER_GLOBAL_CONF) YH_GO(YH_IOU_METRICS, YH_ORDER_GLOBAL_CONF);
-    if (iou_mode == YH_IOU_INFER && order == YH_ORDER_CLASS_GROUPED) YH_GO(YH_IOU_INFER, YH_ORDER_CLASS_GROUPED);
-    if (iou_mode == YH_IOU_INFER && order == YH_ORDER_GLOBAL_CONF) YH_GO(YH_IOU_INFER, YH_ORDER_GLOBAL_CONF);
-#undef YH_GO
-    set_error("yh_decode_nms: unknown iou_mode %d / order %d", iou_mode, order);
+    if (iou_mode == YH_IOU_METRICS)
+        return launch<YH_IOU_METRICS>(pred, N, conf_thr, nms_thr, order, n_keep, keep_k, keep_cls, keep_conf,
+                                      keep_box, n_cand, bad_range, st);
+    if (iou_mode == YH_IOU_INFER)
+        return launch<YH_IOU_INFER>(pred, N, conf_thr, nms_thr, order, n_keep, keep_k, keep_cls, keep_conf,
+                                    keep_box, n_cand, bad_range, st);
+    set_error("yh_decode_nms: unknown iou_mode %d", iou_mode);
     return YH_ERR_BAD_ARG;
 }

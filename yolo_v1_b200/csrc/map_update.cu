@@ -9,7 +9,7 @@
 // relative order in the global stable sort equals their per-image order, so the
 // flags can be finalised here (verified against the
 // reference's tp arrays in tests/golden/map_small.npz).
-#include "head_image.cuh"
+#include "head_nms.cuh"
 
 namespace yh {
 
@@ -26,8 +26,9 @@ struct Thresholds {
 __device__ __forceinline__ int parse_targets(WarpWindow &w, int lane, int *gt_hist,
                                              uint8_t *__restrict__ out_cls, double *__restrict__ out_box) {
     const float *st = reinterpret_cast<const float *>(w.stage);
+    // pass 1: pull the (few) ground-truth cells into registers before the overlay is written
     bool is_gt[2];
-    int cls[2];
+    int cls[2] = {0, 0};
     float x[2], y[2], bw[2], bh[2];
 #pragma unroll
     for (int cs = 0; cs < 2; ++cs) {
@@ -36,6 +37,11 @@ __device__ __forceinline__ int parse_targets(WarpWindow &w, int lane, int *gt_hi
         const float *c = st + (live ? cell : 0) * kD;
         is_gt[cs] = live && (c[4] > 0.f);  // slot-0 confidence only (metrics.py:239)
         x[cs] = c[0]; y[cs] = c[1]; bw[cs] = c[2]; bh[cs] = c[3];
+    }
+#pragma unroll 1
+    for (int cs = 0; cs < 2; ++cs) {
+        if (!(cs == 0 ? is_gt[0] : is_gt[1])) continue;  // object cells are rare (about 1 in 18)
+        const float *c = st + (lane + 32 * cs) * kD;
         float cls_p[kC];
 #pragma unroll
         for (int i = 0; i < kC / 2; ++i) {
@@ -44,7 +50,8 @@ __device__ __forceinline__ int parse_targets(WarpWindow &w, int lane, int *gt_hi
             cls_p[2 * i + 1] = v.y;
         }
         float pv;
-        cls[cs] = argmax_first(cls_p, kC, pv);
+        const int a = argmax_first(cls_p, kC, pv);
+        if (cs == 0) cls[0] = a; else cls[1] = a;
     }
     const unsigned m0 = __ballot_sync(kFull, is_gt[0]), m1 = __ballot_sync(kFull, is_gt[1]);
     const unsigned lt = (1u << lane) - 1u;
@@ -87,20 +94,21 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WarpWindow *windows = reinterpret_cast<WarpWindow *>(smem_raw);
     __shared__ int gt_hist[4 * kC];
+    __shared__ double s_thr[YH_MAX_THRESHOLDS];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     WarpWindow &w = windows[wib];
     const int warps_total = gridDim.x * kWarpsPerCtaM;
+    const int T = thr.n;
     for (int i = threadIdx.x; i < 4 * kC; i += blockDim.x) gt_hist[i] = 0;
+    if (threadIdx.x < YH_MAX_THRESHOLDS) s_thr[threadIdx.x] = thr.t[threadIdx.x];
     __syncthreads();
 
     for (int img = blockIdx.x * kWarpsPerCtaM + wib; img < N; img += warps_total) {
         // ---- predictions: decode, order, NMS
         stage_image(w, pred + (size_t)img * kImgFloats, lane);
-        LaneCands lc;
-        decode_cells(w, lane, conf_thr, lc);
-        const int n = order_candidates(w, lc, lane);
+        const Mask128 valid = decode_image(w, lane, conf_thr, nullptr);
+        const int n = order_candidates(w, valid, lane);
         const Mask128 keep = nms_rounds<YH_IOU_METRICS>(w, n, nms_thr, lane);
-        const int total = count_below(keep, kCand + 30);
         class_group_offsets(w, keep, lane);
 
         // ---- targets: parse into the overlay
@@ -109,72 +117,76 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                                       gt_box ? gt_box + (size_t)img * kCells * 4 : nullptr);
         MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
         if (lane == 0) {
-            n_keep[img] = total;
+            n_keep[img] = keep.count();
             n_gt[img] = ngt;
         }
 
         // ---- best ground truth of every kept detection, per subset
         // subset 0 = all ground truths, 1/2/3 = small/medium/large only
-#pragma unroll
+        unsigned matched = 0;  // bit s: my slot-s detection met a ground truth of its class
+#pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
+            if (!((keep.word(s) >> lane) & 1u)) continue;
             const int p = lane + 32 * s;
-            if (!((keep.w[s] >> lane) & 1u)) continue;
-            const int c = w.scls[p];
-            const Corners d = load_corners(w, p);
-            double bi[4] = {0.0, 0.0, 0.0, 0.0};
-            int bg[4] = {255, 255, 255, 255};
+            const int k = w.order[p], c = w.cand.cls[k];
+            double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+            int g0 = 255, g1 = 255, g2 = 255, g3 = 255;
+            bool met = false;
             for (int g = 0; g < ngt; ++g) {
                 if (mo.gcls[g] != c) continue;
+                met = true;
                 Corners gc;
                 gc.x1 = mo.gx1[g]; gc.y1 = mo.gy1[g]; gc.x2 = mo.gx2[g]; gc.y2 = mo.gy2[g];
                 gc.area = mo.garea[g];
-                const double iou = iou_exact<YH_IOU_METRICS>(d, gc);
+                const double iou = iou_exact<YH_IOU_METRICS>(cand_corners(w, k), gc);
                 const int b = mo.gbucket[g];
-                if (iou > bi[0]) { bi[0] = iou; bg[0] = g; }  // strict: first GT wins ties
-#pragma unroll
-                for (int q = 1; q < 4; ++q)
-                    if (b == q && iou > bi[q]) { bi[q] = iou; bg[q] = g; }
+                if (iou > b0) { b0 = iou; g0 = g; }  // strict: first GT wins ties, IoU 0 never matches
+                if (b == 1 && iou > b1) { b1 = iou; g1 = g; }
+                if (b == 2 && iou > b2) { b2 = iou; g2 = g; }
+                if (b == 3 && iou > b3) { b3 = iou; g3 = g; }
             }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                mo.biou[q][p] = bi[q];
-                mo.bgt[q][p] = (uint8_t)bg[q];
-            }
+            mo.biou[0][p] = b0; mo.biou[1][p] = b1; mo.biou[2][p] = b2; mo.biou[3][p] = b3;
+            mo.bgt[0][p] = (uint8_t)g0; mo.bgt[1][p] = (uint8_t)g1;
+            mo.bgt[2][p] = (uint8_t)g2; mo.bgt[3][p] = (uint8_t)g3;
+            if (met) matched |= 1u << s;
         }
         __syncwarp();
 
         // ---- greedy TP/FP: a detection is a TP at threshold t iff its best IoU >= t
         // and no earlier detection of its class claimed the same ground truth with
         // IoU >= t (metrics.py:406-413).  "Earlier" = lower sorted position.
-#pragma unroll
+#pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
+            if (!((keep.word(s) >> lane) & 1u)) continue;
             const int p = lane + 32 * s;
-            if (!((keep.w[s] >> lane) & 1u)) continue;
-            const int c = w.scls[p];
+            const int k = w.order[p], c = w.cand.cls[k];
             const int lo = w.cls_start[c];
             uint64_t flags = 0;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int g = mo.bgt[q][p];
-                if (g == 255) continue;
-                const double mine = mo.biou[q][p];
-                double rival = 0.0;  // best IoU an earlier detection brought to the same GT
-                for (int e = lo; e < p; ++e) {
-                    if (!test_bit(keep, e)) continue;
-                    if (mo.bgt[q][e] == g) rival = fmax(rival, mo.biou[q][e]);
+            if ((matched >> s) & 1u) {
+#pragma unroll 1
+                for (int q = 0; q < 4; ++q) {
+                    const int g = mo.bgt[q][p];
+                    if (g == 255) continue;
+                    const double mine = mo.biou[q][p];
+                    double rival = 0.0;  // best IoU an earlier detection brought to the same GT
+                    for (int e = lo; e < p; ++e)
+                        if (keep.test(e) && mo.bgt[q][e] == g) rival = fmax(rival, mo.biou[q][e]);
+                    for (int t = 0; t < T; ++t) {
+                        const double th = s_thr[t];
+                        if (mine >= th && !(rival >= th)) flags |= 1ull << (q * T + t);
+                    }
+                    if (q == 0 && mine >= 0.5 && !(rival >= 0.5)) flags |= 1ull << (4 * T);
                 }
-                for (int t = 0; t < thr.n; ++t)
-                    if (mine >= thr.t[t] && !(rival >= thr.t[t])) flags |= 1ull << (q * thr.n + t);
-                if (q == 0 && mine >= 0.5 && !(rival >= 0.5)) flags |= 1ull << (4 * thr.n);
             }
             const int j = count_below(keep, p);  // emission slot: sorted order among the kept
             const size_t o = (size_t)img * kCand + j;
-            rec_key[o] = ~orderable(w.sconf[p] == 0.0 ? 0.0 : w.sconf[p]);
+            const double cf = w.cand.conf[k];
+            rec_key[o] = ~orderable(cf == 0.0 ? 0.0 : cf);
             rec_flags[o] = flags | ((uint64_t)c << 56);
-            rec_k[o] = w.sk[p];
+            rec_k[o] = (uint8_t)k;
             rec_pos[o] = (uint8_t)(w.cls_off[c] + j - count_below(keep, lo));
             if (rec_box != nullptr) {  // the reference's (x, y, w, h) tuple, metrics.py:214-216
-                const int k = w.sk[p], cell = k / kB, b = k % kB;
+                const int cell = k / kB, b = k % kB;
                 const float *raw = pred + (size_t)img * kImgFloats + cell * kD + b * 5;
                 rec_box[4 * o + 0] = abs_coord(cell % kS, __ldg(raw + 0));
                 rec_box[4 * o + 1] = abs_coord(cell / kS, __ldg(raw + 1));
@@ -206,7 +218,7 @@ parse_gt_kernel(const float *__restrict__ tgt, int N, int32_t *__restrict__ n_gt
     }
     const unsigned m0 = __ballot_sync(kFull, is_gt[0]), m1 = __ballot_sync(kFull, is_gt[1]);
     const unsigned lt = (1u << lane) - 1u;
-#pragma unroll
+#pragma unroll 1
     for (int cs = 0; cs < 2; ++cs)
         if (is_gt[cs]) {
             const int cell = lane + 32 * cs;
