@@ -67,17 +67,18 @@ __device__ __forceinline__ double iou_denominator(const Corners &a, const Corner
     return u;
 }
 
+// IEEE fp64 division, kept out of line: the inlined sequence is ~150 instructions
+static __device__ __noinline__ double div_exact(double a, double b) { return __ddiv_rn(a, b); }
+static __device__ __forceinline__ bool quotient_below(double inter, double u, double thr) {
+    return div_exact(inter, u) < thr;
+}
+
 template <int MODE>
 __device__ __forceinline__ double iou_exact(const Corners &a, const Corners &b) {
     double inter = inter_area(a, b);
     double u = iou_denominator<MODE>(a, b, inter);
     if (MODE == YH_IOU_METRICS && u == 0.0) return 0.0;
-    return __ddiv_rn(inter, u);
-}
-
-// the rare exact path of iou_below, kept out of line (code size)
-static __device__ __noinline__ bool quotient_below(double inter, double u, double thr) {
-    return __ddiv_rn(inter, u) < thr;
+    return div_exact(inter, u);
 }
 
 // "is IoU(a, b) < thr" -- the keep test of NMS (metrics.py:293, inference.py:314).
@@ -110,19 +111,30 @@ __device__ __forceinline__ double from_orderable(uint64_t k) {
     return __longlong_as_double((long long)b);
 }
 
-// torch.argmax over the C class scores of one cell: first maximum, NaN maximal.
+// max that returns NaN when either operand is NaN (PTX max.NaN.f32, sm_80+)
+__device__ __forceinline__ float max_nan(float a, float b) {
+    float d;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
+
+// torch.argmax over the C class scores of one cell: first maximum, NaN maximal
+// (the first NaN wins).  Two short passes instead of a compare-and-branch chain:
+// the maximum, then the first index that equals it.
 __device__ __forceinline__ int argmax_first(const float *v, int n, float &best_v) {
-    int best = 0;
-    float bv = v[0];
+    float m = v[0];
 #pragma unroll
-    for (int i = 1; i < n; ++i) {
-        float x = v[i];
-        if ((x > bv) || (x != x && bv == bv)) {
-            best = i;
-            bv = x;
-        }
+    for (int i = 1; i < n; ++i) m = max_nan(m, v[i]);
+    int best = 0;
+    if (m != m) {  // some score is NaN: rare, keep it small
+#pragma unroll 1
+        for (int i = n - 1; i >= 0; --i)
+            if (v[i] != v[i]) best = i;
+    } else {
+#pragma unroll
+        for (int i = n - 1; i >= 0; --i) best = (v[i] == m) ? i : best;
     }
-    best_v = bv;
+    best_v = m;
     return best;
 }
 

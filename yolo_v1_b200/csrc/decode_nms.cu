@@ -31,7 +31,7 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             if (lane == 0) bad_range[img] = anybad ? 1 : 0;
         }
         const int n = order_candidates(w, valid, lane);
-        const Mask128 keep = nms_rounds<MODE>(w, n, nms_thr, lane);
+        const Mask128 keep = nms_pairwise<MODE>(w, n, nms_thr, lane);
         if (lane == 0) {
             n_keep[img] = keep.count();
             if (n_cand != nullptr) n_cand[img] = n;
@@ -45,7 +45,7 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             const int k = w.order[p], c = w.cand.cls[k];
             int pos;
             if (order == YH_ORDER_CLASS_GROUPED) {
-                pos = w.cls_off[c] + count_below(keep, p) - count_below(keep, w.cls_start[c]);
+                pos = w.cls_off[c] + count_below(keep, p) - w.cls_kbase[c];
             } else {
                 // global (confidence desc, candidate asc) rank among the kept
                 const double mine = w.cand.conf[k];

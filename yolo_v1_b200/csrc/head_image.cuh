@@ -46,6 +46,7 @@ struct __align__(16) WarpWindow {
     int count[kC];                  // class histogram, then running cursor
     uint8_t cls_start[kC + 4];      // first sorted position of each class; [kC] = n
     uint8_t cls_off[kC + 4];        // output offset of each class group (class-grouped order)
+    uint8_t cls_kbase[kC + 4];      // kept detections at sorted positions before the class
 };
 
 // Overlay of `stage` after the target image has been parsed into registers.

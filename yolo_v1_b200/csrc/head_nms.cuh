@@ -74,7 +74,7 @@ __device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &va
 // class are tested against it; rounds = max kept per class.  Returns the keep mask
 // over sorted positions.  A NaN threshold means "decode only": keep everything.
 template <int MODE>
-__device__ __forceinline__ Mask128 nms_rounds(const WarpWindow &w, int n, double nms_thr, int lane) {
+static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, int n, double nms_thr, int lane) {
     Mask128 rem, keep = {0, 0, 0, 0};
 #pragma unroll
     for (int s = 0; s < kSlots; ++s) {
@@ -109,6 +109,54 @@ __device__ __forceinline__ Mask128 nms_rounds(const WarpWindow &w, int n, double
     return keep;
 }
 
+// Overlay of `stage` between decode and the next staging: NMS scratch.
+struct NmsOverlay {
+    unsigned long long sup[kCand];  // bit i: the i-th member of my class (i < my rank) overlaps me
+    uint8_t kept[kPad];
+};
+static_assert(sizeof(NmsOverlay) <= sizeof(float2) * (kStagePairs + 1), "overlay too large");
+
+// Same result as nms_rounds, organised for the common case of many small classes:
+//   1. every candidate tests itself against ALL earlier members of its class
+//      (independent work, no rounds) and records the overlaps as a bitmask;
+//   2. one lane per class replays the greedy scan over those bitmasks.
+// Classes with more than 64 members fall back to nms_rounds.
+template <int MODE>
+__device__ __forceinline__ Mask128 nms_pairwise(WarpWindow &w, int n, double nms_thr, int lane) {
+    const int cc = lane < kC ? lane : 0;
+    const int clo = w.cls_start[cc], chi = w.cls_start[cc + 1];
+    const bool big = (lane < kC) && (chi - clo > 64);
+    if (__any_sync(kFull, big) || nms_thr != nms_thr) return nms_rounds<MODE>(w, n, nms_thr, lane);
+    NmsOverlay &no = *reinterpret_cast<NmsOverlay *>(w.stage);
+#pragma unroll 1
+    for (int p = lane; p < n; p += 32) {
+        const int k = w.order[p];
+        const int lo = w.cls_start[w.cand.cls[k]];
+        const Corners me = cand_corners(w, k);
+        unsigned long long sup = 0;
+        for (int e = lo; e < p; ++e)  // reference argument order: iou(current, other)
+            if (!iou_below<MODE>(cand_corners(w, w.order[e]), me, nms_thr)) sup |= 1ull << (e - lo);
+        no.sup[p] = sup;
+    }
+    __syncwarp();
+    if (lane < kC) {
+        unsigned long long km = 0;
+        for (int i = 0; i < chi - clo; ++i) {
+            const bool kp = (no.sup[clo + i] & km) == 0;
+            km |= (unsigned long long)kp << i;
+            no.kept[clo + i] = kp;
+        }
+    }
+    __syncwarp();
+    Mask128 keep;
+    keep.w0 = __ballot_sync(kFull, lane < n && no.kept[lane]);
+    keep.w1 = __ballot_sync(kFull, lane + 32 < n && no.kept[lane + 32]);
+    keep.w2 = __ballot_sync(kFull, lane + 64 < n && no.kept[lane + 64]);
+    keep.w3 = __ballot_sync(kFull, lane + 96 < n && no.kept[lane + 96]);
+    __syncwarp();
+    return keep;
+}
+
 // Output offset of every class group for the class-grouped order of
 // mAPMetric._apply_nms: groups appear in the order of their best member in the
 // global (confidence desc, candidate asc) order.  Fills w.cls_off.
@@ -118,7 +166,8 @@ __device__ __forceinline__ void class_group_offsets(WarpWindow &w, const Mask128
     const bool present = (lane < kC) && hi > lo;
     const int hk = present ? w.order[lo] : 0;
     const double hc = present ? w.cand.conf[hk] : 0.0;
-    const int kc = present ? count_below(keep, hi) - count_below(keep, lo) : 0;
+    const int kbase = present ? count_below(keep, lo) : 0;
+    const int kc = present ? count_below(keep, hi) - kbase : 0;
     const unsigned have = __ballot_sync(kFull, present);
     int off = 0;
     for (unsigned m = have; m; m &= m - 1) {
@@ -128,7 +177,10 @@ __device__ __forceinline__ void class_group_offsets(WarpWindow &w, const Mask128
         const int on = __shfl_sync(kFull, kc, o);
         if ((oc > hc) || (oc == hc && ok < hk)) off += on;
     }
-    if (lane < kC) w.cls_off[lane] = (uint8_t)off;
+    if (lane < kC) {
+        w.cls_off[lane] = (uint8_t)off;
+        w.cls_kbase[lane] = (uint8_t)kbase;
+    }
     __syncwarp();
 }
 

@@ -108,8 +108,10 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         stage_image(w, pred + (size_t)img * kImgFloats, lane);
         const Mask128 valid = decode_image(w, lane, conf_thr, nullptr);
         const int n = order_candidates(w, valid, lane);
-        const Mask128 keep = nms_rounds<YH_IOU_METRICS>(w, n, nms_thr, lane);
+        const Mask128 keep = nms_pairwise<YH_IOU_METRICS>(w, n, nms_thr, lane);
         class_group_offsets(w, keep, lane);
+        const unsigned lt = (1u << lane) - 1u;
+        const int kb1 = __popc(keep.w0), kb2 = kb1 + __popc(keep.w1), kb3 = kb2 + __popc(keep.w2);
 
         // ---- targets: parse into the overlay
         stage_image(w, tgt + (size_t)img * kImgFloats, lane);
@@ -169,8 +171,10 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                     if (g == 255) continue;
                     const double mine = mo.biou[q][p];
                     double rival = 0.0;  // best IoU an earlier detection brought to the same GT
+#pragma unroll 1
                     for (int e = lo; e < p; ++e)
                         if (keep.test(e) && mo.bgt[q][e] == g) rival = fmax(rival, mo.biou[q][e]);
+#pragma unroll 1
                     for (int t = 0; t < T; ++t) {
                         const double th = s_thr[t];
                         if (mine >= th && !(rival >= th)) flags |= 1ull << (q * T + t);
@@ -178,13 +182,14 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                     if (q == 0 && mine >= 0.5 && !(rival >= 0.5)) flags |= 1ull << (4 * T);
                 }
             }
-            const int j = count_below(keep, p);  // emission slot: sorted order among the kept
+            // emission slot: sorted order among the kept
+            const int j = (s == 0 ? 0 : (s == 1 ? kb1 : (s == 2 ? kb2 : kb3))) + __popc(keep.word(s) & lt);
             const size_t o = (size_t)img * kCand + j;
             const double cf = w.cand.conf[k];
             rec_key[o] = ~orderable(cf == 0.0 ? 0.0 : cf);
             rec_flags[o] = flags | ((uint64_t)c << 56);
             rec_k[o] = (uint8_t)k;
-            rec_pos[o] = (uint8_t)(w.cls_off[c] + j - count_below(keep, lo));
+            rec_pos[o] = (uint8_t)(w.cls_off[c] + j - w.cls_kbase[c]);
             if (rec_box != nullptr) {  // the reference's (x, y, w, h) tuple, metrics.py:214-216
                 const int cell = k / kB, b = k % kB;
                 const float *raw = pred + (size_t)img * kImgFloats + cell * kD + b * 5;
