@@ -278,7 +278,7 @@ def main():
     t_upd = time_call(lambda: head.map_update(pred_d, tgt_d, args.conf, args.nms, thr, gt_count))
     chunk = head.map_update(pred_d, tgt_d, args.conf, args.nms, thr, gt_count.zero_())
     kbar = float(chunk.n_keep.float().mean().item())
-    upd_bytes = 2 * IMG_BYTES + 8 + kbar * (8 + 8 + 1 + 1 + 32) + 2.7 * 33
+    upd_bytes = 2 * IMG_BYTES + 8 + kbar * (8 + 8 + 1 + 16) + 2.7 * 18  # records: key, flags, k, raw box
     stages["map_update"] = {"ms": t_upd, "bytes_per_image": upd_bytes, "kept_per_image": kbar,
                             "gbs": upd_bytes * n / (t_upd * 1e-3) / 1e9}
     t_dec = time_call(lambda: head.decode_nms(pred_d, args.conf, args.nms, head.IOU_INFER, head.ORDER_GLOBAL_CONF,

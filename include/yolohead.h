@@ -106,18 +106,29 @@ int yh_decode_nms(const float *pred, int N, int S, int B, int C, double conf_thr
  *   rec_flags[n*K+q] = class << 56
  *                      | bit s*T+t: TP for subset s at thresholds[t]
  *                      | bit 4*T:   TP in the overall pass at IoU 0.5
- *   rec_k[n*K+q]     = candidate index;  rec_pos[n*K+q] = position of this
- *                      detection in the reference's all_predictions[n] list
- *   rec_box[(n*K+q)*4..] = its (x_abs, y_abs, w, h) in fp64 (nullable)
+ *   rec_k[n*K+q]     = candidate index
+ *   rec_raw[(n*K+q)*4..] = the box's raw (x, y, w, h) floats (nullable; feeds yh_list_form)
  *   n_keep[n], n_gt[n]; gt_count[s*C + c] += ground truths (atomic; zero it first)
- *   gt_cls[n*S*S+g], gt_box[(n*S*S+g)*4..]: ground truths in the reference's list
- *                      order and fp64 form (both nullable)
+ *   gt_cell / gt_cls [n*S*S+g], gt_raw[(n*S*S+g)*4..]: cell index, class and raw
+ *                      (x, y, w, h) of every ground truth (all three nullable together)
  * thresholds_host: T doubles on the HOST (copied into the launch parameters). */
 int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int C, double conf_thr,
                   double nms_thr, const double *thresholds_host, int T, int32_t *n_keep,
-                  uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k, uint8_t *rec_pos,
-                  double *rec_box, int32_t *n_gt, uint8_t *gt_cls, double *gt_box,
+                  uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k, float *rec_raw,
+                  int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls, float *gt_raw,
                   int32_t *gt_count, void *stream);
+
+/* The reference keeps its state as two Python lists (metrics.py:70-71, 99-100).
+ * yh_list_form expands the records of yh_map_update into that form on demand:
+ *   rec_pos[n*K+q]       position of record q in all_predictions[n] (class groups in
+ *                        first-appearance order of the confidence-sorted list,
+ *                        metrics.py:274-279)
+ *   rec_box[(n*K+q)*4..] (x_abs, y_abs, w, h) fp64 as metrics.py:200-203 builds them
+ *   gt_box[(n*S*S+g)*4..] the same for ground truths (metrics.py:247-248) */
+int yh_list_form(const int32_t *n_keep, const uint64_t *rec_key, const uint64_t *rec_flags,
+                 const uint8_t *rec_k, const float *rec_raw, const int32_t *n_gt,
+                 const uint8_t *gt_cell, const float *gt_raw, int N, int S, int B, int C,
+                 uint8_t *rec_pos, double *rec_box, double *gt_box, void *stream);
 
 /* Ground truths of a batch in the reference's list form (metrics.py:220-256):
  * gt_cls[n*S*S + g], gt_box[(n*S*S + g)*4] fp64, n_gt[n]. */

@@ -32,6 +32,7 @@ SIGNATURES = {
     "yh_scale_inplace": (_i, [_vp, _i, _sz, _vp, _vp]),
     "yh_decode_nms": (_i, [_vp, _i, _i, _i, _i, _d, _d, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "yh_map_update": (_i, [_vp, _vp, _i, _i, _i, _i, _d, _d, _vp, _i] + [_vp] * 11),
+    "yh_list_form": (_i, [_vp] * 8 + [_i, _i, _i, _i] + [_vp] * 4),
     "yh_parse_gt": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "yh_compact_workspace_bytes": (_sz, [_i]),
     "yh_compact_records": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),

@@ -24,6 +24,7 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
 
     for (int img = blockIdx.x * kWarpsPerCta + wib; img < N; img += warps_total) {
         stage_image(w, pred + (size_t)img * kImgFloats, lane);
+        if (img + warps_total < N) prefetch_image(pred + (size_t)(img + warps_total) * kImgFloats, lane);
         bool bad = false;
         const Mask128 valid = decode_image(w, lane, conf_thr, &bad);
         if (bad_range != nullptr) {

@@ -47,6 +47,9 @@ struct __align__(16) WarpWindow {
     uint8_t cls_start[kC + 4];      // first sorted position of each class; [kC] = n
     uint8_t cls_off[kC + 4];        // output offset of each class group (class-grouped order)
     uint8_t cls_kbase[kC + 4];      // kept detections at sorted positions before the class
+    unsigned validw[4];             // candidates above the threshold, by candidate index
+    unsigned keepw[4];              // kept after NMS, by sorted position
+    uint8_t keepbase[4];            // kept detections in the words before word s
 };
 
 // Overlay of `stage` after the target image has been parsed into registers.
@@ -84,6 +87,16 @@ __device__ __forceinline__ void stage_image(WarpWindow &w, const float *__restri
         if (q < kStagePairs) w.stage[q] = __ldg(src + q);
     }
     __syncwarp();
+}
+
+// Pull one image (5,880 B, 47 lines of 128 B) towards L2 ahead of its staging loads.
+__device__ __forceinline__ void prefetch_image(const float *__restrict__ img, int lane) {
+    const char *p = reinterpret_cast<const char *>(img);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int off = (lane + 32 * i) * 128;
+        if (off < kImgFloats * 4) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + off));
+    }
 }
 
 // 128-bit masks over candidates or sorted positions: word s, bit l <-> 32*s + l.

@@ -19,8 +19,11 @@ __device__ __forceinline__ Corners cand_corners(const WarpWindow &w, int k) {
 __device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &valid, int lane) {
     const int n = valid.count();
     if (lane < kC) w.count[lane] = 0;
+    if (lane == 0) {
+        w.validw[0] = valid.w0; w.validw[1] = valid.w1; w.validw[2] = valid.w2; w.validw[3] = valid.w3;
+    }
     __syncwarp();
-#pragma unroll 1
+#pragma unroll
     for (int s = 0; s < kSlots; ++s)
         if ((valid.word(s) >> lane) & 1u) atomicAdd(&w.count[w.cand.cls[lane + 32 * s]], 1);
     __syncwarp();
@@ -39,7 +42,7 @@ __device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &va
     }
     if (lane == 0) w.cls_start[kC] = (uint8_t)n;
     __syncwarp();
-#pragma unroll 1
+#pragma unroll
     for (int s = 0; s < kSlots; ++s)
         if ((valid.word(s) >> lane) & 1u) {
             const int k = lane + 32 * s;
@@ -51,7 +54,7 @@ __device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &va
     // and earlier candidate -- the stable order of sorted(..., reverse=True))
 #pragma unroll 1
     for (int s = 0; s < kSlots; ++s)
-        if ((valid.word(s) >> lane) & 1u) {
+        if ((w.validw[s] >> lane) & 1u) {
             const int k = lane + 32 * s;
             const int c = w.cand.cls[k];
             const int lo = w.cls_start[c], hi = w.cls_start[c + 1];
@@ -69,10 +72,11 @@ __device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &va
 }
 
 // ---- NMS ---------------------------------------------------------------------------
-// Greedy per-class NMS over the sorted candidates.  Each round, every class's best
-// still-undecided candidate is kept and all later undecided candidates of that
-// class are tested against it; rounds = max kept per class.  Returns the keep mask
-// over sorted positions.  A NaN threshold means "decode only": keep everything.
+// Greedy per-class NMS over the sorted candidates, round-based: every round keeps each
+// class's best undecided candidate and tests all later undecided ones against it.
+// Rounds = max kept per class.  Handles any class size; used as the fallback of
+// nms_pairwise (a class with more than 64 members) and for "decode only" (NaN
+// threshold: keep everything).
 template <int MODE>
 static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, int n, double nms_thr, int lane) {
     Mask128 rem, keep = {0, 0, 0, 0};
@@ -113,35 +117,51 @@ static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, int n, do
 struct NmsOverlay {
     unsigned long long sup[kCand];  // bit i: the i-th member of my class (i < my rank) overlaps me
     uint8_t kept[kPad];
+    unsigned short pair_base[kC + 4];  // pairs of all classes before c
 };
 static_assert(sizeof(NmsOverlay) <= sizeof(float2) * (kStagePairs + 1), "overlay too large");
 
 // Same result as nms_rounds, organised for the common case of many small classes:
-//   1. every candidate tests itself against ALL earlier members of its class
-//      (independent work, no rounds) and records the overlaps as a bitmask;
+//   1. all same-class pairs (a earlier than b) are enumerated flat across the warp, so
+//      every lane tests one pair per step regardless of how the classes are sized;
+//      an overlap sets bit a of sup[b];
 //   2. one lane per class replays the greedy scan over those bitmasks.
-// Classes with more than 64 members fall back to nms_rounds.
 template <int MODE>
 __device__ __forceinline__ Mask128 nms_pairwise(WarpWindow &w, int n, double nms_thr, int lane) {
     const int cc = lane < kC ? lane : 0;
     const int clo = w.cls_start[cc], chi = w.cls_start[cc + 1];
-    const bool big = (lane < kC) && (chi - clo > 64);
-    if (__any_sync(kFull, big) || nms_thr != nms_thr) return nms_rounds<MODE>(w, n, nms_thr, lane);
+    const int m = lane < kC ? chi - clo : 0;
+    if (__any_sync(kFull, m > 64) || nms_thr != nms_thr) return nms_rounds<MODE>(w, n, nms_thr, lane);
     NmsOverlay &no = *reinterpret_cast<NmsOverlay *>(w.stage);
+    const int np = m * (m - 1) / 2;
+    int inc = np;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        int v = __shfl_up_sync(kFull, inc, off);
+        if (lane >= off) inc += v;
+    }
+    const int total = __shfl_sync(kFull, inc, 31);
+    if (lane <= kC) no.pair_base[lane] = (unsigned short)(inc - np);  // [kC] = total
+    for (int p = lane; p < n; p += 32) no.sup[p] = 0;
+    __syncwarp();
+    int c = 0;
 #pragma unroll 1
-    for (int p = lane; p < n; p += 32) {
-        const int k = w.order[p];
-        const int lo = w.cls_start[w.cand.cls[k]];
-        const Corners me = cand_corners(w, k);
-        unsigned long long sup = 0;
-        for (int e = lo; e < p; ++e)  // reference argument order: iou(current, other)
-            if (!iou_below<MODE>(cand_corners(w, w.order[e]), me, nms_thr)) sup |= 1ull << (e - lo);
-        no.sup[p] = sup;
+    for (int t = lane; t < total; t += 32) {
+        while (t >= no.pair_base[c + 1]) ++c;
+        const int u = t - no.pair_base[c];
+        int b = (int)((1.0f + sqrtf((float)(8 * u + 1))) * 0.5f);  // row of the strict lower triangle
+        b -= (b * (b - 1) / 2 > u);
+        b += ((b + 1) * b / 2 <= u);
+        const int a = u - b * (b - 1) / 2;
+        const int lo = w.cls_start[c];
+        // reference argument order: iou(current = earlier, other = later)
+        if (!iou_below<MODE>(cand_corners(w, w.order[lo + a]), cand_corners(w, w.order[lo + b]), nms_thr))
+            atomicOr(&no.sup[lo + b], 1ull << a);
     }
     __syncwarp();
     if (lane < kC) {
         unsigned long long km = 0;
-        for (int i = 0; i < chi - clo; ++i) {
+        for (int i = 0; i < m; ++i) {
             const bool kp = (no.sup[clo + i] & km) == 0;
             km |= (unsigned long long)kp << i;
             no.kept[clo + i] = kp;
@@ -157,9 +177,21 @@ __device__ __forceinline__ Mask128 nms_pairwise(WarpWindow &w, int n, double nms
     return keep;
 }
 
+// Publishes the keep mask and its per-word prefix in shared memory (rolled loops read
+// them with a runtime word index).
+__device__ __forceinline__ void publish_keep(WarpWindow &w, const Mask128 &keep, int lane) {
+    if (lane == 0) {
+        w.keepw[0] = keep.w0; w.keepw[1] = keep.w1; w.keepw[2] = keep.w2; w.keepw[3] = keep.w3;
+        const int k1 = __popc(keep.w0), k2 = k1 + __popc(keep.w1), k3 = k2 + __popc(keep.w2);
+        w.keepbase[0] = 0; w.keepbase[1] = (uint8_t)k1; w.keepbase[2] = (uint8_t)k2; w.keepbase[3] = (uint8_t)k3;
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ bool kept_at(const WarpWindow &w, int p) { return (w.keepw[p >> 5] >> (p & 31)) & 1u; }
+
 // Output offset of every class group for the class-grouped order of
 // mAPMetric._apply_nms: groups appear in the order of their best member in the
-// global (confidence desc, candidate asc) order.  Fills w.cls_off.
+// global (confidence desc, candidate asc) order.  Fills w.cls_off / w.cls_kbase.
 __device__ __forceinline__ void class_group_offsets(WarpWindow &w, const Mask128 &keep, int lane) {
     const int c = lane < kC ? lane : 0;
     const int lo = w.cls_start[c], hi = w.cls_start[c + 1];

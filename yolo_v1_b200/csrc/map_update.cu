@@ -24,7 +24,8 @@ struct Thresholds {
 // Returns the number of ground truths.  gt_hist (shared, 4*kC ints) accumulates
 // the per-(subset, class) counts of this CTA.
 __device__ __forceinline__ int parse_targets(WarpWindow &w, int lane, int *gt_hist,
-                                             uint8_t *__restrict__ out_cls, double *__restrict__ out_box) {
+                                             uint8_t *__restrict__ out_cell, uint8_t *__restrict__ out_cls,
+                                             float4 *__restrict__ out_raw) {
     const float *st = reinterpret_cast<const float *>(w.stage);
     // pass 1: pull the (few) ground-truth cells into registers before the overlay is written
     bool is_gt[2];
@@ -71,10 +72,10 @@ __device__ __forceinline__ int parse_targets(WarpWindow &w, int lane, int *gt_hi
             mo.gcls[g] = (uint8_t)cls[cs];
             const int bucket = (cr.area < small_a) ? 1 : ((cr.area < medium_a) ? 2 : 3);
             mo.gbucket[g] = (uint8_t)bucket;
-            if (out_cls != nullptr) out_cls[g] = (uint8_t)cls[cs];
-            if (out_box != nullptr) {  // the reference's (x, y, w, h) tuple, metrics.py:254
-                out_box[4 * g + 0] = xa; out_box[4 * g + 1] = ya;
-                out_box[4 * g + 2] = (double)bw[cs]; out_box[4 * g + 3] = (double)bh[cs];
+            if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
+                out_cell[g] = (uint8_t)cell;
+                out_cls[g] = (uint8_t)cls[cs];
+                out_raw[g] = make_float4(x[cs], y[cs], bw[cs], bh[cs]);
             }
             atomicAdd(&gt_hist[cls[cs]], 1);
             atomicAdd(&gt_hist[bucket * kC + cls[cs]], 1);
@@ -87,9 +88,9 @@ __global__ void __launch_bounds__(kWarpsPerCtaM * 32)
 map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt, int N,
                   double conf_thr, double nms_thr, Thresholds thr, int32_t *__restrict__ n_keep,
                   uint64_t *__restrict__ rec_key, uint64_t *__restrict__ rec_flags,
-                  uint8_t *__restrict__ rec_k, uint8_t *__restrict__ rec_pos,
-                  double *__restrict__ rec_box, int32_t *__restrict__ n_gt,
-                  uint8_t *__restrict__ gt_cls, double *__restrict__ gt_box,
+                  uint8_t *__restrict__ rec_k, float4 *__restrict__ rec_raw,
+                  int32_t *__restrict__ n_gt, uint8_t *__restrict__ gt_cell,
+                  uint8_t *__restrict__ gt_cls, float4 *__restrict__ gt_raw,
                   int32_t *__restrict__ gt_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WarpWindow *windows = reinterpret_cast<WarpWindow *>(smem_raw);
@@ -106,17 +107,20 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
     for (int img = blockIdx.x * kWarpsPerCtaM + wib; img < N; img += warps_total) {
         // ---- predictions: decode, order, NMS
         stage_image(w, pred + (size_t)img * kImgFloats, lane);
+        prefetch_image(tgt + (size_t)img * kImgFloats, lane);
+        if (img + warps_total < N) prefetch_image(pred + (size_t)(img + warps_total) * kImgFloats, lane);
         const Mask128 valid = decode_image(w, lane, conf_thr, nullptr);
         const int n = order_candidates(w, valid, lane);
         const Mask128 keep = nms_pairwise<YH_IOU_METRICS>(w, n, nms_thr, lane);
-        class_group_offsets(w, keep, lane);
+        publish_keep(w, keep, lane);
         const unsigned lt = (1u << lane) - 1u;
-        const int kb1 = __popc(keep.w0), kb2 = kb1 + __popc(keep.w1), kb3 = kb2 + __popc(keep.w2);
 
         // ---- targets: parse into the overlay
         stage_image(w, tgt + (size_t)img * kImgFloats, lane);
-        const int ngt = parse_targets(w, lane, gt_hist, gt_cls ? gt_cls + (size_t)img * kCells : nullptr,
-                                      gt_box ? gt_box + (size_t)img * kCells * 4 : nullptr);
+        const bool lists = gt_raw != nullptr;
+        const int ngt = parse_targets(w, lane, gt_hist, lists ? gt_cell + (size_t)img * kCells : nullptr,
+                                      lists ? gt_cls + (size_t)img * kCells : nullptr,
+                                      lists ? gt_raw + (size_t)img * kCells : nullptr);
         MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
         if (lane == 0) {
             n_keep[img] = keep.count();
@@ -128,7 +132,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         unsigned matched = 0;  // bit s: my slot-s detection met a ground truth of its class
 #pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
-            if (!((keep.word(s) >> lane) & 1u)) continue;
+            if (!((w.keepw[s] >> lane) & 1u)) continue;
             const int p = lane + 32 * s;
             const int k = w.order[p], c = w.cand.cls[k];
             double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
@@ -159,7 +163,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         // IoU >= t (metrics.py:406-413).  "Earlier" = lower sorted position.
 #pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
-            if (!((keep.word(s) >> lane) & 1u)) continue;
+            if (!((w.keepw[s] >> lane) & 1u)) continue;
             const int p = lane + 32 * s;
             const int k = w.order[p], c = w.cand.cls[k];
             const int lo = w.cls_start[c];
@@ -173,7 +177,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                     double rival = 0.0;  // best IoU an earlier detection brought to the same GT
 #pragma unroll 1
                     for (int e = lo; e < p; ++e)
-                        if (keep.test(e) && mo.bgt[q][e] == g) rival = fmax(rival, mo.biou[q][e]);
+                        if (kept_at(w, e) && mo.bgt[q][e] == g) rival = fmax(rival, mo.biou[q][e]);
 #pragma unroll 1
                     for (int t = 0; t < T; ++t) {
                         const double th = s_thr[t];
@@ -183,20 +187,15 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                 }
             }
             // emission slot: sorted order among the kept
-            const int j = (s == 0 ? 0 : (s == 1 ? kb1 : (s == 2 ? kb2 : kb3))) + __popc(keep.word(s) & lt);
+            const int j = w.keepbase[s] + __popc(w.keepw[s] & lt);
             const size_t o = (size_t)img * kCand + j;
             const double cf = w.cand.conf[k];
             rec_key[o] = ~orderable(cf == 0.0 ? 0.0 : cf);
             rec_flags[o] = flags | ((uint64_t)c << 56);
             rec_k[o] = (uint8_t)k;
-            rec_pos[o] = (uint8_t)(w.cls_off[c] + j - w.cls_kbase[c]);
-            if (rec_box != nullptr) {  // the reference's (x, y, w, h) tuple, metrics.py:214-216
-                const int cell = k / kB, b = k % kB;
-                const float *raw = pred + (size_t)img * kImgFloats + cell * kD + b * 5;
-                rec_box[4 * o + 0] = abs_coord(cell % kS, __ldg(raw + 0));
-                rec_box[4 * o + 1] = abs_coord(cell / kS, __ldg(raw + 1));
-                rec_box[4 * o + 2] = (double)__ldg(raw + 2);
-                rec_box[4 * o + 3] = (double)__ldg(raw + 3);
+            if (rec_raw != nullptr) {  // raw (x, y, w, h) of the box; yh_list_form rebuilds the tuple
+                const float *raw = pred + (size_t)img * kImgFloats + (k / kB) * kD + (k % kB) * 5;
+                rec_raw[o] = make_float4(__ldg(raw + 0), __ldg(raw + 1), __ldg(raw + 2), __ldg(raw + 3));
             }
         }
         __syncwarp();
@@ -251,8 +250,8 @@ using namespace yh;
 extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int C,
                              double conf_thr, double nms_thr, const double *thresholds_host, int T,
                              int32_t *n_keep, uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k,
-                             uint8_t *rec_pos, double *rec_box, int32_t *n_gt, uint8_t *gt_cls,
-                             double *gt_box, int32_t *gt_count, void *stream) {
+                             float *rec_raw, int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls,
+                             float *gt_raw, int32_t *gt_count, void *stream) {
     if (!shape_ok(S, B, C)) {
         set_error("yh_map_update: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
         return YH_ERR_UNSUPPORTED;
@@ -262,12 +261,13 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
         return YH_ERR_UNSUPPORTED;
     }
     if (N < 0 || !pred || !tgt || !thresholds_host || !n_keep || !rec_key || !rec_flags || !rec_k ||
-        !rec_pos || !n_gt || !gt_count) {
+        !n_gt || !gt_count || ((gt_raw != nullptr) != (gt_cell != nullptr)) ||
+        ((gt_raw != nullptr) != (gt_cls != nullptr))) {
         set_error("yh_map_update: bad argument");
         return YH_ERR_BAD_ARG;
     }
-    if (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8)) {
-        set_error("yh_map_update: pred/tgt must be 8-byte aligned");
+    if (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8) || ((uintptr_t)rec_raw % 16) || ((uintptr_t)gt_raw % 16)) {
+        set_error("yh_map_update: pred/tgt must be 8-byte aligned, rec_raw/gt_raw 16-byte aligned");
         return YH_ERR_ALIGNMENT;
     }
     if (N == 0) return 0;
@@ -284,8 +284,8 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
     const int cap = 148 * 5;
     if (ctas > cap) ctas = cap;
     map_update_kernel<<<ctas, kWarpsPerCtaM * 32, smem, (cudaStream_t)stream>>>(
-        pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, rec_pos, rec_box, n_gt, gt_cls,
-        gt_box, gt_count);
+        pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, (float4 *)rec_raw, n_gt, gt_cell,
+        gt_cls, (float4 *)gt_raw, gt_count);
     return check_launch("yh_map_update");
 }
 

@@ -82,12 +82,13 @@ class UpdateChunk:
     n_keep: torch.Tensor     # (N,) int32
     rec_key: torch.Tensor    # (N,K) uint64-as-int64: ~orderable(conf)
     rec_flags: torch.Tensor  # (N,K) int64: class << 56 | TP bits
-    rec_k: torch.Tensor      # (N,K) uint8
-    rec_pos: torch.Tensor    # (N,K) uint8 position in the reference's per-image list
-    rec_box: torch.Tensor | None  # (N,K,4) float64
+    rec_k: torch.Tensor      # (N,K) uint8 candidate index
+    rec_raw: torch.Tensor | None  # (N,K,4) float32 raw (x, y, w, h)
     n_gt: torch.Tensor       # (N,) int32
+    gt_cell: torch.Tensor | None  # (N,S*S) uint8
     gt_cls: torch.Tensor | None   # (N,S*S) uint8
-    gt_box: torch.Tensor | None   # (N,S*S,4) float64
+    gt_raw: torch.Tensor | None   # (N,S*S,4) float32
+    shape: tuple = (S_, B_, C_)
 
 
 def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: float, thresholds,
@@ -107,18 +108,37 @@ def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: 
     rec_key = torch.empty(N, K, **i64)
     rec_flags = torch.empty(N, K, **i64)
     rec_k = torch.empty(N, K, **u8)
-    rec_pos = torch.empty(N, K, **u8)
-    rec_box = torch.empty(N, K, 4, dtype=torch.float64, device=dev) if want_lists else None
+    rec_raw = torch.empty(N, K, 4, dtype=torch.float32, device=dev) if want_lists else None
+    gt_cell = torch.empty(N, G, **u8) if want_lists else None
     gt_cls = torch.empty(N, G, **u8) if want_lists else None
-    gt_box = torch.empty(N, G, 4, dtype=torch.float64, device=dev) if want_lists else None
+    gt_raw = torch.empty(N, G, 4, dtype=torch.float32, device=dev) if want_lists else None
     with torch.cuda.device(dev):
         rc = _lib.lib().yh_map_update(p.data_ptr(), t.data_ptr(), N, S, B, Cn, float(conf_thr), float(nms_thr),
                                       thr_c, len(thr_c), n_keep.data_ptr(), rec_key.data_ptr(),
-                                      rec_flags.data_ptr(), rec_k.data_ptr(), rec_pos.data_ptr(),
-                                      _lib.ptr(rec_box), n_gt.data_ptr(), _lib.ptr(gt_cls), _lib.ptr(gt_box),
-                                      gt_count.data_ptr(), _lib.stream_ptr(dev))
+                                      rec_flags.data_ptr(), rec_k.data_ptr(), _lib.ptr(rec_raw), n_gt.data_ptr(),
+                                      _lib.ptr(gt_cell), _lib.ptr(gt_cls), _lib.ptr(gt_raw), gt_count.data_ptr(),
+                                      _lib.stream_ptr(dev))
     _lib.check(rc, "yh_map_update")
-    return UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, rec_pos, rec_box, n_gt, gt_cls, gt_box)
+    return UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, rec_raw, n_gt, gt_cell, gt_cls, gt_raw, (S, B, Cn))
+
+
+def list_form(ch: UpdateChunk):
+    """yh_list_form: (rec_pos uint8 (N,K), rec_box float64 (N,K,4), gt_box float64 (N,S*S,4))."""
+    if ch.rec_raw is None:
+        raise _lib.YoloHeadError("this batch was accumulated without list data (want_lists=False)")
+    S, B, Cn = ch.shape
+    N, K = ch.rec_key.shape
+    dev = ch.rec_key.device
+    rec_pos = torch.empty(N, K, dtype=torch.uint8, device=dev)
+    rec_box = torch.empty(N, K, 4, dtype=torch.float64, device=dev)
+    gt_box = torch.empty(N, S * S, 4, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().yh_list_form(ch.n_keep.data_ptr(), ch.rec_key.data_ptr(), ch.rec_flags.data_ptr(),
+                                     ch.rec_k.data_ptr(), ch.rec_raw.data_ptr(), ch.n_gt.data_ptr(),
+                                     ch.gt_cell.data_ptr(), ch.gt_raw.data_ptr(), N, S, B, Cn, rec_pos.data_ptr(),
+                                     rec_box.data_ptr(), gt_box.data_ptr(), _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_list_form")
+    return rec_pos, rec_box, gt_box
 
 
 def compact_records(chunk: UpdateChunk):

@@ -86,10 +86,11 @@ class mAPMetric:
             n_gt = ch.n_gt.cpu().numpy()
             conf = _conf_from_key(ch.rec_key.cpu().numpy())
             cls = (ch.rec_flags.cpu().numpy().view(np.uint64) >> np.uint64(56)).astype(np.int64)
-            pos = ch.rec_pos.cpu().numpy()
-            box = ch.rec_box.cpu().numpy()
+            rec_pos, rec_box, gt_box = head.list_form(ch)
+            pos = rec_pos.cpu().numpy()
+            box = rec_box.cpu().numpy()
             gcls = ch.gt_cls.cpu().numpy()
-            gbox = ch.gt_box.cpu().numpy()
+            gbox = gt_box.cpu().numpy()
             for i in range(ch.n):
                 k = int(n_keep[i])
                 dets = [None] * k
