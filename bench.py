@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--nms", type=float, default=0.4)
     ap.add_argument("--cpu-sample", type=int, default=4096, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="class_shard", choices=["class_shard", "gather"],
+                    help="N>1: how compute() makes the per-class order global (yolo_v1_b200/distributed.py)")
     return ap.parse_args()
 
 
@@ -195,7 +197,7 @@ def main():
     if world > 1:
         from yolo_v1_b200.distributed import DistributedMAP
 
-        metric = DistributedMAP(metric)
+        metric = DistributedMAP(metric, mode=args.exchange)
 
     def step(p, t):
         p = p.requires_grad_(True)

@@ -157,6 +157,19 @@ size_t yh_ap_workspace_bytes(int64_t M, int C, int T);
 int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int32_t *gt_count, int C, int T,
                  double *ap, int64_t *totals, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ------------------------------------------------- multi-GPU exchange ----
+ * Average precision is independent per class (metrics.py:126-141, 382), so N ranks
+ * can each sort and reduce a subset of the classes.  yh_partition_records lays the
+ * M compact records of one rank out as n_parts contiguous runs (run p = records
+ * whose class c has owner_of_class_host[c] == p), each run in the input (image)
+ * order, and writes the run lengths to part_count[n_parts] (device, int64): the
+ * split sizes of one all_to_all_single.  n_parts <= 32. */
+size_t yh_partition_workspace_bytes(int64_t M);
+int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M,
+                         const uint8_t *owner_of_class_host, int C, int n_parts, uint64_t *out_key,
+                         uint64_t *out_flags, int64_t *part_count, void *workspace,
+                         size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------- list-form entry points ----
  * The reference's helpers also accept arbitrary Python lists (tests call
  * _apply_nms / non_max_suppression / _calculate_iou / iou on hand-built boxes,

@@ -332,3 +332,22 @@ def test_sort_stability_and_scale():
     got = m3.compute()
     for k in want:
         assert float(got[k]) == pytest.approx(float(want[k]), rel=1e-9, abs=1e-12), k
+
+
+# ----------------------------------------------------------------------------- partition (multi-GPU exchange)
+@pytest.mark.gpu
+@pytest.mark.parametrize("m,parts", [(0, 2), (1, 2), (1023, 3), (1024, 8), (50_000, 8), (300_001, 32)])
+def test_partition_records_is_a_stable_partition(m, parts):
+    from yolo_v1_b200 import distributed as D
+
+    rng = np.random.default_rng(m + parts)
+    key = rng.integers(-2**62, 2**62, size=max(m, 1), dtype=np.int64)[:m]
+    cls = rng.integers(0, 20, size=m, dtype=np.int64)
+    flg = (cls << 56) | np.arange(m, dtype=np.int64)
+    owners = D.class_owners(20, parts)
+    k, f, cnt = D.partition_records(torch.from_numpy(key).cuda(), torch.from_numpy(flg).cuda(), m, owners, parts)
+    own = np.array(owners)[cls]
+    perm = np.argsort(own, kind="stable")
+    assert cnt == [int((own == p).sum()) for p in range(parts)]
+    assert np.array_equal(k[:m].cpu().numpy(), key[perm])
+    assert np.array_equal(f[:m].cpu().numpy(), flg[perm])

@@ -1,0 +1,208 @@
+"""Image-sharded mAP over the GPUs of one box.
+
+The reference is single-process (its "distributed" is one remote GPU), so this
+module has no counterpart file there; it extends `mAPMetric` the way the
+north-star prescribes: every rank runs the fused update kernel on a CONTIGUOUS
+range of the images, and only `compute()` talks to the other ranks.
+
+TP/FP flags are final per image (csrc/map_update.cu), so what has to be global is
+just the per-class confidence-sorted order and the ground-truth counts
+(metrics.py:382, 415-436).  Two exchange modes, same results bit for bit:
+
+  "gather"       one all-gather of the compact records (16 B each) in rank order
+                 + an all-reduce of the 4*C ground-truth counts; every rank then
+                 runs yh_ap_reduce on the full record set (the north-star's form).
+  "class_shard"  records are stably partitioned by class owner
+                 (yh_partition_records) and exchanged with ONE all_to_all_single;
+                 each rank sorts/reduces only its own classes and the 4*C*T AP
+                 table is summed with an all-reduce (classes a rank does not own
+                 contribute exact zeros).  R x fewer bytes per rank, sort sharded.
+
+Tie order: the reference's stable sort leaves equal confidences in image order.
+Ranks own contiguous image ranges and both modes concatenate in rank order, so the
+stable radix sort of yh_ap_reduce sees the same sequence as a single process.
+
+The collectives are plain `torch.distributed` calls and work on any backend
+(NCCL over NVLink on the box; gloo in the CPU tests of the exchange logic).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib, head
+from .metrics import mAPMetric
+
+
+def shard_range(n_images: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous image range [lo, hi) of `rank`: ceil(n/world) images each, the tail ranks may be short or empty."""
+    per = -(-n_images // world) if world > 0 else n_images
+    lo = min(n_images, rank * per)
+    return lo, min(n_images, lo + per)
+
+
+def class_owners(num_classes: int, world: int) -> List[int]:
+    """Owner rank of every class for the class-sharded reduce: contiguous blocks of ceil(C/world)."""
+    per = -(-num_classes // world)
+    return [min(world - 1, c // per) for c in range(num_classes)]
+
+
+# ------------------------------------------------------------------ exchange plumbing (backend agnostic)
+def _all_counts(n_local: int, device, group) -> List[int]:
+    world = dist.get_world_size(group)
+    mine = torch.tensor([n_local], dtype=torch.int64, device=device)
+    out = torch.empty(world, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(out, mine, group=group)
+    return [int(v) for v in out.tolist()]
+
+
+def gather_records(key: torch.Tensor, flags: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor, List[int]]:
+    """All-gather variable-length (key, flags) record arrays in rank order.
+
+    Returns (key_all, flags_all, counts).  One padded all_gather_into_tensor of a
+    (2, max_count) int64 block per rank, then the pads are dropped."""
+    world = dist.get_world_size(group)
+    m = key.numel()
+    counts = _all_counts(m, key.device, group)
+    cap = max(max(counts), 1)
+    send = torch.zeros(2, cap, dtype=torch.int64, device=key.device)
+    send[0, :m] = key
+    send[1, :m] = flags
+    flat = torch.empty(world * 2 * cap, dtype=torch.int64, device=key.device)
+    dist.all_gather_into_tensor(flat, send.view(-1), group=group)
+    recv = flat.view(world, 2, cap)
+    key_all = torch.cat([recv[r, 0, :counts[r]] for r in range(world)])
+    flags_all = torch.cat([recv[r, 1, :counts[r]] for r in range(world)])
+    return key_all, flags_all, counts
+
+
+def exchange_by_owner(key: torch.Tensor, flags: torch.Tensor, part_count: List[int], group=None):
+    """all_to_all of records already laid out as `world` contiguous runs (run r goes to rank r).
+
+    Returns (key_mine, flags_mine): runs received from rank 0, 1, ... concatenated in rank order."""
+    world = dist.get_world_size(group)
+    dev = key.device
+    send_n = torch.tensor(part_count, dtype=torch.int64, device=dev)
+    recv_n = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(recv_n, send_n, group=group)
+    recv_counts = [int(v) for v in recv_n.tolist()]
+    total = sum(recv_counts)
+    out_k = torch.empty(total, dtype=torch.int64, device=dev)
+    out_f = torch.empty(total, dtype=torch.int64, device=dev)
+    m = sum(part_count)
+    dist.all_to_all_single(out_k, key[:m].contiguous(), recv_counts, list(part_count), group=group)
+    dist.all_to_all_single(out_f, flags[:m].contiguous(), recv_counts, list(part_count), group=group)
+    return out_k, out_f
+
+
+def partition_records(key: torch.Tensor, flags: torch.Tensor, m: int, owners: List[int], n_parts: int):
+    """yh_partition_records: stable partition by class owner.  Returns (key, flags, part_count list)."""
+    _lib.require_cuda(key, "records")
+    dev = key.device
+    lib = _lib.lib()
+    out_k = torch.empty(max(m, 1), dtype=torch.int64, device=dev)
+    out_f = torch.empty(max(m, 1), dtype=torch.int64, device=dev)
+    cnt = torch.zeros(n_parts, dtype=torch.int64, device=dev)
+    ws = torch.empty(lib.yh_partition_workspace_bytes(int(m)) + 256, dtype=torch.uint8, device=dev)
+    tab = (_lib.C.c_uint8 * len(owners))(*owners)
+    with torch.cuda.device(dev):
+        rc = lib.yh_partition_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m), tab,
+                                      len(owners), int(n_parts), out_k.data_ptr(), out_f.data_ptr(),
+                                      cnt.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_partition_records")
+    return out_k, out_f, [int(v) for v in cnt.tolist()]
+
+
+# ------------------------------------------------------------------ the metric
+class DistributedMAP:
+    """`mAPMetric` whose `compute()` is global over a process group.
+
+    Each rank calls `update()` with ITS images only -- rank r must hold the r-th
+    contiguous block of the evaluation set (`shard_range`) for tie order to match
+    the single-process reference.  `compute()` is collective and returns the same
+    dict on every rank.  Everything else (`reset`, thresholds, attributes) is the
+    wrapped metric's."""
+
+    def __init__(self, metric: mAPMetric, group=None, mode: str = "class_shard"):
+        if mode not in ("gather", "class_shard"):
+            raise ValueError(f"unknown exchange mode {mode!r}")
+        self.metric = metric
+        self.group = group
+        self.mode = mode
+
+    def __getattr__(self, name):
+        return getattr(self.metric, name)
+
+    def reset(self):
+        self.metric.reset()
+
+    def update(self, predictions: torch.Tensor, targets: torch.Tensor):
+        self.metric.update(predictions, targets)
+
+    def _local_records(self, dev):
+        m = self.metric
+        C = m.num_classes
+        if m._lists_live or m._pred_lists:
+            raise _lib.YoloHeadError("DistributedMAP: the Python list state was touched on this rank; the sharded "
+                                     "compute() runs from the device records only")
+        keys, flags, total = [], [], 0
+        for ch in m._chunks:
+            k, f, off = head.compact_records(ch)
+            n = int(off[-1].item())
+            keys.append(k[:n])
+            flags.append(f[:n])
+            total += n
+        if not keys:
+            z = torch.empty(0, dtype=torch.int64, device=dev)
+            return z, z.clone(), 0, torch.zeros(4 * C, dtype=torch.int32, device=dev)
+        key = keys[0] if len(keys) == 1 else torch.cat(keys)
+        flg = flags[0] if len(flags) == 1 else torch.cat(flags)
+        return key, flg, total, m._gt_count.clone()
+
+    def compute(self) -> Dict[str, float]:
+        m, g = self.metric, self.group
+        world = dist.get_world_size(g)
+        dev = m._device if m._device is not None else torch.device("cuda", torch.cuda.current_device())
+        T, C = len(m.iou_thresholds), m.num_classes
+        key, flg, total, gt_count = self._local_records(dev)
+        n_img = torch.tensor([len(m._pred_lists) + sum(c.n for c in m._chunks)], dtype=torch.int64, device=dev)
+        dist.all_reduce(n_img, group=g)
+        if int(n_img.item()) == 0:
+            return {"mAP50:95": 0.0, "mAP50": 0.0, "mAP75": 0.0, "precision": 0.0, "recall": 0.0}
+        dist.all_reduce(gt_count, group=g)
+        if self.mode == "gather":
+            key, flg, counts = gather_records(key, flg, g)
+            ap, totals = head.ap_reduce(key, flg, sum(counts), gt_count, C, T)
+        else:
+            pk, pf, part = partition_records(key, flg, total, class_owners(C, world), world)
+            key, flg = exchange_by_owner(pk, pf, part, g)
+            ap, totals = head.ap_reduce(key, flg, key.numel(), gt_count, C, T)
+            dist.all_reduce(ap, group=g)       # classes a rank does not own are exact zeros
+            dist.all_reduce(totals, group=g)
+        totals = totals.cpu().numpy()
+        gtc = gt_count.cpu().numpy().reshape(4, C)
+        return m._results(ap.cpu().numpy(), int(totals[0]), int(totals[1]), gtc, int(gtc[0].sum()), T, C)
+
+
+def evaluate_sharded(model, images: torch.Tensor, targets: torch.Tensor, batch: int = 256, group=None,
+                     mode: str = "class_shard", metric: Optional[mAPMetric] = None, **metric_kw) -> Dict[str, float]:
+    """evaluate_model (metrics.py:654-714) over an in-memory set, image-sharded over the group.
+
+    `images` / `targets` are the FULL set on every rank (host or device); each rank runs the
+    model only on its contiguous `shard_range`.  model=None treats `images` as predictions."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    lo, hi = shard_range(images.shape[0], rank, world)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    dm = DistributedMAP(metric or mAPMetric(**({"num_classes": 20} | metric_kw)), group, mode)
+    if model is not None:
+        model.eval()
+    with torch.no_grad():
+        for s in range(lo, hi, batch):
+            e = min(hi, s + batch)
+            x = images[s:e].to(dev, non_blocking=True)
+            t = targets[s:e].to(dev, non_blocking=True)
+            dm.update(model(x) if model is not None else x, t)
+    return dm.compute()
