@@ -1,0 +1,153 @@
+"""Adversarial inputs for the fused update kernel: flags / keeps vs the CPU oracle, bit-exact.
+
+Dense same-class scenes (49 ground truths and 98 detections of one class), NaN and
+infinite values, every threshold count the flag word carries, unaligned views, and
+full-size (65,536 images) invariants that need no oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import c_oracle, results
+from yolo_v1_b200 import head, mAPMetric, synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+DEFAULT_THR = [0.5 + 0.05 * i for i in range(10)]
+
+
+def _check(pred, tgt, conf_thr, thr=DEFAULT_THR, nms=0.4):
+    n = pred.shape[0]
+    st = c_oracle.update_batch(pred.numpy(), tgt.numpy(), conf_thr, nms, n_threads=4)
+    ref = c_oracle.compute(st, thr, n_threads=4)
+    m = mAPMetric(num_classes=20, iou_thresholds=list(thr), conf_threshold=conf_thr, nms_threshold=nms)
+    m.update(pred.to(DEV), tgt.to(DEV))
+    ch = m._chunks[0]
+    n_keep = ch.n_keep.cpu().numpy()
+    np.testing.assert_array_equal(n_keep, st["n_det"])
+    np.testing.assert_array_equal(ch.n_gt.cpu().numpy(), st["n_gt"])
+    ks = ch.rec_k.cpu().numpy()
+    fl = ch.rec_flags.cpu().numpy().view(np.uint64) & np.uint64((1 << 56) - 1)
+    for i in range(n):
+        mine = {int(ks[i, q]): int(fl[i, q]) for q in range(n_keep[i])}
+        want = {int(st["det_k"][i, q]): int(ref["flags"][i, q]) for q in range(st["n_det"][i])}
+        assert mine == want, f"image {i}"
+    got = m.compute()
+    want = results.assemble(ref["ap"], ref["overall"], ref["sizes"], list(thr), 20, n)
+    assert sorted(got) == sorted(want)
+    for k in want:
+        assert float(got[k]) == pytest.approx(float(want[k]), rel=1e-9, abs=1e-12), k
+    return m
+
+
+def _dense_scene(n, seed, n_cls):
+    """Every cell holds a ground truth; every candidate is confident; only n_cls classes occur."""
+    g = torch.Generator().manual_seed(seed)
+    tgt = torch.zeros(n, 7, 7, 30)
+    tgt[..., 0:2] = torch.rand(n, 7, 7, 2, generator=g)
+    tgt[..., 2:4] = torch.rand(n, 7, 7, 2, generator=g) * 0.3 + 0.02
+    tgt[..., 4] = 1.0
+    cls = torch.randint(0, n_cls, (n, 7, 7), generator=g)
+    tgt[..., 10:].scatter_(-1, cls[..., None], 1.0)
+    pred = torch.rand(n, 7, 7, 30, generator=g) * 0.2
+    pred[..., 0:4] = tgt[..., 0:4] + torch.randn(n, 7, 7, 4, generator=g) * 0.02
+    pred[..., 5:9] = tgt[..., 0:4] + torch.randn(n, 7, 7, 4, generator=g) * 0.05
+    pred[..., 4] = torch.rand(n, 7, 7, generator=g) * 0.5 + 0.5
+    pred[..., 9] = torch.rand(n, 7, 7, generator=g) * 0.5 + 0.5
+    pcls = torch.where(torch.rand(n, 7, 7, generator=g) < 0.8, cls, torch.randint(0, n_cls, (n, 7, 7), generator=g))
+    pred[..., 10:].scatter_(-1, pcls[..., None], 0.9)
+    return pred, tgt
+
+
+@pytest.mark.parametrize("n_cls", [1, 2, 20])
+def test_dense_scenes_49_ground_truths(n_cls):
+    pred, tgt = _dense_scene(48, 10 + n_cls, n_cls)
+    _check(pred, tgt, 0.05)
+    _check(pred, tgt, 0.05, nms=0.95)   # almost nothing suppressed: up to 98 kept of one class
+
+
+def test_duplicate_boxes_share_a_ground_truth():
+    # many identical detections claim the same ground truth: only the first (stable order) may be a TP
+    pred, tgt = _dense_scene(16, 3, 1)
+    pred[..., 5:9] = pred[..., 0:4]
+    pred[..., 9] = pred[..., 4]
+    _check(pred, tgt, 0.05, nms=1.5)    # threshold above any IoU: NMS keeps all 98
+
+
+@pytest.mark.parametrize("T", [1, 2, 7, 13])
+def test_threshold_counts(T):
+    thr = [0.3 + 0.05 * i for i in range(T)]
+    tgt = synth.make_targets(200, seed=5, p_obj=0.2, size_mix=True)
+    pred = synth.make_preds(200, "correlated", seed=5, targets=tgt)
+    _check(pred, tgt, 0.01, thr=thr)
+
+
+def test_unsorted_and_repeated_thresholds():
+    tgt = synth.make_targets(128, seed=6, p_obj=0.2, size_mix=True)
+    pred = synth.make_preds(128, "correlated", seed=6, targets=tgt)
+    _check(pred, tgt, 0.01, thr=[0.9, 0.5, 0.5, 0.75, 0.1])
+
+
+def test_nan_and_inf_values():
+    tgt = synth.make_targets(64, seed=8, p_obj=0.3, size_mix=True)
+    pred = synth.make_preds(64, "correlated", seed=8, targets=tgt)
+    g = torch.Generator().manual_seed(8)
+    hit = torch.rand(pred.shape, generator=g)
+    pred[hit < 0.01] = float("nan")
+    pred[(hit >= 0.01) & (hit < 0.015)] = float("inf")
+    pred[(hit >= 0.015) & (hit < 0.02)] = float("-inf")
+    _check(pred, tgt, 0.01)
+
+
+def test_rawhead_negative_sizes_and_zero_area():
+    tgt = synth.make_targets(256, seed=9, p_obj=0.2, size_mix=True)
+    pred = synth.make_preds(256, "rawhead", seed=9, targets=tgt)
+    pred[:64, :, :, 2] = 0.0            # zero-width boxes: union can be 0 (metrics.py:337-338)
+    tgt[:32, :, :, 2] *= 0.0
+    _check(pred, tgt, 0.01)
+
+
+def test_unaligned_views_are_accepted():
+    tgt = synth.make_targets(33, seed=4, p_obj=0.2, size_mix=True)
+    pred = synth.make_preds(33, "correlated", seed=4, targets=tgt)
+    buf = torch.zeros(pred.numel() + 1, device=DEV)
+    buf[1:] = pred.to(DEV).reshape(-1)
+    view = buf[1:].view_as(pred)        # 4-byte aligned only
+    a = mAPMetric(num_classes=20)
+    a.update(view, tgt.to(DEV))
+    b = mAPMetric(num_classes=20)
+    b.update(pred.to(DEV), tgt.to(DEV))
+    assert a.compute() == b.compute()
+
+
+def test_full_size_invariants():
+    n = 65536
+    tgt = synth.make_targets(n, seed=1234, p_obj=0.055, size_mix=True)
+    pred = synth.make_preds(n, "uniform", seed=1234, targets=tgt)
+    gt_count = torch.zeros(80, dtype=torch.int32, device=DEV)
+    ch = head.map_update(pred.to(DEV), tgt.to(DEV), 0.3, 0.4, DEFAULT_THR, gt_count)
+    dec = head.decode_nms(pred.to(DEV), 0.3, 0.4, head.IOU_METRICS, head.ORDER_CLASS_GROUPED, want_boxes=False)
+    assert torch.equal(ch.n_keep, dec.n_keep)                       # fused update == stand-alone decode+NMS
+    assert bool((dec.n_keep <= dec.n_cand).all())                   # kept is a subset of the candidates
+    n_keep = ch.n_keep.cpu().numpy()
+    valid = np.arange(98)[None, :] < n_keep[:, None]
+    ks_f = np.sort(np.where(valid, ch.rec_k.cpu().numpy(), 255), axis=1)
+    ks_d = np.sort(np.where(valid, dec.keep_k.cpu().numpy(), 255), axis=1)
+    assert np.array_equal(ks_f, ks_d)                               # same kept set per image
+    fl = ch.rec_flags.cpu().numpy().view(np.uint64)
+    cls = (fl >> np.uint64(56)).astype(np.int64)
+    gtc = gt_count.cpu().numpy().reshape(4, 20)
+    assert gtc[0].sum() == int(ch.n_gt.sum()) and np.array_equal(gtc[0], gtc[1:].sum(0))
+    for s in range(4):                                              # TPs never exceed the ground truths
+        for t in (0, 9):
+            bit = ((fl >> np.uint64(s * 10 + t)) & np.uint64(1)).astype(bool) & valid
+            tp_per_class = np.bincount(cls[bit], minlength=20)
+            assert (tp_per_class <= gtc[s]).all(), (s, t)
+    # a TP at a higher threshold is a TP at every lower one only per ground truth, but the count is monotone
+    tp_lo = int((((fl >> np.uint64(0)) & np.uint64(1)).astype(bool) & valid).sum())
+    tp_hi = int((((fl >> np.uint64(9)) & np.uint64(1)).astype(bool) & valid).sum())
+    assert tp_hi <= tp_lo
+    # sorted keys inside each image's class groups: (class asc, confidence desc)
+    key = ch.rec_key.cpu().numpy().view(np.uint64)
+    same = valid[:, 1:] & (cls[:, 1:] == cls[:, :-1])
+    assert (key[:, 1:][same] >= key[:, :-1][same]).all()
+    assert (cls[:, 1:][valid[:, 1:]] >= cls[:, :-1][valid[:, 1:]]).all()

@@ -229,7 +229,10 @@ class mAPMetric:
                 out[f"mAP50_{name}"] = 0.0
                 out[f"mAP75_{name}"] = 0.0
                 continue
-            by_thr = {t: [float(ap[s, c, ti]) for c in range(C)] for ti, t in enumerate(thr)}
+            by_thr = {t: [] for t in thr}  # a repeated threshold appends twice to one list, as metrics.py:543-550
+            for c in range(C):
+                for ti, t in enumerate(thr):
+                    by_thr[t].append(float(ap[s, c, ti]))
             if 0.5 in thr:
                 out[f"mAP50_{name}"] = np.mean(by_thr[0.5])
             if 0.75 in thr:
