@@ -31,8 +31,8 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             const unsigned anybad = __ballot_sync(kFull, bad);
             if (lane == 0) bad_range[img] = anybad ? 1 : 0;
         }
-        const int n = order_candidates(w, valid, lane);
-        const Mask128 keep = nms_pairwise<MODE>(w, n, nms_thr, lane);
+        int n;
+        const Mask128 keep = order_and_nms<MODE>(w, valid, nms_thr, lane, n);
         if (lane == 0) {
             n_keep[img] = keep.count();
             if (n_cand != nullptr) n_cand[img] = n;

@@ -13,10 +13,11 @@ __device__ __forceinline__ Corners cand_corners(const WarpWindow &w, int k) {
     return c;
 }
 
-// ---- ordering --------------------------------------------------------------------
-// Sorted position p = (class asc, confidence desc, candidate asc): fills w.order[p] = k
-// and w.cls_start[c]; returns n.  Lane owns candidates k = lane + 32*s.
-__device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &valid, int lane) {
+// ---- class segments -------------------------------------------------------------------
+// Sorted position p = (class asc, confidence desc, candidate asc).  build_members groups
+// the valid candidates by class (w.member, unordered inside a class; w.cls_start) and
+// returns n.  Lane owns candidates k = lane + 32*s.
+__device__ __forceinline__ int build_members(WarpWindow &w, const Mask128 &valid, int lane) {
     const int n = valid.count();
     if (lane < kC) w.count[lane] = 0;
     if (lane == 0) {
@@ -50,8 +51,14 @@ __device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &va
             w.member[at] = (uint8_t)k;
         }
     __syncwarp();
-    // rank inside the class: members that beat me (higher confidence, or equal confidence
-    // and earlier candidate -- the stable order of sorted(..., reverse=True))
+    return n;
+}
+
+// Fills w.order[p] = k by counting, for every candidate, the members of its class that
+// beat it (higher confidence, or equal confidence and earlier candidate -- the stable
+// order of sorted(..., reverse=True)).  General path; the common case gets its ranks
+// from the pair loop of order_and_nms.
+static __device__ __noinline__ void rank_members(WarpWindow &w, int lane) {
 #pragma unroll 1
     for (int s = 0; s < kSlots; ++s)
         if ((w.validw[s] >> lane) & 1u) {
@@ -68,7 +75,6 @@ __device__ __forceinline__ int order_candidates(WarpWindow &w, const Mask128 &va
             w.order[lo + r] = (uint8_t)k;
         }
     __syncwarp();
-    return n;
 }
 
 // ---- NMS ---------------------------------------------------------------------------
@@ -115,23 +121,35 @@ static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, int n, do
 
 // Overlay of `stage` between decode and the next staging: NMS scratch.
 struct NmsOverlay {
-    unsigned long long sup[kCand];  // bit i: the i-th member of my class (i < my rank) overlaps me
-    uint8_t kept[kPad];
+    unsigned long long sup[kCand];  // by member position: bit i = member i of my class is earlier and overlaps me
+    int beaten[kPad];               // by member position: members of my class that come before me
+    uint8_t kept[kPad];             // by sorted position
+    uint8_t ordm[kPad];             // sorted position -> member index inside its class
     unsigned short pair_base[kC + 4];  // pairs of all classes before c
 };
 static_assert(sizeof(NmsOverlay) <= sizeof(float2) * (kStagePairs + 1), "overlay too large");
 
-// Same result as nms_rounds, organised for the common case of many small classes:
-//   1. all same-class pairs (a earlier than b) are enumerated flat across the warp, so
-//      every lane tests one pair per step regardless of how the classes are sized;
-//      an overlap sets bit a of sup[b];
-//   2. one lane per class replays the greedy scan over those bitmasks.
+// Ordering and greedy per-class NMS in one sweep over the same-class pairs:
+//   1. all unordered pairs of a class are enumerated flat across the warp, so every
+//      lane handles one pair per step however the classes are sized.  The pair is
+//      ordered by (confidence desc, candidate asc); the later box gets one more
+//      `beaten` count and, if the two overlap, the earlier one's bit in its `sup` mask;
+//   2. beaten[] is the rank inside the class: scatter to w.order / ordm;
+//   3. one lane per class replays the greedy scan over the bitmasks in rank order.
+// Returns n and the keep mask by sorted position.  A class with more than 64 members,
+// or a NaN threshold ("decode only": keep everything), takes rank_members + nms_rounds.
 template <int MODE>
-__device__ __forceinline__ Mask128 nms_pairwise(WarpWindow &w, int n, double nms_thr, int lane) {
+__device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const Mask128 &valid, double nms_thr, int lane,
+                                                 int &n_out) {
+    const int n = build_members(w, valid, lane);
+    n_out = n;
     const int cc = lane < kC ? lane : 0;
     const int clo = w.cls_start[cc], chi = w.cls_start[cc + 1];
     const int m = lane < kC ? chi - clo : 0;
-    if (__any_sync(kFull, m > 64) || nms_thr != nms_thr) return nms_rounds<MODE>(w, n, nms_thr, lane);
+    if (__any_sync(kFull, m > 64) || nms_thr != nms_thr) {
+        rank_members(w, lane);
+        return nms_rounds<MODE>(w, n, nms_thr, lane);
+    }
     NmsOverlay &no = *reinterpret_cast<NmsOverlay *>(w.stage);
     const int np = m * (m - 1) / 2;
     int inc = np;
@@ -142,29 +160,46 @@ __device__ __forceinline__ Mask128 nms_pairwise(WarpWindow &w, int n, double nms
     }
     const int total = __shfl_sync(kFull, inc, 31);
     if (lane <= kC) no.pair_base[lane] = (unsigned short)(inc - np);  // [kC] = total
-    for (int p = lane; p < n; p += 32) no.sup[p] = 0;
+    for (int p = lane; p < n; p += 32) {
+        no.sup[p] = 0;
+        no.beaten[p] = 0;
+    }
     __syncwarp();
     int c = 0;
 #pragma unroll 1
     for (int t = lane; t < total; t += 32) {
         while (t >= no.pair_base[c + 1]) ++c;
         const int u = t - no.pair_base[c];
-        int b = (int)((1.0f + sqrtf((float)(8 * u + 1))) * 0.5f);  // row of the strict lower triangle
-        b -= (b * (b - 1) / 2 > u);
-        b += ((b + 1) * b / 2 <= u);
-        const int a = u - b * (b - 1) / 2;
+        int j = (int)((1.0f + sqrtf((float)(8 * u + 1))) * 0.5f);  // row of the strict lower triangle
+        j -= (j * (j - 1) / 2 > u);
+        j += ((j + 1) * j / 2 <= u);
+        const int i = u - j * (j - 1) / 2;                           // i < j, member indices
         const int lo = w.cls_start[c];
+        const int ki = w.member[lo + i], kj = w.member[lo + j];
+        const double ci = w.cand.conf[ki], cj = w.cand.conf[kj];
+        const bool i_first = (ci > cj) || (ci == cj && ki < kj);
+        const int e = i_first ? i : j, l = i_first ? j : i;          // earlier / later member
+        atomicAdd(&no.beaten[lo + l], 1);
         // reference argument order: iou(current = earlier, other = later)
-        if (!iou_below<MODE>(cand_corners(w, w.order[lo + a]), cand_corners(w, w.order[lo + b]), nms_thr))
-            atomicOr(&no.sup[lo + b], 1ull << a);
+        if (!iou_below<MODE>(cand_corners(w, i_first ? ki : kj), cand_corners(w, i_first ? kj : ki), nms_thr))
+            atomicOr(&no.sup[lo + l], 1ull << e);
+    }
+    __syncwarp();
+    for (int p = lane; p < n; p += 32) {
+        const int k = w.member[p];
+        const int lo = w.cls_start[w.cand.cls[k]];
+        const int r = lo + no.beaten[p];
+        w.order[r] = (uint8_t)k;
+        no.ordm[r] = (uint8_t)(p - lo);
     }
     __syncwarp();
     if (lane < kC) {
         unsigned long long km = 0;
-        for (int i = 0; i < m; ++i) {
-            const bool kp = (no.sup[clo + i] & km) == 0;
-            km |= (unsigned long long)kp << i;
-            no.kept[clo + i] = kp;
+        for (int r = 0; r < m; ++r) {
+            const int mi = no.ordm[clo + r];
+            const bool kp = (no.sup[clo + mi] & km) == 0;
+            km |= (unsigned long long)kp << mi;
+            no.kept[clo + r] = kp;
         }
     }
     __syncwarp();

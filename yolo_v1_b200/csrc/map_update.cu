@@ -110,8 +110,8 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         prefetch_image(tgt + (size_t)img * kImgFloats, lane);
         if (img + warps_total < N) prefetch_image(pred + (size_t)(img + warps_total) * kImgFloats, lane);
         const Mask128 valid = decode_image(w, lane, conf_thr, nullptr);
-        const int n = order_candidates(w, valid, lane);
-        const Mask128 keep = nms_pairwise<YH_IOU_METRICS>(w, n, nms_thr, lane);
+        int n;
+        const Mask128 keep = order_and_nms<YH_IOU_METRICS>(w, valid, nms_thr, lane, n);
         publish_keep(w, keep, lane);
         const unsigned lt = (1u << lane) - 1u;
 
