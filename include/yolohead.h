@@ -107,14 +107,15 @@ int yh_decode_nms(const float *pred, int N, int S, int B, int C, double conf_thr
  *                      | bit s*T+t: TP for subset s at thresholds[t]
  *                      | bit 4*T:   TP in the overall pass at IoU 0.5
  *   rec_k[n*K+q]     = candidate index
- *   rec_raw[(n*K+q)*4..] = the box's raw (x, y, w, h) floats (nullable; feeds yh_list_form)
+ *   rec_box[(n*K+q)*24 B] = the box as the reference stores it: x_abs, y_abs as fp64 and
+ *                      (w, h) as two fp32 in the third 8 bytes (nullable; feeds yh_list_form)
  *   n_keep[n], n_gt[n]; gt_count[s*C + c] += ground truths (atomic; zero it first)
  *   gt_cell / gt_cls [n*S*S+g], gt_raw[(n*S*S+g)*4..]: cell index, class and raw
  *                      (x, y, w, h) of every ground truth (all three nullable together)
  * thresholds_host: T doubles on the HOST (copied into the launch parameters). */
 int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int C, double conf_thr,
                   double nms_thr, const double *thresholds_host, int T, int32_t *n_keep,
-                  uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k, float *rec_raw,
+                  uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k, void *rec_box,
                   int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls, float *gt_raw,
                   int32_t *gt_count, void *stream);
 
@@ -124,9 +125,10 @@ int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int 
  *                        first-appearance order of the confidence-sorted list,
  *                        metrics.py:274-279)
  *   rec_box[(n*K+q)*4..] (x_abs, y_abs, w, h) fp64 as metrics.py:200-203 builds them
+ *                        (expanded from the 24-byte rec_box3 records of yh_map_update)
  *   gt_box[(n*S*S+g)*4..] the same for ground truths (metrics.py:247-248) */
 int yh_list_form(const int32_t *n_keep, const uint64_t *rec_key, const uint64_t *rec_flags,
-                 const uint8_t *rec_k, const float *rec_raw, const int32_t *n_gt,
+                 const uint8_t *rec_k, const void *rec_box3, const int32_t *n_gt,
                  const uint8_t *gt_cell, const float *gt_raw, int N, int S, int B, int C,
                  uint8_t *rec_pos, double *rec_box, double *gt_box, void *stream);
 

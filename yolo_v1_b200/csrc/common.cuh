@@ -125,17 +125,57 @@ __device__ __forceinline__ int argmax_first(const float *v, int n, float &best_v
     float m = v[0];
 #pragma unroll
     for (int i = 1; i < n; ++i) m = max_nan(m, v[i]);
+    // first index that holds the maximum; a NaN maximum matches the first NaN.  Fully
+    // unrolled with constant indices so v[] stays in registers.
     int best = 0;
-    if (m != m) {  // some score is NaN: rare, keep it small
-#pragma unroll 1
-        for (int i = n - 1; i >= 0; --i)
-            if (v[i] != v[i]) best = i;
+    if (m != m) {
+#pragma unroll
+        for (int i = n - 1; i >= 0; --i) best = (v[i] != v[i]) ? i : best;
     } else {
 #pragma unroll
         for (int i = n - 1; i >= 0; --i) best = (v[i] == m) ? i : best;
     }
     best_v = m;
     return best;
+}
+
+// Class of one staged prediction cell (cell = pointer to its kD floats in shared memory,
+// 8-byte aligned): best_v = the largest class score; the return value is its first index
+// -- but only when a box of the cell can pass the confidence threshold (otherwise the
+// class is never looked at and the index search is skipped; a NaN maximum makes both
+// confidences NaN, which never pass).  Out of line: one copy for all call sites keeps
+// the per-image kernels inside the instruction cache.
+static __device__ __noinline__ int cell_class_shared(const float *cell, double conf_thr, float &best_v) {
+    const unsigned addr = (unsigned)__cvta_generic_to_shared(cell + kB * 5);
+    float v[kC];
+#pragma unroll
+    for (int i = 0; i < kC / 2; ++i)
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v[2 * i]), "=f"(v[2 * i + 1]) : "r"(addr + 8 * i) : "memory");
+    float m = v[0];
+#pragma unroll
+    for (int i = 1; i < kC; ++i) m = max_nan(m, v[i]);
+    best_v = m;
+    const double prob = (double)m;
+    bool need = false;
+#pragma unroll
+    for (int b = 0; b < kB; ++b) need |= __dmul_rn((double)cell[b * 5 + 4], prob) > conf_thr;
+    int best = 0;
+    if (need) {
+#pragma unroll
+        for (int i = kC - 1; i >= 0; --i) best = (v[i] == m) ? i : best;
+    }
+    return best;
+}
+static __device__ __noinline__ int cell_class_global(const float *cell) {
+    float cls_p[kC];
+#pragma unroll
+    for (int i = 0; i < kC / 2; ++i) {
+        const float2 v = __ldg(reinterpret_cast<const float2 *>(cell + kB * 5) + i);
+        cls_p[2 * i] = v.x;
+        cls_p[2 * i + 1] = v.y;
+    }
+    float pv;
+    return argmax_first(cls_p, kC, pv);
 }
 
 }  // namespace yh

@@ -8,9 +8,17 @@
 namespace yh {
 
 constexpr int kWarpsPerCta = 4;
+constexpr int kCtasPerSm = 7;
+
+// Overlay of `stage` after NMS: the kept detections' sort keys, compact.
+struct GlobalOrderOverlay {
+    uint64_t key[kCand];
+    uint8_t k[kPad];
+};
+static_assert(sizeof(GlobalOrderOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
 
 template <int MODE>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm)
 decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double nms_thr, int order,
                   int32_t *__restrict__ n_keep, uint8_t *__restrict__ keep_k,
                   uint8_t *__restrict__ keep_cls, double *__restrict__ keep_conf,
@@ -23,10 +31,10 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
     const int warps_total = gridDim.x * kWarpsPerCta;
 
     for (int img = blockIdx.x * kWarpsPerCta + wib; img < N; img += warps_total) {
-        stage_image(w, pred + (size_t)img * kImgFloats, lane);
-        if (img + warps_total < N) prefetch_image(pred + (size_t)(img + warps_total) * kImgFloats, lane);
+        const float *pimg = pred + (size_t)img * kImgFloats;
+        if (img + warps_total < N) prefetch_image(pimg + (size_t)warps_total * kImgFloats, lane);
         bool bad = false;
-        const Mask128 valid = decode_image(w, lane, conf_thr, &bad);
+        const Mask128 valid = decode_image(w, pimg, lane, conf_thr, bad_range != nullptr ? &bad : nullptr);
         if (bad_range != nullptr) {
             const unsigned anybad = __ballot_sync(kFull, bad);
             if (lane == 0) bad_range[img] = anybad ? 1 : 0;
@@ -39,6 +47,28 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
         }
         if (order == YH_ORDER_CLASS_GROUPED) class_group_offsets(w, keep, lane);
 
+        // global (confidence desc, candidate asc) order: rank each kept detection among the kept.
+        // The kept are listed compactly (orderable key, candidate) so the rank loop is one 8-byte
+        // shared load and an integer compare per rival.
+        GlobalOrderOverlay &go = *reinterpret_cast<GlobalOrderOverlay *>(w.stage);
+        int n_kept = 0;
+        if (order == YH_ORDER_GLOBAL_CONF) {
+            __syncwarp();
+#pragma unroll
+            for (int s = 0; s < kSlots; ++s) {
+                const unsigned kw = keep.word(s);
+                if ((kw >> lane) & 1u) {
+                    const int k = w.order[lane + 32 * s];
+                    const int q = n_kept + __popc(kw & ((1u << lane) - 1u));
+                    // ascending composite = confidence descending, then candidate ascending
+                    go.key[q] = ~orderable(w.cand.conf[k]);
+                    go.k[q] = (uint8_t)k;
+                }
+                n_kept += __popc(kw);
+            }
+            __syncwarp();
+        }
+
 #pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
             const int p = lane + 32 * s;
@@ -48,14 +78,11 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             if (order == YH_ORDER_CLASS_GROUPED) {
                 pos = w.cls_off[c] + count_below(keep, p) - w.cls_kbase[c];
             } else {
-                // global (confidence desc, candidate asc) rank among the kept
-                const double mine = w.cand.conf[k];
+                const uint64_t mine = ~orderable(w.cand.conf[k]);
                 pos = 0;
-                for (int q = 0; q < n; ++q) {
-                    if (!keep.test(q)) continue;
-                    const int ok = w.order[q];
-                    const double oc = w.cand.conf[ok];
-                    pos += (oc > mine) || (oc == mine && ok < k);
+                for (int q = 0; q < n_kept; ++q) {
+                    const uint64_t other = go.key[q];
+                    pos += (other < mine) || (other == mine && go.k[q] < k);
                 }
             }
             const size_t o = (size_t)img * kCand + pos;
@@ -63,13 +90,12 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             if (keep_cls != nullptr) keep_cls[o] = (uint8_t)c;
             if (keep_conf != nullptr) keep_conf[o] = w.cand.conf[k];
             if (keep_box != nullptr) {
-                // (x, y, w, h) as the reference stores them, rebuilt from the raw cell values
-                const int cell = k / kB, b = k % kB;
-                const float *raw = pred + (size_t)img * kImgFloats + cell * kD + b * 5;
-                keep_box[4 * o + 0] = abs_coord(cell % kS, __ldg(raw + 0));
-                keep_box[4 * o + 1] = abs_coord(cell / kS, __ldg(raw + 1));
-                keep_box[4 * o + 2] = (double)__ldg(raw + 2);
-                keep_box[4 * o + 3] = (double)__ldg(raw + 3);
+                // (x, y, w, h) as the reference stores them (metrics.py:200-203, inference.py:184-193)
+                const float2 wh = w.cand.wh[k];
+                keep_box[4 * o + 0] = w.cand.xa[k];
+                keep_box[4 * o + 1] = w.cand.ya[k];
+                keep_box[4 * o + 2] = (double)wh.x;
+                keep_box[4 * o + 3] = (double)wh.y;
             }
         }
         __syncwarp();
@@ -87,7 +113,7 @@ static int launch(const float *pred, int N, double conf_thr, double nms_thr, int
         attr_done = true;
     }
     int ctas = (N + kWarpsPerCta - 1) / kWarpsPerCta;
-    const int cap = 148 * 5;
+    const int cap = 148 * kCtasPerSm;
     if (ctas > cap) ctas = cap;
     decode_nms_kernel<MODE><<<ctas, kWarpsPerCta * 32, smem, st>>>(
         pred, N, conf_thr, nms_thr, order, n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad_range);

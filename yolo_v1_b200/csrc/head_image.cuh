@@ -26,21 +26,26 @@
 namespace yh {
 
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kStagePairs = kImgFloats / 2;  // 735 float2 per image
-constexpr int kSlots = 4;                    // candidates a lane can own
-constexpr int kPad = 104;                    // 98 rounded up to a multiple of 8
+constexpr int kStagePairs = kImgFloats / 2;   // 735 float2 per image
+constexpr int kHalfCells = 32;                // cells staged per half: 0..31, then 32..48
+constexpr int kHalfPairs = kHalfCells * kD / 2;  // 480 float2 = 3,840 B
+constexpr int kSlots = 4;                     // candidates a lane can own
+constexpr int kPad = 104;                     // 98 rounded up to a multiple of 8
 
 // Candidate table, indexed by candidate k = 2*cell + b.  Only entries whose
-// confidence passed the threshold are written / read.
+// confidence passed the threshold are written / read.  Centre in fp64 (it is the
+// quotient (col + x) / S), width / height as the raw floats: corners and area are
+// rebuilt on demand (9 fp64 operations) instead of being stored (40 B -> 24 B).
 struct CandTable {
-    double x1[kCand], y1[kCand], x2[kCand], y2[kCand], area[kCand], conf[kCand];
+    double xa[kCand], ya[kCand], conf[kCand];
+    float2 wh[kCand];
     uint8_t cls[kPad];
 };
 
-// Shared-memory window of one warp.
+// Shared-memory window of one warp: 7.4 KB, so 28 warps (7 CTAs of 4) fit an SM.
 struct __align__(16) WarpWindow {
-    float2 stage[kStagePairs + 1];  // 5,888 B: raw image; reused as MatchOverlay later
-    CandTable cand;                 // 4,808 B
+    float2 stage[kHalfPairs];       // 3,840 B: half an image; reused as NmsOverlay / MatchOverlay
+    CandTable cand;                 // 3,240 B
     uint8_t order[kPad];            // sorted position p -> candidate k
     uint8_t member[kPad];           // class-segmented member lists (scratch of the ordering)
     int count[kC];                  // class histogram, then running cursor
@@ -51,15 +56,6 @@ struct __align__(16) WarpWindow {
     unsigned keepw[4];              // kept after NMS, by sorted position
     uint8_t keepbase[4];            // kept detections in the words before word s
 };
-
-// Overlay of `stage` after the target image has been parsed into registers.
-struct MatchOverlay {
-    double gx1[kCells], gy1[kCells], gx2[kCells], gy2[kCells], garea[kCells];  // 1,960 B
-    uint8_t gcls[kCells + 7], gbucket[kCells + 7];                              // 112 B
-    double biou[4][kCand];                                                      // 3,136 B
-    uint8_t bgt[4][kPad];                                                       // 416 B
-};
-static_assert(sizeof(MatchOverlay) <= sizeof(float2) * (kStagePairs + 1), "overlay too large");
 
 // ---- exact (j + v) / 7 ----------------------------------------------------------
 // x / 7 correctly rounded without the generic division sequence: q = x * RN(1/7),
@@ -79,12 +75,16 @@ __device__ __forceinline__ double abs_coord(int cell_coord, float v) {
 }
 
 // ---- staging ------------------------------------------------------------------
-__device__ __forceinline__ void stage_image(WarpWindow &w, const float *__restrict__ img, int lane) {
-    const float2 *src = reinterpret_cast<const float2 *>(img);
+// Half h of an image -> w.stage: cells [32h, 32h + 32) (half 1 holds 17 cells).  An
+// image start is only 8-byte aligned, so the widest coalesced access is 8 B.
+__device__ __forceinline__ void stage_half(WarpWindow &w, const float *__restrict__ img, int half, int lane) {
+    const float2 *src = reinterpret_cast<const float2 *>(img) + half * kHalfPairs;
+    const int count = half ? (kStagePairs - kHalfPairs) : kHalfPairs;  // 255 or 480
+    __syncwarp();  // every lane is done with what the buffer held before
 #pragma unroll
-    for (int i = 0; i < (kStagePairs + 31) / 32; ++i) {
+    for (int i = 0; i < kHalfPairs / 32; ++i) {
         int q = lane + 32 * i;
-        if (q < kStagePairs) w.stage[q] = __ldg(src + q);
+        if (q < count) w.stage[q] = __ldg(src + q);
     }
     __syncwarp();
 }
@@ -144,27 +144,23 @@ __device__ __forceinline__ unsigned spread16(unsigned x) {
 }
 
 // ---- decode ---------------------------------------------------------------------
-// Each lane decodes cells `lane` and `lane + 32`; candidate k = 2*cell + b.  Fills
-// w.cand for every candidate above conf_thr and returns the validity mask (indexed
-// by k).  bad (optional) reports a kept candidate outside [0,1] (schemas.py:9-16,88).
-__device__ __forceinline__ Mask128 decode_image(WarpWindow &w, int lane, double conf_thr, bool *bad) {
+// Each lane decodes cells `lane` and `lane + 32` (one per staged half); candidate
+// k = 2*cell + b.  Fills w.cand for every candidate above conf_thr and returns the
+// validity mask (indexed by k).  bad (optional) reports a kept candidate outside
+// [0,1] (schemas.py:9-16,88).
+__device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__restrict__ img, int lane,
+                                                double conf_thr, bool *bad) {
     const float *st = reinterpret_cast<const float *>(w.stage);
     Mask128 valid = {0, 0, 0, 0};
     bool any_bad = false;
 #pragma unroll 1
     for (int cs = 0; cs < 2; ++cs) {
+        stage_half(w, img, cs, lane);
         const int cell = lane + 32 * cs;
         const bool live = cell < kCells;
-        const float *c = st + (live ? cell : 0) * kD;
-        float cls_p[kC];
-#pragma unroll
-        for (int i = 0; i < kC / 2; ++i) {
-            float2 v = *reinterpret_cast<const float2 *>(c + kB * 5 + 2 * i);
-            cls_p[2 * i] = v.x;
-            cls_p[2 * i + 1] = v.y;
-        }
+        const float *c = st + (live ? lane : 0) * kD;
         float pv;
-        const int cls = argmax_first(cls_p, kC, pv);
+        const int cls = cell_class_shared(c, conf_thr, pv);
         const double prob = (double)pv;
         const int col = cell % kS, row = cell / kS;
         bool ok[kB];
@@ -176,14 +172,16 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, int lane, double 
             if (ok[b]) {
                 const int k = cell * kB + b;
                 const double xa = abs_coord(col, bx[0]), ya = abs_coord(row, bx[1]);
-                const double ww = (double)bx[2], hh = (double)bx[3];
-                const Corners cr = corners_of(xa, ya, ww, hh);
-                w.cand.x1[k] = cr.x1; w.cand.y1[k] = cr.y1; w.cand.x2[k] = cr.x2; w.cand.y2[k] = cr.y2;
-                w.cand.area[k] = cr.area;
+                w.cand.xa[k] = xa;
+                w.cand.ya[k] = ya;
+                w.cand.wh[k] = make_float2(bx[2], bx[3]);
                 w.cand.conf[k] = conf;
                 w.cand.cls[k] = (uint8_t)cls;
-                any_bad |= !(xa >= 0.0 && xa <= 1.0 && ya >= 0.0 && ya <= 1.0 && ww >= 0.0 && ww <= 1.0 &&
-                             hh >= 0.0 && hh <= 1.0 && conf >= 0.0 && conf <= 1.0);
+                if (bad != nullptr) {
+                    const double ww = (double)bx[2], hh = (double)bx[3];
+                    any_bad |= !(xa >= 0.0 && xa <= 1.0 && ya >= 0.0 && ya <= 1.0 && ww >= 0.0 && ww <= 1.0 &&
+                                 hh >= 0.0 && hh <= 1.0 && conf >= 0.0 && conf <= 1.0);
+                }
             }
         }
         // k = 2*cell + b = 2*lane + b + 64*cs: interleave the two ballots into words 2cs, 2cs+1

@@ -6,11 +6,10 @@
 
 namespace yh {
 
+// corners and area of candidate k, built as the reference does (x - w / 2, ..., w * h)
 __device__ __forceinline__ Corners cand_corners(const WarpWindow &w, int k) {
-    Corners c;
-    c.x1 = w.cand.x1[k]; c.y1 = w.cand.y1[k]; c.x2 = w.cand.x2[k]; c.y2 = w.cand.y2[k];
-    c.area = w.cand.area[k];
-    return c;
+    const float2 wh = w.cand.wh[k];
+    return corners_of(w.cand.xa[k], w.cand.ya[k], (double)wh.x, (double)wh.y);
 }
 
 // ---- class segments -------------------------------------------------------------------
@@ -127,7 +126,7 @@ struct NmsOverlay {
     uint8_t ordm[kPad];             // sorted position -> member index inside its class
     unsigned short pair_base[kC + 4];  // pairs of all classes before c
 };
-static_assert(sizeof(NmsOverlay) <= sizeof(float2) * (kStagePairs + 1), "overlay too large");
+static_assert(sizeof(NmsOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
 
 // Ordering and greedy per-class NMS in one sweep over the same-class pairs:
 //   1. all unordered pairs of a class are enumerated flat across the warp, so every

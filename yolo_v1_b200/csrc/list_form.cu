@@ -16,7 +16,7 @@ namespace yh {
 __global__ void __launch_bounds__(128)
 list_form_kernel(const int32_t *__restrict__ n_keep, const uint64_t *__restrict__ rec_key,
                  const uint64_t *__restrict__ rec_flags, const uint8_t *__restrict__ rec_k,
-                 const float4 *__restrict__ rec_raw, const int32_t *__restrict__ n_gt,
+                 const uint64_t *__restrict__ rec_box3, const int32_t *__restrict__ n_gt,
                  const uint8_t *__restrict__ gt_cell, const float4 *__restrict__ gt_raw, int N,
                  uint8_t *__restrict__ rec_pos, double *__restrict__ rec_box, double *__restrict__ gt_box) {
     __shared__ int s_first[4][32], s_count[4][32], s_off[4][32];
@@ -53,13 +53,13 @@ list_form_kernel(const int32_t *__restrict__ n_keep, const uint64_t *__restrict_
     for (int q = lane; q < n; q += 32) {
         const int c = (int)(rec_flags[base + q] >> 56) & 31;
         rec_pos[base + q] = (uint8_t)(s_off[wib][c] + q - s_first[wib][c]);
-        const int cell = rec_k[base + q] / kB;
-        const float4 r = rec_raw[base + q];
+        const uint64_t *r = rec_box3 + 3 * (base + q);  // (x_abs, y_abs) fp64, (w, h) fp32
+        const uint64_t wh = r[2];
         double *o = rec_box + 4 * (base + q);
-        o[0] = abs_coord(cell % kS, r.x);
-        o[1] = abs_coord(cell / kS, r.y);
-        o[2] = (double)r.z;
-        o[3] = (double)r.w;
+        o[0] = __longlong_as_double((long long)r[0]);
+        o[1] = __longlong_as_double((long long)r[1]);
+        o[2] = (double)__uint_as_float((unsigned)wh);
+        o[3] = (double)__uint_as_float((unsigned)(wh >> 32));
     }
     const int ng = n_gt[img];
     const size_t gb = (size_t)img * kCells;
@@ -79,21 +79,21 @@ list_form_kernel(const int32_t *__restrict__ n_keep, const uint64_t *__restrict_
 using namespace yh;
 
 extern "C" int yh_list_form(const int32_t *n_keep, const uint64_t *rec_key, const uint64_t *rec_flags,
-                            const uint8_t *rec_k, const float *rec_raw, const int32_t *n_gt,
+                            const uint8_t *rec_k, const void *rec_box3, const int32_t *n_gt,
                             const uint8_t *gt_cell, const float *gt_raw, int N, int S, int B, int C,
                             uint8_t *rec_pos, double *rec_box, double *gt_box, void *stream) {
     if (!shape_ok(S, B, C)) {
         set_error("yh_list_form: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
         return YH_ERR_UNSUPPORTED;
     }
-    if (N < 0 || !n_keep || !rec_key || !rec_flags || !rec_k || !rec_raw || !n_gt || !gt_cell || !gt_raw ||
+    if (N < 0 || !n_keep || !rec_key || !rec_flags || !rec_k || !rec_box3 || !n_gt || !gt_cell || !gt_raw ||
         !rec_pos || !rec_box || !gt_box) {
         set_error("yh_list_form: bad argument");
         return YH_ERR_BAD_ARG;
     }
     if (N == 0) return 0;
     list_form_kernel<<<(N + 3) / 4, 128, 0, (cudaStream_t)stream>>>(
-        n_keep, rec_key, rec_flags, rec_k, (const float4 *)rec_raw, n_gt, gt_cell, (const float4 *)gt_raw, N,
+        n_keep, rec_key, rec_flags, rec_k, (const uint64_t *)rec_box3, n_gt, gt_cell, (const float4 *)gt_raw, N,
         rec_pos, rec_box, gt_box);
     return check_launch("yh_list_form");
 }

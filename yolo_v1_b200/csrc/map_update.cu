@@ -14,82 +14,86 @@
 namespace yh {
 
 constexpr int kWarpsPerCtaM = 4;
+constexpr int kCtasPerSmM = 7;
 
 struct Thresholds {
     double t[YH_MAX_THRESHOLDS];
     int n;
 };
 
+// Overlay of `stage` once the target image has been parsed into registers.
+struct MatchOverlay {
+    double gx1[kCells], gy1[kCells], gx2[kCells], gy2[kCells], garea[kCells];  // 1,960 B, compact, cell order
+    uint8_t gcls[kCells + 7], gbucket[kCells + 7];                              // 112 B
+    unsigned long long flags[kCand];  // TP bits by sorted position                 784 B
+    uint8_t bgt[kCand][4];            // by item: best ground truth per subset (255 = none)
+    uint8_t ik[kPad], icls[kPad], ipos[kPad];  // by item: candidate, class, sorted position
+};
+static_assert(sizeof(MatchOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
+
+// Best IoU of a matched detection against the ground truths of one size bucket
+// (1 small / 2 medium / 3 large), indexed by candidate k.  The three tables reuse
+// the candidate's geometry slots (xa, ya, wh): a lane overwrites them only after it
+// has finished with its own candidate's corners, and nobody else reads them.
+__device__ __forceinline__ double *bucket_iou(WarpWindow &w, int bucket) {
+    return bucket == 1 ? w.cand.xa : (bucket == 2 ? w.cand.ya : reinterpret_cast<double *>(w.cand.wh));
+}
+
 // Ground truths of one target image -> MatchOverlay (compact, in cell order).
-// Returns the number of ground truths.  gt_hist (shared, 4*kC ints) accumulates
-// the per-(subset, class) counts of this CTA.
-__device__ __forceinline__ int parse_targets(WarpWindow &w, int lane, int *gt_hist,
+// The target tensor is almost empty (an object in about 1 cell of 18), so it is not
+// staged: tconf0/tconf1 are the slot-0 confidences of cells `lane` and `lane + 32`
+// (loaded by the caller long before, 49 sectors per image), and only object cells
+// fetch their box and class scores.  Returns the number of ground truths; cls_mask
+// gets bit c for every class present.  gt_hist (shared, 4*kC ints) accumulates the
+// per-(subset, class) counts of this CTA.
+__device__ __forceinline__ int parse_targets(WarpWindow &w, const float *__restrict__ img, int lane,
+                                             float tconf0, float tconf1, int *gt_hist, unsigned &cls_mask,
                                              uint8_t *__restrict__ out_cell, uint8_t *__restrict__ out_cls,
                                              float4 *__restrict__ out_raw) {
-    const float *st = reinterpret_cast<const float *>(w.stage);
-    // pass 1: pull the (few) ground-truth cells into registers before the overlay is written
-    bool is_gt[2];
-    int cls[2] = {0, 0};
-    float x[2], y[2], bw[2], bh[2];
-#pragma unroll
-    for (int cs = 0; cs < 2; ++cs) {
-        const int cell = lane + 32 * cs;
-        const bool live = cell < kCells;
-        const float *c = st + (live ? cell : 0) * kD;
-        is_gt[cs] = live && (c[4] > 0.f);  // slot-0 confidence only (metrics.py:239)
-        x[cs] = c[0]; y[cs] = c[1]; bw[cs] = c[2]; bh[cs] = c[3];
-    }
-#pragma unroll 1
-    for (int cs = 0; cs < 2; ++cs) {
-        if (!(cs == 0 ? is_gt[0] : is_gt[1])) continue;  // object cells are rare (about 1 in 18)
-        const float *c = st + (lane + 32 * cs) * kD;
-        float cls_p[kC];
-#pragma unroll
-        for (int i = 0; i < kC / 2; ++i) {
-            float2 v = *reinterpret_cast<const float2 *>(c + kB * 5 + 2 * i);
-            cls_p[2 * i] = v.x;
-            cls_p[2 * i + 1] = v.y;
-        }
-        float pv;
-        const int a = argmax_first(cls_p, kC, pv);
-        if (cs == 0) cls[0] = a; else cls[1] = a;
-    }
-    const unsigned m0 = __ballot_sync(kFull, is_gt[0]), m1 = __ballot_sync(kFull, is_gt[1]);
+    const bool gt0 = tconf0 > 0.f, gt1 = (lane + 32 < kCells) && tconf1 > 0.f;  // metrics.py:239
+    const unsigned m0 = __ballot_sync(kFull, gt0), m1 = __ballot_sync(kFull, gt1);
     const unsigned lt = (1u << lane) - 1u;
-    __syncwarp();  // all lanes hold their cells; `stage` may be overwritten now
     MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
     const double small_a = __dmul_rn(__ddiv_rn(32.0, 448.0), __ddiv_rn(32.0, 448.0));   // metrics.py:511
     const double medium_a = __dmul_rn(__ddiv_rn(96.0, 448.0), __ddiv_rn(96.0, 448.0));  // metrics.py:512
-#pragma unroll
-    for (int cs = 0; cs < 2; ++cs)
-        if (is_gt[cs]) {
-            const int g = cs ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
-            const int cell = lane + 32 * cs;
-            const double xa = abs_coord(cell % kS, x[cs]), ya = abs_coord(cell / kS, y[cs]);
-            const Corners cr = corners_of(xa, ya, (double)bw[cs], (double)bh[cs]);
-            mo.gx1[g] = cr.x1; mo.gy1[g] = cr.y1; mo.gx2[g] = cr.x2; mo.gy2[g] = cr.y2;
-            mo.garea[g] = cr.area;
-            mo.gcls[g] = (uint8_t)cls[cs];
-            const int bucket = (cr.area < small_a) ? 1 : ((cr.area < medium_a) ? 2 : 3);
-            mo.gbucket[g] = (uint8_t)bucket;
-            if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
-                out_cell[g] = (uint8_t)cell;
-                out_cls[g] = (uint8_t)cls[cs];
-                out_raw[g] = make_float4(x[cs], y[cs], bw[cs], bh[cs]);
-            }
-            atomicAdd(&gt_hist[cls[cs]], 1);
-            atomicAdd(&gt_hist[bucket * kC + cls[cs]], 1);
+    unsigned mine = 0;
+    __syncwarp();  // every lane is done with what the overlay region held before
+#pragma unroll 1
+    for (int cs = 0; cs < 2; ++cs) {
+        if (!(cs ? gt1 : gt0)) continue;
+        const int cell = lane + 32 * cs;
+        const float *c = img + cell * kD;
+        const float2 xy = __ldg(reinterpret_cast<const float2 *>(c));
+        const float2 wh = __ldg(reinterpret_cast<const float2 *>(c) + 1);
+        const int cls = cell_class_global(c);
+        const int g = cs ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
+        const double xa = abs_coord(cell % kS, xy.x), ya = abs_coord(cell / kS, xy.y);
+        const Corners cr = corners_of(xa, ya, (double)wh.x, (double)wh.y);
+        mo.gx1[g] = cr.x1; mo.gy1[g] = cr.y1; mo.gx2[g] = cr.x2; mo.gy2[g] = cr.y2;
+        mo.garea[g] = cr.area;
+        mo.gcls[g] = (uint8_t)cls;
+        const int bucket = (cr.area < small_a) ? 1 : ((cr.area < medium_a) ? 2 : 3);
+        mo.gbucket[g] = (uint8_t)bucket;
+        if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
+            out_cell[g] = (uint8_t)cell;
+            out_cls[g] = (uint8_t)cls;
+            out_raw[g] = make_float4(xy.x, xy.y, wh.x, wh.y);
         }
+        atomicAdd(&gt_hist[cls], 1);
+        atomicAdd(&gt_hist[bucket * kC + cls], 1);
+        mine |= 1u << cls;
+    }
+    cls_mask = __reduce_or_sync(kFull, mine);
     __syncwarp();
     return __popc(m0) + __popc(m1);
 }
 
-__global__ void __launch_bounds__(kWarpsPerCtaM * 32)
+__global__ void __launch_bounds__(kWarpsPerCtaM * 32, kCtasPerSmM)
 map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt, int N,
-                  double conf_thr, double nms_thr, Thresholds thr, int32_t *__restrict__ n_keep,
-                  uint64_t *__restrict__ rec_key, uint64_t *__restrict__ rec_flags,
-                  uint8_t *__restrict__ rec_k, float4 *__restrict__ rec_raw,
-                  int32_t *__restrict__ n_gt, uint8_t *__restrict__ gt_cell,
+                  double conf_thr, double nms_thr, const __grid_constant__ Thresholds thr,
+                  int32_t *__restrict__ n_keep, uint64_t *__restrict__ rec_key,
+                  uint64_t *__restrict__ rec_flags, uint8_t *__restrict__ rec_k,
+                  uint64_t *__restrict__ rec_box, int32_t *__restrict__ n_gt, uint8_t *__restrict__ gt_cell,
                   uint8_t *__restrict__ gt_cls, float4 *__restrict__ gt_raw,
                   int32_t *__restrict__ gt_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -100,25 +104,49 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
     WarpWindow &w = windows[wib];
     const int warps_total = gridDim.x * kWarpsPerCtaM;
     const int T = thr.n;
+    const unsigned lt = (1u << lane) - 1u;
     for (int i = threadIdx.x; i < 4 * kC; i += blockDim.x) gt_hist[i] = 0;
     if (threadIdx.x < YH_MAX_THRESHOLDS) s_thr[threadIdx.x] = thr.t[threadIdx.x];
     __syncthreads();
 
     for (int img = blockIdx.x * kWarpsPerCtaM + wib; img < N; img += warps_total) {
+        const float *pimg = pred + (size_t)img * kImgFloats, *timg = tgt + (size_t)img * kImgFloats;
+        // slot-0 confidence of my two target cells: in flight while the predictions are decoded
+        const float tconf0 = __ldg(timg + lane * kD + 4);
+        const float tconf1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 4);
         // ---- predictions: decode, order, NMS
-        stage_image(w, pred + (size_t)img * kImgFloats, lane);
-        prefetch_image(tgt + (size_t)img * kImgFloats, lane);
-        if (img + warps_total < N) prefetch_image(pred + (size_t)(img + warps_total) * kImgFloats, lane);
-        const Mask128 valid = decode_image(w, lane, conf_thr, nullptr);
+        if (img + warps_total < N) prefetch_image(pimg + (size_t)warps_total * kImgFloats, lane);
+        const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr);
+        // object cells of the target (rare): pull their lines towards L2 while NMS runs
+#pragma unroll
+        for (int cs = 0; cs < 2; ++cs)
+            if (lane + 32 * cs < kCells && (cs ? tconf1 : tconf0) > 0.f) {
+                const float *c = timg + (lane + 32 * cs) * kD;  // 120 B: may straddle two lines
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(c));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(c + kD - 1));
+            }
         int n;
         const Mask128 keep = order_and_nms<YH_IOU_METRICS>(w, valid, nms_thr, lane, n);
         publish_keep(w, keep, lane);
-        const unsigned lt = (1u << lane) - 1u;
+        const bool lists = gt_raw != nullptr;
+        if (rec_box != nullptr) {
+            // the kept boxes as the reference stores them: (x_abs, y_abs) fp64, (w, h) fp32.
+            // Written now: the matching below reuses the geometry slots of the table.
+#pragma unroll 1
+            for (int s = 0; s < kSlots; ++s) {
+                if (!((w.keepw[s] >> lane) & 1u)) continue;
+                const int k = w.order[lane + 32 * s];
+                uint64_t *o = rec_box + 3 * ((size_t)img * kCand + w.keepbase[s] + __popc(w.keepw[s] & lt));
+                o[0] = (uint64_t)__double_as_longlong(w.cand.xa[k]);
+                o[1] = (uint64_t)__double_as_longlong(w.cand.ya[k]);
+                o[2] = *reinterpret_cast<const uint64_t *>(&w.cand.wh[k]);
+            }
+        }
 
         // ---- targets: parse into the overlay
-        stage_image(w, tgt + (size_t)img * kImgFloats, lane);
-        const bool lists = gt_raw != nullptr;
-        const int ngt = parse_targets(w, lane, gt_hist, lists ? gt_cell + (size_t)img * kCells : nullptr,
+        unsigned cls_mask;
+        const int ngt = parse_targets(w, timg, lane, tconf0, tconf1, gt_hist, cls_mask,
+                                      lists ? gt_cell + (size_t)img * kCells : nullptr,
                                       lists ? gt_cls + (size_t)img * kCells : nullptr,
                                       lists ? gt_raw + (size_t)img * kCells : nullptr);
         MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
@@ -127,78 +155,116 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             n_gt[img] = ngt;
         }
 
-        // ---- best ground truth of every kept detection, per subset
-        // subset 0 = all ground truths, 1/2/3 = small/medium/large only
-        unsigned matched = 0;  // bit s: my slot-s detection met a ground truth of its class
+        // ---- items: kept detections whose class has a ground truth, in sorted order
+        int n_items = 0;
 #pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
-            if (!((w.keepw[s] >> lane) & 1u)) continue;
             const int p = lane + 32 * s;
-            const int k = w.order[p], c = w.cand.cls[k];
-            double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
-            int g0 = 255, g1 = 255, g2 = 255, g3 = 255;
-            bool met = false;
+            const bool kept = (w.keepw[s] >> lane) & 1u;
+            int k = 0, c = 0;
+            if (kept) {
+                k = w.order[p];
+                c = w.cand.cls[k];
+                mo.flags[p] = 0;
+            }
+            const bool is_item = kept && ((cls_mask >> c) & 1u);
+            const unsigned im = __ballot_sync(kFull, is_item);
+            if (is_item) {
+                const int it = n_items + __popc(im & lt);
+                mo.ik[it] = (uint8_t)k;
+                mo.icls[it] = (uint8_t)c;
+                mo.ipos[it] = (uint8_t)p;
+            }
+            n_items += __popc(im);
+        }
+        __syncwarp();
+
+        // ---- best ground truth of every item per size bucket; "all sizes" follows from the three
+#pragma unroll 1
+        for (int it = lane; it < n_items; it += 32) {
+            const int k = mo.ik[it], c = mo.icls[it];
+            const Corners dc = cand_corners(w, k);
+            double b1 = 0.0, b2 = 0.0, b3 = 0.0;
+            int g1 = 255, g2 = 255, g3 = 255;
             for (int g = 0; g < ngt; ++g) {
                 if (mo.gcls[g] != c) continue;
-                met = true;
                 Corners gc;
                 gc.x1 = mo.gx1[g]; gc.y1 = mo.gy1[g]; gc.x2 = mo.gx2[g]; gc.y2 = mo.gy2[g];
                 gc.area = mo.garea[g];
-                const double iou = iou_exact<YH_IOU_METRICS>(cand_corners(w, k), gc);
+                const double iou = iou_exact<YH_IOU_METRICS>(dc, gc);
                 const int b = mo.gbucket[g];
-                if (iou > b0) { b0 = iou; g0 = g; }  // strict: first GT wins ties, IoU 0 never matches
+                // strict: the first ground truth wins ties, IoU 0 never matches (metrics.py:393-403)
                 if (b == 1 && iou > b1) { b1 = iou; g1 = g; }
                 if (b == 2 && iou > b2) { b2 = iou; g2 = g; }
                 if (b == 3 && iou > b3) { b3 = iou; g3 = g; }
             }
-            mo.biou[0][p] = b0; mo.biou[1][p] = b1; mo.biou[2][p] = b2; mo.biou[3][p] = b3;
-            mo.bgt[0][p] = (uint8_t)g0; mo.bgt[1][p] = (uint8_t)g1;
-            mo.bgt[2][p] = (uint8_t)g2; mo.bgt[3][p] = (uint8_t)g3;
-            if (met) matched |= 1u << s;
+            // over all sizes: the largest of the three, the earliest ground truth on a tie
+            double b0 = b1;
+            int g0 = g1;
+            if (b2 > b0 || (b2 == b0 && g2 < g0)) { b0 = b2; g0 = g2; }
+            if (b3 > b0 || (b3 == b0 && g3 < g0)) { b0 = b3; g0 = g3; }
+            w.cand.xa[k] = b1;  // bucket_iou(w, 1..3)[k]: this candidate's geometry is no longer needed
+            w.cand.ya[k] = b2;
+            reinterpret_cast<double *>(w.cand.wh)[k] = b3;
+            *reinterpret_cast<unsigned *>(mo.bgt[it]) =
+                (unsigned)g0 | ((unsigned)g1 << 8) | ((unsigned)g2 << 16) | ((unsigned)g3 << 24);
         }
         __syncwarp();
 
-        // ---- greedy TP/FP: a detection is a TP at threshold t iff its best IoU >= t
-        // and no earlier detection of its class claimed the same ground truth with
-        // IoU >= t (metrics.py:406-413).  "Earlier" = lower sorted position.
+        // ---- greedy TP/FP: an item is a TP at threshold t iff its best IoU >= t and no
+        // earlier detection of its class claimed the same ground truth with IoU >= t
+        // (metrics.py:406-413).  "Earlier" = lower sorted position = lower item index.
+#pragma unroll 1
+        for (int it = lane; it < n_items; it += 32) {
+            const unsigned mine = *reinterpret_cast<const unsigned *>(mo.bgt[it]);
+            if (mine == 0xffffffffu) continue;
+            const int k = mo.ik[it], c = mo.icls[it];
+            double rival[4] = {0.0, 0.0, 0.0, 0.0};  // best IoU an earlier item brought to the same ground truth
+            for (int e = it - 1; e >= 0 && mo.icls[e] == c; --e) {
+                const unsigned theirs = *reinterpret_cast<const unsigned *>(mo.bgt[e]);
+                const unsigned diff = theirs ^ mine;
+                if ((diff & 0xffu) && (diff & 0xff00u) && (diff & 0xff0000u) && (diff & 0xff000000u)) continue;
+                const int ke = mo.ik[e];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const unsigned g = (mine >> (8 * q)) & 0xffu;
+                    if (g == 255u || ((diff >> (8 * q)) & 0xffu)) continue;
+                    // subset 0: e's best over all sizes is g, so its IoU sits in g's bucket table
+                    const int bucket = q ? q : mo.gbucket[g];
+                    rival[q] = fmax(rival[q], bucket_iou(w, bucket)[ke]);
+                }
+            }
+            uint64_t flags = 0;
+#pragma unroll 1
+            for (int q = 0; q < 4; ++q) {
+                const unsigned g = (mine >> (8 * q)) & 0xffu;
+                if (g == 255u) continue;
+                const int bucket = q ? q : mo.gbucket[g];
+                const double best = bucket_iou(w, bucket)[k];
+                const double rv = q == 0 ? rival[0] : (q == 1 ? rival[1] : (q == 2 ? rival[2] : rival[3]));
+#pragma unroll 1
+                for (int t = 0; t < T; ++t) {
+                    const double th = s_thr[t];
+                    if (best >= th && !(rv >= th)) flags |= 1ull << (q * T + t);
+                }
+                if (q == 0 && best >= 0.5 && !(rv >= 0.5)) flags |= 1ull << (4 * T);
+            }
+            mo.flags[mo.ipos[it]] = flags;
+        }
+        __syncwarp();
+
+        // ---- records, in sorted order among the kept
 #pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
             if (!((w.keepw[s] >> lane) & 1u)) continue;
             const int p = lane + 32 * s;
             const int k = w.order[p], c = w.cand.cls[k];
-            const int lo = w.cls_start[c];
-            uint64_t flags = 0;
-            if ((matched >> s) & 1u) {
-#pragma unroll 1
-                for (int q = 0; q < 4; ++q) {
-                    const int g = mo.bgt[q][p];
-                    if (g == 255) continue;
-                    const double mine = mo.biou[q][p];
-                    double rival = 0.0;  // best IoU an earlier detection brought to the same GT
-#pragma unroll 1
-                    for (int e = lo; e < p; ++e)
-                        if (kept_at(w, e) && mo.bgt[q][e] == g) rival = fmax(rival, mo.biou[q][e]);
-#pragma unroll 1
-                    for (int t = 0; t < T; ++t) {
-                        const double th = s_thr[t];
-                        if (mine >= th && !(rival >= th)) flags |= 1ull << (q * T + t);
-                    }
-                    if (q == 0 && mine >= 0.5 && !(rival >= 0.5)) flags |= 1ull << (4 * T);
-                }
-            }
-            // emission slot: sorted order among the kept
-            const int j = w.keepbase[s] + __popc(w.keepw[s] & lt);
-            const size_t o = (size_t)img * kCand + j;
+            const size_t o = (size_t)img * kCand + w.keepbase[s] + __popc(w.keepw[s] & lt);
             const double cf = w.cand.conf[k];
             rec_key[o] = ~orderable(cf == 0.0 ? 0.0 : cf);
-            rec_flags[o] = flags | ((uint64_t)c << 56);
+            rec_flags[o] = mo.flags[p] | ((uint64_t)c << 56);
             rec_k[o] = (uint8_t)k;
-            if (rec_raw != nullptr) {  // raw (x, y, w, h) of the box; yh_list_form rebuilds the tuple
-                const float *raw = pred + (size_t)img * kImgFloats + (k / kB) * kD + (k % kB) * 5;
-                rec_raw[o] = make_float4(__ldg(raw + 0), __ldg(raw + 1), __ldg(raw + 2), __ldg(raw + 3));
-            }
         }
-        __syncwarp();
     }
 
     __syncthreads();
@@ -250,7 +316,7 @@ using namespace yh;
 extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int C,
                              double conf_thr, double nms_thr, const double *thresholds_host, int T,
                              int32_t *n_keep, uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k,
-                             float *rec_raw, int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls,
+                             void *rec_box, int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls,
                              float *gt_raw, int32_t *gt_count, void *stream) {
     if (!shape_ok(S, B, C)) {
         set_error("yh_map_update: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
@@ -266,8 +332,8 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
         set_error("yh_map_update: bad argument");
         return YH_ERR_BAD_ARG;
     }
-    if (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8) || ((uintptr_t)rec_raw % 16) || ((uintptr_t)gt_raw % 16)) {
-        set_error("yh_map_update: pred/tgt must be 8-byte aligned, rec_raw/gt_raw 16-byte aligned");
+    if (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8) || ((uintptr_t)rec_box % 8) || ((uintptr_t)gt_raw % 16)) {
+        set_error("yh_map_update: pred/tgt/rec_box must be 8-byte aligned, gt_raw 16-byte aligned");
         return YH_ERR_ALIGNMENT;
     }
     if (N == 0) return 0;
@@ -281,10 +347,10 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
         attr_done = true;
     }
     int ctas = (N + kWarpsPerCtaM - 1) / kWarpsPerCtaM;
-    const int cap = 148 * 5;
+    const int cap = 148 * kCtasPerSmM;
     if (ctas > cap) ctas = cap;
     map_update_kernel<<<ctas, kWarpsPerCtaM * 32, smem, (cudaStream_t)stream>>>(
-        pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, (float4 *)rec_raw, n_gt, gt_cell,
+        pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, (uint64_t *)rec_box, n_gt, gt_cell,
         gt_cls, (float4 *)gt_raw, gt_count);
     return check_launch("yh_map_update");
 }

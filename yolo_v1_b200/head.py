@@ -83,7 +83,7 @@ class UpdateChunk:
     rec_key: torch.Tensor    # (N,K) uint64-as-int64: ~orderable(conf)
     rec_flags: torch.Tensor  # (N,K) int64: class << 56 | TP bits
     rec_k: torch.Tensor      # (N,K) uint8 candidate index
-    rec_raw: torch.Tensor | None  # (N,K,4) float32 raw (x, y, w, h)
+    rec_raw: torch.Tensor | None  # (N,K,3) int64 words: x_abs, y_abs (fp64 bits), (w, h) fp32 pair
     n_gt: torch.Tensor       # (N,) int32
     gt_cell: torch.Tensor | None  # (N,S*S) uint8
     gt_cls: torch.Tensor | None   # (N,S*S) uint8
@@ -108,7 +108,7 @@ def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: 
     rec_key = torch.empty(N, K, **i64)
     rec_flags = torch.empty(N, K, **i64)
     rec_k = torch.empty(N, K, **u8)
-    rec_raw = torch.empty(N, K, 4, dtype=torch.float32, device=dev) if want_lists else None
+    rec_raw = torch.empty(N, K, 3, dtype=torch.int64, device=dev) if want_lists else None
     gt_cell = torch.empty(N, G, **u8) if want_lists else None
     gt_cls = torch.empty(N, G, **u8) if want_lists else None
     gt_raw = torch.empty(N, G, 4, dtype=torch.float32, device=dev) if want_lists else None
