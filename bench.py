@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--nms", type=float, default=0.4)
     ap.add_argument("--cpu-sample", type=int, default=4096, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=8, help="mini-batches the e2e step streams from the host")
     ap.add_argument("--exchange", default="class_shard", choices=["class_shard", "gather"],
                     help="N>1: how compute() makes the per-class order global (yolo_v1_b200/distributed.py)")
     return ap.parse_args()
@@ -192,21 +193,28 @@ def main():
     pred_h, tgt_h = make_batch(n, args.profile, 1234 + rank)
     pred_h, tgt_h = pred_h.pin_memory(), tgt_h.pin_memory()
     pred_d, tgt_d = pred_h.to(dev), tgt_h.to(dev)
-    crit = YOLOLoss()
+    # defer_loss_dict: the five loss floats are read back when first looked at (end of the step)
+    # instead of stalling the host inside forward(); see yolo_v1_b200/loss.py:LossDict
+    crit = YOLOLoss(defer_loss_dict=True)
     metric = mAPMetric(num_classes=C, conf_threshold=args.conf, nms_threshold=args.nms)
     if world > 1:
         from yolo_v1_b200.distributed import DistributedMAP
 
         metric = DistributedMAP(metric, mode=args.exchange)
 
-    def step(p, t):
+    def head_pass(p, t):
+        """loss fwd+bwd and the metric update of one (mini-)batch already on the device."""
         p = p.requires_grad_(True)
         total, parts = crit(p, t)
         total.backward()
-        metric.reset()
         metric.update(p.detach(), t)
+        return parts
+
+    def step(p, t):
+        metric.reset()
+        parts = head_pass(p, t)
         res = metric.compute()
-        return parts, res
+        return float(parts["total"]), float(res["mAP50:95"])  # both read back inside the step
 
     def barrier():
         if world > 1:
@@ -233,21 +241,59 @@ def main():
         step(pred_d.detach(), tgt_d)
     l0 = _lib.lib().yh_launch_count()
     with ClockSampler(local) as clk:
-        ms, (parts, res) = timed(lambda: step(pred_d.detach(), tgt_d), args.steps)
+        ms, (loss_total, map5095) = timed(lambda: step(pred_d.detach(), tgt_d), args.steps)
     launches = (_lib.lib().yh_launch_count() - l0) // args.steps
     value = world * n / (ms * 1e-3)
 
-    # ---- end to end: host buffers in, results out
+    # ---- end to end: host buffers in, results out.  The batch arrives from pinned host memory
+    # in `e2e_chunks` mini-batches on a copy stream; each is consumed (loss fwd+bwd, update) as
+    # soon as it lands, so the head overlaps the PCIe transfer of the next mini-batch.
+    n_chunks = max(1, min(args.e2e_chunks, n))
+    bounds = [(i * n) // n_chunks for i in range(n_chunks + 1)]
+    copy_stream = torch.cuda.Stream(device=dev)
+    main_stream = torch.cuda.current_stream(dev)
+
     def e2e_step():
-        p = pred_h.to(dev, non_blocking=True)
-        t = tgt_h.to(dev, non_blocking=True)
-        parts, res = step(p, t)
-        return float(parts["total"]), float(res["mAP50:95"])
+        metric.reset()
+        copy_stream.wait_stream(main_stream)
+        landed = []
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in zip(bounds, bounds[1:]):
+                p = pred_h[lo:hi].to(dev, non_blocking=True)
+                t = tgt_h[lo:hi].to(dev, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+                landed.append((p, t, ev))
+        losses = []
+        for p, t, ev in landed:
+            main_stream.wait_event(ev)
+            p.record_stream(main_stream)
+            t.record_stream(main_stream)
+            losses.append((head_pass(p, t), p.shape[0]))
+        res = metric.compute()
+        total = sum(float(parts["total"]) * m for parts, m in losses) / n  # batch mean from mini-batch means
+        return total, float(res["mAP50:95"])
 
     e2e_step()
-    e2e_ms, _ = timed(e2e_step, max(2, args.steps // 2))
+    e2e_ms, (e2e_loss, e2e_map) = timed(e2e_step, max(2, args.steps // 2))
+    h2d_ms = None
+    if rank == 0:  # the PCIe floor of the same transfer, for reference
+        def h2d_only():
+            pred_h.to(dev, non_blocking=True)
+            tgt_h.to(dev, non_blocking=True)
+        h2d_only()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            h2d_only()
+        e1.record()
+        torch.cuda.synchronize()
+        h2d_ms = e0.elapsed_time(e1) / 3
     e2e = {"value": world * n / (e2e_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": 2 * n * IMG_BYTES,
-           "d2h_bytes_per_step": 5 * 4 + 4 * C * 10 * 8 + 16 + 4 * C * 4, "ms_per_step": e2e_ms}
+           "d2h_bytes_per_step": n_chunks * 5 * 4 + (4 * C * 10 + 3 + 4 * C) * 8, "ms_per_step": e2e_ms,
+           "mini_batches": n_chunks, "h2d_only_ms": h2d_ms,
+           "result_check": {"loss_total": e2e_loss, "mAP50:95": e2e_map}}
 
     # ---- per-stage kernels, timed alone with CUDA events on the launching stream
     stages = {}
@@ -280,15 +326,28 @@ def main():
     t_upd = time_call(lambda: head.map_update(pred_d, tgt_d, args.conf, args.nms, thr, gt_count))
     chunk = head.map_update(pred_d, tgt_d, args.conf, args.nms, thr, gt_count.zero_())
     kbar = float(chunk.n_keep.float().mean().item())
-    upd_bytes = 2 * IMG_BYTES + 8 + kbar * (8 + 8 + 1 + 16) + 2.7 * 18  # records: key, flags, k, raw box
-    stages["map_update"] = {"ms": t_upd, "bytes_per_image": upd_bytes, "kept_per_image": kbar,
+    gbar = float(chunk.n_gt.float().mean().item())
+    # read pred + tgt, write per image: 2 counters; per kept box: key 8 + flags 8 + candidate 1 + box 24;
+    # per ground truth: cell 1 + class 1 + raw box 16
+    upd_bytes = 2 * IMG_BYTES + 8 + kbar * (8 + 8 + 1 + 24) + gbar * 18
+    stages["map_update"] = {"ms": t_upd, "bytes_per_image": upd_bytes, "kept_per_image": kbar, "gt_per_image": gbar,
                             "gbs": upd_bytes * n / (t_upd * 1e-3) / 1e9}
     t_dec = time_call(lambda: head.decode_nms(pred_d, args.conf, args.nms, head.IOU_INFER, head.ORDER_GLOBAL_CONF,
                                               want_boxes=False))
     stages["decode_nms_infer"] = {"ms": t_dec, "bytes_per_image": IMG_BYTES + 128,
                                   "gbs": (IMG_BYTES + 128) * n / (t_dec * 1e-3) / 1e9}
+    t_decm = time_call(lambda: head.decode_nms(pred_d, args.conf, args.nms, head.IOU_METRICS,
+                                               head.ORDER_CLASS_GROUPED, want_boxes=False))
+    stages["decode_nms_metrics"] = {"ms": t_decm, "bytes_per_image": IMG_BYTES + 128,
+                                    "gbs": (IMG_BYTES + 128) * n / (t_decm * 1e-3) / 1e9}
     key, flg, off = head.compact_records(chunk)
     M = int(off[-1].item())
+    # radix passes the sort needs for these keys: bits that vary over the input + 5 class bits, 8 per pass
+    kk = key[:M]
+    k_np = kk.cpu().numpy().view(np.uint64)
+    v_bits = int(np.bitwise_or.reduce(k_np) & np.bitwise_or.reduce(~k_np)) if M else 0
+    nb = (v_bits.bit_length() - ((v_bits & -v_bits).bit_length() - 1)) if v_bits else 0
+    passes = (nb + 5 + 7) // 8
 
     def ap_only():
         k2, f2 = key[:M].clone(), flg[:M].clone()
@@ -296,16 +355,30 @@ def main():
 
     t_clone = time_call(lambda: (key[:M].clone(), flg[:M].clone()))
     t_ap = time_call(ap_only) - t_clone
-    ap_bytes = M * 16 * (1 + 2 * 9 + 2)  # histogram read + 9 passes r+w + two flag sweeps
-    stages["ap_reduce"] = {"ms": t_ap, "records": M, "bytes": ap_bytes, "gbs": ap_bytes / (t_ap * 1e-3) / 1e9}
+    # key-range read 8 + histogram read 16 + passes x (read 16 + write 16) + two flag sweeps 8 + 8
+    ap_bytes = M * (8 + 16 + 32 * passes + 16)
+    stages["ap_reduce"] = {"ms": t_ap, "records": M, "radix_passes": passes, "bytes": ap_bytes,
+                           "gbs": ap_bytes / (t_ap * 1e-3) / 1e9}
     t_cmp = time_call(lambda: head.compact_records(chunk))
-    stages["compact_records"] = {"ms": t_cmp}
+    stages["compact_records"] = {"ms": t_cmp, "bytes": M * 32 + n * 4, "gbs": (M * 32 + n * 4) / (t_cmp * 1e-3) / 1e9}
 
+    # dominant kernel = the longest single launch of the step (the sort's passes are ~0.07 ms each)
     dom = max(("loss_fwd_bwd", "map_update"), key=lambda k: stages[k]["ms"])
-    roof = {"bound": "hbm", "kernel": {"loss_fwd_bwd": "loss_kernel<float>", "map_update": "map_update_kernel"}[dom],
+    kernel_name = {"loss_fwd_bwd": "loss_kernel<float>", "map_update": "map_update_kernel"}[dom]
+    traffic = None
+    try:  # DRAM bytes per launch from the committed ncu --set full capture of the same workload
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tj.get("images") == n and tj.get("profile") == args.profile:
+            traffic = tj["kernels"].get(kernel_name)
+    except Exception:
+        pass
+    step_kernel_ms = stages["loss_fwd_bwd"]["ms"] + stages["map_update"]["ms"] + stages["compact_records"]["ms"] + \
+        stages["ap_reduce"]["ms"]
+    roof = {"bound": "hbm", "kernel": kernel_name,
             "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": stages[dom]["gbs"] / peak,
-            "traffic": None, "peak_source": peak_src,
+            "traffic": traffic, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": stages[dom]["bytes_per_image"] * n,
+            "launch_ms": stages[dom]["ms"], "share_of_step_kernel_time": stages[dom]["ms"] / step_kernel_ms,
             "all": {k: {"gbs": v.get("gbs"), "frac": (v["gbs"] / peak) if v.get("gbs") else None, "ms": v["ms"]}
                     for k, v in stages.items()}}
 
@@ -319,7 +392,7 @@ def main():
             "vs_baseline": None, "dtype": "f32 loss / f64 geometry", "data": "synthetic",
             "config": workload_config(args, n), "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cpu, "stages": stages,
-            "result_check": {"loss_total": float(parts["total"]), "mAP50:95": float(res["mAP50:95"])},
+            "result_check": {"loss_total": loss_total, "mAP50:95": map5095},
         }
         print(json.dumps(line))
     if world > 1:

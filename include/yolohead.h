@@ -138,12 +138,16 @@ int yh_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t *n_gt, uin
                 double *gt_box, void *stream);
 
 /* Compacts the fixed-stride records of yh_map_update into dense arrays in image
- * order: offsets[n] = exclusive prefix of n_keep (offsets[N] = total).  Uses
- * `workspace` of yh_compact_workspace_bytes(N). */
+ * order.  running_total (device int64, nullable) chains calls: the records of this
+ * batch are appended behind the *running_total records already in out_key /
+ * out_flags and the scalar is advanced, all on the stream (no host round trip).
+ * offsets[n] = position of image n's first record in the dense arrays,
+ * offsets[N] = position one past the last.  Uses `workspace` of
+ * yh_compact_workspace_bytes(N). */
 size_t yh_compact_workspace_bytes(int N);
 int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key, const uint64_t *rec_flags,
                        int N, int K, int64_t *offsets, uint64_t *out_key, uint64_t *out_flags,
-                       void *workspace, size_t workspace_bytes, void *stream);
+                       int64_t *running_total, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------------------ AP reduce ----
  * Replaces the sort / cumsum / 11-point interpolation of
@@ -156,8 +160,14 @@ int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key, const uin
  *   totals[0] = overall TP (bit 4*T), totals[1] = M  (int64)
  * gt_count[4*C] as produced by yh_map_update. */
 size_t yh_ap_workspace_bytes(int64_t M, int C, int T);
-int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int32_t *gt_count, int C, int T,
-                 double *ap, int64_t *totals, void *workspace, size_t workspace_bytes, void *stream);
+/* M_dev (device int64, nullable): the actual record count, min(*M_dev, M); M is then
+ * only the capacity the buffers and the workspace were sized for, so the host never
+ * has to read the count back.  packed (nullable, 4*C*T + 3 + 4*C doubles) receives
+ * everything a caller reads back in one buffer: ap[], totals[0], totals[1], an
+ * internal error flag (0 = ok), gt_count[] as doubles. */
+int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int64_t *M_dev,
+                 const int32_t *gt_count, int C, int T, double *ap, int64_t *totals, double *packed,
+                 void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------- multi-GPU exchange ----
  * Average precision is independent per class (metrics.py:126-141, 382), so N ranks

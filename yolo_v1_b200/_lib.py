@@ -35,9 +35,9 @@ SIGNATURES = {
     "yh_list_form": (_i, [_vp] * 8 + [_i, _i, _i, _i] + [_vp] * 4),
     "yh_parse_gt": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "yh_compact_workspace_bytes": (_sz, [_i]),
-    "yh_compact_records": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "yh_compact_records": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_ap_workspace_bytes": (_sz, [_i64, _i, _i]),
-    "yh_ap_reduce": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "yh_ap_reduce": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_partition_workspace_bytes": (_sz, [_i64]),
     "yh_partition_records": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_iou_pairs": (_i, [_vp, _vp, _i64, _i, _vp, _vp]),

@@ -4,6 +4,11 @@
 
 namespace yh {
 
+// the sorted records sit in buffer (npasses & 1): a = caller's arrays, b = workspace copies
+__device__ __forceinline__ const uint64_t *sorted_flags(const SortCtl *ctl, const uint64_t *a, const uint64_t *b) {
+    return (key_plan(ctl).npasses & 1) ? b : a;
+}
+
 struct ApCtl {                        // zeroed per call, follows SortCtl in the workspace
     unsigned bit_total[kMaxBits];     // set bits per flag position over all records
     unsigned seg_bits[32][kMaxBits];  // set bits at positions before the start of class c
@@ -33,8 +38,12 @@ __device__ __forceinline__ void count_bits_round(uint64_t flags, bool ok, int nb
 
 // tile_bits[tile][b] = set bits b inside the tile (records in sorted order)
 __global__ void __launch_bounds__(kSortThreads)
-tile_bit_counts(const uint64_t *__restrict__ val, int64_t M, int nbits, unsigned *__restrict__ tile_bits) {
+tile_bit_counts(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__ val_b, int64_t Mcap,
+                const int64_t *__restrict__ Mdev, const SortCtl *__restrict__ ctl, int nbits,
+                unsigned *__restrict__ tile_bits) {
     __shared__ unsigned s_acc[kSortWarps][kMaxBits];
+    const int64_t M = count_of(Mcap, Mdev);
+    const uint64_t *val = sorted_flags(ctl, val_a, val_b);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const int64_t first = (int64_t)blockIdx.x * kSortTile + wp * kWarpSpan + lane;
     unsigned acc[2] = {0, 0};
@@ -56,26 +65,54 @@ tile_bit_counts(const uint64_t *__restrict__ val, int64_t M, int nbits, unsigned
     }
 }
 
-// exclusive scan over tiles, one thread per bit (tiles are few thousand at most)
-__global__ void __launch_bounds__(kMaxBits)
+// exclusive scan over tiles: one CTA per flag bit; a thread sums a short run of
+// consecutive tiles, the CTA scans the 1,024 sums, the thread writes its run back
+__global__ void __launch_bounds__(1024)
 scan_tile_bits(unsigned *__restrict__ tile_bits, int ntiles, ApCtl *__restrict__ ap) {
-    const int b = threadIdx.x;
-    unsigned run = 0;
-    for (int t = 0; t < ntiles; ++t) {
+    __shared__ unsigned s_w[32];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const int per = (ntiles + 1023) / 1024;
+    const int t0 = tid * per, t1 = min(ntiles, t0 + per);
+    unsigned sum = 0;
+    for (int t = t0; t < t1; ++t) sum += tile_bits[(size_t)t * kMaxBits + b];
+    unsigned inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) s_w[wp] = inc;
+    __syncthreads();
+    if (wp == 0) {
+        const unsigned x = s_w[lane];
+        unsigned xi = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned u = __shfl_up_sync(0xffffffffu, xi, o);
+            if (lane >= o) xi += u;
+        }
+        s_w[lane] = xi - x;
+        if (lane == 31) ap->bit_total[b] = xi;
+    }
+    __syncthreads();
+    unsigned run = s_w[wp] + inc - sum;
+    for (int t = t0; t < t1; ++t) {
         const unsigned c = tile_bits[(size_t)t * kMaxBits + b];
         tile_bits[(size_t)t * kMaxBits + b] = run;
         run += c;
     }
-    ap->bit_total[b] = run;
 }
 
 // seg_bits[c][b] = set bits b at sorted positions < start of class c (one CTA per class)
 __global__ void __launch_bounds__(kSortThreads)
-class_start_bits(const uint64_t *__restrict__ val, int64_t M, int nbits, const SortCtl *__restrict__ ctl,
+class_start_bits(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__ val_b, int64_t Mcap,
+                 const int64_t *__restrict__ Mdev, int nbits, const SortCtl *__restrict__ ctl,
                  const unsigned *__restrict__ tile_bits, ApCtl *__restrict__ ap) {
     __shared__ unsigned s_acc[kSortWarps][kMaxBits];
+    const int64_t M = count_of(Mcap, Mdev);
+    const uint64_t *val = sorted_flags(ctl, val_a, val_b);
     const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
-    const int64_t start = ctl->hist[8][c];  // records whose class is < c
+    const int64_t start = ctl->class_start[c];  // records whose class is < c
     const int64_t tile = start / kSortTile, tile0 = tile * kSortTile;
     unsigned acc[2] = {0, 0};
     // count inside [tile0, start); warp-strided rounds of 32 records
@@ -100,10 +137,14 @@ class_start_bits(const uint64_t *__restrict__ val, int64_t M, int nbits, const S
 // For every TP: ordinal within its class, rank within its class -> precision, recall
 // -> atomicMax into the highest recall level it reaches.
 __global__ void __launch_bounds__(kSortThreads)
-emit_precisions(const uint64_t *__restrict__ val, int64_t M, int C, int T, const SortCtl *__restrict__ ctl,
+emit_precisions(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__ val_b, int64_t Mcap,
+                const int64_t *__restrict__ Mdev, int C, int T, const SortCtl *__restrict__ ctl,
                 const unsigned *__restrict__ tile_bits, const int32_t *__restrict__ gt_count,
                 ApCtl *__restrict__ ap) {
     __shared__ unsigned s_acc[kSortWarps][kMaxBits];
+    const int64_t M = count_of(Mcap, Mdev);
+    if ((int64_t)blockIdx.x * kSortTile >= M) return;
+    const uint64_t *val = sorted_flags(ctl, val_a, val_b);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const int nbits = 4 * T;  // the overall bit (4*T) only needs its total
     const int64_t first = (int64_t)blockIdx.x * kSortTile + wp * kWarpSpan + lane;
@@ -150,7 +191,7 @@ emit_precisions(const uint64_t *__restrict__ val, int64_t M, int C, int T, const
                 if ((mine >> bb) & 1u) {
                     const int b = bb + 32 * h, s = b / T, t = b % T;
                     const unsigned ordinal = before + __popc(m & le) - ap->seg_bits[c][b];
-                    const int64_t rank = idx - (int64_t)ctl->hist[8][c];  // 0-based within class
+                    const int64_t rank = idx - (int64_t)ctl->class_start[c];  // 0-based within class
                     const int ngt = gt_count[s * C + c];
                     const double prec = __ddiv_rn((double)ordinal, __dadd_rn((double)(rank + 1), 1e-6));
                     const double rec = __ddiv_rn((double)ordinal, (double)ngt);
@@ -169,20 +210,31 @@ emit_precisions(const uint64_t *__restrict__ val, int64_t M, int C, int T, const
 }
 
 // ap[(s*C+c)*T+t]; totals[0] = TP of the overall pass, totals[1] = M
-__global__ void finalize_ap(int C, int T, int64_t M, const SortCtl *__restrict__ ctl,
-                            const int32_t *__restrict__ gt_count, const ApCtl *__restrict__ apc,
-                            double *__restrict__ ap, int64_t *__restrict__ totals) {
+__global__ void finalize_ap(int C, int T, int64_t Mcap, const int64_t *__restrict__ Mdev,
+                            const SortCtl *__restrict__ ctl, const int32_t *__restrict__ gt_count,
+                            const ApCtl *__restrict__ apc, double *__restrict__ ap,
+                            int64_t *__restrict__ totals, double *__restrict__ packed) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t M = count_of(Mcap, Mdev);
+    if (packed != nullptr) {  // everything compute() reads back, in one buffer of doubles
+        if (i == 0) {
+            packed[4 * C * T] = (double)apc->bit_total[4 * T];
+            packed[4 * C * T + 1] = (double)M;
+            packed[4 * C * T + 2] = (double)ctl->err;
+        }
+        if (i < 4 * C) packed[4 * C * T + 3 + i] = (double)gt_count[i];
+    }
     if (i == 0) {
         totals[0] = apc->bit_total[4 * T];
         totals[1] = M;
     }
     if (i >= 4 * C * T) return;
     const int c = (i / T) % C, s = i / (T * C);
-    const unsigned n_pred = ((c + 1 < 256) ? ctl->hist[8][c + 1] : (unsigned)M) - ctl->hist[8][c];
+    const unsigned n_pred = ctl->class_start[c + 1] - ctl->class_start[c];
     const int ngt = gt_count[s * C + c];
     if (ngt == 0 || n_pred == 0) {  // metrics.py:375-379, 592-603
         ap[i] = 0.0;
+        if (packed != nullptr) packed[i] = 0.0;
         return;
     }
     double p[kLevels];
@@ -198,6 +250,7 @@ __global__ void finalize_ap(int C, int T, int64_t M, const SortCtl *__restrict__
 #pragma unroll
     for (int r = 0; r < kLevels; ++r) a = __dadd_rn(a, __ddiv_rn(p[r], 11.0));
     ap[i] = a;
+    if (packed != nullptr) packed[i] = a;
 }
 
 }  // namespace yh

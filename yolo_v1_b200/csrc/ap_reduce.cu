@@ -23,7 +23,13 @@
 namespace yh {
 
 constexpr int kSortThreads = 256;
-constexpr int kSortItems = 8;
+#ifndef YH_SORT_ITEMS
+#define YH_SORT_ITEMS 8
+#endif
+#ifndef YH_SORT_MINBLOCKS
+#define YH_SORT_MINBLOCKS 4
+#endif
+constexpr int kSortItems = YH_SORT_ITEMS;
 constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 records per tile
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kWarpSpan = 32 * kSortItems;            // records a warp owns inside a tile
@@ -61,7 +67,8 @@ scan_counts_local(const int32_t *__restrict__ cnt, int N, int64_t *__restrict__ 
 }
 
 __global__ void __launch_bounds__(1024)
-scan_block_totals(int64_t *__restrict__ block_tot, int nb, int64_t *__restrict__ total_out) {
+scan_block_totals(int64_t *__restrict__ block_tot, int nb, int64_t *__restrict__ total_out,
+                  int64_t *__restrict__ running, int64_t *__restrict__ base_copy) {
     // single CTA; sequential chunks of 1024 with a running carry
     __shared__ int64_t s_w[32];
     __shared__ int64_t s_carry;
@@ -94,18 +101,24 @@ scan_block_totals(int64_t *__restrict__ block_tot, int nb, int64_t *__restrict__
         if (threadIdx.x == 1023) s_carry = carry + s_w[wp] + inc;
         __syncthreads();
     }
-    if (threadIdx.x == 0) *total_out = s_carry;
+    if (threadIdx.x == 0) {
+        // records already in the output arrays (chained calls append behind them)
+        const int64_t base = running != nullptr ? *running : 0;
+        *base_copy = base;
+        *total_out = base + s_carry;
+        if (running != nullptr) *running = base + s_carry;
+    }
 }
 
 // one warp per image: add the block base to its offset and copy its records
 __global__ void __launch_bounds__(256)
 gather_records(const int32_t *__restrict__ cnt, const uint64_t *__restrict__ rec_key,
                const uint64_t *__restrict__ rec_flags, int N, int K, int64_t *__restrict__ off,
-               const int64_t *__restrict__ block_base, uint64_t *__restrict__ out_key,
-               uint64_t *__restrict__ out_flags) {
+               const int64_t *__restrict__ block_base, const int64_t *__restrict__ base_copy,
+               uint64_t *__restrict__ out_key, uint64_t *__restrict__ out_flags) {
     const int img = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (img >= N) return;
-    const int64_t o = off[img] + block_base[img >> 10];
+    const int64_t o = off[img] + block_base[img >> 10] + *base_copy;
     const int n = cnt[img];
     __syncwarp();
     if (lane == 0) off[img] = o;
@@ -126,8 +139,8 @@ extern "C" size_t yh_compact_workspace_bytes(int N) {
 
 extern "C" int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key,
                                   const uint64_t *rec_flags, int N, int K, int64_t *offsets,
-                                  uint64_t *out_key, uint64_t *out_flags, void *workspace,
-                                  size_t workspace_bytes, void *stream) {
+                                  uint64_t *out_key, uint64_t *out_flags, int64_t *running_total,
+                                  void *workspace, size_t workspace_bytes, void *stream) {
     if (N < 0 || K <= 0 || !n_keep || !rec_key || !rec_flags || !offsets || !out_key || !out_flags ||
         !workspace) {
         set_error("yh_compact_records: bad argument");
@@ -140,13 +153,14 @@ extern "C" int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key
     cudaStream_t st = (cudaStream_t)stream;
     int64_t *block_tot = (int64_t *)((char *)workspace + 256);
     const int nb = (N + 1023) / 1024;
+    int64_t *base_copy = (int64_t *)workspace;
     if (N == 0) {
-        cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
+        scan_block_totals<<<1, 1024, 0, st>>>(block_tot, 0, offsets, running_total, base_copy);
         return check_launch("yh_compact_records");
     }
     scan_counts_local<<<nb, 1024, 0, st>>>(n_keep, N, offsets, block_tot);
-    scan_block_totals<<<1, 1024, 0, st>>>(block_tot, nb, offsets + N);
-    gather_records<<<(N + 7) / 8, 256, 0, st>>>(n_keep, rec_key, rec_flags, N, K, offsets, block_tot,
+    scan_block_totals<<<1, 1024, 0, st>>>(block_tot, nb, offsets + N, running_total, base_copy);
+    gather_records<<<(N + 7) / 8, 256, 0, st>>>(n_keep, rec_key, rec_flags, N, K, offsets, block_tot, base_copy,
                                                 out_key, out_flags);
     return check_launch("yh_compact_records", 3);
 }
@@ -154,41 +168,102 @@ extern "C" int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key
 // ======================================================================= sort
 namespace yh {
 
-struct SortCtl {                 // lives at the head of the workspace, zeroed per call
-    unsigned tile_counter[16];   // dynamic tile ids, one counter per pass
-    unsigned err;                // set if a look-back spin gave up (never expected)
-    unsigned pad[15];
+struct SortCtl {                  // lives at the head of the workspace, zeroed per call
+    unsigned tile_counter[16];    // dynamic tile ids, one counter per pass
+    unsigned err;                 // set if a look-back spin gave up (never expected)
+    unsigned pad0;
+    unsigned long long key_or;    // OR of all keys
+    unsigned long long key_nand;  // OR of all ~keys: a bit varies over the input iff set in both
+    unsigned pad1[10];
     unsigned hist[kPasses][256];  // global digit histograms -> exclusive digit offsets
+    unsigned class_start[40];     // records whose class is < c  (c = 0..32)
 };
 
-__device__ __forceinline__ unsigned digit_of(uint64_t key, uint64_t val, int pass) {
-    return pass < 8 ? (unsigned)((key >> (8 * pass)) & 0xff) : (unsigned)(val >> 56);
+// The sort key is the pair (class, confidence key).  Only the key bits that differ
+// somewhere in the input can influence the order, and they form one range [lo, lo+nb)
+// (sign / high exponent bits above it and the zero tail of a 24 x 24-bit product below
+// it are common to all records).  The radix sort runs over the composite
+// (class << nb) | key[lo, lo+nb): ceil((nb + 5) / 8) passes instead of nine.
+struct KeyPlan {
+    int lo, nb, npasses;
+};
+__device__ __forceinline__ KeyPlan key_plan(const SortCtl *ctl) {
+    const unsigned long long vary = ctl->key_or & ctl->key_nand;
+    KeyPlan p;
+    p.lo = vary ? __ffsll((long long)vary) - 1 : 0;
+    p.nb = vary ? 64 - __clzll((long long)vary) - p.lo : 0;
+    p.npasses = (p.nb + 5 + 7) / 8;
+    return p;
+}
+__device__ __forceinline__ unsigned digit_of(uint64_t key, uint64_t val, int pass, const KeyPlan &pl) {
+    const unsigned cls = (unsigned)(val >> 56) & 31u;
+    const int sh = 8 * pass;
+    unsigned d;
+    if (sh >= pl.nb) {
+        d = cls >> (sh - pl.nb);
+    } else {
+        d = (unsigned)((key >> pl.lo) >> sh);
+        const int left = pl.nb - sh;  // key bits available to this digit
+        if (left < 8) d = (d & ((1u << left) - 1u)) | (cls << left);
+    }
+    return d & 0xffu;
+}
+__device__ __forceinline__ int64_t count_of(int64_t cap, const int64_t *dev) {
+    if (dev == nullptr) return cap;
+    const int64_t m = *dev;
+    return m < cap ? m : cap;
 }
 
-// all nine digit histograms in one read of the records
+// which key bits vary
 __global__ void __launch_bounds__(256)
-digit_histograms(const uint64_t *__restrict__ key, const uint64_t *__restrict__ val, int64_t M,
-                 SortCtl *__restrict__ ctl) {
+key_range(const uint64_t *__restrict__ key, int64_t Mcap, const int64_t *__restrict__ Mdev,
+          SortCtl *__restrict__ ctl) {
+    const int64_t M = count_of(Mcap, Mdev);
+    uint64_t o = 0, n = 0;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < M; i += (int64_t)gridDim.x * 256) {
+        const uint64_t k = __ldg(key + i);
+        o |= k;
+        n |= ~k;
+    }
+    const unsigned olo = __reduce_or_sync(0xffffffffu, (unsigned)o), ohi = __reduce_or_sync(0xffffffffu, (unsigned)(o >> 32));
+    const unsigned nlo = __reduce_or_sync(0xffffffffu, (unsigned)n), nhi = __reduce_or_sync(0xffffffffu, (unsigned)(n >> 32));
+    if ((threadIdx.x & 31) == 0) {
+        atomicOr(&ctl->key_or, ((unsigned long long)ohi << 32) | olo);
+        atomicOr(&ctl->key_nand, ((unsigned long long)nhi << 32) | nlo);
+    }
+}
+
+// all digit histograms (and the class histogram) in one read of the records
+__global__ void __launch_bounds__(256)
+digit_histograms(const uint64_t *__restrict__ key, const uint64_t *__restrict__ val, int64_t Mcap,
+                 const int64_t *__restrict__ Mdev, SortCtl *__restrict__ ctl) {
     __shared__ unsigned s_h[kPasses][256];
+    __shared__ unsigned s_c[32];
+    const int64_t M = count_of(Mcap, Mdev);
+    const KeyPlan pl = key_plan(ctl);
     for (int i = threadIdx.x; i < kPasses * 256; i += 256) (&s_h[0][0])[i] = 0;
+    if (threadIdx.x < 32) s_c[threadIdx.x] = 0;
     __syncthreads();
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < M; i += (int64_t)gridDim.x * 256) {
         const uint64_t k = __ldg(key + i), v = __ldg(val + i);
-#pragma unroll
-        for (int p = 0; p < kPasses; ++p) atomicAdd(&s_h[p][digit_of(k, v, p)], 1u);
+        for (int p = 0; p < pl.npasses; ++p) atomicAdd(&s_h[p][digit_of(k, v, p, pl)], 1u);
+        atomicAdd(&s_c[(unsigned)(v >> 56) & 31u], 1u);
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < kPasses * 256; i += 256) {
+    for (int i = threadIdx.x; i < pl.npasses * 256; i += 256) {
         const unsigned c = (&s_h[0][0])[i];
         if (c) atomicAdd(&ctl->hist[0][0] + i, c);
     }
+    if (threadIdx.x < 32 && s_c[threadIdx.x]) atomicAdd(&ctl->class_start[threadIdx.x], s_c[threadIdx.x]);
 }
 
-// hist[p][d] -> number of records whose digit is < d  (one CTA per pass)
+// hist[p][d] -> number of records whose digit is < d  (one CTA per pass);
+// the last CTA turns the class histogram into class_start[0..32]
 __global__ void __launch_bounds__(256) digit_offsets(SortCtl *__restrict__ ctl) {
     __shared__ unsigned s_w[8];
     const int p = blockIdx.x, d = threadIdx.x, lane = d & 31, wp = d >> 5;
-    const unsigned v = ctl->hist[p][d];
+    const bool classes = p == kPasses;
+    const unsigned v = classes ? (d < 32 ? ctl->class_start[d] : 0u) : ctl->hist[p][d];
     unsigned inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -199,22 +274,41 @@ __global__ void __launch_bounds__(256) digit_offsets(SortCtl *__restrict__ ctl) 
     __syncthreads();
     unsigned base = 0;
     for (int q = 0; q < wp; ++q) base += s_w[q];
-    ctl->hist[p][d] = base + inc - v;
+    if (!classes) {
+        ctl->hist[p][d] = base + inc - v;
+    } else if (d < 32) {
+        ctl->class_start[d] = inc - v;
+        if (d == 31) ctl->class_start[32] = inc;
+    }
 }
 
-__global__ void __launch_bounds__(kSortThreads)
-radix_pass(const uint64_t *__restrict__ kin, const uint64_t *__restrict__ vin,
-           uint64_t *__restrict__ kout, uint64_t *__restrict__ vout, int64_t M, int pass,
+// One pass of the stable LSD sort.  A tile (2,048 records) is ranked in registers,
+// exchanged through shared memory so that records of one digit leave the CTA as one
+// contiguous run (coalesced stores), and chained to its predecessors with a
+// decoupled look-back.  Pass p reads buffer (p & 1) and writes the other one.
+__global__ void __launch_bounds__(kSortThreads, YH_SORT_MINBLOCKS)
+radix_pass(uint64_t *__restrict__ key_a, uint64_t *__restrict__ val_a, uint64_t *__restrict__ key_b,
+           uint64_t *__restrict__ val_b, int64_t Mcap, const int64_t *__restrict__ Mdev, int pass,
            SortCtl *__restrict__ ctl, unsigned *__restrict__ status) {
+    __shared__ uint64_t x_key[kSortTile], x_val[kSortTile];  // 32 KB exchange
     __shared__ unsigned s_hist[kSortWarps][256];
-    __shared__ unsigned s_base[256];
+    __shared__ unsigned s_gbase[256];   // global position of the first record of digit d of this tile
+    __shared__ unsigned s_lstart[256];  // tile-local position of the first record of digit d
+    __shared__ unsigned s_wsum[kSortWarps];
     __shared__ unsigned s_tile;
+    const KeyPlan pl = key_plan(ctl);
+    if (pass >= pl.npasses) return;
+    const int64_t M = count_of(Mcap, Mdev);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(&ctl->tile_counter[pass], 1u);
     for (int i = tid; i < kSortWarps * 256; i += kSortThreads) (&s_hist[0][0])[i] = 0;
     __syncthreads();
     const unsigned tile = s_tile;
-    const int64_t first = (int64_t)tile * kSortTile + wp * kWarpSpan + lane;
+    const int64_t tile0 = (int64_t)tile * kSortTile;
+    if (tile0 >= M) return;
+    const uint64_t *kin = (pass & 1) ? key_b : key_a, *vin = (pass & 1) ? val_b : val_a;
+    uint64_t *kout = (pass & 1) ? key_a : key_b, *vout = (pass & 1) ? val_a : val_b;
+    const int64_t first = tile0 + wp * kWarpSpan + lane;
 
     uint64_t k[kSortItems], v[kSortItems];
     unsigned dg[kSortItems], rk[kSortItems];
@@ -222,15 +316,15 @@ radix_pass(const uint64_t *__restrict__ kin, const uint64_t *__restrict__ vin,
     for (int i = 0; i < kSortItems; ++i) {
         const int64_t idx = first + 32 * i;
         const bool ok = idx < M;
-        k[i] = ok ? __ldg(kin + idx) : 0;
-        v[i] = ok ? __ldg(vin + idx) : 0;
+        k[i] = ok ? kin[idx] : 0;
+        v[i] = ok ? vin[idx] : 0;
     }
     // stable rank of every record among the records of its warp with the same digit
     const unsigned lt = (1u << lane) - 1u;
 #pragma unroll
     for (int i = 0; i < kSortItems; ++i) {
         const bool ok = (first + 32 * i) < M;
-        dg[i] = digit_of(k[i], v[i], pass);
+        dg[i] = digit_of(k[i], v[i], pass, pl);
         const unsigned act = __ballot_sync(0xffffffffu, ok);
         unsigned peers = 0, pre = 0;
         if (ok) {
@@ -245,7 +339,7 @@ radix_pass(const uint64_t *__restrict__ kin, const uint64_t *__restrict__ vin,
         __syncwarp();
     }
     __syncthreads();
-    {   // thread d owns digit d: warp offsets inside the tile, then the chained scan
+    {   // thread d owns digit d: warp offsets inside the tile, the chained scan, the local layout
         const int d = tid;
         unsigned tot = 0;
 #pragma unroll
@@ -254,6 +348,14 @@ radix_pass(const uint64_t *__restrict__ kin, const uint64_t *__restrict__ vin,
             s_hist[q][d] = tot;
             tot += c;
         }
+        // exclusive scan of tot over the 256 digits -> tile-local run starts
+        unsigned inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_wsum[wp] = inc;
         volatile unsigned *st = status;
         unsigned excl = 0;
         if (tile == 0) {
@@ -261,30 +363,48 @@ radix_pass(const uint64_t *__restrict__ kin, const uint64_t *__restrict__ vin,
         } else {
             st[(size_t)tile * 256 + d] = kFlagAgg | tot;
             for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
-                unsigned s = st[(size_t)t * 256 + d];
+                unsigned sv = st[(size_t)t * 256 + d];
                 unsigned spins = 0;
-                while ((s >> 30) == 0) {
-                    __nanosleep(32);
-                    s = st[(size_t)t * 256 + d];
+                while ((sv >> 30) == 0) {
+                    __nanosleep(20);
+                    sv = st[(size_t)t * 256 + d];
                     if (++spins > (1u << 22)) {
                         atomicExch(&ctl->err, 1u);
                         break;
                     }
                 }
-                excl += s & kValMask;
-                if ((s >> 30) == 2 || (s >> 30) == 0) break;
+                excl += sv & kValMask;
+                if ((sv >> 30) == 2 || (sv >> 30) == 0) break;
             }
             st[(size_t)tile * 256 + d] = kFlagIncl | (excl + tot);
         }
-        s_base[d] = ctl->hist[pass][d] + excl;
+        s_gbase[d] = ctl->hist[pass][d] + excl;
+        __syncthreads();
+        unsigned wbase = 0;
+#pragma unroll
+        for (int q = 0; q < kSortWarps; ++q) wbase += (q < wp) ? s_wsum[q] : 0u;
+        s_lstart[d] = wbase + inc - tot;
     }
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < kSortItems; ++i) {
         if ((first + 32 * i) < M) {
-            const unsigned pos = s_base[dg[i]] + s_hist[wp][dg[i]] + rk[i];
-            kout[pos] = k[i];
-            vout[pos] = v[i];
+            const unsigned q = s_lstart[dg[i]] + s_hist[wp][dg[i]] + rk[i];
+            x_key[q] = k[i];
+            x_val[q] = v[i];
+        }
+    }
+    __syncthreads();
+    const int count = (int)((M - tile0) < kSortTile ? (M - tile0) : kSortTile);
+#pragma unroll
+    for (int i = 0; i < kSortItems; ++i) {
+        const int q = tid + kSortThreads * i;
+        if (q < count) {
+            const uint64_t kk = x_key[q], vv = x_val[q];
+            const unsigned d = digit_of(kk, vv, pass, pl);
+            const unsigned pos = s_gbase[d] + (unsigned)q - s_lstart[d];
+            kout[pos] = kk;
+            vout[pos] = vv;
         }
     }
 }
@@ -325,9 +445,9 @@ extern "C" size_t yh_ap_workspace_bytes(int64_t M, int C, int T) {
     return ap_layout(M, C, T).total;
 }
 
-extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int32_t *gt_count, int C,
-                            int T, double *ap, int64_t *totals, void *workspace,
-                            size_t workspace_bytes, void *stream) {
+extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int64_t *M_dev,
+                            const int32_t *gt_count, int C, int T, double *ap, int64_t *totals,
+                            double *packed, void *workspace, size_t workspace_bytes, void *stream) {
     if (C < 1 || C > 32 || T < 1 || T > YH_MAX_THRESHOLDS) {
         set_error("yh_ap_reduce: C=%d / T=%d outside what this build carries (C<=32, T<=%d)", C, T,
                   YH_MAX_THRESHOLDS);
@@ -358,26 +478,24 @@ extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int
         set_error("yh_ap_reduce: memset: %s", cudaGetErrorString(e));
         return (int)e;
     }
-    const uint64_t *sorted_val = flags;
+    int launched = 1;
     if (M > 0) {
         int hb = (int)((M + 256 * 16 - 1) / (256 * 16));
         if (hb > 148 * 8) hb = 148 * 8;
-        digit_histograms<<<hb, 256, 0, st>>>(key, flags, M, ctl);
-        digit_offsets<<<kPasses, 256, 0, st>>>(ctl);
-        uint64_t *ki = key, *vi = flags, *ko = kb, *vo = vb;
-        for (int p = 0; p < kPasses; ++p) {
-            radix_pass<<<L.ntiles, kSortThreads, 0, st>>>(ki, vi, ko, vo, M, p, ctl,
+        key_range<<<hb, 256, 0, st>>>(key, M, M_dev, ctl);
+        digit_histograms<<<hb, 256, 0, st>>>(key, flags, M, M_dev, ctl);
+        digit_offsets<<<kPasses + 1, 256, 0, st>>>(ctl);
+        // passes beyond the plan's count return at once (the count is only known on the device)
+        for (int p = 0; p < kPasses; ++p)
+            radix_pass<<<L.ntiles, kSortThreads, 0, st>>>(key, flags, kb, vb, M, M_dev, p, ctl,
                                                           status + (size_t)p * L.ntiles * 256);
-            uint64_t *t = ki; ki = ko; ko = t;
-            t = vi; vi = vo; vo = t;
-        }
-        sorted_val = vi;  // nine passes: the sorted records sit in the workspace copies
         const int nbits = 4 * T + 1;
-        tile_bit_counts<<<L.ntiles, kSortThreads, 0, st>>>(sorted_val, M, nbits, tile_bits);
-        scan_tile_bits<<<1, kMaxBits, 0, st>>>(tile_bits, L.ntiles, apc);
-        class_start_bits<<<C, kSortThreads, 0, st>>>(sorted_val, M, nbits, ctl, tile_bits, apc);
-        emit_precisions<<<L.ntiles, kSortThreads, 0, st>>>(sorted_val, M, C, T, ctl, tile_bits, gt_count, apc);
+        tile_bit_counts<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, ctl, nbits, tile_bits);
+        scan_tile_bits<<<kMaxBits, 1024, 0, st>>>(tile_bits, L.ntiles, apc);
+        class_start_bits<<<C, kSortThreads, 0, st>>>(flags, vb, M, M_dev, nbits, ctl, tile_bits, apc);
+        emit_precisions<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, C, T, ctl, tile_bits, gt_count, apc);
+        launched += 3 + kPasses + 4;
     }
-    finalize_ap<<<(4 * C * T + 127) / 128, 128, 0, st>>>(C, T, M, ctl, gt_count, apc, ap, totals);
-    return check_launch("yh_ap_reduce", M > 0 ? 2 + kPasses + 4 + 1 : 1);
+    finalize_ap<<<(4 * C * T + 127) / 128, 128, 0, st>>>(C, T, M, M_dev, ctl, gt_count, apc, ap, totals, packed);
+    return check_launch("yh_ap_reduce", launched);
 }

@@ -32,7 +32,9 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
 
     for (int img = blockIdx.x * kWarpsPerCta + wib; img < N; img += warps_total) {
         const float *pimg = pred + (size_t)img * kImgFloats;
+#ifndef YH_NO_PREFETCH
         if (img + warps_total < N) prefetch_image(pimg + (size_t)warps_total * kImgFloats, lane);
+#endif
         bool bad = false;
         const Mask128 valid = decode_image(w, pimg, lane, conf_thr, bad_range != nullptr ? &bad : nullptr);
         if (bad_range != nullptr) {

@@ -115,7 +115,9 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         const float tconf0 = __ldg(timg + lane * kD + 4);
         const float tconf1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 4);
         // ---- predictions: decode, order, NMS
+#ifndef YH_NO_PREFETCH
         if (img + warps_total < N) prefetch_image(pimg + (size_t)warps_total * kImgFloats, lane);
+#endif
         const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr);
         // object cells of the target (rare): pull their lines towards L2 while NMS runs
 #pragma unroll

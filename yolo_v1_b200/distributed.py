@@ -175,11 +175,11 @@ class DistributedMAP:
         dist.all_reduce(gt_count, group=g)
         if self.mode == "gather":
             key, flg, counts = gather_records(key, flg, g)
-            ap, totals = head.ap_reduce(key, flg, sum(counts), gt_count, C, T)
+            ap, totals, _ = head.ap_reduce(key, flg, sum(counts), gt_count, C, T)
         else:
             pk, pf, part = partition_records(key, flg, total, class_owners(C, world), world)
             key, flg = exchange_by_owner(pk, pf, part, g)
-            ap, totals = head.ap_reduce(key, flg, key.numel(), gt_count, C, T)
+            ap, totals, _ = head.ap_reduce(key, flg, key.numel(), gt_count, C, T)
             dist.all_reduce(ap, group=g)       # classes a rank does not own are exact zeros
             dist.all_reduce(totals, group=g)
         totals = totals.cpu().numpy()

@@ -141,44 +141,74 @@ def list_form(ch: UpdateChunk):
     return rec_pos, rec_box, gt_box
 
 
-def compact_records(chunk: UpdateChunk):
-    """Dense (key, flags) arrays of a chunk in image order; capacity N*K, `total` valid (device scalar).
+def compact_records(chunk: UpdateChunk, out_key: torch.Tensor | None = None, out_flags: torch.Tensor | None = None,
+                    running: torch.Tensor | None = None):
+    """Dense (key, flags) arrays of a chunk in image order.
 
-    Returns (key, flags, offsets) with offsets[N] = number of records."""
+    Stand-alone: returns (key, flags, offsets) with capacity N*K and offsets[N] = number of
+    records (a device scalar).  Chained: pass shared out_key / out_flags buffers and `running`
+    (device int64 scalar = records already there); this batch is appended and `running` advanced
+    on the stream, without a host round trip."""
     N, K = chunk.rec_key.shape
     dev = chunk.rec_key.device
     lib = _lib.lib()
     offsets = torch.empty(N + 1, dtype=torch.int64, device=dev)
-    out_key = torch.empty(N * K, dtype=torch.int64, device=dev)
-    out_flags = torch.empty(N * K, dtype=torch.int64, device=dev)
+    if out_key is None:
+        out_key = torch.empty(N * K, dtype=torch.int64, device=dev)
+        out_flags = torch.empty(N * K, dtype=torch.int64, device=dev)
     ws = torch.empty(lib.yh_compact_workspace_bytes(N), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         rc = lib.yh_compact_records(chunk.n_keep.data_ptr(), chunk.rec_key.data_ptr(), chunk.rec_flags.data_ptr(),
                                     N, K, offsets.data_ptr(), out_key.data_ptr(), out_flags.data_ptr(),
-                                    ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
+                                    _lib.ptr(running), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
     _lib.check(rc, "yh_compact_records")
     return out_key, out_flags, offsets
 
 
-def ap_reduce(key: torch.Tensor, flags: torch.Tensor, M: int, gt_count: torch.Tensor, Cn: int, T: int):
-    """yh_ap_reduce over the first M records.  key/flags are clobbered.
+_AP_WS: dict = {}
 
-    Returns (ap (4,C,T) float64 device tensor, totals (2,) int64 device tensor)."""
+
+def _ap_workspace(dev, nbytes: int) -> torch.Tensor:
+    """Per-device scratch for yh_ap_reduce, grown on demand and reused (256-byte aligned view)."""
+    buf = _AP_WS.get(dev)
+    if buf is None or buf.numel() < nbytes + 256:
+        buf = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
+        _AP_WS[dev] = buf
+    pad = (-buf.data_ptr()) % 256
+    return buf[pad:pad + nbytes]
+
+
+def ap_reduce(key: torch.Tensor, flags: torch.Tensor, M: int, gt_count: torch.Tensor, Cn: int, T: int,
+              m_dev: torch.Tensor | None = None):
+    """yh_ap_reduce over the first M records (or min(*m_dev, M) when the count lives on the
+    device).  key/flags are clobbered.
+
+    Returns (ap (4,C,T) float64, totals (2,) int64, packed float64 [4*C*T + 3 + 4*C]) on the device;
+    `packed` holds ap, totals, an error flag and gt_count, so one copy brings everything to the host."""
     dev = gt_count.device
     lib = _lib.lib()
     nbytes = lib.yh_ap_workspace_bytes(int(M), Cn, T)
     if nbytes == 0:
         raise NotImplementedError(f"yh_ap_reduce: C={Cn}, T={T} outside this build")
-    ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
-    pad = (-ws.data_ptr()) % 256
+    ws = _ap_workspace(dev, nbytes)
     ap = torch.empty(4, Cn, T, dtype=torch.float64, device=dev)
     totals = torch.empty(2, dtype=torch.int64, device=dev)
+    packed = torch.empty(4 * Cn * T + 3 + 4 * Cn, dtype=torch.float64, device=dev)
     with torch.cuda.device(dev):
         rc = lib.yh_ap_reduce(key.data_ptr() if M else None, flags.data_ptr() if M else None, int(M),
-                              gt_count.data_ptr(), Cn, T, ap.data_ptr(), totals.data_ptr(),
-                              ws.data_ptr() + pad, nbytes, _lib.stream_ptr(dev))
+                              _lib.ptr(m_dev), gt_count.data_ptr(), Cn, T, ap.data_ptr(), totals.data_ptr(),
+                              packed.data_ptr(), ws.data_ptr(), nbytes, _lib.stream_ptr(dev))
     _lib.check(rc, "yh_ap_reduce")
-    return ap, totals
+    return ap, totals, packed
+
+
+def unpack_ap(packed: torch.Tensor, Cn: int, T: int):
+    """Host view of ap_reduce's packed buffer: (ap ndarray (4,C,T), tp_total, n_records, gt_count ndarray (4,C))."""
+    h = packed.cpu().numpy()
+    n = 4 * Cn * T
+    if h[n + 2] != 0.0:
+        raise _lib.YoloHeadError("yh_ap_reduce: the chained scan of the radix sort gave up (internal error)")
+    return h[:n].reshape(4, Cn, T), int(h[n]), int(h[n + 1]), h[n + 3:].astype("int64").reshape(4, Cn)
 
 
 def iou_pairs(box_a, box_b, iou_mode: int, device) -> torch.Tensor:

@@ -64,6 +64,51 @@ def loss_fwd_bwd(pred: torch.Tensor, tgt: torch.Tensor, S: int, B: int, C: int, 
     return parts, grad
 
 
+class LossDict(dict):
+    """The loss_dict of YOLOLoss.forward: a dict[str, float] with the reference's five keys
+    (loss.py:164-170) whose values are copied from the device the first time anything is read.
+
+    The reference calls .item() five times inside forward, which stalls the host on every
+    training step; here the kernel's five floats stay on the device until somebody looks, so
+    forward + backward are enqueued without a host round trip.  Reading any entry (or iterating,
+    printing, comparing, copying, pickling) does the one 20-byte copy and from then on this is a
+    plain dict.  Opt-in (YOLOLoss(defer_loss_dict=True)): C-level fast paths that look inside a
+    dict without calling its methods (json's C encoder, for one) would see it empty before the
+    first read, so the default stays the reference's eager dict of floats."""
+
+    __slots__ = ("_parts",)
+
+    def __init__(self, parts: torch.Tensor):
+        super().__init__()
+        self._parts = parts
+
+    def _fill(self):
+        parts = self._parts
+        if parts is not None:
+            self._parts = None
+            dict.update(self, zip(_KEYS, parts.tolist()))
+
+    def _wrap(name):  # noqa: N805 - helper run at class-creation time
+        base = getattr(dict, name)
+
+        def method(self, *a, **kw):
+            self._fill()
+            return base(self, *a, **kw)
+
+        method.__name__ = name
+        return method
+
+    for _n in ("__getitem__", "__iter__", "__len__", "__contains__", "__repr__", "__eq__", "__ne__", "__or__",
+               "__ror__", "__setitem__", "__delitem__", "__reversed__", "keys", "values", "items", "get", "pop",
+               "popitem", "setdefault", "update", "copy", "clear"):
+        locals()[_n] = _wrap(_n)
+    del _n, _wrap
+
+    def __reduce__(self):
+        self._fill()
+        return (dict, (dict(self),))
+
+
 class _YoloLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, pred, tgt, S, B, C, lc, ln):
@@ -91,15 +136,19 @@ class YOLOLoss(nn.Module):
     """YOLO v1 loss (reference: src/yolo/loss.py:7-53 for the constructor contract)."""
 
     def __init__(self, S: int = 7, B: int = 2, C: int = 20, lambda_coord: float = 5.0,
-                 lambda_noobj: float = 0.5):
+                 lambda_noobj: float = 0.5, *, defer_loss_dict: bool = False):
         super().__init__()
         self.S, self.B, self.C = S, B, C
         self.lambda_coord = lambda_coord
         self.lambda_noobj = lambda_noobj
+        # extension (keyword-only): return a LossDict that is read from the device when first used
+        self.defer_loss_dict = defer_loss_dict
 
     def forward(self, predictions: torch.Tensor, targets: torch.Tensor) -> tuple[torch.Tensor, dict[str, float]]:
         total, parts = _YoloLossFn.apply(predictions, targets, self.S, self.B, self.C, self.lambda_coord,
                                          self.lambda_noobj)
+        if self.defer_loss_dict:
+            return total, LossDict(parts)
         vals = parts.tolist()  # the one device->host read the loss_dict API requires (loss.py:164-170)
         return total, dict(zip(_KEYS, vals))
 
