@@ -175,9 +175,10 @@ int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int64_t *M_dev
  * M compact records of one rank out as n_parts contiguous runs (run p = records
  * whose class c has owner_of_class_host[c] == p), each run in the input (image)
  * order, and writes the run lengths to part_count[n_parts] (device, int64): the
- * split sizes of one all_to_all_single.  n_parts <= 32. */
+ * split sizes of one all_to_all_single.  n_parts <= 32.  M_dev as in yh_ap_reduce:
+ * nullable device count, M is then the capacity. */
 size_t yh_partition_workspace_bytes(int64_t M);
-int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M,
+int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M, const int64_t *M_dev,
                          const uint8_t *owner_of_class_host, int C, int n_parts, uint64_t *out_key,
                          uint64_t *out_flags, int64_t *part_count, void *workspace,
                          size_t workspace_bytes, void *stream);

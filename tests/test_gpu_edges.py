@@ -151,3 +151,69 @@ def test_full_size_invariants():
     same = valid[:, 1:] & (cls[:, 1:] == cls[:, :-1])
     assert (key[:, 1:][same] >= key[:, :-1][same]).all()
     assert (cls[:, 1:][valid[:, 1:]] >= cls[:, :-1][valid[:, 1:]]).all()
+
+
+# ----------------------------------------------------------------------------- sort plan / AP reduce on raw records
+def _ap_from_records(key, flags, gt_count, C, T):
+    """numpy restatement of metrics.py:382-436 over (key, flags) records: stable sort per class by key
+    (ascending key = descending confidence), cumulative TP, precision / recall, 11-point AP."""
+    ap = np.zeros((4, C, T))
+    cls = (flags >> np.uint64(56)).astype(np.int64)
+    levels = np.linspace(0, 1, 11)
+    for c in range(C):
+        idx = np.nonzero(cls == c)[0]
+        order = idx[np.argsort(key[idx], kind="stable")]
+        f = flags[order]
+        for s in range(4):
+            ngt = int(gt_count[s * C + c])
+            if ngt == 0 or len(order) == 0:
+                continue
+            for t in range(T):
+                tp = ((f >> np.uint64(s * T + t)) & np.uint64(1)).astype(np.float64)
+                tpc, fpc = np.cumsum(tp), np.cumsum(1 - tp)
+                prec = np.concatenate([[1.0], tpc / (tpc + fpc + 1e-6)])
+                rec = np.concatenate([[0.0], tpc / ngt])
+                a = 0.0
+                for lv in levels:
+                    a += (prec[rec >= lv].max() if (rec >= lv).any() else 0.0) / 11
+                ap[s, c, t] = a
+    return ap
+
+
+@pytest.mark.parametrize("kind", ["full64", "equal", "narrow", "high_bits", "two_values", "one_record", "tile_edge"])
+def test_ap_reduce_sort_plans(kind):
+    rng = np.random.default_rng(len(kind) * 131 + ord(kind[0]))
+    C, T = 20, 3
+    m = {"one_record": 1, "tile_edge": 2048 * 3, "full64": 70_001}.get(kind, 30_000)
+    if kind == "full64":
+        key = rng.integers(0, 2**64, size=m, dtype=np.uint64)
+    elif kind == "equal":
+        key = np.full(m, 0x3FE0_0000_0000_0000, np.uint64)
+    elif kind == "narrow":
+        key = np.uint64(0x4000_0000_0000_0000) + (rng.integers(0, 1 << 13, size=m).astype(np.uint64) << np.uint64(20))
+    elif kind == "high_bits":
+        key = rng.integers(0, 4, size=m).astype(np.uint64) << np.uint64(62)
+    elif kind == "two_values":
+        key = np.where(rng.random(m) < 0.5, np.uint64(5), np.uint64(1 << 40)).astype(np.uint64)
+    else:
+        key = rng.integers(0, 2**64, size=m, dtype=np.uint64)
+    cls = rng.integers(0, C, size=m).astype(np.uint64)
+    bits = rng.integers(0, 1 << (4 * T + 1), size=m).astype(np.uint64)
+    flags = (cls << np.uint64(56)) | bits
+    gt_count = rng.integers(0, 200, size=4 * C).astype(np.int32) + 400
+    gt_count[3] = 0
+    want = _ap_from_records(key, flags, gt_count, C, T)
+    k = torch.from_numpy(key.view(np.int64).copy()).to(DEV)
+    f = torch.from_numpy(flags.view(np.int64).copy()).to(DEV)
+    g = torch.from_numpy(gt_count).to(DEV)
+    ap, totals, packed = head.ap_reduce(k, f, m, g, C, T)
+    np.testing.assert_allclose(ap.cpu().numpy(), want, rtol=1e-12, atol=0)
+    assert int(totals[1]) == m and int(totals[0]) == int(((bits >> np.uint64(4 * T)) & np.uint64(1)).sum())
+    # same records, count supplied from the device with a larger capacity
+    cap = m + 5000
+    k2 = torch.zeros(cap, dtype=torch.int64, device=DEV); k2[:m] = torch.from_numpy(key.view(np.int64).copy()).to(DEV)
+    f2 = torch.zeros(cap, dtype=torch.int64, device=DEV); f2[:m] = torch.from_numpy(flags.view(np.int64).copy()).to(DEV)
+    ap2, _, packed2 = head.ap_reduce(k2, f2, cap, g, C, T, m_dev=torch.tensor([m], dtype=torch.int64, device=DEV))
+    assert torch.equal(ap2, ap)
+    a, tp, n, gc = head.unpack_ap(packed2, C, T)
+    assert n == m and np.array_equal(gc.reshape(-1), gt_count) and np.array_equal(a, ap.cpu().numpy())

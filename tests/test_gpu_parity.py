@@ -348,6 +348,6 @@ def test_partition_records_is_a_stable_partition(m, parts):
     k, f, cnt = D.partition_records(torch.from_numpy(key).cuda(), torch.from_numpy(flg).cuda(), m, owners, parts)
     own = np.array(owners)[cls]
     perm = np.argsort(own, kind="stable")
-    assert cnt == [int((own == p).sum()) for p in range(parts)]
+    assert cnt.tolist() == [int((own == p).sum()) for p in range(parts)]
     assert np.array_equal(k[:m].cpu().numpy(), key[perm])
     assert np.array_equal(f[:m].cpu().numpy(), flg[perm])

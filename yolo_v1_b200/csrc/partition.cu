@@ -26,13 +26,20 @@ struct OwnerTable {
     uint8_t of_class[256];
 };
 
+__device__ __forceinline__ int64_t part_count_of(int64_t cap, const int64_t *dev) {
+    if (dev == nullptr) return cap;
+    const int64_t m = *dev;
+    return m < cap ? m : cap;
+}
+
 __device__ __forceinline__ int owner_of(const OwnerTable &tab, uint64_t flags) { return tab.of_class[flags >> 56]; }
 
 // tile_cnt[tile][p] = records of the tile that go to part p
 __global__ void __launch_bounds__(kPartThreads)
-part_tile_counts(const uint64_t *__restrict__ flags, int64_t M, const __grid_constant__ OwnerTable tab,
-                 unsigned *__restrict__ tile_cnt) {
+part_tile_counts(const uint64_t *__restrict__ flags, int64_t Mcap, const int64_t *__restrict__ Mdev,
+                 const __grid_constant__ OwnerTable tab, unsigned *__restrict__ tile_cnt) {
     __shared__ unsigned s_cnt[kMaxParts];
+    const int64_t M = part_count_of(Mcap, Mdev);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     if (tid < kMaxParts) s_cnt[tid] = 0;
     __syncthreads();
@@ -52,44 +59,60 @@ part_tile_counts(const uint64_t *__restrict__ flags, int64_t M, const __grid_con
     if (tid < kMaxParts) tile_cnt[(size_t)blockIdx.x * kMaxParts + tid] = s_cnt[tid];
 }
 
-// One CTA, warp p scans column p of tile_cnt over the tiles (exclusive, in place),
-// then the part bases: part_base[p] = records of parts < p; part_count[p] = its size.
-__global__ void __launch_bounds__(kMaxParts * 32)
-part_scan(unsigned *__restrict__ tile_cnt, int ntiles, int n_parts, int64_t *__restrict__ part_base,
-          int64_t *__restrict__ part_count) {
-    __shared__ unsigned s_tot[kMaxParts];
-    const int lane = threadIdx.x & 31, p = threadIdx.x >> 5;
-    unsigned carry = 0;
-    for (int base = 0; base < ntiles; base += 32) {
-        const int t = base + lane;
-        const unsigned v = (t < ntiles) ? tile_cnt[(size_t)t * kMaxParts + p] : 0u;
-        unsigned inc = v;
+// One CTA per part: exclusive scan of column p of tile_cnt over the tiles, in place.  A
+// thread sums a short run of consecutive tiles, the CTA scans the 1,024 sums, the thread
+// writes its run back.  part_count[p] = size of the part.
+__global__ void __launch_bounds__(1024)
+part_scan(unsigned *__restrict__ tile_cnt, int ntiles, int64_t *__restrict__ part_count) {
+    __shared__ unsigned s_w[32];
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const int per = (ntiles + 1023) / 1024;
+    const int t0 = tid * per, t1 = min(ntiles, t0 + per);
+    unsigned sum = 0;
+    for (int t = t0; t < t1; ++t) sum += tile_cnt[(size_t)t * kMaxParts + p];
+    unsigned inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) s_w[wp] = inc;
+    __syncthreads();
+    if (wp == 0) {
+        const unsigned x = s_w[lane];
+        unsigned xi = x;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += u;
+            const unsigned u = __shfl_up_sync(0xffffffffu, xi, o);
+            if (lane >= o) xi += u;
         }
-        if (t < ntiles) tile_cnt[(size_t)t * kMaxParts + p] = carry + inc - v;
-        carry += __shfl_sync(0xffffffffu, inc, 31);
+        s_w[lane] = xi - x;
+        if (lane == 31) part_count[p] = xi;
     }
-    if (lane == 0) s_tot[p] = carry;
     __syncthreads();
-    if (threadIdx.x < n_parts) {
-        int64_t b = 0;
-        for (int q = 0; q < (int)threadIdx.x; ++q) b += s_tot[q];
-        part_base[threadIdx.x] = b;
-        part_count[threadIdx.x] = s_tot[threadIdx.x];
+    unsigned run = s_w[wp] + inc - sum;
+    for (int t = t0; t < t1; ++t) {
+        const unsigned c = tile_cnt[(size_t)t * kMaxParts + p];
+        tile_cnt[(size_t)t * kMaxParts + p] = run;
+        run += c;
     }
 }
 
 __global__ void __launch_bounds__(kPartThreads)
-part_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flags, int64_t M,
-             const __grid_constant__ OwnerTable tab, const unsigned *__restrict__ tile_pre,
-             const int64_t *__restrict__ part_base, uint64_t *__restrict__ out_key,
+part_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flags, int64_t Mcap,
+             const int64_t *__restrict__ Mdev, const __grid_constant__ OwnerTable tab, const unsigned *__restrict__ tile_pre,
+             const int64_t *__restrict__ part_count, int n_parts, uint64_t *__restrict__ out_key,
              uint64_t *__restrict__ out_flags) {
     __shared__ unsigned s_w[kPartWarps][kMaxParts];  // per-warp counts, then running cursors
+    __shared__ int64_t part_base[kMaxParts];         // records of the parts before p
+    const int64_t M = part_count_of(Mcap, Mdev);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     s_w[wp][lane] = 0;
+    if (tid < kMaxParts) {
+        int64_t b = 0;
+        for (int q = 0; q < tid && q < n_parts; ++q) b += part_count[q];
+        part_base[tid] = b;
+    }
     __syncwarp();
     const int64_t first = (int64_t)blockIdx.x * kPartTile + wp * kPartSpan + lane;
     const unsigned lt = (1u << lane) - 1u;
@@ -150,7 +173,7 @@ extern "C" size_t yh_partition_workspace_bytes(int64_t M) {
 }
 
 extern "C" int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M,
-                                    const uint8_t *owner_of_class_host, int C, int n_parts,
+                                    const int64_t *M_dev, const uint8_t *owner_of_class_host, int C, int n_parts,
                                     uint64_t *out_key, uint64_t *out_flags, int64_t *part_count,
                                     void *workspace, size_t workspace_bytes, void *stream) {
     if (C < 1 || C > 256 || n_parts < 1 || n_parts > kMaxParts) {
@@ -186,8 +209,8 @@ extern "C" int yh_partition_records(const uint64_t *key, const uint64_t *flags, 
     int64_t *part_base = (int64_t *)ws;
     unsigned *tile_cnt = (unsigned *)(ws + part_up256(sizeof(int64_t) * kMaxParts));
     const int ntiles = (int)((M + kPartTile - 1) / kPartTile);
-    part_tile_counts<<<ntiles, kPartThreads, 0, st>>>(flags, M, tab, tile_cnt);
-    part_scan<<<1, kMaxParts * 32, 0, st>>>(tile_cnt, ntiles, n_parts, part_base, part_count);
-    part_scatter<<<ntiles, kPartThreads, 0, st>>>(key, flags, M, tab, tile_cnt, part_base, out_key, out_flags);
+    part_tile_counts<<<ntiles, kPartThreads, 0, st>>>(flags, M, M_dev, tab, tile_cnt);
+    part_scan<<<n_parts, 1024, 0, st>>>(tile_cnt, ntiles, part_count);
+    part_scatter<<<ntiles, kPartThreads, 0, st>>>(key, flags, M, M_dev, tab, tile_cnt, part_count, n_parts, out_key, out_flags);
     return check_launch("yh_partition_records", 3);
 }

@@ -59,19 +59,24 @@ def _all_counts(n_local: int, device, group) -> List[int]:
     return [int(v) for v in out.tolist()]
 
 
-def gather_records(key: torch.Tensor, flags: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor, List[int]]:
+def gather_records(key: torch.Tensor, flags: torch.Tensor, group=None, count: Optional[torch.Tensor] = None):
     """All-gather variable-length (key, flags) record arrays in rank order.
 
-    Returns (key_all, flags_all, counts).  One padded all_gather_into_tensor of a
-    (2, max_count) int64 block per rank, then the pads are dropped."""
+    `count` (device int64 [1], optional) is the number of valid records when the arrays are
+    over-allocated.  Returns (key_all, flags_all, counts).  One count exchange (the only host
+    read), one padded all_gather_into_tensor of a (2, max_count) block per rank, pads dropped."""
     world = dist.get_world_size(group)
-    m = key.numel()
-    counts = _all_counts(m, key.device, group)
+    dev = key.device
+    mine = count.reshape(1) if count is not None else torch.tensor([key.numel()], dtype=torch.int64, device=dev)
+    allc = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(allc, mine, group=group)
+    counts = [int(v) for v in allc.tolist()]
+    m = counts[dist.get_rank(group)]
     cap = max(max(counts), 1)
-    send = torch.zeros(2, cap, dtype=torch.int64, device=key.device)
-    send[0, :m] = key
-    send[1, :m] = flags
-    flat = torch.empty(world * 2 * cap, dtype=torch.int64, device=key.device)
+    send = torch.zeros(2, cap, dtype=torch.int64, device=dev)
+    send[0, :m] = key[:m]
+    send[1, :m] = flags[:m]
+    flat = torch.empty(world * 2 * cap, dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(flat, send.view(-1), group=group)
     recv = flat.view(world, 2, cap)
     key_all = torch.cat([recv[r, 0, :counts[r]] for r in range(world)])
@@ -79,27 +84,33 @@ def gather_records(key: torch.Tensor, flags: torch.Tensor, group=None) -> Tuple[
     return key_all, flags_all, counts
 
 
-def exchange_by_owner(key: torch.Tensor, flags: torch.Tensor, part_count: List[int], group=None):
+def exchange_by_owner(key: torch.Tensor, flags: torch.Tensor, part_count, group=None):
     """all_to_all of records already laid out as `world` contiguous runs (run r goes to rank r).
 
-    Returns (key_mine, flags_mine): runs received from rank 0, 1, ... concatenated in rank order."""
+    part_count: the run lengths, a host list or a device int64 tensor (then this does the one
+    host read both split-size lists need).  Returns (key_mine, flags_mine): runs received from
+    rank 0, 1, ... concatenated in rank order."""
     world = dist.get_world_size(group)
     dev = key.device
-    send_n = torch.tensor(part_count, dtype=torch.int64, device=dev)
+    send_n = part_count if torch.is_tensor(part_count) else torch.tensor(part_count, dtype=torch.int64, device=dev)
     recv_n = torch.empty(world, dtype=torch.int64, device=dev)
     dist.all_to_all_single(recv_n, send_n, group=group)
-    recv_counts = [int(v) for v in recv_n.tolist()]
-    total = sum(recv_counts)
+    both = torch.cat([send_n, recv_n]).tolist()
+    send_counts, recv_counts = [int(v) for v in both[:world]], [int(v) for v in both[world:]]
+    total, m = sum(recv_counts), sum(send_counts)
     out_k = torch.empty(total, dtype=torch.int64, device=dev)
     out_f = torch.empty(total, dtype=torch.int64, device=dev)
-    m = sum(part_count)
-    dist.all_to_all_single(out_k, key[:m].contiguous(), recv_counts, list(part_count), group=group)
-    dist.all_to_all_single(out_f, flags[:m].contiguous(), recv_counts, list(part_count), group=group)
+    dist.all_to_all_single(out_k, key[:m].contiguous(), recv_counts, send_counts, group=group)
+    dist.all_to_all_single(out_f, flags[:m].contiguous(), recv_counts, send_counts, group=group)
     return out_k, out_f
 
 
-def partition_records(key: torch.Tensor, flags: torch.Tensor, m: int, owners: List[int], n_parts: int):
-    """yh_partition_records: stable partition by class owner.  Returns (key, flags, part_count list)."""
+def partition_records(key: torch.Tensor, flags: torch.Tensor, m: int, owners: List[int], n_parts: int,
+                      m_dev: Optional[torch.Tensor] = None):
+    """yh_partition_records: stable partition by class owner.
+
+    m is the record count, or the capacity when m_dev (device int64 [1]) carries the count.
+    Returns (key, flags, part_count) with part_count a device int64 [n_parts] tensor."""
     _lib.require_cuda(key, "records")
     dev = key.device
     lib = _lib.lib()
@@ -109,11 +120,12 @@ def partition_records(key: torch.Tensor, flags: torch.Tensor, m: int, owners: Li
     ws = torch.empty(lib.yh_partition_workspace_bytes(int(m)) + 256, dtype=torch.uint8, device=dev)
     tab = (_lib.C.c_uint8 * len(owners))(*owners)
     with torch.cuda.device(dev):
-        rc = lib.yh_partition_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m), tab,
-                                      len(owners), int(n_parts), out_k.data_ptr(), out_f.data_ptr(),
-                                      cnt.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
+        rc = lib.yh_partition_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m),
+                                      _lib.ptr(m_dev), tab, len(owners), int(n_parts), out_k.data_ptr(),
+                                      out_f.data_ptr(), cnt.data_ptr(), ws.data_ptr(), ws.numel(),
+                                      _lib.stream_ptr(dev))
     _lib.check(rc, "yh_partition_records")
-    return out_k, out_f, [int(v) for v in cnt.tolist()]
+    return out_k, out_f, cnt
 
 
 # ------------------------------------------------------------------ the metric
@@ -124,7 +136,10 @@ class DistributedMAP:
     contiguous block of the evaluation set (`shard_range`) for tie order to match
     the single-process reference.  `compute()` is collective and returns the same
     dict on every rank.  Everything else (`reset`, thresholds, attributes) is the
-    wrapped metric's."""
+    wrapped metric's.
+
+    Host round trips per compute(): one for the exchange's split sizes and one for the
+    packed result; everything else (compaction, partition, sort, AP) is enqueued."""
 
     def __init__(self, metric: mAPMetric, group=None, mode: str = "class_shard"):
         if mode not in ("gather", "class_shard"):
@@ -143,48 +158,47 @@ class DistributedMAP:
         self.metric.update(predictions, targets)
 
     def _local_records(self, dev):
+        """(key, flags, capacity, count) of this rank: all batches compacted into one buffer behind
+        a device-side running count -- nothing is read back."""
         m = self.metric
         C = m.num_classes
         if m._lists_live or m._pred_lists:
             raise _lib.YoloHeadError("DistributedMAP: the Python list state was touched on this rank; the sharded "
                                      "compute() runs from the device records only")
-        keys, flags, total = [], [], 0
+        cap = sum(ch.rec_key.numel() for ch in m._chunks)
+        key = torch.empty(max(cap, 1), dtype=torch.int64, device=dev)
+        flg = torch.empty(max(cap, 1), dtype=torch.int64, device=dev)
+        running = torch.zeros(1, dtype=torch.int64, device=dev)
         for ch in m._chunks:
-            k, f, off = head.compact_records(ch)
-            n = int(off[-1].item())
-            keys.append(k[:n])
-            flags.append(f[:n])
-            total += n
-        if not keys:
-            z = torch.empty(0, dtype=torch.int64, device=dev)
-            return z, z.clone(), 0, torch.zeros(4 * C, dtype=torch.int32, device=dev)
-        key = keys[0] if len(keys) == 1 else torch.cat(keys)
-        flg = flags[0] if len(flags) == 1 else torch.cat(flags)
-        return key, flg, total, m._gt_count.clone()
+            head.compact_records(ch, key, flg, running)
+        gt_count = m._gt_count.clone() if m._gt_count is not None else torch.zeros(4 * C, dtype=torch.int32, device=dev)
+        return key, flg, cap, running, gt_count
 
     def compute(self) -> Dict[str, float]:
         m, g = self.metric, self.group
         world = dist.get_world_size(g)
         dev = m._device if m._device is not None else torch.device("cuda", torch.cuda.current_device())
         T, C = len(m.iou_thresholds), m.num_classes
-        key, flg, total, gt_count = self._local_records(dev)
-        n_img = torch.tensor([len(m._pred_lists) + sum(c.n for c in m._chunks)], dtype=torch.int64, device=dev)
-        dist.all_reduce(n_img, group=g)
-        if int(n_img.item()) == 0:
-            return {"mAP50:95": 0.0, "mAP50": 0.0, "mAP75": 0.0, "precision": 0.0, "recall": 0.0}
-        dist.all_reduce(gt_count, group=g)
+        key, flg, cap, running, gt_count = self._local_records(dev)
+        # ground-truth counts and the image count travel in one all-reduce
+        glob = torch.cat([gt_count.to(torch.int64),
+                          torch.tensor([len(m._pred_lists) + sum(c.n for c in m._chunks)], dtype=torch.int64, device=dev)])
+        dist.all_reduce(glob, group=g)
+        gt_count = glob[:4 * C].to(torch.int32)
         if self.mode == "gather":
-            key, flg, counts = gather_records(key, flg, g)
-            ap, totals, _ = head.ap_reduce(key, flg, sum(counts), gt_count, C, T)
+            key, flg, counts = gather_records(key, flg, g, count=running)
+            _, _, packed = head.ap_reduce(key, flg, sum(counts), gt_count, C, T)
         else:
-            pk, pf, part = partition_records(key, flg, total, class_owners(C, world), world)
+            pk, pf, part = partition_records(key, flg, cap, class_owners(C, world), world, m_dev=running)
             key, flg = exchange_by_owner(pk, pf, part, g)
-            ap, totals, _ = head.ap_reduce(key, flg, key.numel(), gt_count, C, T)
-            dist.all_reduce(ap, group=g)       # classes a rank does not own are exact zeros
-            dist.all_reduce(totals, group=g)
-        totals = totals.cpu().numpy()
-        gtc = gt_count.cpu().numpy().reshape(4, C)
-        return m._results(ap.cpu().numpy(), int(totals[0]), int(totals[1]), gtc, int(gtc[0].sum()), T, C)
+            _, _, packed = head.ap_reduce(key, flg, key.numel(), gt_count, C, T)
+            # ap table, TP total, record count, error flag: classes a rank does not own are exact zeros
+            dist.all_reduce(packed[:4 * C * T + 3], group=g)
+        host = torch.cat([packed, glob[4 * C:].to(torch.float64)]).cpu()
+        if int(host[-1]) == 0:
+            return {"mAP50:95": 0.0, "mAP50": 0.0, "mAP75": 0.0, "precision": 0.0, "recall": 0.0}
+        ap, tp_total, n_pred, gtc = head.unpack_ap(host[:-1], C, T)
+        return m._results(ap, tp_total, n_pred, gtc, int(gtc[0].sum()), T, C)
 
 
 def evaluate_sharded(model, images: torch.Tensor, targets: torch.Tensor, batch: int = 256, group=None,
