@@ -26,6 +26,9 @@ constexpr int kSortThreads = 256;
 #ifndef YH_SORT_ITEMS
 #define YH_SORT_ITEMS 8
 #endif
+#ifndef YH_SORT_LOOK
+#define YH_SORT_LOOK 4
+#endif
 #ifndef YH_SORT_MINBLOCKS
 #define YH_SORT_MINBLOCKS 4
 #endif
@@ -36,7 +39,7 @@ constexpr int kWarpSpan = 32 * kSortItems;            // records a warp owns ins
 constexpr int kPasses = 9;                             // 8 key digits + the class digit
 constexpr int kMaxBits = 64;
 constexpr int kLevels = 11;                            // np.linspace(0, 1, 11)
-constexpr unsigned kFlagAgg = 1u << 30, kFlagIncl = 2u << 30, kValMask = (1u << 30) - 1u;
+enum : unsigned { kFlagAgg = 1u << 30, kFlagIncl = 2u << 30, kValMask = (1u << 30) - 1u };
 
 // ------------------------------------------------------------------ compaction
 __global__ void __launch_bounds__(1024)
@@ -339,15 +342,18 @@ radix_pass(uint64_t *__restrict__ key_a, uint64_t *__restrict__ val_a, uint64_t 
         __syncwarp();
     }
     __syncthreads();
-    {   // thread d owns digit d: warp offsets inside the tile, the chained scan, the local layout
+    volatile unsigned *st = status;
+    unsigned tot = 0;
+    {   // thread d owns digit d: warp offsets inside the tile, the tile total, the local layout
         const int d = tid;
-        unsigned tot = 0;
 #pragma unroll
         for (int q = 0; q < kSortWarps; ++q) {
             const unsigned c = s_hist[q][d];
             s_hist[q][d] = tot;
             tot += c;
         }
+        // successors can already add this tile's counts while it is still looking back itself
+        st[(size_t)tile * 256 + d] = (tile == 0 ? kFlagIncl : kFlagAgg) | tot;
         // exclusive scan of tot over the 256 digits -> tile-local run starts
         unsigned inc = tot;
 #pragma unroll
@@ -356,29 +362,6 @@ radix_pass(uint64_t *__restrict__ key_a, uint64_t *__restrict__ val_a, uint64_t 
             if (lane >= o) inc += t;
         }
         if (lane == 31) s_wsum[wp] = inc;
-        volatile unsigned *st = status;
-        unsigned excl = 0;
-        if (tile == 0) {
-            st[(size_t)tile * 256 + d] = kFlagIncl | tot;
-        } else {
-            st[(size_t)tile * 256 + d] = kFlagAgg | tot;
-            for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
-                unsigned sv = st[(size_t)t * 256 + d];
-                unsigned spins = 0;
-                while ((sv >> 30) == 0) {
-                    __nanosleep(20);
-                    sv = st[(size_t)t * 256 + d];
-                    if (++spins > (1u << 22)) {
-                        atomicExch(&ctl->err, 1u);
-                        break;
-                    }
-                }
-                excl += sv & kValMask;
-                if ((sv >> 30) == 2 || (sv >> 30) == 0) break;
-            }
-            st[(size_t)tile * 256 + d] = kFlagIncl | (excl + tot);
-        }
-        s_gbase[d] = ctl->hist[pass][d] + excl;
         __syncthreads();
         unsigned wbase = 0;
 #pragma unroll
@@ -386,6 +369,7 @@ radix_pass(uint64_t *__restrict__ key_a, uint64_t *__restrict__ val_a, uint64_t 
         s_lstart[d] = wbase + inc - tot;
     }
     __syncthreads();
+    // exchange: records of one digit become contiguous inside the tile
 #pragma unroll
     for (int i = 0; i < kSortItems; ++i) {
         if ((first + 32 * i) < M) {
@@ -393,6 +377,45 @@ radix_pass(uint64_t *__restrict__ key_a, uint64_t *__restrict__ val_a, uint64_t 
             x_key[q] = k[i];
             x_val[q] = v[i];
         }
+    }
+    // decoupled look-back, thread d for digit d: walk back over the tiles that have only
+    // published their own counts until one with an inclusive prefix is met.  It runs after
+    // the exchange was issued, so most predecessors have published by now.
+    {
+        const int d = tid;
+        unsigned excl = 0;
+        if (tile > 0) {
+            // kLook status words are fetched per round trip, then consumed nearest first
+            constexpr int kLook = YH_SORT_LOOK;
+            int64_t t = (int64_t)tile - 1;
+            unsigned spins = 0;
+            bool done = false;
+            while (!done) {
+                unsigned sv[kLook];
+#pragma unroll
+                for (int j = 0; j < kLook; ++j) sv[j] = (t - j >= 0) ? st[(size_t)(t - j) * 256 + d] : (unsigned)kFlagIncl;
+                int used = 0;
+#pragma unroll
+                for (int j = 0; j < kLook; ++j) {
+                    if (done || used < j) continue;      // stopped at an earlier word of this batch
+                    const unsigned flag = sv[j] >> 30;
+                    if (flag == 0) continue;              // not published yet: reread from here
+                    excl += sv[j] & kValMask;
+                    used = j + 1;
+                    done = flag == 2;
+                }
+                t -= used;
+                if (!done && used < kLook) {
+                    __nanosleep(20);
+                    if (++spins > (1u << 22)) {
+                        atomicExch(&ctl->err, 1u);
+                        break;
+                    }
+                }
+            }
+            st[(size_t)tile * 256 + d] = kFlagIncl | (excl + tot);
+        }
+        s_gbase[d] = ctl->hist[pass][d] + excl;
     }
     __syncthreads();
     const int count = (int)((M - tile0) < kSortTile ? (M - tile0) : kSortTile);
