@@ -17,6 +17,24 @@ struct GlobalOrderOverlay {
 };
 static_assert(sizeof(GlobalOrderOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
 
+// one kept detection -> output slot `pos` of image `img`
+__device__ __forceinline__ void emit_kept(const WarpWindow &w, int img, int pos, int k, uint8_t *__restrict__ keep_k,
+                                          uint8_t *__restrict__ keep_cls, double *__restrict__ keep_conf,
+                                          double *__restrict__ keep_box) {
+    const size_t o = (size_t)img * kCand + pos;
+    keep_k[o] = (uint8_t)k;
+    if (keep_cls != nullptr) keep_cls[o] = w.cand.cls[k];
+    if (keep_conf != nullptr) keep_conf[o] = w.cand.conf[k];
+    if (keep_box != nullptr) {
+        // (x, y, w, h) as the reference stores them (metrics.py:200-203, inference.py:184-193)
+        const float2 wh = w.cand.wh[k];
+        keep_box[4 * o + 0] = w.cand.xa[k];
+        keep_box[4 * o + 1] = w.cand.ya[k];
+        keep_box[4 * o + 2] = (double)wh.x;
+        keep_box[4 * o + 3] = (double)wh.y;
+    }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm)
 decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double nms_thr, int order,
@@ -71,33 +89,28 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             __syncwarp();
         }
 
+        if (order == YH_ORDER_GLOBAL_CONF) {
+            // lanes take the compact kept list round-robin, so the rank loop runs ceil(kept / 32)
+            // times however the kept boxes are spread over the sorted positions
 #pragma unroll 1
-        for (int s = 0; s < kSlots; ++s) {
-            const int p = lane + 32 * s;
-            if (!((keep.word(s) >> lane) & 1u)) continue;
-            const int k = w.order[p], c = w.cand.cls[k];
-            int pos;
-            if (order == YH_ORDER_CLASS_GROUPED) {
-                pos = w.cls_off[c] + count_below(keep, p) - w.cls_kbase[c];
-            } else {
-                const uint64_t mine = ~orderable(w.cand.conf[k]);
-                pos = 0;
-                for (int q = 0; q < n_kept; ++q) {
-                    const uint64_t other = go.key[q];
-                    pos += (other < mine) || (other == mine && go.k[q] < k);
+            for (int q = lane; q < n_kept; q += 32) {
+                const uint64_t mine = go.key[q];
+                const int k = go.k[q];
+                int pos = 0;
+                for (int r = 0; r < n_kept; ++r) {
+                    const uint64_t other = go.key[r];
+                    pos += (other < mine) || (other == mine && go.k[r] < k);
                 }
+                emit_kept(w, img, pos, k, keep_k, keep_cls, keep_conf, keep_box);
             }
-            const size_t o = (size_t)img * kCand + pos;
-            keep_k[o] = (uint8_t)k;
-            if (keep_cls != nullptr) keep_cls[o] = (uint8_t)c;
-            if (keep_conf != nullptr) keep_conf[o] = w.cand.conf[k];
-            if (keep_box != nullptr) {
-                // (x, y, w, h) as the reference stores them (metrics.py:200-203, inference.py:184-193)
-                const float2 wh = w.cand.wh[k];
-                keep_box[4 * o + 0] = w.cand.xa[k];
-                keep_box[4 * o + 1] = w.cand.ya[k];
-                keep_box[4 * o + 2] = (double)wh.x;
-                keep_box[4 * o + 3] = (double)wh.y;
+        } else {
+#pragma unroll 1
+            for (int s = 0; s < kSlots; ++s) {
+                const int p = lane + 32 * s;
+                if (!((keep.word(s) >> lane) & 1u)) continue;
+                const int k = w.order[p];
+                const int pos = w.cls_off[w.cand.cls[k]] + count_below(keep, p) - w.cls_kbase[w.cand.cls[k]];
+                emit_kept(w, img, pos, k, keep_k, keep_cls, keep_conf, keep_box);
             }
         }
         __syncwarp();

@@ -236,21 +236,23 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                     rival[q] = fmax(rival[q], bucket_iou(w, bucket)[ke]);
                 }
             }
-            uint64_t flags = 0;
-#pragma unroll 1
+            // best IoU per subset; NaN where the subset has no ground truth for this item (never >= t)
+            double best[4];
+#pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const unsigned g = (mine >> (8 * q)) & 0xffu;
-                if (g == 255u) continue;
-                const int bucket = q ? q : mo.gbucket[g];
-                const double best = bucket_iou(w, bucket)[k];
-                const double rv = q == 0 ? rival[0] : (q == 1 ? rival[1] : (q == 2 ? rival[2] : rival[3]));
-#pragma unroll 1
-                for (int t = 0; t < T; ++t) {
-                    const double th = s_thr[t];
-                    if (best >= th && !(rv >= th)) flags |= 1ull << (q * T + t);
-                }
-                if (q == 0 && best >= 0.5 && !(rv >= 0.5)) flags |= 1ull << (4 * T);
+                const int bucket = q ? q : mo.gbucket[g == 255u ? 0 : g];
+                best[q] = g == 255u ? __longlong_as_double(0x7ff8000000000000ll) : bucket_iou(w, bucket)[k];
             }
+            uint64_t flags = 0;
+#pragma unroll 1
+            for (int t = 0; t < T; ++t) {
+                const double th = s_thr[t];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (best[q] >= th && !(rival[q] >= th)) flags |= 1ull << (q * T + t);
+            }
+            if (best[0] >= 0.5 && !(rival[0] >= 0.5)) flags |= 1ull << (4 * T);
             mo.flags[mo.ipos[it]] = flags;
         }
         __syncwarp();
