@@ -60,7 +60,7 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             if (lane == 0) bad_range[img] = anybad ? 1 : 0;
         }
         int n;
-        const Mask128 keep = order_and_nms<MODE>(w, valid, nms_thr, lane, n);
+        const Mask128 keep = order_and_nms<MODE, true>(w, valid, nms_thr, lane, n);
         if (lane == 0) {
             n_keep[img] = keep.count();
             if (n_cand != nullptr) n_cand[img] = n;

@@ -118,6 +118,8 @@ static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, int n, do
     return keep;
 }
 
+constexpr int kPairTable = 256;
+
 // Overlay of `stage` between decode and the next staging: NMS scratch.
 struct NmsOverlay {
     unsigned long long sup[kCand];  // by member position: bit i = member i of my class is earlier and overlaps me
@@ -125,6 +127,7 @@ struct NmsOverlay {
     uint8_t kept[kPad];             // by sorted position
     uint8_t ordm[kPad];             // sorted position -> member index inside its class
     unsigned short pair_base[kC + 4];  // pairs of all classes before c
+    uint8_t pair_cls[kPairTable];      // class of pair t, when the image has at most kPairTable pairs
 };
 static_assert(sizeof(NmsOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
 
@@ -137,7 +140,7 @@ static_assert(sizeof(NmsOverlay) <= sizeof(float2) * kHalfPairs, "overlay too la
 //   3. one lane per class replays the greedy scan over the bitmasks in rank order.
 // Returns n and the keep mask by sorted position.  A class with more than 64 members,
 // or a NaN threshold ("decode only": keep everything), takes rank_members + nms_rounds.
-template <int MODE>
+template <int MODE, bool PAIR_TABLE>
 __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const Mask128 &valid, double nms_thr, int lane,
                                                  int &n_out) {
     const int n = build_members(w, valid, lane);
@@ -163,11 +166,18 @@ __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const Mask128 &v
         no.sup[p] = 0;
         no.beaten[p] = 0;
     }
+    // class of every pair: with few pairs (the usual case) each class lane labels its own
+    // range; otherwise a lane walks the class boundaries as its pair index grows
+    const bool table = PAIR_TABLE && total <= kPairTable;  // measured: helps decode_nms, not map_update
+    if (table)
+        for (int u = 0, base = inc - np; u < np; ++u) no.pair_cls[base + u] = (uint8_t)lane;
     __syncwarp();
     int c = 0;
 #pragma unroll 1
     for (int t = lane; t < total; t += 32) {
-        while (t >= no.pair_base[c + 1]) ++c;
+        if (table) c = no.pair_cls[t];
+        else
+            while (t >= no.pair_base[c + 1]) ++c;
         const int u = t - no.pair_base[c];
         int j = (int)((1.0f + sqrtf((float)(8 * u + 1))) * 0.5f);  // row of the strict lower triangle
         j -= (j * (j - 1) / 2 > u);

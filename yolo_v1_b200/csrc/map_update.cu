@@ -128,7 +128,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(c + kD - 1));
             }
         int n;
-        const Mask128 keep = order_and_nms<YH_IOU_METRICS>(w, valid, nms_thr, lane, n);
+        const Mask128 keep = order_and_nms<YH_IOU_METRICS, false>(w, valid, nms_thr, lane, n);
         publish_keep(w, keep, lane);
         const bool lists = gt_raw != nullptr;
         if (rec_box != nullptr) {
