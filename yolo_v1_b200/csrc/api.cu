@@ -27,6 +27,18 @@ int check_launch(const char *what, int kernels_launched) {
     return 0;
 }
 
+constexpr int kTicketSlots = 256;
+__device__ unsigned g_tickets[kTicketSlots];
+static std::atomic<unsigned> g_ticket_next{0};
+
+unsigned *fresh_ticket(cudaStream_t stream) {
+    static unsigned *base = nullptr;
+    if (base == nullptr) cudaGetSymbolAddress((void **)&base, g_tickets);
+    unsigned *t = base + (g_ticket_next.fetch_add(1, std::memory_order_relaxed) % kTicketSlots);
+    cudaMemsetAsync(t, 0, sizeof(unsigned), stream);
+    return t;
+}
+
 }  // namespace yh
 
 extern "C" int yh_version(void) { return YH_VERSION; }

@@ -22,6 +22,10 @@ constexpr int kCand = kCells * kB;    // 98 candidates per image
 constexpr int kImgFloats = kCells * kD;  // 1470 floats = 5880 B per image
 
 void set_error(const char *fmt, ...);
+// A zeroed device counter for one launch's dynamic image schedule (api.cu): slots are handed
+// out round-robin from a ring, so launches in flight on different streams never share one,
+// and the slot is cleared on the launch's own stream.
+unsigned *fresh_ticket(cudaStream_t stream);
 int check_launch(const char *what, int kernels_launched = 1);
 
 inline bool shape_ok(int S, int B, int C) { return S == kS && B == kB && C == kC; }

@@ -41,18 +41,18 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
                   int32_t *__restrict__ n_keep, uint8_t *__restrict__ keep_k,
                   uint8_t *__restrict__ keep_cls, double *__restrict__ keep_conf,
                   double *__restrict__ keep_box, int32_t *__restrict__ n_cand,
-                  uint8_t *__restrict__ bad_range) {
+                  uint8_t *__restrict__ bad_range, unsigned *__restrict__ ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WarpWindow *windows = reinterpret_cast<WarpWindow *>(smem_raw);
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     WarpWindow &w = windows[wib];
     const int warps_total = gridDim.x * kWarpsPerCta;
 
-    for (int img = blockIdx.x * kWarpsPerCta + wib; img < N; img += warps_total) {
+    // first image by position, further ones from the ticket counter (see map_update.cu)
+    for (int img = blockIdx.x * kWarpsPerCta + wib; img < N;) {
+        unsigned next_ticket = 0;
+        if (lane == 0) next_ticket = atomicAdd(ticket, 1u);
         const float *pimg = pred + (size_t)img * kImgFloats;
-#ifndef YH_NO_PREFETCH
-        if (img + warps_total < N) prefetch_image(pimg + (size_t)warps_total * kImgFloats, lane);
-#endif
         bool bad = false;
         const Mask128 valid = decode_image(w, pimg, lane, conf_thr, bad_range != nullptr ? &bad : nullptr);
         if (bad_range != nullptr) {
@@ -114,6 +114,8 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             }
         }
         __syncwarp();
+        const unsigned drawn = __shfl_sync(kFull, next_ticket, 0);
+        img = drawn < (unsigned)N ? warps_total + (int)drawn : N;
     }
 }
 
@@ -131,7 +133,8 @@ static int launch(const float *pred, int N, double conf_thr, double nms_thr, int
     const int cap = 148 * kCtasPerSm;
     if (ctas > cap) ctas = cap;
     decode_nms_kernel<MODE><<<ctas, kWarpsPerCta * 32, smem, st>>>(
-        pred, N, conf_thr, nms_thr, order, n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad_range);
+        pred, N, conf_thr, nms_thr, order, n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad_range,
+        fresh_ticket(st));
     return check_launch("yh_decode_nms");
 }
 

@@ -76,8 +76,11 @@ __device__ __forceinline__ float min_mask(float self, float other) {
     return (self > other) ? 0.f : ((self == other) ? 0.5f : 1.f);
 }
 
+#ifndef YH_LOSS_MINBLOCKS
+#define YH_LOSS_MINBLOCKS 5
+#endif
 template <typename T>
-__global__ void __launch_bounds__(kTile)
+__global__ void __launch_bounds__(kTile, YH_LOSS_MINBLOCKS)
 loss_kernel(const typename Pair<T>::G *__restrict__ pred, const float2 *__restrict__ tgt,
             typename Pair<T>::G *__restrict__ grad, long long n_cells, float lambda_coord,
             float lambda_noobj, float inv_n, double *__restrict__ partials,

@@ -95,7 +95,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                   uint64_t *__restrict__ rec_flags, uint8_t *__restrict__ rec_k,
                   uint64_t *__restrict__ rec_box, int32_t *__restrict__ n_gt, uint8_t *__restrict__ gt_cell,
                   uint8_t *__restrict__ gt_cls, float4 *__restrict__ gt_raw,
-                  int32_t *__restrict__ gt_count) {
+                  int32_t *__restrict__ gt_count, unsigned *__restrict__ ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WarpWindow *windows = reinterpret_cast<WarpWindow *>(smem_raw);
     __shared__ int gt_hist[4 * kC];
@@ -109,15 +109,17 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
     if (threadIdx.x < YH_MAX_THRESHOLDS) s_thr[threadIdx.x] = thr.t[threadIdx.x];
     __syncthreads();
 
-    for (int img = blockIdx.x * kWarpsPerCtaM + wib; img < N; img += warps_total) {
+    // A warp's first image is fixed by its position; every further one is taken from a
+    // global ticket counter, so warps that drew cheap images take more of them and the
+    // grid drains evenly.  The ticket for the next round is drawn a whole image ahead.
+    for (int img = blockIdx.x * kWarpsPerCtaM + wib; img < N;) {
+        unsigned next_ticket = 0;
+        if (lane == 0) next_ticket = atomicAdd(ticket, 1u);
         const float *pimg = pred + (size_t)img * kImgFloats, *timg = tgt + (size_t)img * kImgFloats;
         // slot-0 confidence of my two target cells: in flight while the predictions are decoded
         const float tconf0 = __ldg(timg + lane * kD + 4);
         const float tconf1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 4);
         // ---- predictions: decode, order, NMS
-#ifndef YH_NO_PREFETCH
-        if (img + warps_total < N) prefetch_image(pimg + (size_t)warps_total * kImgFloats, lane);
-#endif
         const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr);
         // object cells of the target (rare): pull their lines towards L2 while NMS runs
 #pragma unroll
@@ -269,6 +271,8 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             rec_flags[o] = mo.flags[p] | ((uint64_t)c << 56);
             rec_k[o] = (uint8_t)k;
         }
+        const unsigned drawn = __shfl_sync(kFull, next_ticket, 0);
+        img = drawn < (unsigned)N ? warps_total + (int)drawn : N;
     }
 
     __syncthreads();
@@ -353,9 +357,10 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
     int ctas = (N + kWarpsPerCtaM - 1) / kWarpsPerCtaM;
     const int cap = 148 * kCtasPerSmM;
     if (ctas > cap) ctas = cap;
+    unsigned *ticket = fresh_ticket((cudaStream_t)stream);
     map_update_kernel<<<ctas, kWarpsPerCtaM * 32, smem, (cudaStream_t)stream>>>(
         pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, (uint64_t *)rec_box, n_gt, gt_cell,
-        gt_cls, (float4 *)gt_raw, gt_count);
+        gt_cls, (float4 *)gt_raw, gt_count, ticket);
     return check_launch("yh_map_update");
 }
 
