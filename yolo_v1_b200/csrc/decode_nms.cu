@@ -114,6 +114,7 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
             }
         }
         __syncwarp();
+        asm volatile("" : "+r"(next_ticket)::"memory");  // keep the (slow) ticket read down here
         const unsigned drawn = __shfl_sync(kFull, next_ticket, 0);
         img = drawn < (unsigned)N ? warps_total + (int)drawn : N;
     }

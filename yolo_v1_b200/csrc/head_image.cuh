@@ -148,8 +148,12 @@ __device__ __forceinline__ unsigned spread16(unsigned x) {
 // k = 2*cell + b.  Fills w.cand for every candidate above conf_thr and returns the
 // validity mask (indexed by k).  bad (optional) reports a kept candidate outside
 // [0,1] (schemas.py:9-16,88).
+// tgt_img / tconf0 / tconf1 (optional): the target image and the slot-0 confidences of this
+// lane's two target cells; object cells get their lines prefetched towards L2 between the
+// two halves, a good while before the caller parses them.
 __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__restrict__ img, int lane,
-                                                double conf_thr, bool *bad) {
+                                                double conf_thr, bool *bad, const float *__restrict__ tgt_img = nullptr,
+                                                float tconf0 = 0.f, float tconf1 = 0.f) {
     const float *st = reinterpret_cast<const float *>(w.stage);
     Mask128 valid = {0, 0, 0, 0};
     bool any_bad = false;
@@ -188,6 +192,15 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
         const unsigned m0 = __ballot_sync(kFull, ok[0]), m1 = __ballot_sync(kFull, ok[1]);
         valid.set_word(2 * cs, spread16(m0 & 0xffffu) | (spread16(m1 & 0xffffu) << 1));
         valid.set_word(2 * cs + 1, spread16(m0 >> 16) | (spread16(m1 >> 16) << 1));
+        if (cs == 0 && tgt_img != nullptr) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                if (lane + 32 * h < kCells && (h ? tconf1 : tconf0) > 0.f) {
+                    const float *c = tgt_img + (lane + 32 * h) * kD;  // 120 B: may straddle two lines
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(c));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(c + kD - 1));
+                }
+        }
     }
     if (bad != nullptr) *bad = any_bad;
     __syncwarp();

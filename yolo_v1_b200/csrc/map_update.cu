@@ -120,15 +120,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         const float tconf0 = __ldg(timg + lane * kD + 4);
         const float tconf1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 4);
         // ---- predictions: decode, order, NMS
-        const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr);
-        // object cells of the target (rare): pull their lines towards L2 while NMS runs
-#pragma unroll
-        for (int cs = 0; cs < 2; ++cs)
-            if (lane + 32 * cs < kCells && (cs ? tconf1 : tconf0) > 0.f) {
-                const float *c = timg + (lane + 32 * cs) * kD;  // 120 B: may straddle two lines
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(c));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(c + kD - 1));
-            }
+        const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr, timg, tconf0, tconf1);
         int n;
         const Mask128 keep = order_and_nms<YH_IOU_METRICS, false>(w, valid, nms_thr, lane, n);
         publish_keep(w, keep, lane);
@@ -271,6 +263,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             rec_flags[o] = mo.flags[p] | ((uint64_t)c << 56);
             rec_k[o] = (uint8_t)k;
         }
+        asm volatile("" : "+r"(next_ticket)::"memory");  // keep the (slow) ticket read down here
         const unsigned drawn = __shfl_sync(kFull, next_ticket, 0);
         img = drawn < (unsigned)N ? warps_total + (int)drawn : N;
     }
