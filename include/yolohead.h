@@ -183,6 +183,16 @@ int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M, 
                          uint64_t *out_flags, int64_t *part_count, void *workspace,
                          size_t workspace_bytes, void *stream);
 
+/* ------------------------------------------------------ target encoder ----
+ * Replaces VOCDetectionYOLO._encode_target (src/yolo/dataset.py:487-532) for a batch:
+ * image n owns boxes [offsets[n], offsets[n+1]) of `boxes` (fp64 x_center, y_center, w, h,
+ * normalised) and `cls`; out[n] is its (S, S, B*5 + C) fp32 target: the first box of a
+ * cell in list order fills slot 0 (cell-relative x, y; w; h; confidence 1) and the class
+ * one-hot, later boxes of the same cell are dropped.  bad[n] (nullable) = 1 where the
+ * reference would raise (non-finite centre, cell or class index out of range). */
+int yh_encode_targets(const double *boxes, const int32_t *cls, const int64_t *offsets, int N, int S,
+                      int B, int C, float *out, uint8_t *bad, void *stream);
+
 /* ------------------------------------------- list-form entry points ----
  * The reference's helpers also accept arbitrary Python lists (tests call
  * _apply_nms / non_max_suppression / _calculate_iou / iou on hand-built boxes,

@@ -5,7 +5,7 @@ Run in the build container only (the GPU box has no /root/reference):
     python tests/golden/make_golden.py            # small fixtures (seconds..minutes)
     python tests/golden/make_golden.py --big      # + the 4,952-image compute() case (slow)
 
-Outputs (committed): tests/golden/loss.npz, decode_nms.npz, map_small.npz, map_big.npz.
+Outputs (committed): tests/golden/loss.npz, decode_nms.npz, map_small.npz, map_big.npz, encode.npz.
 The reference is imported, never copied; only its outputs are stored.
 """
 from __future__ import annotations
@@ -291,6 +291,41 @@ def gen_map_big(out, n, name):
     print(name, "mAP50:95 =", vals[keys.index("mAP50:95")])
 
 
+def encode_cases():
+    """(name, bboxes per sample, class ids per sample) for the target-encoder fixtures: VOC-like
+    scenes, several boxes in one cell (first wins), boxes on the right/bottom edge (clamped to the
+    last cell), slightly negative centres (Python's negative-index wrap), negative class ids."""
+    rng = np.random.default_rng(20240611)
+    cases = []
+    for n_obj in (0, 1, 3, 8, 40):
+        boxes = [[float(v) for v in rng.random(4)] for _ in range(n_obj)]
+        cases.append((f"random{n_obj}", boxes, [int(c) for c in rng.integers(0, 20, n_obj)]))
+    cases.append(("same_cell", [[0.50, 0.50, 0.2, 0.3], [0.52, 0.51, 0.1, 0.1], [0.55, 0.56, 0.4, 0.4]], [3, 4, 5]))
+    cases.append(("edges", [[1.0, 1.0, 0.1, 0.1], [0.999999, 0.0, 0.2, 0.2], [0.0, 1.0, 0.3, 0.3], [1.2, 0.5, 0.1, 0.1]],
+                  [0, 19, 7, 9]))
+    cases.append(("negative", [[-0.05, 0.3, 0.1, 0.1], [0.3, -0.2, 0.2, 0.2], [-0.99, -0.99, 0.1, 0.1]], [1, 2, 3]))
+    cases.append(("negative_class", [[0.2, 0.2, 0.1, 0.1], [0.7, 0.7, 0.1, 0.1]], [-1, -20]))
+    cases.append(("thirds", [[1 / 3, 2 / 3, 0.1, 0.1], [1 / 7, 6 / 7, 0.2, 0.2], [3 / 7, 3 / 7, 0.3, 0.3]], [5, 6, 7]))
+    return cases
+
+
+def gen_encode(out):
+    """VOCDetectionYOLO._encode_target (dataset.py:487-532) run unbound on a stand-in self."""
+    from types import SimpleNamespace
+
+    from yolo.dataset import VOCDetectionYOLO  # reference
+
+    fake = SimpleNamespace(S=S, B=B, C=C)
+    names = []
+    for name, boxes, cls in encode_cases():
+        t = VOCDetectionYOLO._encode_target(fake, boxes, cls)
+        out[f"{name}/boxes"] = np.asarray(boxes, dtype=np.float64).reshape(-1, 4)
+        out[f"{name}/cls"] = np.asarray(cls, dtype=np.int64)
+        out[f"{name}/target"] = t.numpy()
+        names.append(name)
+    out["names"] = np.asarray(names)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--big", action="store_true")
@@ -298,7 +333,7 @@ def main():
     a = ap.parse_args()
     warnings.simplefilter("ignore")
     torch.set_num_threads(1)
-    jobs = {"loss": gen_loss, "decode_nms": gen_decode_nms, "map_small": gen_map_small}
+    jobs = {"loss": gen_loss, "decode_nms": gen_decode_nms, "map_small": gen_map_small, "encode": gen_encode}
     for name, fn in jobs.items():
         if a.only and a.only != name:
             continue

@@ -351,3 +351,44 @@ def test_partition_records_is_a_stable_partition(m, parts):
     assert cnt.tolist() == [int((own == p).sum()) for p in range(parts)]
     assert np.array_equal(k[:m].cpu().numpy(), key[perm])
     assert np.array_equal(f[:m].cpu().numpy(), flg[perm])
+
+
+# ----------------------------------------------------------------------------- target encoder
+@pytest.mark.gpu
+def test_encode_targets_matches_reference_golden(golden):
+    from yolo_v1_b200 import targets
+
+    g = golden("encode")
+    names = [str(n) for n in g["names"]]
+    boxes = [g[f"{n}/boxes"].tolist() for n in names]
+    cls = [g[f"{n}/cls"].tolist() for n in names]
+    out = targets.encode_targets(boxes, cls, device=DEV).cpu().numpy()
+    for i, n in enumerate(names):
+        assert out[i].tobytes() == g[f"{n}/target"].tobytes(), n
+    one = targets.encode_target(boxes[3], cls[3], device=DEV).cpu().numpy()
+    assert one.tobytes() == g[f"{names[3]}/target"].tobytes()
+
+
+@pytest.mark.gpu
+def test_encode_targets_matches_oracle_and_raises_like_the_reference():
+    from oracle import encode_oracle
+    from yolo_v1_b200 import targets
+
+    rng = np.random.default_rng(5)
+    boxes = [[[float(v) for v in rng.random(4)] for _ in range(int(k))] for k in rng.integers(0, 60, 300)]
+    cls = [[int(c) for c in rng.integers(0, 20, len(b))] for b in boxes]
+    out = targets.encode_targets(boxes, cls, device=DEV).cpu().numpy()
+    for i in range(len(boxes)):
+        assert out[i].tobytes() == encode_oracle.encode_target(boxes[i], cls[i]).tobytes(), i
+    # feeds the loss / metric kernels directly
+    m = mAPMetric(num_classes=20)
+    t = torch.from_numpy(out[:8]).to(DEV)
+    m.update(t.clone(), t)                      # a target used as its own prediction: every kept box is a TP
+    res = m.compute()
+    assert float(res["precision"]) == pytest.approx(1.0, abs=1e-5) and float(res["recall"]) > 0.3
+    for bad_boxes, bad_cls in ([[[0.5, -1.5, 0.1, 0.1]]], [[0]]), ([[[float("nan"), 0.5, 0.1, 0.1]]], [[0]]), \
+            ([[[0.5, 0.5, 0.1, 0.1]]], [[20]]):
+        with pytest.raises((IndexError, ValueError)):
+            encode_oracle.encode_target(bad_boxes[0], bad_cls[0])
+        with pytest.raises((IndexError, ValueError)):
+            targets.encode_targets(bad_boxes, bad_cls, device=DEV)

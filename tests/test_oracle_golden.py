@@ -99,3 +99,12 @@ def test_nms_known_answer():
     keep = c_oracle.nms_lists([0, 0, 1], [0.9, 0.8, 0.85],
                               [(0.5, 0.5, 0.2, 0.2), (0.52, 0.52, 0.2, 0.2), (0.7, 0.7, 0.15, 0.15)], 0.5)
     assert list(keep) == [0, 2]
+
+
+def test_encode_oracle_matches_reference(golden):
+    from oracle import encode_oracle
+
+    g = golden("encode")
+    for name in [str(n) for n in g["names"]]:
+        got = encode_oracle.encode_target(g[f"{name}/boxes"].tolist(), g[f"{name}/cls"].tolist())
+        assert got.tobytes() == g[f"{name}/target"].tobytes(), name

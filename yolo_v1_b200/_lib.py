@@ -40,6 +40,7 @@ SIGNATURES = {
     "yh_ap_reduce": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_partition_workspace_bytes": (_sz, [_i64]),
     "yh_partition_records": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "yh_encode_targets": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "yh_iou_pairs": (_i, [_vp, _vp, _i64, _i, _vp, _vp]),
     "yh_nms_lists": (_i, [_vp, _i, _vp, _vp, _vp, _d, _i, _i, _vp, _vp, _i, _vp]),
     "yh_match_lists": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp]),
