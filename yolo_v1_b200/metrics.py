@@ -129,7 +129,10 @@ class mAPMetric:
     # ------------------------------------------------------------------ update
     def update(self, predictions: torch.Tensor, targets: torch.Tensor):
         """Accumulate a batch: predictions and targets of shape (batch, S, S, B*5 + C)."""
-        _lib.require_cuda(predictions, "predictions")
+        # the kernels run on CUDA only; host tensors (the reference's own tests pass them) are
+        # copied to the GPU first -- with no CUDA device this raises, there is no CPU path
+        if not predictions.is_cuda:
+            predictions = predictions.to(_cuda_device(self._device))
         dev = predictions.device
         targets = targets.to(dev)
         if self._gt_count is None or self._device != dev:
@@ -293,6 +296,8 @@ class mAPMetric:
     # --------------------------------------------------- helpers the reference exposes
     def _parse_predictions(self, pred: torch.Tensor) -> List[Tuple[int, float, Tuple[float, float, float, float]]]:
         """(S,S,B*5+C) tensor -> [(class_id, confidence, (x, y, w, h))] in cell/box order (metrics.py:173-218)."""
+        if not pred.is_cuda:
+            pred = pred.to(_cuda_device(self._device))
         r = head.decode_nms(pred, self.conf_threshold, float("nan"), head.IOU_METRICS, head.ORDER_CLASS_GROUPED,
                             self.S, self.B, self.num_classes)
         n = int(r.n_keep[0].item())
@@ -305,6 +310,8 @@ class mAPMetric:
 
     def _parse_ground_truth(self, target: torch.Tensor) -> List[Tuple[int, Tuple[float, float, float, float]]]:
         """(S,S,B*5+C) target -> [(class_id, (x, y, w, h))] (metrics.py:220-256)."""
+        if not target.is_cuda:
+            target = target.to(_cuda_device(self._device))
         t = head._check_pred(target, "target", self.S, self.B, self.num_classes)
         dev, G = t.device, self.S * self.S
         n_gt = torch.zeros(1, dtype=torch.int32, device=dev)
