@@ -183,6 +183,43 @@ int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M, 
                          uint64_t *out_flags, int64_t *part_count, void *workspace,
                          size_t workspace_bytes, void *stream);
 
+/* -------------------------------- fused partition + exchange over peer memory ----
+ * The same stable partition, with each run written straight into its owner's receive
+ * buffer through peer-mapped memory (NVLink / NVSwitch): partition and all-to-all are one
+ * kernel and the run lengths never visit the host.  There is no reference counterpart
+ * (the reference is single-process); it serves DistributedMAP.compute().
+ *
+ * Peer blocks.  yh_peer_alloc is the one allocating call of this library (a block other
+ * processes map must come from cudaMalloc): it returns a zeroed device block and its
+ * 64-byte CUDA IPC handle; the other ranks of the box map it with yh_peer_open.  A rank's
+ * block is yh_peer_block_bytes(capacity) long: control words, then capacity keys at
+ * yh_peer_key_offset and capacity flag words at yh_peer_flags_offset.
+ *
+ * yh_exchange_records (collective over `world` ranks, every rank with the same capacity
+ * and the same `epoch` > 0, which must grow by one per call): peer_block_host[r] is rank
+ * r's block as mapped in THIS process (the rank's own allocation at [rank]).  On return
+ * (stream order) this rank's block holds, in rank order and inside a rank in input
+ * order, every record whose class this rank owns; info[0] = their count (use it as M_dev
+ * of yh_ap_reduce with M = capacity), info[1] = images summed over ranks, info[2] = 1 if a
+ * receive buffer would have overflowed (nothing was moved; identical on every rank --
+ * fall back to the NCCL exchange and re-create larger blocks), info[3] = 1 if a wait
+ * on a peer gave up after 4 s.  gt_count_global[4*C] = the ranks' gt_count_local summed.
+ * Between two calls the ranks must be ordered by some collective that completes after the
+ * receive buffer was consumed (DistributedMAP's all-reduce of the AP table is one). */
+int yh_peer_alloc(size_t bytes, void **ptr, void *handle64);
+int yh_peer_open(const void *handle64, void **ptr);
+int yh_peer_close(void *ptr);
+int yh_peer_free(void *ptr);
+size_t yh_peer_block_bytes(int64_t capacity);
+size_t yh_peer_key_offset(int64_t capacity);
+size_t yh_peer_flags_offset(int64_t capacity);
+size_t yh_exchange_workspace_bytes(int64_t M);
+int yh_exchange_records(const uint64_t *key, const uint64_t *flags, int64_t M, const int64_t *M_dev,
+                        const uint8_t *owner_of_class_host, int C, int world, int rank,
+                        void *const *peer_block_host, int64_t capacity, unsigned epoch,
+                        const int32_t *gt_count_local, int64_t n_images_local, int32_t *gt_count_global,
+                        int64_t *info, void *workspace, size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------------------ target encoder ----
  * Replaces VOCDetectionYOLO._encode_target (src/yolo/dataset.py:487-532) for a batch:
  * image n owns boxes [offsets[n], offsets[n+1]) of `boxes` (fp64 x_center, y_center, w, h,

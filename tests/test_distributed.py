@@ -118,7 +118,7 @@ def _gpu_worker(rank, world, port, n, mode, q):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["gather", "class_shard"])
+@pytest.mark.parametrize("mode", ["gather", "class_shard", "peer"])
 def test_sharded_metric_equals_single_gpu_and_oracle(mode):
     from oracle import c_oracle, results
     from yolo_v1_b200 import mAPMetric, synth
@@ -148,3 +148,75 @@ def test_sharded_metric_equals_single_gpu_and_oracle(mode):
         for k in want:
             assert got[r][k] == want[k], (mode, r, k, got[r][k], want[k])     # bit-exact vs one GPU
             assert abs(got[r][k] - float(orc[k])) <= 1e-12 * max(1.0, abs(float(orc[k]))), (k, got[r][k], orc[k])
+
+
+def _peer_growth_worker(rank, world, port, backend, sizes, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dev = torch.device("cuda", rank % torch.cuda.device_count())
+    torch.cuda.set_device(dev)
+    kw = {"device_id": dev} if backend == "nccl" else {}
+    dist.init_process_group(backend, rank=rank, world_size=world, **kw)
+    try:
+        from yolo_v1_b200 import mAPMetric, synth
+
+        dm = D.DistributedMAP(mAPMetric(num_classes=20, conf_threshold=0.01), mode="peer")
+        out = []
+        for n in sizes:
+            tgt = synth.make_targets(n, seed=n, p_obj=0.055, size_mix=True)
+            pred = synth.make_preds(n, "correlated", seed=n, targets=tgt)
+            lo, hi = D.shard_range(n, rank, world)
+            dm.reset()
+            for s in range(lo, hi, 128):
+                dm.update(pred[s:min(hi, s + 128)].to(dev), tgt[s:min(hi, s + 128)].to(dev))
+            res = dm.compute()
+            out.append(({k: float(v) for k, v in res.items()}, dm.peer_fallbacks, dm._peer.capacity))
+        dm.close()
+        q.put((rank, out))
+    finally:
+        dist.destroy_process_group()
+
+
+def _run_peer_growth(world, backend, sizes):
+    from yolo_v1_b200 import mAPMetric, synth
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_growth_worker, args=(r, world, port, backend, sizes, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(60)
+    want = []
+    for n in sizes:
+        tgt = synth.make_targets(n, seed=n, p_obj=0.055, size_mix=True)
+        pred = synth.make_preds(n, "correlated", seed=n, targets=tgt)
+        single = mAPMetric(num_classes=20, conf_threshold=0.01)
+        single.update(pred.cuda(), tgt.cuda())
+        want.append({k: float(v) for k, v in single.compute().items()})
+    return got, want
+
+
+@pytest.mark.gpu
+def test_peer_blocks_overflow_falls_back_and_grows():
+    """The receive blocks are sized by the first compute(); a later, larger set overflows them:
+    that call takes the NCCL exchange (same bits) and the blocks are re-created larger."""
+    world = 2 if torch.cuda.device_count() >= 2 else 1
+    got, want = _run_peer_growth(world, "nccl", (40, 600, 600))   # 600 does not fit blocks sized for 40
+    for r in range(world):
+        (r0, f0, c0), (r1, f1, c1), (r2, f2, c2) = got[r]
+        assert (f0, f1, f2) == (0, 1, 1) and c1 > c0 and c2 == c1, (f0, f1, f2, c0, c1, c2)
+        for res, w in zip((r0, r1, r2), want):
+            assert res == w
+
+
+@pytest.mark.gpu
+def test_peer_exchange_between_two_processes_sharing_one_gpu():
+    """CUDA IPC mapping + the flag protocol with two ranks even on a one-GPU box (gloo carries
+    the handles; the kernels of the two processes time-slice the device)."""
+    got, want = _run_peer_growth(2, "gloo", (600, 333, 40))
+    for r in range(2):
+        assert [f for _, f, _ in got[r]] == [0, 0, 0]
+        for (res, _, _), w in zip(got[r], want):
+            assert res == w

@@ -11,10 +11,6 @@ n = 65536
 tgt = synth.make_targets(n, seed=1234 + rank, p_obj=0.055, size_mix=True)
 pred = synth.make_preds(n, "uniform", seed=1234 + rank, targets=tgt).to(dev); tgt = tgt.to(dev)
 metric = D.DistributedMAP(mAPMetric(20, conf_threshold=0.3), mode=sys.argv[1] if len(sys.argv) > 1 else "class_shard")
-try:
-    import symm  # noqa
-except Exception:
-    pass
 for it in range(6):
     metric.reset(); metric.update(pred, tgt)
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
@@ -24,6 +20,10 @@ for it in range(6):
     t1 = time.perf_counter()
     if rank == 0 and it >= 3:
         print(f"compute() {1e3 * (t1 - t0):.3f} ms")
+if metric.mode == "peer":
+    if rank == 0:
+        print("peer capacity", metric._peer.capacity, "fallbacks", metric.peer_fallbacks)
+    metric.close(); dist.destroy_process_group(); sys.exit(0)
 # phase split: host enqueue time / time until the device is idle, per phase
 m = metric.metric
 def phase(fn):

@@ -11,6 +11,8 @@
 //
 // Three streaming launches over M records (16 B each): per-tile run counts, a scan
 // over tiles, and the scatter (each record read twice, written once).
+#include <string.h>
+
 #include "common.cuh"
 
 namespace yh {
@@ -160,6 +162,245 @@ part_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
     }
 }
 
+
+// ===================================================================== peer exchange
+// yh_exchange_records: the same stable partition, but every run is written straight
+// into its owner's receive buffer through peer-mapped memory (NVLink / NVSwitch) --
+// the partition and the all-to-all are one kernel, and the run lengths never visit the
+// host.  Per rank one peer-mapped block holds a PeerCtl and the receive arrays:
+//
+//   publish   row[me][d] = records I send to rank d, my ground-truth counts and image
+//             count, stored into EVERY rank's PeerCtl; then ready[me] = epoch (release.sys)
+//   scatter   every CTA waits for all ready[] flags (acquire.sys), derives from the full
+//             R x R matrix where my run starts in each receive buffer
+//             (sum of row[r][d] over r < me: rank order = image order, what the
+//             reference's stable sort breaks confidence ties by), orders its 1,024-record
+//             tile by owner in shared memory and writes each run with consecutive lanes on
+//             consecutive remote addresses; the last CTA to finish sets done[me] = epoch
+//             on every rank
+//   finish    one CTA waits for all done[] flags, then publishes the received record
+//             count, the summed ground-truth counts and the global image count for
+//             yh_ap_reduce (M_dev) -- still no host read.
+//
+// If a receive buffer would overflow (known to all ranks from the same matrix before a
+// single record moves) nothing is scattered, info[2] is set on every rank and the host
+// falls back to the NCCL exchange and grows the buffers.  Waits give up after a few
+// seconds (info[3]) instead of hanging the GPU.
+
+constexpr int kGtWords = 4 * 32 + 2;  // 4 subsets x (C <= 32) counts + image count (2 words)
+
+struct PeerCtl {
+    unsigned ready[kMaxParts];
+    unsigned done[kMaxParts];
+    long long row[kMaxParts][kMaxParts];
+    int gt[kMaxParts][kGtWords];
+};
+
+struct PeerTable {
+    PeerCtl *ctl[kMaxParts];
+    uint64_t *key[kMaxParts];
+    uint64_t *flags[kMaxParts];
+};
+
+struct ExchangeLocal {        // head of the workspace, zeroed per call
+    unsigned finished_ctas;
+    unsigned timed_out;
+    unsigned overflow;
+    unsigned pad;
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long now_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+constexpr unsigned long long kWaitLimitNs = 4000000000ull;
+
+// true once *flag == epoch; false if the limit ran out
+__device__ __forceinline__ bool wait_flag(const unsigned *flag, unsigned epoch) {
+    if (ld_acquire_sys(flag) == epoch) return true;
+    const unsigned long long t0 = now_ns();
+    while (ld_acquire_sys(flag) != epoch) {
+        __nanosleep(200);
+        if (now_ns() - t0 > kWaitLimitNs) return false;
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(1024)
+peer_publish(const __grid_constant__ PeerTable peers, int world, int me, unsigned epoch,
+             const int64_t *__restrict__ part_count, const int32_t *__restrict__ gt_local, int n_gt,
+             long long n_images) {
+    const int tid = threadIdx.x;
+    const int per = world + n_gt + 2;  // words of one rank's message
+    for (int q = tid; q < world * per; q += blockDim.x) {
+        const int d = q / per, i = q - d * per;
+        PeerCtl *c = peers.ctl[d];
+        if (i < world)
+            c->row[me][i] = part_count[i];
+        else if (i < world + n_gt)
+            c->gt[me][i - world] = gt_local[i - world];
+        else
+            c->gt[me][kGtWords - 2 + (i - world - n_gt)] = (int)((unsigned long long)n_images >> (32 * (i - world - n_gt)));
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < world) st_release_sys(&peers.ctl[tid]->ready[me], epoch);
+}
+
+__global__ void __launch_bounds__(kPartThreads)
+peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flags, int64_t Mcap,
+             const int64_t *__restrict__ Mdev, const __grid_constant__ OwnerTable tab,
+             const unsigned *__restrict__ tile_pre, const __grid_constant__ PeerTable peers, int world, int me,
+             unsigned epoch, long long capacity, ExchangeLocal *__restrict__ loc) {
+    __shared__ unsigned s_w[kPartWarps][kMaxParts];  // per-warp counts, then running cursors
+    __shared__ long long dst_base[kMaxParts];        // where my run starts in rank d's receive buffer
+    __shared__ unsigned tile_start[kMaxParts + 1];   // tile-local start of each part
+    __shared__ uint64_t s_key[kPartTile], s_flg[kPartTile];
+    __shared__ int s_state;
+    const int64_t M = part_count_of(Mcap, Mdev);
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const PeerCtl *mine = peers.ctl[me];
+    if (tid == 0) s_state = 0;
+    s_w[wp][lane] = 0;
+    __syncthreads();
+    if (tid < world && !wait_flag(&mine->ready[tid], epoch)) s_state = 1;
+    __syncthreads();
+    if (s_state) {
+        if (tid == 0) loc->timed_out = 1;
+        return;
+    }
+    if (tid < kMaxParts) {
+        long long before = 0, total = 0;
+        if (tid < world)
+            for (int r = 0; r < world; ++r) {
+                const long long c = mine->row[r][tid];
+                if (r < me) before += c;
+                total += c;
+            }
+        dst_base[tid] = before;
+        if (total > capacity) s_state = 2;
+    }
+    __syncthreads();
+    const bool overflow = s_state == 2;
+    if (overflow && tid == 0 && blockIdx.x == 0) loc->overflow = 1;
+    if (!overflow) {
+        const int64_t first = (int64_t)blockIdx.x * kPartTile + wp * kPartSpan + lane;
+        const unsigned lt = (1u << lane) - 1u;
+        uint64_t k[kPartRounds], f[kPartRounds];
+        int part[kPartRounds];
+#pragma unroll
+        for (int r = 0; r < kPartRounds; ++r) {
+            const int64_t idx = first + 32 * r;
+            const bool ok = idx < M;
+            k[r] = ok ? __ldg(key + idx) : 0;
+            f[r] = ok ? __ldg(flags + idx) : 0;
+            part[r] = ok ? owner_of(tab, f[r]) : -1;
+            const unsigned act = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const unsigned peers_m = __match_any_sync(act, part[r]);
+                if ((peers_m & lt) == 0) s_w[wp][part[r]] += __popc(peers_m);
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        if (tid < kMaxParts) {  // per part: exclusive prefix over the warps (tile-local)
+            unsigned run = 0;
+#pragma unroll
+            for (int q = 0; q < kPartWarps; ++q) {
+                const unsigned c = s_w[q][tid];
+                s_w[q][tid] = run;
+                run += c;
+            }
+            // tile_start = exclusive scan of the part totals over the parts (one warp)
+            unsigned inc = run;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += u;
+            }
+            tile_start[tid] = inc - run;
+            if (tid == kMaxParts - 1) tile_start[kMaxParts] = inc;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < kPartRounds; ++r) {
+            const bool ok = part[r] >= 0;
+            const unsigned act = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const unsigned peers_m = __match_any_sync(act, part[r]);
+                const unsigned cur = s_w[wp][part[r]];
+                const unsigned pos = tile_start[part[r]] + cur + __popc(peers_m & lt);
+                s_key[pos] = k[r];
+                s_flg[pos] = f[r];
+                __syncwarp(act);
+                if ((peers_m & lt) == 0) s_w[wp][part[r]] = cur + __popc(peers_m);
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        // consecutive threads -> consecutive addresses of one run in one receive buffer
+        const unsigned n_tile = tile_start[kMaxParts];
+        for (unsigned i = tid; i < n_tile; i += kPartThreads) {
+            int p = 0;
+#pragma unroll
+            for (int h = kMaxParts / 2; h > 0; h >>= 1)
+                if (tile_start[p + h] <= i) p += h;
+            const long long pos = dst_base[p] + tile_pre[(size_t)blockIdx.x * kMaxParts + p] + (i - tile_start[p]);
+            peers.key[p][pos] = s_key[i];
+            peers.flags[p][pos] = s_flg[i];
+        }
+    }
+    // completion: my stores are visible system-wide before the count moves; the last CTA raises done[me]
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) s_state = (atomicAdd(&loc->finished_ctas, 1u) == gridDim.x - 1) ? 3 : 0;
+    __syncthreads();
+    if (s_state == 3 && tid < world) {
+        __threadfence_system();
+        st_release_sys(&peers.ctl[tid]->done[me], epoch);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+peer_finish(const __grid_constant__ PeerTable peers, int world, int me, unsigned epoch, int n_gt,
+            const ExchangeLocal *__restrict__ loc, int32_t *__restrict__ gt_global, int64_t *__restrict__ info) {
+    __shared__ int s_bad;
+    const int tid = threadIdx.x;
+    const PeerCtl *mine = peers.ctl[me];
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
+    if (tid < world && !wait_flag(&mine->done[tid], epoch)) s_bad = 1;
+    __syncthreads();
+    const bool bad = s_bad || loc->timed_out;
+    const bool overflow = loc->overflow != 0;
+    for (int i = tid; i < n_gt; i += blockDim.x) {
+        int s = 0;
+        for (int r = 0; r < world; ++r) s += mine->gt[r][i];
+        gt_global[i] = s;
+    }
+    if (tid == 0) {
+        long long total = 0, images = 0;
+        for (int r = 0; r < world; ++r) {
+            total += mine->row[r][me];
+            images += (long long)(((unsigned long long)(unsigned)mine->gt[r][kGtWords - 1] << 32) |
+                                  (unsigned)mine->gt[r][kGtWords - 2]);
+        }
+        info[0] = (bad || overflow) ? 0 : total;
+        info[1] = images;
+        info[2] = overflow ? 1 : 0;
+        info[3] = bad ? 1 : 0;
+    }
+}
+
 }  // namespace yh
 
 using namespace yh;
@@ -213,4 +454,156 @@ extern "C" int yh_partition_records(const uint64_t *key, const uint64_t *flags, 
     part_scan<<<n_parts, 1024, 0, st>>>(tile_cnt, ntiles, part_count);
     part_scatter<<<ntiles, kPartThreads, 0, st>>>(key, flags, M, M_dev, tab, tile_cnt, part_count, n_parts, out_key, out_flags);
     return check_launch("yh_partition_records", 3);
+}
+
+// ------------------------------------------------------------------ peer-mapped memory
+// The one place this library allocates: a block other processes can map must come from
+// cudaMalloc (not from the caller's caching allocator) to be exportable as an IPC handle.
+extern "C" int yh_peer_alloc(size_t bytes, void **ptr, void *handle64) {
+    if (!ptr || !handle64 || bytes == 0) {
+        set_error("yh_peer_alloc: bad argument");
+        return YH_ERR_BAD_ARG;
+    }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e == cudaSuccess) e = cudaMemset(p, 0, bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        set_error("yh_peer_alloc(%zu): %s", bytes, cudaGetErrorString(e));
+        if (p) cudaFree(p);
+        cudaGetLastError();
+        return (int)e;
+    }
+    memcpy(handle64, &h, 64);
+    *ptr = p;
+    return 0;
+}
+
+extern "C" int yh_peer_open(const void *handle64, void **ptr) {
+    if (!ptr || !handle64) {
+        set_error("yh_peer_open: bad argument");
+        return YH_ERR_BAD_ARG;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void *p = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        set_error("yh_peer_open: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        return (int)e;
+    }
+    *ptr = p;
+    return 0;
+}
+
+extern "C" int yh_peer_close(void *ptr) {
+    const cudaError_t e = ptr ? cudaIpcCloseMemHandle(ptr) : cudaSuccess;
+    if (e != cudaSuccess) {
+        set_error("yh_peer_close: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        return (int)e;
+    }
+    return 0;
+}
+
+extern "C" int yh_peer_free(void *ptr) {
+    const cudaError_t e = ptr ? cudaFree(ptr) : cudaSuccess;
+    if (e != cudaSuccess) {
+        set_error("yh_peer_free: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        return (int)e;
+    }
+    return 0;
+}
+
+// Layout of a rank's peer block: PeerCtl | key[capacity] | flags[capacity]
+extern "C" size_t yh_peer_block_bytes(int64_t capacity) {
+    if (capacity < 0) return 0;
+    return part_up256(sizeof(PeerCtl)) + 2 * part_up256(sizeof(uint64_t) * (size_t)capacity);
+}
+extern "C" size_t yh_peer_key_offset(int64_t capacity) {
+    (void)capacity;
+    return part_up256(sizeof(PeerCtl));
+}
+extern "C" size_t yh_peer_flags_offset(int64_t capacity) {
+    return part_up256(sizeof(PeerCtl)) + part_up256(sizeof(uint64_t) * (size_t)(capacity < 0 ? 0 : capacity));
+}
+
+extern "C" size_t yh_exchange_workspace_bytes(int64_t M) {
+    if (M < 0) return 0;
+    const size_t ntiles = (size_t)((M + kPartTile - 1) / kPartTile) + 1;
+    return 256 + 256 + part_up256(sizeof(int64_t) * kMaxParts) + sizeof(unsigned) * ntiles * kMaxParts;
+}
+
+extern "C" int yh_exchange_records(const uint64_t *key, const uint64_t *flags, int64_t M, const int64_t *M_dev,
+                                   const uint8_t *owner_of_class_host, int C, int world, int rank,
+                                   void *const *peer_block_host, int64_t capacity, unsigned epoch,
+                                   const int32_t *gt_count_local, int64_t n_images_local,
+                                   int32_t *gt_count_global, int64_t *info, void *workspace,
+                                   size_t workspace_bytes, void *stream) {
+    if (C < 1 || C > 32 || world < 1 || world > kMaxParts) {
+        set_error("yh_exchange_records: C=%d / world=%d outside this build (C<=32, world<=%d)", C, world, kMaxParts);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (M < 0 || M >= (1ll << 31) || rank < 0 || rank >= world || capacity < 0 || epoch == 0 ||
+        !owner_of_class_host || !peer_block_host || !gt_count_local || !gt_count_global || !info || !workspace ||
+        (M > 0 && (!key || !flags))) {
+        set_error("yh_exchange_records: bad argument (M=%lld rank=%d world=%d)", (long long)M, rank, world);
+        return YH_ERR_BAD_ARG;
+    }
+    if (workspace_bytes < yh_exchange_workspace_bytes(M)) {
+        set_error("yh_exchange_records: workspace too small");
+        return YH_ERR_WORKSPACE;
+    }
+    OwnerTable tab;
+    for (int c = 0; c < 256; ++c) {
+        const int o = c < C ? owner_of_class_host[c] : 0;
+        if (o >= world) {
+            set_error("yh_exchange_records: class %d is owned by rank %d >= world %d", c, o, world);
+            return YH_ERR_BAD_ARG;
+        }
+        tab.of_class[c] = (uint8_t)o;
+    }
+    PeerTable peers;
+    for (int r = 0; r < kMaxParts; ++r) {
+        char *base = (char *)peer_block_host[r < world ? r : rank];
+        if (!base) {
+            set_error("yh_exchange_records: peer block %d is null", r);
+            return YH_ERR_BAD_ARG;
+        }
+        peers.ctl[r] = (PeerCtl *)base;
+        peers.key[r] = (uint64_t *)(base + yh_peer_key_offset(capacity));
+        peers.flags[r] = (uint64_t *)(base + yh_peer_flags_offset(capacity));
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    char *ws = (char *)workspace;
+    ws += (256 - ((uintptr_t)ws & 255)) & 255;
+    ExchangeLocal *loc = (ExchangeLocal *)ws;
+    int64_t *part_count = (int64_t *)(ws + 256);
+    unsigned *tile_cnt = (unsigned *)(ws + 256 + part_up256(sizeof(int64_t) * kMaxParts));
+    const int ntiles = (int)((M + kPartTile - 1) / kPartTile);
+    const int grid = ntiles > 0 ? ntiles : 1;
+    cudaError_t e = cudaMemsetAsync(ws, 0, 256 + part_up256(sizeof(int64_t) * kMaxParts), st);
+    if (e != cudaSuccess) {
+        set_error("yh_exchange_records: memset: %s", cudaGetErrorString(e));
+        return (int)e;
+    }
+    int launched = 3;
+    if (ntiles > 0) {
+        part_tile_counts<<<ntiles, kPartThreads, 0, st>>>(flags, M, M_dev, tab, tile_cnt);
+        part_scan<<<world, 1024, 0, st>>>(tile_cnt, ntiles, part_count);
+        launched += 2;
+    } else {
+        cudaMemsetAsync(tile_cnt, 0, sizeof(unsigned) * kMaxParts, st);
+    }
+    peer_publish<<<1, 1024, 0, st>>>(peers, world, rank, epoch, part_count, gt_count_local, 4 * C,
+                                     (long long)n_images_local);
+    peer_scatter<<<grid, kPartThreads, 0, st>>>(key, flags, M, M_dev, tab, tile_cnt, peers, world, rank, epoch,
+                                                (long long)capacity, loc);
+    peer_finish<<<1, 256, 0, st>>>(peers, world, rank, epoch, 4 * C, loc, gt_count_global, info);
+    return check_launch("yh_exchange_records", launched);
 }

@@ -18,6 +18,13 @@ just the per-class confidence-sorted order and the ground-truth counts
                  table is summed with an all-reduce (classes a rank does not own
                  contribute exact zeros).  R x fewer bytes per rank, sort sharded.
 
+  "peer"         class_shard with the partition and the all-to-all fused into one kernel
+                 that writes every run straight into its owner's receive buffer over
+                 peer-mapped memory (yh_exchange_records, CUDA IPC blocks on NVLink);
+                 run lengths, ground-truth counts and the image count travel the same
+                 way, so compute() has ONE host read (the packed result) and one NCCL
+                 call (the all-reduce of the AP table).  Ranks must share a box.
+
 Tie order: the reference's stable sort leaves equal confidences in image order.
 Ranks own contiguous image ranges and both modes concatenate in rank order, so the
 stable radix sort of yh_ap_reduce sees the same sequence as a single process.
@@ -128,6 +135,93 @@ def partition_records(key: torch.Tensor, flags: torch.Tensor, m: int, owners: Li
     return out_k, out_f, cnt
 
 
+# ------------------------------------------------------------------ peer-memory exchange
+class _DeviceBlock:
+    """Raw device memory as a zero-copy tensor source (`torch.as_tensor` reads the interface)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 3, "strides": None}
+
+
+class PeerExchange:
+    """One receive block per rank, mapped into every rank of the group (all on one box).
+
+    Construction and close() are collective.  exchange() enqueues yh_exchange_records on
+    the current stream and returns views of this rank's receive buffer; it never reads
+    anything back."""
+
+    def __init__(self, capacity: int, device: torch.device, group=None):
+        lib = _lib.lib()
+        self.group, self.device = group, device
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.capacity = int(max(capacity, 1024))
+        self.epoch = 0
+        self.nbytes = int(lib.yh_peer_block_bytes(self.capacity))
+        self._own = _lib.C.c_void_p()
+        self._opened: List[int] = []
+        handle = (_lib.C.c_ubyte * 64)()
+        with torch.cuda.device(device):
+            _lib.check(lib.yh_peer_alloc(self.nbytes, _lib.C.byref(self._own), handle), "yh_peer_alloc")
+        blocks = [None] * self.world
+        blocks[self.rank] = self._own.value
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle), group=group)
+            with torch.cuda.device(device):
+                for r, h in enumerate(handles):
+                    if r == self.rank:
+                        continue
+                    p = _lib.C.c_void_p()
+                    buf = (_lib.C.c_ubyte * 64).from_buffer_copy(h)
+                    _lib.check(lib.yh_peer_open(buf, _lib.C.byref(p)), f"yh_peer_open(rank {r})")
+                    blocks[r] = p.value
+                    self._opened.append(p.value)
+        self._blocks = (_lib.C.c_void_p * self.world)(*blocks)
+        raw = torch.as_tensor(_DeviceBlock(self._own.value, self.nbytes), device=device)
+        ko, fo = int(lib.yh_peer_key_offset(self.capacity)), int(lib.yh_peer_flags_offset(self.capacity))
+        self.recv_key = raw[ko:ko + 8 * self.capacity].view(torch.int64)
+        self.recv_flags = raw[fo:fo + 8 * self.capacity].view(torch.int64)
+        self._ws = None
+        if self.world > 1:
+            dist.barrier(group=group)          # every block is mapped before anyone writes
+
+    def exchange(self, key, flags, m: int, m_dev, owners: List[int], gt_count: torch.Tensor, n_images: int):
+        """Returns (recv_key, recv_flags, gt_count_global int32 [4C], info int64 [4]); see yolohead.h."""
+        lib, dev = _lib.lib(), self.device
+        self.epoch += 1
+        need = int(lib.yh_exchange_workspace_bytes(int(m))) + 256
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        gt_glob = torch.empty_like(gt_count)
+        info = torch.empty(4, dtype=torch.int64, device=dev)
+        tab = (_lib.C.c_uint8 * len(owners))(*owners)
+        with torch.cuda.device(dev):
+            rc = lib.yh_exchange_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m),
+                                         _lib.ptr(m_dev), tab, len(owners), self.world, self.rank, self._blocks,
+                                         self.capacity, self.epoch, gt_count.data_ptr(), int(n_images),
+                                         gt_glob.data_ptr(), info.data_ptr(), self._ws.data_ptr(),
+                                         self._ws.numel(), _lib.stream_ptr(dev))
+        _lib.check(rc, "yh_exchange_records")
+        return self.recv_key, self.recv_flags, gt_glob, info
+
+    def close(self):
+        """Collective: unmap the peers' blocks, then free the own one once nobody maps it."""
+        if self._own.value is None:
+            return
+        lib = _lib.lib()
+        torch.cuda.synchronize(self.device)
+        self.recv_key = self.recv_flags = None
+        with torch.cuda.device(self.device):
+            for p in self._opened:
+                lib.yh_peer_close(p)
+            self._opened = []
+            if self.world > 1:
+                dist.barrier(group=self.group)
+            lib.yh_peer_free(self._own)
+        self._own = _lib.C.c_void_p()
+
+
 # ------------------------------------------------------------------ the metric
 class DistributedMAP:
     """`mAPMetric` whose `compute()` is global over a process group.
@@ -138,15 +232,50 @@ class DistributedMAP:
     dict on every rank.  Everything else (`reset`, thresholds, attributes) is the
     wrapped metric's.
 
-    Host round trips per compute(): one for the exchange's split sizes and one for the
-    packed result; everything else (compaction, partition, sort, AP) is enqueued."""
+    Host round trips per compute(): "peer" has one (the packed result); "class_shard" and
+    "gather" add one for the exchange's split sizes.  Everything else (compaction, partition,
+    exchange, sort, AP) is enqueued.  "peer" maps CUDA IPC blocks between the ranks on first
+    use (collective, ranks on one box); call close() (collective) to release them."""
 
     def __init__(self, metric: mAPMetric, group=None, mode: str = "class_shard"):
-        if mode not in ("gather", "class_shard"):
+        if mode not in ("gather", "class_shard", "peer"):
             raise ValueError(f"unknown exchange mode {mode!r}")
         self.metric = metric
         self.group = group
         self.mode = mode
+        self._peer: Optional[PeerExchange] = None
+        self.peer_fallbacks = 0            # compute() calls that overflowed the receive blocks
+
+    def close(self):
+        if self._peer is not None:
+            self._peer.close()
+            self._peer = None
+
+    def _peer_blocks(self, dev, cap_local: int, need: Optional[int] = None) -> PeerExchange:
+        """The mapped receive blocks, created on first use (collective; one host read).
+
+        Capacity: what a rank receives when classes are spread evenly -- the largest local
+        capacity x world x (largest share of classes one rank owns) -- or 1.25 x `need`
+        after an overflow.  A skewed class mix that does not fit falls back to the NCCL
+        exchange for that call and re-creates the blocks larger."""
+        if self._peer is not None and need is None:
+            return self._peer
+        g = self.group
+        world = dist.get_world_size(g)
+        want = torch.tensor([cap_local if need is None else need], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(want, op=dist.ReduceOp.MAX, group=g)
+        top = int(want.item())
+        if need is None:
+            owners = class_owners(self.metric.num_classes, world)
+            share = max(owners.count(r) for r in range(world)) / float(self.metric.num_classes)
+            capacity = int(np.ceil(top * min(float(world), world * share)))
+        else:
+            capacity = int(np.ceil(1.25 * top))
+        if self._peer is not None:
+            self._peer.close()
+        self._peer = PeerExchange(capacity, dev, g)
+        return self._peer
 
     def __getattr__(self, name):
         return getattr(self.metric, name)
@@ -180,9 +309,25 @@ class DistributedMAP:
         dev = m._device if m._device is not None else torch.device("cuda", torch.cuda.current_device())
         T, C = len(m.iou_thresholds), m.num_classes
         key, flg, cap, running, gt_count = self._local_records(dev)
+        n_images = len(m._pred_lists) + sum(c.n for c in m._chunks)
+        if self.mode == "peer":
+            px = self._peer_blocks(dev, cap)
+            rk, rf, gt_glob, info = px.exchange(key, flg, cap, running, class_owners(C, world), gt_count, n_images)
+            _, _, packed = head.ap_reduce(rk, rf, px.capacity, gt_glob, C, T, m_dev=info[:1])
+            if world > 1:
+                dist.all_reduce(packed[:4 * C * T + 3], group=g)
+            host = torch.cat([packed, info.to(torch.float64)]).cpu()
+            if host[-1] != 0:
+                raise _lib.YoloHeadError("yh_exchange_records: a rank of the group did not show up within 4 s")
+            if host[-2] == 0:
+                if int(host[-3]) == 0:
+                    return {"mAP50:95": 0.0, "mAP50": 0.0, "mAP75": 0.0, "precision": 0.0, "recall": 0.0}
+                ap, tp_total, n_pred, gtc = head.unpack_ap(host[:-4], C, T)
+                return m._results(ap, tp_total, n_pred, gtc, int(gtc[0].sum()), T, C)
+            self.peer_fallbacks += 1           # a receive block was too small: NCCL path now, larger blocks next
         # ground-truth counts and the image count travel in one all-reduce
         glob = torch.cat([gt_count.to(torch.int64),
-                          torch.tensor([len(m._pred_lists) + sum(c.n for c in m._chunks)], dtype=torch.int64, device=dev)])
+                          torch.tensor([n_images], dtype=torch.int64, device=dev)])
         dist.all_reduce(glob, group=g)
         gt_count = glob[:4 * C].to(torch.int32)
         if self.mode == "gather":
@@ -191,6 +336,8 @@ class DistributedMAP:
         else:
             pk, pf, part = partition_records(key, flg, cap, class_owners(C, world), world, m_dev=running)
             key, flg = exchange_by_owner(pk, pf, part, g)
+            if self.mode == "peer":
+                self._peer_blocks(dev, cap, need=key.numel())
             _, _, packed = head.ap_reduce(key, flg, key.numel(), gt_count, C, T)
             # ap table, TP total, record count, error flag: classes a rank does not own are exact zeros
             dist.all_reduce(packed[:4 * C * T + 3], group=g)
@@ -213,10 +360,13 @@ def evaluate_sharded(model, images: torch.Tensor, targets: torch.Tensor, batch: 
     dm = DistributedMAP(metric or mAPMetric(**({"num_classes": 20} | metric_kw)), group, mode)
     if model is not None:
         model.eval()
-    with torch.no_grad():
-        for s in range(lo, hi, batch):
-            e = min(hi, s + batch)
-            x = images[s:e].to(dev, non_blocking=True)
-            t = targets[s:e].to(dev, non_blocking=True)
-            dm.update(model(x) if model is not None else x, t)
-    return dm.compute()
+    try:
+        with torch.no_grad():
+            for s in range(lo, hi, batch):
+                e = min(hi, s + batch)
+                x = images[s:e].to(dev, non_blocking=True)
+                t = targets[s:e].to(dev, non_blocking=True)
+                dm.update(model(x) if model is not None else x, t)
+        return dm.compute()
+    finally:
+        dm.close()
