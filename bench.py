@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=4096, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunks", type=int, default=8, help="mini-batches the e2e step streams from the host")
-    ap.add_argument("--exchange", default="class_shard", choices=["class_shard", "gather", "peer"],
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "class_shard", "gather"],
                     help="N>1: how compute() makes the per-class order global (yolo_v1_b200/distributed.py)")
     return ap.parse_args()
 
@@ -394,8 +394,11 @@ def main():
             "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cpu, "stages": stages,
             "result_check": {"loss_total": loss_total, "mAP50:95": map5095},
         }
+        if world > 1:
+            line["exchange"] = {"mode": metric.mode, "overflow_fallbacks": metric.peer_fallbacks}
         print(json.dumps(line))
     if world > 1:
+        metric.close()
         dist.destroy_process_group()
 
 

@@ -205,7 +205,14 @@ int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M, 
  * fall back to the NCCL exchange and re-create larger blocks), info[3] = 1 if a wait
  * on a peer gave up after 4 s.  gt_count_global[4*C] = the ranks' gt_count_local summed.
  * Between two calls the ranks must be ordered by some collective that completes after the
- * receive buffer was consumed (DistributedMAP's all-reduce of the AP table is one). */
+ * receive buffer was consumed (yh_peer_sum of the AP table is one). */
+/* yh_peer_sum (collective, same epoch rule): vec[n] (device doubles, n <= 4*32*13 + 4) becomes
+ * the sum over the ranks, in rank order, through the peer blocks -- the all-reduce of the
+ * packed AP table without a second library.  vec[err_index] is set to 1 if a peer did not
+ * show up.  A rank past this call knows every peer has consumed its receive buffer, which
+ * is the ordering yh_exchange_records asks for between two calls. */
+int yh_peer_sum(double *vec, int n, int err_index, int world, int rank, void *const *peer_block_host,
+                unsigned epoch, void *stream);
 int yh_peer_alloc(size_t bytes, void **ptr, void *handle64);
 int yh_peer_open(const void *handle64, void **ptr);
 int yh_peer_close(void *ptr);

@@ -20,15 +20,35 @@ for it in range(6):
     t1 = time.perf_counter()
     if rank == 0 and it >= 3:
         print(f"compute() {1e3 * (t1 - t0):.3f} ms")
-if metric.mode == "peer":
-    if rank == 0:
-        print("peer capacity", metric._peer.capacity, "fallbacks", metric.peer_fallbacks)
-    metric.close(); dist.destroy_process_group(); sys.exit(0)
-# phase split: host enqueue time / time until the device is idle, per phase
-m = metric.metric
 def phase(fn):
     t0 = time.perf_counter(); out = fn(); t1 = time.perf_counter(); torch.cuda.synchronize(); t2 = time.perf_counter()
     return out, 1e3 * (t1 - t0), 1e3 * (t2 - t0)
+if os.environ.get("YH_KERNEL_TABLE"):
+    from torch.profiler import profile, ProfilerActivity
+    metric.reset(); metric.update(pred, tgt); dist.barrier(); torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(3):
+            metric.compute()
+        torch.cuda.synchronize()
+    if rank == 0:
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=60))
+if metric.mode == "peer":
+    if rank == 0:
+        print("peer capacity", metric._peer.capacity, "fallbacks", metric.peer_fallbacks)
+    px = metric._peer
+    for it in range(4):
+        metric.reset(); metric.update(pred, tgt); dist.barrier(); torch.cuda.synchronize()
+        rows = []
+        (key, flg, cap, running, gt_count), a, b = phase(lambda: metric._local_records(dev)); rows.append(("compact", a, b))
+        (rk, rf, gtg, info), a, b = phase(lambda: px.exchange(key, flg, cap, running, D.class_owners(20, world), gt_count, n)); rows.append(("exchange", a, b))
+        (_, _, packed), a, b = phase(lambda: head.ap_reduce(rk, rf, px.capacity, gtg, 20, 10, m_dev=info[:1])); rows.append(("ap_reduce", a, b))
+        _, a, b = phase(lambda: px.sum_results(packed, 803, 802)); rows.append(("peer_sum", a, b))
+        _, a, b = phase(lambda: torch.cat([packed, info.to(torch.float64)]).cpu()); rows.append(("d2h", a, b))
+        if rank == 0 and it == 3:
+            print(" | ".join(f"{nm} host {x:.3f} done {y:.3f}" for nm, x, y in rows), "recv", int(info[0]))
+    metric.close(); dist.destroy_process_group(); sys.exit(0)
+# phase split: host enqueue time / time until the device is idle, per phase
+m = metric.metric
 for it in range(4):
     metric.reset(); metric.update(pred, tgt); dist.barrier(); torch.cuda.synchronize()
     rows = []

@@ -40,6 +40,7 @@ SIGNATURES = {
     "yh_ap_reduce": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_partition_workspace_bytes": (_sz, [_i64]),
     "yh_partition_records": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "yh_peer_sum": (_i, [_vp, _i, _i, _i, _i, _vp, C.c_uint, _vp]),
     "yh_peer_alloc": (_i, [_sz, _vp, _vp]),
     "yh_peer_open": (_i, [_vp, _vp]),
     "yh_peer_close": (_i, [_vp]),

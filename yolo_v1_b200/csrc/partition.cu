@@ -189,11 +189,16 @@ part_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
 
 constexpr int kGtWords = 4 * 32 + 2;  // 4 subsets x (C <= 32) counts + image count (2 words)
 
+constexpr int kResWords = 4 * 32 * YH_MAX_THRESHOLDS + 4;  // AP table + totals + error flag of one rank
+
 struct PeerCtl {
     unsigned ready[kMaxParts];
     unsigned done[kMaxParts];
+    unsigned res_ready[kMaxParts];
+    unsigned pad[kMaxParts];
     long long row[kMaxParts][kMaxParts];
     int gt[kMaxParts][kGtWords];
+    double res[kMaxParts][kResWords];
 };
 
 struct PeerTable {
@@ -235,17 +240,86 @@ __device__ __forceinline__ bool wait_flag(const unsigned *flag, unsigned epoch) 
     return true;
 }
 
+// A CTA of the exchange owns a contiguous range of tiles (the same range in the count and in
+// the scatter kernel), so per-tile prefixes are never stored: the count kernel leaves one
+// total per CTA and part, the scatter kernel re-derives the rest walking its tiles in order.
+__device__ __forceinline__ void cta_tile_range(int64_t M, int &t0, int &t1) {
+    const int ntiles = (int)((M + kPartTile - 1) / kPartTile);
+    const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;
+    t0 = min(ntiles, (int)blockIdx.x * per);
+    t1 = min(ntiles, t0 + per);
+}
+
+// cta_cnt[cta][p] = records of the CTA's tile range that go to part p
+__global__ void __launch_bounds__(kPartThreads)
+peer_count(const uint64_t *__restrict__ flags, int64_t Mcap, const int64_t *__restrict__ Mdev,
+           const __grid_constant__ OwnerTable tab, unsigned *__restrict__ cta_cnt) {
+    __shared__ unsigned s_cnt[kMaxParts];
+    const int64_t M = part_count_of(Mcap, Mdev);
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    if (tid < kMaxParts) s_cnt[tid] = 0;
+    __syncthreads();
+    int t0, t1;
+    cta_tile_range(M, t0, t1);
+    for (int tile = t0; tile < t1; ++tile) {
+        const int64_t first = (int64_t)tile * kPartTile + wp * kPartSpan + lane;
+        uint64_t f[kPartRounds];
+#pragma unroll
+        for (int r = 0; r < kPartRounds; ++r) f[r] = first + 32 * r < M ? __ldg(flags + first + 32 * r) : 0;
+#pragma unroll
+        for (int r = 0; r < kPartRounds; ++r) {
+            const bool ok = first + 32 * r < M;
+            const int p = ok ? owner_of(tab, f[r]) : 0;
+            const unsigned act = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const unsigned grp = __match_any_sync(act, p);
+                if ((grp & ((1u << lane) - 1u)) == 0) atomicAdd(&s_cnt[p], __popc(grp));
+            }
+        }
+    }
+    __syncthreads();
+    if (tid < kMaxParts) cta_cnt[(size_t)blockIdx.x * kMaxParts + tid] = s_cnt[tid];
+}
+
+// One CTA: per part an exclusive scan of the CTA totals (in place), then this rank's message --
+// run lengths, ground-truth counts, image count -- goes to every rank and ready[me] is raised.
 __global__ void __launch_bounds__(1024)
-peer_publish(const __grid_constant__ PeerTable peers, int world, int me, unsigned epoch,
-             const int64_t *__restrict__ part_count, const int32_t *__restrict__ gt_local, int n_gt,
-             long long n_images) {
-    const int tid = threadIdx.x;
+peer_scan_publish(unsigned *__restrict__ cta_cnt, int nctas, const __grid_constant__ PeerTable peers, int world,
+                  int me, unsigned epoch, const int32_t *__restrict__ gt_local, int n_gt, long long n_images) {
+    __shared__ unsigned s_warp[32];
+    __shared__ long long s_total[kMaxParts];
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    for (int p = 0; p < world; ++p) {
+        const unsigned c = tid < nctas ? cta_cnt[(size_t)tid * kMaxParts + p] : 0;
+        unsigned inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        if (lane == 31) s_warp[wp] = inc;
+        __syncthreads();
+        if (wp == 0) {
+            const unsigned x = s_warp[lane];
+            unsigned xi = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned u = __shfl_up_sync(0xffffffffu, xi, o);
+                if (lane >= o) xi += u;
+            }
+            s_warp[lane] = xi - x;
+            if (lane == 31) s_total[p] = xi;
+        }
+        __syncthreads();
+        if (tid < nctas) cta_cnt[(size_t)tid * kMaxParts + p] = s_warp[wp] + inc - c;
+        __syncthreads();
+    }
     const int per = world + n_gt + 2;  // words of one rank's message
     for (int q = tid; q < world * per; q += blockDim.x) {
         const int d = q / per, i = q - d * per;
         PeerCtl *c = peers.ctl[d];
         if (i < world)
-            c->row[me][i] = part_count[i];
+            c->row[me][i] = s_total[i];
         else if (i < world + n_gt)
             c->gt[me][i - world] = gt_local[i - world];
         else
@@ -259,7 +333,7 @@ peer_publish(const __grid_constant__ PeerTable peers, int world, int me, unsigne
 __global__ void __launch_bounds__(kPartThreads)
 peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flags, int64_t Mcap,
              const int64_t *__restrict__ Mdev, const __grid_constant__ OwnerTable tab,
-             const unsigned *__restrict__ tile_pre, const __grid_constant__ PeerTable peers, int world, int me,
+             const unsigned *__restrict__ cta_pre, const __grid_constant__ PeerTable peers, int world, int me,
              unsigned epoch, long long capacity, ExchangeLocal *__restrict__ loc) {
     __shared__ unsigned s_w[kPartWarps][kMaxParts];  // per-warp counts, then running cursors
     __shared__ long long dst_base[kMaxParts];        // where my run starts in rank d's receive buffer
@@ -270,8 +344,8 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const PeerCtl *mine = peers.ctl[me];
     if (tid == 0) s_state = 0;
-    s_w[wp][lane] = 0;
     __syncthreads();
+    // persistent CTAs: one wait for the peers' rows per CTA, one system fence at the end
     if (tid < world && !wait_flag(&mine->ready[tid], epoch)) s_state = 1;
     __syncthreads();
     if (s_state) {
@@ -286,15 +360,21 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
                 if (r < me) before += c;
                 total += c;
             }
-        dst_base[tid] = before;
+        // start of my run in rank tid's buffer + what the CTAs before this one put there
+        dst_base[tid] = before + cta_pre[(size_t)blockIdx.x * kMaxParts + tid];
         if (total > capacity) s_state = 2;
     }
     __syncthreads();
     const bool overflow = s_state == 2;
     if (overflow && tid == 0 && blockIdx.x == 0) loc->overflow = 1;
-    if (!overflow) {
-        const int64_t first = (int64_t)blockIdx.x * kPartTile + wp * kPartSpan + lane;
-        const unsigned lt = (1u << lane) - 1u;
+    int t0, t1;
+    cta_tile_range(M, t0, t1);
+    if (overflow) t1 = t0;
+    const unsigned lt = (1u << lane) - 1u;
+    for (int tile = t0; tile < t1; ++tile) {
+        s_w[wp][lane] = 0;
+        __syncwarp();
+        const int64_t first = (int64_t)tile * kPartTile + wp * kPartSpan + lane;
         uint64_t k[kPartRounds], f[kPartRounds];
         int part[kPartRounds];
 #pragma unroll
@@ -303,6 +383,10 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
             const bool ok = idx < M;
             k[r] = ok ? __ldg(key + idx) : 0;
             f[r] = ok ? __ldg(flags + idx) : 0;
+        }
+#pragma unroll
+        for (int r = 0; r < kPartRounds; ++r) {
+            const bool ok = first + 32 * r < M;
             part[r] = ok ? owner_of(tab, f[r]) : -1;
             const unsigned act = __ballot_sync(0xffffffffu, ok);
             if (ok) {
@@ -312,7 +396,7 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
             __syncwarp();
         }
         __syncthreads();
-        if (tid < kMaxParts) {  // per part: exclusive prefix over the warps (tile-local)
+        if (tid < kMaxParts) {  // per part: exclusive prefix over the warps, then over the parts (tile-local)
             unsigned run = 0;
 #pragma unroll
             for (int q = 0; q < kPartWarps; ++q) {
@@ -320,7 +404,6 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
                 s_w[q][tid] = run;
                 run += c;
             }
-            // tile_start = exclusive scan of the part totals over the parts (one warp)
             unsigned inc = run;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -329,6 +412,7 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
             }
             tile_start[tid] = inc - run;
             if (tid == kMaxParts - 1) tile_start[kMaxParts] = inc;
+            dst_base[tid] -= (long long)(inc - run);  // so that position = dst_base[p] + tile-local index
         }
         __syncthreads();
 #pragma unroll
@@ -354,10 +438,13 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
 #pragma unroll
             for (int h = kMaxParts / 2; h > 0; h >>= 1)
                 if (tile_start[p + h] <= i) p += h;
-            const long long pos = dst_base[p] + tile_pre[(size_t)blockIdx.x * kMaxParts + p] + (i - tile_start[p]);
+            const long long pos = dst_base[p] + i;  // = run start + records before the tile + (i - tile_start[p])
             peers.key[p][pos] = s_key[i];
             peers.flags[p][pos] = s_flg[i];
         }
+        __syncthreads();
+        if (tid < kMaxParts) dst_base[tid] += (long long)tile_start[tid + 1];  // undo the shift, add the tile's count
+        __syncthreads();
     }
     // completion: my stores are visible system-wide before the count moves; the last CTA raises done[me]
     __threadfence_system();
@@ -456,6 +543,59 @@ extern "C" int yh_partition_records(const uint64_t *key, const uint64_t *flags, 
     return check_launch("yh_partition_records", 3);
 }
 
+// Sum of the ranks' result vectors (AP table, totals, error flag) in rank order, through the
+// same peer blocks: store mine into everybody's slot, raise res_ready, wait for the others,
+// add.  Every class is non-zero on exactly one rank and the totals are integers, so the
+// sum is exact in any order.  A rank that saw its peers' results has, by stream order,
+// peers that are done with their receive buffers: this is also what orders two exchanges.
+namespace yh {
+__global__ void __launch_bounds__(1024)
+peer_sum_results(const __grid_constant__ PeerTable peers, int world, int me, unsigned epoch, int n, int err_index,
+                 double *__restrict__ vec) {
+    __shared__ int s_bad;
+    const int tid = threadIdx.x;
+    const PeerCtl *mine = peers.ctl[me];
+    if (tid == 0) s_bad = 0;
+    for (int q = tid; q < world * n; q += blockDim.x) {
+        const int d = q / n, i = q - d * n;
+        peers.ctl[d]->res[me][i] = vec[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < world) {
+        st_release_sys(&peers.ctl[tid]->res_ready[me], epoch);
+        if (!wait_flag(&mine->res_ready[tid], epoch)) s_bad = 1;
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) {
+        double s = 0.0;
+        for (int r = 0; r < world; ++r) s += mine->res[r][i];
+        vec[i] = (i == err_index && s_bad) ? 1.0 : s;
+    }
+}
+}  // namespace yh
+
+extern "C" int yh_peer_sum(double *vec, int n, int err_index, int world, int rank, void *const *peer_block_host,
+                           unsigned epoch, void *stream) {
+    if (!vec || n < 1 || n > kResWords || world < 1 || world > kMaxParts || rank < 0 || rank >= world ||
+        !peer_block_host || epoch == 0) {
+        set_error("yh_peer_sum: bad argument (n=%d world=%d rank=%d)", n, world, rank);
+        return YH_ERR_BAD_ARG;
+    }
+    PeerTable peers;
+    for (int r = 0; r < kMaxParts; ++r) {
+        peers.ctl[r] = (PeerCtl *)peer_block_host[r < world ? r : rank];
+        peers.key[r] = nullptr;
+        peers.flags[r] = nullptr;
+        if (!peers.ctl[r]) {
+            set_error("yh_peer_sum: peer block %d is null", r);
+            return YH_ERR_BAD_ARG;
+        }
+    }
+    peer_sum_results<<<1, 1024, 0, (cudaStream_t)stream>>>(peers, world, rank, epoch, n, err_index, vec);
+    return check_launch("yh_peer_sum");
+}
+
 // ------------------------------------------------------------------ peer-mapped memory
 // The one place this library allocates: a block other processes can map must come from
 // cudaMalloc (not from the caller's caching allocator) to be exportable as an IPC handle.
@@ -533,10 +673,11 @@ extern "C" size_t yh_peer_flags_offset(int64_t capacity) {
     return part_up256(sizeof(PeerCtl)) + part_up256(sizeof(uint64_t) * (size_t)(capacity < 0 ? 0 : capacity));
 }
 
+constexpr int kExchangeCtas = 148 * 6;   // <= 1024: peer_scan_publish scans one CTA total per thread
+
 extern "C" size_t yh_exchange_workspace_bytes(int64_t M) {
     if (M < 0) return 0;
-    const size_t ntiles = (size_t)((M + kPartTile - 1) / kPartTile) + 1;
-    return 256 + 256 + part_up256(sizeof(int64_t) * kMaxParts) + sizeof(unsigned) * ntiles * kMaxParts;
+    return 256 + 256 + sizeof(unsigned) * (size_t)kExchangeCtas * kMaxParts;
 }
 
 extern "C" int yh_exchange_records(const uint64_t *key, const uint64_t *flags, int64_t M, const int64_t *M_dev,
@@ -583,27 +724,20 @@ extern "C" int yh_exchange_records(const uint64_t *key, const uint64_t *flags, i
     char *ws = (char *)workspace;
     ws += (256 - ((uintptr_t)ws & 255)) & 255;
     ExchangeLocal *loc = (ExchangeLocal *)ws;
-    int64_t *part_count = (int64_t *)(ws + 256);
-    unsigned *tile_cnt = (unsigned *)(ws + 256 + part_up256(sizeof(int64_t) * kMaxParts));
+    unsigned *cta_cnt = (unsigned *)(ws + 256);
     const int ntiles = (int)((M + kPartTile - 1) / kPartTile);
-    const int grid = ntiles > 0 ? ntiles : 1;
-    cudaError_t e = cudaMemsetAsync(ws, 0, 256 + part_up256(sizeof(int64_t) * kMaxParts), st);
+    int grid = ntiles < kExchangeCtas ? ntiles : kExchangeCtas;  // persistent: a CTA owns a contiguous tile range
+    if (grid < 1) grid = 1;
+    cudaError_t e = cudaMemsetAsync(ws, 0, 256, st);
     if (e != cudaSuccess) {
         set_error("yh_exchange_records: memset: %s", cudaGetErrorString(e));
         return (int)e;
     }
-    int launched = 3;
-    if (ntiles > 0) {
-        part_tile_counts<<<ntiles, kPartThreads, 0, st>>>(flags, M, M_dev, tab, tile_cnt);
-        part_scan<<<world, 1024, 0, st>>>(tile_cnt, ntiles, part_count);
-        launched += 2;
-    } else {
-        cudaMemsetAsync(tile_cnt, 0, sizeof(unsigned) * kMaxParts, st);
-    }
-    peer_publish<<<1, 1024, 0, st>>>(peers, world, rank, epoch, part_count, gt_count_local, 4 * C,
-                                     (long long)n_images_local);
-    peer_scatter<<<grid, kPartThreads, 0, st>>>(key, flags, M, M_dev, tab, tile_cnt, peers, world, rank, epoch,
+    peer_count<<<grid, kPartThreads, 0, st>>>(flags, M, M_dev, tab, cta_cnt);
+    peer_scan_publish<<<1, 1024, 0, st>>>(cta_cnt, grid, peers, world, rank, epoch, gt_count_local, 4 * C,
+                                          (long long)n_images_local);
+    peer_scatter<<<grid, kPartThreads, 0, st>>>(key, flags, M, M_dev, tab, cta_cnt, peers, world, rank, epoch,
                                                 (long long)capacity, loc);
     peer_finish<<<1, 256, 0, st>>>(peers, world, rank, epoch, 4 * C, loc, gt_count_global, info);
-    return check_launch("yh_exchange_records", launched);
+    return check_launch("yh_exchange_records", 4);
 }

@@ -22,8 +22,9 @@ just the per-class confidence-sorted order and the ground-truth counts
                  that writes every run straight into its owner's receive buffer over
                  peer-mapped memory (yh_exchange_records, CUDA IPC blocks on NVLink);
                  run lengths, ground-truth counts and the image count travel the same
-                 way, so compute() has ONE host read (the packed result) and one NCCL
-                 call (the all-reduce of the AP table).  Ranks must share a box.
+                 way, and the AP table is summed through the same blocks (yh_peer_sum):
+                 compute() has ONE host read (the packed result) and no NCCL call.
+                 Ranks must share a box.
 
 Tie order: the reference's stable sort leaves equal confidences in image order.
 Ranks own contiguous image ranges and both modes concatenate in rank order, so the
@@ -144,6 +145,10 @@ class _DeviceBlock:
                                          "version": 3, "strides": None}
 
 
+class PeerUnavailable(_lib.YoloHeadError):
+    """The ranks could not map each other's memory (not one box, or CUDA IPC is blocked)."""
+
+
 class PeerExchange:
     """One receive block per rank, mapped into every rank of the group (all on one box).
 
@@ -161,30 +166,43 @@ class PeerExchange:
         self._own = _lib.C.c_void_p()
         self._opened: List[int] = []
         handle = (_lib.C.c_ubyte * 64)()
+        problem = None
         with torch.cuda.device(device):
-            _lib.check(lib.yh_peer_alloc(self.nbytes, _lib.C.byref(self._own), handle), "yh_peer_alloc")
+            if lib.yh_peer_alloc(self.nbytes, _lib.C.byref(self._own), handle) != 0:
+                problem = "yh_peer_alloc: " + lib.yh_last_error().decode("utf-8", "replace")
         blocks = [None] * self.world
         blocks[self.rank] = self._own.value
         if self.world > 1:
             handles = [None] * self.world
-            dist.all_gather_object(handles, bytes(handle), group=group)
+            dist.all_gather_object(handles, None if problem else bytes(handle), group=group)
             with torch.cuda.device(device):
                 for r, h in enumerate(handles):
-                    if r == self.rank:
+                    if r == self.rank or problem:
                         continue
+                    if h is None:
+                        problem = f"rank {r} could not allocate its block"
+                        break
                     p = _lib.C.c_void_p()
                     buf = (_lib.C.c_ubyte * 64).from_buffer_copy(h)
-                    _lib.check(lib.yh_peer_open(buf, _lib.C.byref(p)), f"yh_peer_open(rank {r})")
+                    if lib.yh_peer_open(buf, _lib.C.byref(p)) != 0:
+                        problem = f"yh_peer_open(rank {r}): " + lib.yh_last_error().decode("utf-8", "replace")
+                        break
                     blocks[r] = p.value
                     self._opened.append(p.value)
+            # every block is mapped everywhere before anyone writes -- or nobody uses the blocks
+            ok = torch.tensor([0 if problem else 1], dtype=torch.int32, device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
+                self._release(collective=False)
+                raise PeerUnavailable(problem or "another rank could not map the peer blocks")
+        elif problem:
+            raise PeerUnavailable(problem)
         self._blocks = (_lib.C.c_void_p * self.world)(*blocks)
         raw = torch.as_tensor(_DeviceBlock(self._own.value, self.nbytes), device=device)
         ko, fo = int(lib.yh_peer_key_offset(self.capacity)), int(lib.yh_peer_flags_offset(self.capacity))
         self.recv_key = raw[ko:ko + 8 * self.capacity].view(torch.int64)
         self.recv_flags = raw[fo:fo + 8 * self.capacity].view(torch.int64)
         self._ws = None
-        if self.world > 1:
-            dist.barrier(group=group)          # every block is mapped before anyone writes
 
     def exchange(self, key, flags, m: int, m_dev, owners: List[int], gt_count: torch.Tensor, n_images: int):
         """Returns (recv_key, recv_flags, gt_count_global int32 [4C], info int64 [4]); see yolohead.h."""
@@ -205,8 +223,18 @@ class PeerExchange:
         _lib.check(rc, "yh_exchange_records")
         return self.recv_key, self.recv_flags, gt_glob, info
 
+    def sum_results(self, vec: torch.Tensor, n: int, err_index: int) -> None:
+        """vec[:n] (float64, in place) summed over the ranks through the peer blocks (yh_peer_sum)."""
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().yh_peer_sum(vec.data_ptr(), int(n), int(err_index), self.world, self.rank, self._blocks,
+                                        self.epoch, _lib.stream_ptr(self.device))
+        _lib.check(rc, "yh_peer_sum")
+
     def close(self):
         """Collective: unmap the peers' blocks, then free the own one once nobody maps it."""
+        self._release(collective=True)
+
+    def _release(self, collective: bool):
         if self._own.value is None:
             return
         lib = _lib.lib()
@@ -216,7 +244,7 @@ class PeerExchange:
             for p in self._opened:
                 lib.yh_peer_close(p)
             self._opened = []
-            if self.world > 1:
+            if collective and self.world > 1:
                 dist.barrier(group=self.group)
             lib.yh_peer_free(self._own)
         self._own = _lib.C.c_void_p()
@@ -235,10 +263,11 @@ class DistributedMAP:
     Host round trips per compute(): "peer" has one (the packed result); "class_shard" and
     "gather" add one for the exchange's split sizes.  Everything else (compaction, partition,
     exchange, sort, AP) is enqueued.  "peer" maps CUDA IPC blocks between the ranks on first
-    use (collective, ranks on one box); call close() (collective) to release them."""
+    use (collective, ranks on one box); call close() (collective) to release them.
+    "auto" = "peer" if that mapping works on every rank, else "class_shard"."""
 
     def __init__(self, metric: mAPMetric, group=None, mode: str = "class_shard"):
-        if mode not in ("gather", "class_shard", "peer"):
+        if mode not in ("gather", "class_shard", "peer", "auto"):
             raise ValueError(f"unknown exchange mode {mode!r}")
         self.metric = metric
         self.group = group
@@ -310,12 +339,21 @@ class DistributedMAP:
         T, C = len(m.iou_thresholds), m.num_classes
         key, flg, cap, running, gt_count = self._local_records(dev)
         n_images = len(m._pred_lists) + sum(c.n for c in m._chunks)
+        if self.mode == "auto":            # "peer" where the ranks can map each other's memory
+            try:
+                self._peer_blocks(dev, cap)
+                self.mode = "peer"
+            except PeerUnavailable as e:   # raised on every rank together
+                import warnings
+
+                warnings.warn(f"DistributedMAP: peer-memory exchange unavailable ({e}); using the NCCL exchange")
+                self.mode = "class_shard"
         if self.mode == "peer":
             px = self._peer_blocks(dev, cap)
             rk, rf, gt_glob, info = px.exchange(key, flg, cap, running, class_owners(C, world), gt_count, n_images)
             _, _, packed = head.ap_reduce(rk, rf, px.capacity, gt_glob, C, T, m_dev=info[:1])
             if world > 1:
-                dist.all_reduce(packed[:4 * C * T + 3], group=g)
+                px.sum_results(packed, 4 * C * T + 3, 4 * C * T + 2)
             host = torch.cat([packed, info.to(torch.float64)]).cpu()
             if host[-1] != 0:
                 raise _lib.YoloHeadError("yh_exchange_records: a rank of the group did not show up within 4 s")
