@@ -105,8 +105,34 @@ def require_cuda(t: torch.Tensor, name: str) -> None:
             "Move the tensor to the GPU first.")
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(device) -> int:
+    """cudaStream_t of torch's current stream on `device` (the raw-handle call skips building a Stream object)."""
+    if _raw_stream is not None:
+        idx = device.index if isinstance(device, torch.device) else torch.device(device).index
+        return _raw_stream(torch.cuda.current_device() if idx is None else idx)
     return torch.cuda.current_stream(device).cuda_stream
+
+
+class _NoSwitch:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NO_SWITCH = _NoSwitch()
+
+
+def on_device(device):
+    """Context in which `device` is the current CUDA device: free when it already is."""
+    idx = device.index if isinstance(device, torch.device) else torch.device(device).index
+    if idx is None or idx == torch.cuda.current_device():
+        return _NO_SWITCH
+    return torch.cuda.device(idx)
 
 
 def ptr(t):

@@ -127,7 +127,7 @@ def partition_records(key: torch.Tensor, flags: torch.Tensor, m: int, owners: Li
     cnt = torch.zeros(n_parts, dtype=torch.int64, device=dev)
     ws = torch.empty(lib.yh_partition_workspace_bytes(int(m)) + 256, dtype=torch.uint8, device=dev)
     tab = (_lib.C.c_uint8 * len(owners))(*owners)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = lib.yh_partition_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m),
                                       _lib.ptr(m_dev), tab, len(owners), int(n_parts), out_k.data_ptr(),
                                       out_f.data_ptr(), cnt.data_ptr(), ws.data_ptr(), ws.numel(),
@@ -167,7 +167,7 @@ class PeerExchange:
         self._opened: List[int] = []
         handle = (_lib.C.c_ubyte * 64)()
         problem = None
-        with torch.cuda.device(device):
+        with _lib.on_device(device):
             if lib.yh_peer_alloc(self.nbytes, _lib.C.byref(self._own), handle) != 0:
                 problem = "yh_peer_alloc: " + lib.yh_last_error().decode("utf-8", "replace")
         blocks = [None] * self.world
@@ -175,7 +175,7 @@ class PeerExchange:
         if self.world > 1:
             handles = [None] * self.world
             dist.all_gather_object(handles, None if problem else bytes(handle), group=group)
-            with torch.cuda.device(device):
+            with _lib.on_device(device):
                 for r, h in enumerate(handles):
                     if r == self.rank or problem:
                         continue
@@ -214,7 +214,7 @@ class PeerExchange:
         gt_glob = torch.empty_like(gt_count)
         info = torch.empty(4, dtype=torch.int64, device=dev)
         tab = (_lib.C.c_uint8 * len(owners))(*owners)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             rc = lib.yh_exchange_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m),
                                          _lib.ptr(m_dev), tab, len(owners), self.world, self.rank, self._blocks,
                                          self.capacity, self.epoch, gt_count.data_ptr(), int(n_images),
@@ -225,7 +225,7 @@ class PeerExchange:
 
     def sum_results(self, vec: torch.Tensor, n: int, err_index: int) -> None:
         """vec[:n] (float64, in place) summed over the ranks through the peer blocks (yh_peer_sum)."""
-        with torch.cuda.device(self.device):
+        with _lib.on_device(self.device):
             rc = _lib.lib().yh_peer_sum(vec.data_ptr(), int(n), int(err_index), self.world, self.rank, self._blocks,
                                         self.epoch, _lib.stream_ptr(self.device))
         _lib.check(rc, "yh_peer_sum")
@@ -240,7 +240,7 @@ class PeerExchange:
         lib = _lib.lib()
         torch.cuda.synchronize(self.device)
         self.recv_key = self.recv_flags = None
-        with torch.cuda.device(self.device):
+        with _lib.on_device(self.device):
             for p in self._opened:
                 lib.yh_peer_close(p)
             self._opened = []

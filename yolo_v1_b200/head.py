@@ -66,7 +66,7 @@ def decode_nms(pred: torch.Tensor, conf_thr: float, nms_thr: float, iou_mode: in
     keep_cls = torch.empty(N, K, dtype=torch.uint8, device=dev)
     keep_conf = torch.empty(N, K, dtype=torch.float64, device=dev)
     keep_box = torch.empty(N, K, 4, dtype=torch.float64, device=dev) if want_boxes else None
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = _lib.lib().yh_decode_nms(p.data_ptr(), N, S, B, Cn, float(conf_thr), float(nms_thr), int(iou_mode),
                                       int(order), n_keep.data_ptr(), keep_k.data_ptr(), keep_cls.data_ptr(),
                                       keep_conf.data_ptr(), _lib.ptr(keep_box), n_cand.data_ptr(),
@@ -112,7 +112,7 @@ def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: 
     gt_cell = torch.empty(N, G, **u8) if want_lists else None
     gt_cls = torch.empty(N, G, **u8) if want_lists else None
     gt_raw = torch.empty(N, G, 4, dtype=torch.float32, device=dev) if want_lists else None
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = _lib.lib().yh_map_update(p.data_ptr(), t.data_ptr(), N, S, B, Cn, float(conf_thr), float(nms_thr),
                                       thr_c, len(thr_c), n_keep.data_ptr(), rec_key.data_ptr(),
                                       rec_flags.data_ptr(), rec_k.data_ptr(), _lib.ptr(rec_raw), n_gt.data_ptr(),
@@ -132,7 +132,7 @@ def list_form(ch: UpdateChunk):
     rec_pos = torch.empty(N, K, dtype=torch.uint8, device=dev)
     rec_box = torch.empty(N, K, 4, dtype=torch.float64, device=dev)
     gt_box = torch.empty(N, S * S, 4, dtype=torch.float64, device=dev)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = _lib.lib().yh_list_form(ch.n_keep.data_ptr(), ch.rec_key.data_ptr(), ch.rec_flags.data_ptr(),
                                      ch.rec_k.data_ptr(), ch.rec_raw.data_ptr(), ch.n_gt.data_ptr(),
                                      ch.gt_cell.data_ptr(), ch.gt_raw.data_ptr(), N, S, B, Cn, rec_pos.data_ptr(),
@@ -157,7 +157,7 @@ def compact_records(chunk: UpdateChunk, out_key: torch.Tensor | None = None, out
         out_key = torch.empty(N * K, dtype=torch.int64, device=dev)
         out_flags = torch.empty(N * K, dtype=torch.int64, device=dev)
     ws = torch.empty(lib.yh_compact_workspace_bytes(N), dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = lib.yh_compact_records(chunk.n_keep.data_ptr(), chunk.rec_key.data_ptr(), chunk.rec_flags.data_ptr(),
                                     N, K, offsets.data_ptr(), out_key.data_ptr(), out_flags.data_ptr(),
                                     _lib.ptr(running), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
@@ -194,7 +194,7 @@ def ap_reduce(key: torch.Tensor, flags: torch.Tensor, M: int, gt_count: torch.Te
     ap = torch.empty(4, Cn, T, dtype=torch.float64, device=dev)
     totals = torch.empty(2, dtype=torch.int64, device=dev)
     packed = torch.empty(4 * Cn * T + 3 + 4 * Cn, dtype=torch.float64, device=dev)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = lib.yh_ap_reduce(key.data_ptr() if M else None, flags.data_ptr() if M else None, int(M),
                               _lib.ptr(m_dev), gt_count.data_ptr(), Cn, T, ap.data_ptr(), totals.data_ptr(),
                               packed.data_ptr(), ws.data_ptr(), nbytes, _lib.stream_ptr(dev))
@@ -216,7 +216,7 @@ def iou_pairs(box_a, box_b, iou_mode: int, device) -> torch.Tensor:
     b = torch.as_tensor(box_b, dtype=torch.float64).reshape(-1, 4).to(device)
     _lib.require_cuda(a, "boxes")
     out = torch.empty(a.shape[0], dtype=torch.float64, device=a.device)
-    with torch.cuda.device(a.device):
+    with _lib.on_device(a.device):
         rc = _lib.lib().yh_iou_pairs(a.data_ptr(), b.data_ptr(), a.shape[0], int(iou_mode), out.data_ptr(),
                                      _lib.stream_ptr(a.device))
     _lib.check(rc, "yh_iou_pairs")
@@ -235,7 +235,7 @@ def nms_lists(offsets, cls, conf, box, nms_thr: float, iou_mode: int, order: int
     box_d = torch.as_tensor(box, dtype=torch.float64).reshape(-1, 4).to(device)
     n_keep = torch.zeros(max(n_lists, 1), dtype=torch.int32, device=device)
     keep_idx = torch.zeros(max(cls_d.numel(), 1), dtype=torch.int32, device=device)
-    with torch.cuda.device(off_d.device):
+    with _lib.on_device(off_d.device):
         rc = _lib.lib().yh_nms_lists(off_d.data_ptr(), n_lists, cls_d.data_ptr(), conf_d.data_ptr(),
                                      box_d.data_ptr(), float(nms_thr), int(iou_mode), int(order),
                                      n_keep.data_ptr(), keep_idx.data_ptr(), max_len,
@@ -254,7 +254,7 @@ def match_lists(det_off, det_cls, det_conf, det_box, gt_off, gt_cls, gt_box, Cn:
     max_dets = int((det_off[1:] - det_off[:-1]).max()) if n_lists > 0 else 0
     rec_key = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
     rec_flags = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = _lib.lib().yh_match_lists(det_off.data_ptr(), det_cls.data_ptr(), det_conf.data_ptr(),
                                        det_box.data_ptr(), gt_off.data_ptr(), gt_cls.data_ptr(),
                                        gt_box.data_ptr(), n_lists, Cn, thr_c, len(thr_c), rec_key.data_ptr(),

@@ -47,8 +47,12 @@ def loss_fwd_bwd(pred: torch.Tensor, tgt: torch.Tensor, S: int, B: int, C: int, 
     N = pred.shape[0]
     if N == 0:
         raise ValueError("empty batch")
-    p = pred.detach().contiguous()
-    t = tgt.detach().to(torch.float32).contiguous()
+    p = pred.detach()
+    if not p.is_contiguous():
+        p = p.contiguous()
+    t = tgt.detach()
+    if t.dtype is not torch.float32 or not t.is_contiguous():
+        t = t.to(torch.float32).contiguous()
     lib = _lib.lib()
     parts = torch.empty(5, dtype=torch.float32, device=p.device)
     grad = torch.empty_like(p) if want_grad else None
@@ -56,7 +60,7 @@ def loss_fwd_bwd(pred: torch.Tensor, tgt: torch.Tensor, S: int, B: int, C: int, 
     if nbytes == 0:
         raise NotImplementedError(f"YOLOLoss kernels are built for S=7,B=2,C=20 only (got {S},{B},{C})")
     ws = _WS.get(p.device, nbytes)
-    with torch.cuda.device(p.device):
+    with _lib.on_device(p.device):
         rc = lib.yh_loss_fwd_bwd(p.data_ptr(), _lib.dtype_code(p), t.data_ptr(), N, S, B, C,
                                  float(lambda_coord), float(lambda_noobj), parts.data_ptr(), _lib.ptr(grad),
                                  ws.data_ptr(), ws.numel(), _lib.stream_ptr(p.device))
@@ -125,7 +129,7 @@ class _YoloLossFn(torch.autograd.Function):
             return (None,) * 7
         ctx.saved_grad = None
         scale = g_total.detach().to(torch.float32).reshape(1).contiguous()
-        with torch.cuda.device(grad.device):
+        with _lib.on_device(grad.device):
             rc = _lib.lib().yh_scale_inplace(grad.data_ptr(), _lib.dtype_code(grad), grad.numel(),
                                              scale.data_ptr(), _lib.stream_ptr(grad.device))
         _lib.check(rc, "yh_scale_inplace")

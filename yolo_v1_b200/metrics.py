@@ -48,6 +48,19 @@ def _conf_from_key(key: np.ndarray) -> np.ndarray:
     return bits.view(np.float64)
 
 
+_CLASS_KEYS: Dict[int, tuple] = {}
+
+
+def _class_keys(C: int):
+    """The per-class result keys (metrics.py:131-139), built once per class count."""
+    k = _CLASS_KEYS.get(C)
+    if k is None:
+        k = ([f"AP50_class_{c}" for c in range(C)], [f"AP75_class_{c}" for c in range(C)],
+             [f"AP50:95_class_{c}" for c in range(C)])
+        _CLASS_KEYS[C] = k
+    return k
+
+
 class mAPMetric:
     """Mean average precision (PASCAL VOC 11-point) at one or more IoU thresholds."""
 
@@ -204,7 +217,7 @@ class mAPMetric:
         ap, tp_total, n_pred, gtc = head.unpack_ap(packed, C, T)
         return ap, tp_total, n_pred, gtc.reshape(-1), G
 
-    def _results(self, ap, tp_total, n_pred, gt_count, n_gt_total, T, C) -> Dict[str, float]:
+    def _results(self, ap, tp_total, n_pred, gt_count, n_gt_total, T, C) -> Dict[str, float]:  # noqa: C901
         """Result dict with the reference's keys and its np.mean call sites (metrics.py:126-171, 531-564)."""
         thr = self.iou_thresholds
         if len(set(thr)) == len(thr):
@@ -263,12 +276,20 @@ class mAPMetric:
         cls_mean = np.add.reduce(a0, axis=1) / T
         col50 = a0[:, i50].tolist() if i50 >= 0 else None
         col75 = a0[:, i75].tolist() if i75 >= 0 else None
-        for c in range(C):
-            if i50 >= 0:
-                out[f"AP50_class_{c}"] = col50[c]
-            if i75 >= 0:
-                out[f"AP75_class_{c}"] = col75[c]
-            out[f"AP50:95_class_{c}"] = cls_mean[c]
+        k50, k75, kall = _class_keys(C)
+        per_class = list(cls_mean)           # np.float64 items, as np.mean returns
+        if i50 >= 0 and i75 >= 0:            # same insertion order as the loop above
+            for c in range(C):
+                out[k50[c]] = col50[c]
+                out[k75[c]] = col75[c]
+                out[kall[c]] = per_class[c]
+        else:
+            for c in range(C):
+                if i50 >= 0:
+                    out[k50[c]] = col50[c]
+                if i75 >= 0:
+                    out[k75[c]] = col75[c]
+                out[kall[c]] = per_class[c]
 
         def means(a, prefix, suffix):
             if i50 >= 0:
@@ -317,7 +338,7 @@ class mAPMetric:
         n_gt = torch.zeros(1, dtype=torch.int32, device=dev)
         gt_cls = torch.empty(1, G, dtype=torch.uint8, device=dev)
         gt_box = torch.empty(1, G, 4, dtype=torch.float64, device=dev)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             rc = _lib.lib().yh_parse_gt(t.data_ptr(), 1, self.S, self.B, self.num_classes, n_gt.data_ptr(),
                                         gt_cls.data_ptr(), gt_box.data_ptr(), _lib.stream_ptr(dev))
         _lib.check(rc, "yh_parse_gt")

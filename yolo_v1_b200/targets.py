@@ -41,7 +41,7 @@ def encode_targets(bboxes: Sequence[Sequence[Sequence[float]]], class_ids: Seque
     off_d = torch.tensor(off, dtype=torch.int64).to(dev)
     out = torch.empty(n, S, S, B * 5 + C, dtype=torch.float32, device=dev)
     bad = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = _lib.lib().yh_encode_targets(boxes_d.data_ptr(), cls_d.data_ptr(), off_d.data_ptr(), n, S, B, C,
                                           out.data_ptr(), bad.data_ptr(), _lib.stream_ptr(dev))
     _lib.check(rc, "yh_encode_targets")
