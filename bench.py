@@ -295,6 +295,58 @@ def main():
            "mini_batches": n_chunks, "h2d_only_ms": h2d_ms,
            "result_check": {"loss_total": e2e_loss, "mAP50:95": e2e_map}}
 
+    # ---- e2e, targets as the dataset holds them: boxes + class ids on the host, encoded on the GPU
+    # (yh_encode_targets, the batched _encode_target of dataset.py:487-532).  Secondary figure: the
+    # reference's loader ships encoded (S,S,30) targets, which is what `e2e` above does.
+    from yolo_v1_b200 import encode_targets_csr
+
+    obj = tgt_h[..., 4] > 0                                   # (n, S, S) object cells, slot 0
+    idx = obj.nonzero()                                       # image-major, then row, then column
+    cellv = tgt_h[idx[:, 0], idx[:, 1], idx[:, 2]].to(torch.float64)
+    boxes_h = torch.stack([(idx[:, 2] + cellv[:, 0]) / S, (idx[:, 1] + cellv[:, 1]) / S, cellv[:, 2], cellv[:, 3]], 1)
+    cls_h = cellv[:, 10:].argmax(1).to(torch.int32)
+    off_h = torch.zeros(n + 1, dtype=torch.int64)
+    off_h[1:] = obj.reshape(n, -1).sum(1).cumsum(0)
+    boxes_h, cls_h, off_h = boxes_h.contiguous().pin_memory(), cls_h.pin_memory(), off_h.pin_memory()
+    enc, bad = encode_targets_csr(boxes_h.to(dev), cls_h.to(dev), off_h.to(dev))
+    targets_match = bool(torch.equal(enc, tgt_d)) and not bool(bad.any())
+    del enc, obj, idx, cellv
+
+    def e2e_boxes_step():
+        metric.reset()
+        copy_stream.wait_stream(main_stream)
+        landed = []
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in zip(bounds, bounds[1:]):
+                b0, b1 = int(off_h[lo]), int(off_h[hi])
+                p = pred_h[lo:hi].to(dev, non_blocking=True)
+                bx = boxes_h[b0:b1].to(dev, non_blocking=True)
+                cl = cls_h[b0:b1].to(dev, non_blocking=True)
+                of = off_h[lo:hi + 1].to(dev, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+                landed.append((p, bx, cl, of, b0, ev))
+        losses = []
+        for p, bx, cl, of, b0, ev in landed:
+            main_stream.wait_event(ev)
+            for x in (p, bx, cl, of):
+                x.record_stream(main_stream)
+            t, _ = encode_targets_csr(bx, cl, of - b0)
+            losses.append((head_pass(p, t), p.shape[0]))
+        res = metric.compute()
+        total = sum(float(parts["total"]) * m for parts, m in losses) / n
+        return total, float(res["mAP50:95"])
+
+    e2e_boxes_step()
+    eb_ms, (eb_loss, eb_map) = timed(e2e_boxes_step, max(2, args.steps // 2))
+    box_bytes = n * IMG_BYTES + boxes_h.numel() * 8 + cls_h.numel() * 4 + (n + n_chunks) * 8
+    e2e["boxes_variant"] = {
+        "what": "same step with targets shipped as boxes + class ids (36 B per object + 8 B per image) and encoded "
+                "on the GPU by yh_encode_targets; predictions still come from the host",
+        "value": world * n / (eb_ms * 1e-3), "unit": "images/s", "ms_per_step": eb_ms,
+        "h2d_bytes_per_step": int(box_bytes), "encoded_targets_identical": targets_match,
+        "result_check": {"loss_total": eb_loss, "mAP50:95": eb_map}}
+
     # ---- per-stage kernels, timed alone with CUDA events on the launching stream
     stages = {}
     peaks = {}

@@ -9,9 +9,9 @@ from .inference import YOLOInference
 from .loss import YOLOLoss
 from .metrics import evaluate_model, mAPMetric
 from .schemas import BoundingBox, Detection
-from .targets import encode_target, encode_targets
+from .targets import encode_target, encode_targets, encode_targets_csr
 
 __version__ = "0.1.0"
 
 __all__ = ["BoundingBox", "Detection", "YOLOInference", "YOLOLoss", "encode_target", "encode_targets",
-           "evaluate_model", "mAPMetric"]
+           "encode_targets_csr", "evaluate_model", "mAPMetric"]

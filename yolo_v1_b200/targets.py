@@ -39,17 +39,36 @@ def encode_targets(bboxes: Sequence[Sequence[Sequence[float]]], class_ids: Seque
     boxes_d = torch.tensor(flat_b if flat_b else [[0.0] * 4], dtype=torch.float64).reshape(-1, 4).to(dev)
     cls_d = torch.tensor(flat_c if flat_c else [0], dtype=torch.int32).to(dev)
     off_d = torch.tensor(off, dtype=torch.int64).to(dev)
-    out = torch.empty(n, S, S, B * 5 + C, dtype=torch.float32, device=dev)
-    bad = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
-    with _lib.on_device(dev):
-        rc = _lib.lib().yh_encode_targets(boxes_d.data_ptr(), cls_d.data_ptr(), off_d.data_ptr(), n, S, B, C,
-                                          out.data_ptr(), bad.data_ptr(), _lib.stream_ptr(dev))
-    _lib.check(rc, "yh_encode_targets")
+    out, bad = encode_targets_csr(boxes_d, cls_d, off_d, S, B, C)
     if n and bool(bad.any()):
         which = int(torch.nonzero(bad)[0])
         raise IndexError(f"sample {which}: a box centre or class id falls outside the target tensor "
                          "(the reference's _encode_target raises here too)")
     return out
+
+
+def encode_targets_csr(boxes: torch.Tensor, class_ids: torch.Tensor, offsets: torch.Tensor, S: int = 7, B: int = 2,
+                       C: int = 20):
+    """Tensor form for loaders that keep a batch's boxes flat on the device: boxes (M, 4) float64
+    (x_center, y_center, w, h), class_ids (M,) int32, offsets (N + 1,) int64 with image n owning
+    rows [offsets[n], offsets[n + 1]).  Returns (targets (N, S, S, B*5 + C) float32, bad (N,) uint8)
+    without reading anything back; bad[n] = 1 where the reference would raise for sample n."""
+    for t, name in ((boxes, "boxes"), (class_ids, "class_ids"), (offsets, "offsets")):
+        _lib.require_cuda(t, name)
+    if boxes.dtype is not torch.float64 or class_ids.dtype is not torch.int32 or offsets.dtype is not torch.int64:
+        raise TypeError("encode_targets_csr wants float64 boxes, int32 class_ids and int64 offsets")
+    dev = boxes.device
+    n = offsets.numel() - 1
+    if n < 0:
+        raise ValueError("offsets must hold N + 1 entries")
+    boxes, class_ids, offsets = boxes.contiguous(), class_ids.contiguous(), offsets.contiguous()
+    out = torch.empty(n, S, S, B * 5 + C, dtype=torch.float32, device=dev)
+    bad = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
+    with _lib.on_device(dev):
+        rc = _lib.lib().yh_encode_targets(boxes.data_ptr(), class_ids.data_ptr(), offsets.data_ptr(), n, S, B, C,
+                                          out.data_ptr(), bad.data_ptr(), _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_encode_targets")
+    return out, bad[:n]
 
 
 def encode_target(bboxes: Sequence[Sequence[float]], class_ids: Sequence[int], S: int = 7, B: int = 2, C: int = 20,
