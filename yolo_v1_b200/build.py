@@ -39,16 +39,20 @@ def is_stale() -> bool:
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
+    extra = os.environ.get("YH_NVCC_EXTRA", "").split()  # experiments only, e.g. -DYH_SORT_LOOK=2
+    flags_file = LIB + ".flags"                          # a change of experiment flags is a rebuild too
+    last = open(flags_file).read() if os.path.exists(flags_file) else ""
+    if not force and not is_stale() and last == " ".join(extra):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    extra = os.environ.get("YH_NVCC_EXTRA", "").split()  # experiments only, e.g. -DYH_NO_PREFETCH
     cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources()
     res = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed building libyolohead.so")
+    with open(flags_file, "w") as f:
+        f.write(" ".join(extra))
     return LIB
 
 

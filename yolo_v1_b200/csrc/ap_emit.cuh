@@ -65,41 +65,59 @@ tile_bit_counts(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__
     }
 }
 
-// exclusive scan over tiles: one CTA per flag bit; a thread sums a short run of
-// consecutive tiles, the CTA scans the 1,024 sums, the thread writes its run back
+// exclusive scan over tiles: one CTA per EIGHT flag bits (one 32-byte sector of a tile's row, so
+// every access is a full sector and no two CTAs write the same one); a thread sums a short run of
+// consecutive tiles, the CTA scans the 1,024 sums per bit, the thread writes its run back
+constexpr int kScanCols = 8;
 __global__ void __launch_bounds__(1024)
 scan_tile_bits(unsigned *__restrict__ tile_bits, int ntiles, ApCtl *__restrict__ ap) {
-    __shared__ unsigned s_w[32];
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    __shared__ unsigned s_w[kScanCols][32];
+    const int b0 = blockIdx.x * kScanCols, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const int per = (ntiles + 1023) / 1024;
     const int t0 = tid * per, t1 = min(ntiles, t0 + per);
-    unsigned sum = 0;
-    for (int t = t0; t < t1; ++t) sum += tile_bits[(size_t)t * kMaxBits + b];
-    unsigned inc = sum;
+    unsigned sum[kScanCols];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += u;
+    for (int j = 0; j < kScanCols; ++j) sum[j] = 0;
+    for (int t = t0; t < t1; ++t) {
+        const uint4 *row = reinterpret_cast<const uint4 *>(tile_bits + (size_t)t * kMaxBits + b0);
+        const uint4 a = row[0], b = row[1];
+        sum[0] += a.x, sum[1] += a.y, sum[2] += a.z, sum[3] += a.w;
+        sum[4] += b.x, sum[5] += b.y, sum[6] += b.z, sum[7] += b.w;
     }
-    if (lane == 31) s_w[wp] = inc;
+    unsigned inc[kScanCols];
+#pragma unroll
+    for (int j = 0; j < kScanCols; ++j) {
+        inc[j] = sum[j];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned u = __shfl_up_sync(0xffffffffu, inc[j], o);
+            if (lane >= o) inc[j] += u;
+        }
+        if (lane == 31) s_w[j][wp] = inc[j];
+    }
     __syncthreads();
-    if (wp == 0) {
-        const unsigned x = s_w[lane];
+    if (wp < kScanCols) {  // warp j scans the 32 warp totals of bit b0 + j
+        const unsigned x = s_w[wp][lane];
         unsigned xi = x;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const unsigned u = __shfl_up_sync(0xffffffffu, xi, o);
             if (lane >= o) xi += u;
         }
-        s_w[lane] = xi - x;
-        if (lane == 31) ap->bit_total[b] = xi;
+        s_w[wp][lane] = xi - x;
+        if (lane == 31) ap->bit_total[b0 + wp] = xi;
     }
     __syncthreads();
-    unsigned run = s_w[wp] + inc - sum;
+    unsigned run[kScanCols];
+#pragma unroll
+    for (int j = 0; j < kScanCols; ++j) run[j] = s_w[j][wp] + inc[j] - sum[j];
     for (int t = t0; t < t1; ++t) {
-        const unsigned c = tile_bits[(size_t)t * kMaxBits + b];
-        tile_bits[(size_t)t * kMaxBits + b] = run;
-        run += c;
+        uint4 *row = reinterpret_cast<uint4 *>(tile_bits + (size_t)t * kMaxBits + b0);
+        const uint4 a = row[0], b = row[1];
+        row[0] = make_uint4(run[0], run[1], run[2], run[3]);
+        row[1] = make_uint4(run[4], run[5], run[6], run[7]);
+        run[0] += a.x, run[1] += a.y, run[2] += a.z, run[3] += a.w;
+        run[4] += b.x, run[5] += b.y, run[6] += b.z, run[7] += b.w;
     }
 }
 

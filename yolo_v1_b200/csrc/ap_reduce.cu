@@ -169,6 +169,9 @@ extern "C" int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key
 }
 
 // ======================================================================= sort
+#ifndef YH_HIST_CTAS_PER_SM
+#define YH_HIST_CTAS_PER_SM 4
+#endif
 namespace yh {
 
 struct SortCtl {                  // lives at the head of the workspace, zeroed per call
@@ -211,6 +214,12 @@ __device__ __forceinline__ unsigned digit_of(uint64_t key, uint64_t val, int pas
     }
     return d & 0xffu;
 }
+// (class << nb) | key[lo, lo+nb) as one word: digit p is then bits [8p, 8p+8).  Needs nb + 5 <= 64.
+constexpr int kCompositeMaxBits = 59;
+__device__ __forceinline__ uint64_t composite_of(uint64_t key, uint64_t val, const KeyPlan &pl) {
+    const uint64_t mask = pl.nb ? (~0ull >> (64 - pl.nb)) : 0ull;
+    return ((key >> pl.lo) & mask) | (((val >> 56) & 31ull) << pl.nb);
+}
 __device__ __forceinline__ int64_t count_of(int64_t cap, const int64_t *dev) {
     if (dev == nullptr) return cap;
     const int64_t m = *dev;
@@ -223,16 +232,36 @@ key_range(const uint64_t *__restrict__ key, int64_t Mcap, const int64_t *__restr
           SortCtl *__restrict__ ctl) {
     const int64_t M = count_of(Mcap, Mdev);
     uint64_t o = 0, n = 0;
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < M; i += (int64_t)gridDim.x * 256) {
+    // four independent loads per thread and round: the kernel is latency-bound otherwise
+    const int64_t stride = (int64_t)gridDim.x * 256;
+    int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    for (; i + 3 * stride < M; i += 4 * stride) {
+        const uint64_t k0 = __ldg(key + i), k1 = __ldg(key + i + stride), k2 = __ldg(key + i + 2 * stride),
+                       k3 = __ldg(key + i + 3 * stride);
+        o |= (k0 | k1) | (k2 | k3);
+        n |= ~((k0 & k1) & (k2 & k3));
+    }
+    for (; i < M; i += stride) {
         const uint64_t k = __ldg(key + i);
         o |= k;
         n |= ~k;
     }
+    // one pair of global atomics per CTA: they all hit the same two words and serialise in L2
+    __shared__ unsigned s_or[4];
+    if (threadIdx.x < 4) s_or[threadIdx.x] = 0;
+    __syncthreads();
     const unsigned olo = __reduce_or_sync(0xffffffffu, (unsigned)o), ohi = __reduce_or_sync(0xffffffffu, (unsigned)(o >> 32));
     const unsigned nlo = __reduce_or_sync(0xffffffffu, (unsigned)n), nhi = __reduce_or_sync(0xffffffffu, (unsigned)(n >> 32));
     if ((threadIdx.x & 31) == 0) {
-        atomicOr(&ctl->key_or, ((unsigned long long)ohi << 32) | olo);
-        atomicOr(&ctl->key_nand, ((unsigned long long)nhi << 32) | nlo);
+        atomicOr(&s_or[0], olo);
+        atomicOr(&s_or[1], ohi);
+        atomicOr(&s_or[2], nlo);
+        atomicOr(&s_or[3], nhi);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        atomicOr(&ctl->key_or, ((unsigned long long)s_or[1] << 32) | s_or[0]);
+        atomicOr(&ctl->key_nand, ((unsigned long long)s_or[3] << 32) | s_or[2]);
     }
 }
 
@@ -247,10 +276,28 @@ digit_histograms(const uint64_t *__restrict__ key, const uint64_t *__restrict__ 
     for (int i = threadIdx.x; i < kPasses * 256; i += 256) (&s_h[0][0])[i] = 0;
     if (threadIdx.x < 32) s_c[threadIdx.x] = 0;
     __syncthreads();
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < M; i += (int64_t)gridDim.x * 256) {
-        const uint64_t k = __ldg(key + i), v = __ldg(val + i);
-        for (int p = 0; p < pl.npasses; ++p) atomicAdd(&s_h[p][digit_of(k, v, p, pl)], 1u);
-        atomicAdd(&s_c[(unsigned)(v >> 56) & 31u], 1u);
+    const int64_t stride = (int64_t)gridDim.x * 256;
+    for (int64_t i0 = (int64_t)blockIdx.x * 256 + threadIdx.x; i0 < M; i0 += 4 * stride) {
+        uint64_t k[4], v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {  // all eight loads in flight before the first atomic
+            const int64_t i = i0 + u * stride;
+            k[u] = i < M ? __ldg(key + i) : 0;
+            v[u] = i < M ? __ldg(val + i) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (i0 + u * stride >= M) break;
+            if (pl.nb <= kCompositeMaxBits) {
+                const uint64_t comp = composite_of(k[u], v[u], pl);
+#pragma unroll
+                for (int p = 0; p < kPasses; ++p)
+                    if (p < pl.npasses) atomicAdd(&s_h[p][(unsigned)(comp >> (8 * p)) & 0xffu], 1u);
+            } else {
+                for (int p = 0; p < pl.npasses; ++p) atomicAdd(&s_h[p][digit_of(k[u], v[u], p, pl)], 1u);
+            }
+            atomicAdd(&s_c[(unsigned)(v[u] >> 56) & 31u], 1u);
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < pl.npasses * 256; i += 256) {
@@ -504,7 +551,7 @@ extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int
     int launched = 1;
     if (M > 0) {
         int hb = (int)((M + 256 * 16 - 1) / (256 * 16));
-        if (hb > 148 * 8) hb = 148 * 8;
+        if (hb > 148 * YH_HIST_CTAS_PER_SM) hb = 148 * YH_HIST_CTAS_PER_SM;  // every CTA ends with global atomics
         key_range<<<hb, 256, 0, st>>>(key, M, M_dev, ctl);
         digit_histograms<<<hb, 256, 0, st>>>(key, flags, M, M_dev, ctl);
         digit_offsets<<<kPasses + 1, 256, 0, st>>>(ctl);
@@ -514,7 +561,7 @@ extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int
                                                           status + (size_t)p * L.ntiles * 256);
         const int nbits = 4 * T + 1;
         tile_bit_counts<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, ctl, nbits, tile_bits);
-        scan_tile_bits<<<kMaxBits, 1024, 0, st>>>(tile_bits, L.ntiles, apc);
+        scan_tile_bits<<<kMaxBits / kScanCols, 1024, 0, st>>>(tile_bits, L.ntiles, apc);
         class_start_bits<<<C, kSortThreads, 0, st>>>(flags, vb, M, M_dev, nbits, ctl, tile_bits, apc);
         emit_precisions<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, C, T, ctl, tile_bits, gt_count, apc);
         launched += 3 + kPasses + 4;
