@@ -216,6 +216,19 @@ loss_kernel(const typename Pair<T>::G *__restrict__ pred, const float2 *__restri
     }
     __syncthreads();
 
+    // The partials are published (four stores, fenced by the four threads that made them) BEFORE
+    // the gradient tile goes out: a fence after 15 KB of stores would hold every thread until
+    // all of them are acknowledged.
+    if (tid < 4) {
+        double s = 0.0;
+#pragma unroll
+        for (int wdx = 0; wdx < kTile / 32; ++wdx) s += s_red[wdx][tid];
+        partials[(size_t)blockIdx.x * 4 + tid] = s;
+        __threadfence();
+    }
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+
     if (grad != nullptr) {
 #pragma unroll
         for (int i = 0; i < kPairs; ++i) {
@@ -223,16 +236,6 @@ loss_kernel(const typename Pair<T>::G *__restrict__ pred, const float2 *__restri
             if (q < pairs_here) grad[pair0 + q] = Pair<T>::store(s_pred[q]);
         }
     }
-
-    if (tid < 4) {
-        double s = 0.0;
-#pragma unroll
-        for (int wdx = 0; wdx < kTile / 32; ++wdx) s += s_red[wdx][tid];
-        partials[(size_t)blockIdx.x * 4 + tid] = s;
-    }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
     __syncthreads();
     if (!s_last) return;
 
