@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=4096, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunks", type=int, default=8, help="mini-batches the e2e step streams from the host")
+    ap.add_argument("--no-graph", action="store_true", help="time the eager step only (no CapturedHeadStep)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "class_shard", "gather"],
                     help="N>1: how compute() makes the per-class order global (yolo_v1_b200/distributed.py)")
     return ap.parse_args()
@@ -243,6 +244,26 @@ def main():
     with ClockSampler(local) as clk:
         ms, (loss_total, map5095) = timed(lambda: step(pred_d.detach(), tgt_d), args.steps)
     launches = (_lib.lib().yh_launch_count() - l0) // args.steps
+    eager_ms, step_launch = ms, "eager (one Python call per stage)"
+    # The same step captured once as a CUDA graph (yolo_v1_b200.CapturedHeadStep: same kernels, same
+    # results, one launch + one read-back per step).  It is the `value` when it is available -- with
+    # N > 1 that needs the peer-memory exchange -- and the eager figure stays in the line beside it.
+    if not args.no_graph and (world == 1 or metric.mode == "peer"):
+        from yolo_v1_b200 import CapturedHeadStep
+
+        captured = CapturedHeadStep(crit, metric, pred_d, tgt_d)
+
+        def graph_step():
+            loss, res = captured.replay()
+            return float(loss["total"]), float(res["mAP50:95"])
+
+        for _ in range(max(args.warmup, 3)):
+            g_out = graph_step()
+        assert g_out == (loss_total, map5095), (g_out, loss_total, map5095)   # same bits as the eager step
+        with ClockSampler(local) as clk:
+            ms, (loss_total, map5095) = timed(graph_step, args.steps)
+        launches = captured.launches_per_replay
+        step_launch = "cuda_graph (CapturedHeadStep)"
     value = world * n / (ms * 1e-3)
 
     # ---- end to end: host buffers in, results out.  The batch arrives from pinned host memory
@@ -446,6 +467,8 @@ def main():
             "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cpu, "stages": stages,
             "result_check": {"loss_total": loss_total, "mAP50:95": map5095},
         }
+        line["step_launch"] = step_launch
+        line["eager"] = {"value": world * n / (eager_ms * 1e-3), "ms_per_step": eager_ms}
         if world > 1:
             line["exchange"] = {"mode": metric.mode, "overflow_fallbacks": metric.peer_fallbacks}
         print(json.dumps(line))

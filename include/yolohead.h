@@ -196,7 +196,9 @@ int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M, 
  * yh_peer_key_offset and capacity flag words at yh_peer_flags_offset.
  *
  * yh_exchange_records (collective over `world` ranks, every rank with the same capacity
- * and the same `epoch` > 0, which must grow by one per call): peer_block_host[r] is rank
+ * and the same `epoch`: either > 0 and growing by one per call, or 0 on every rank = "use the
+ * call counter the library keeps in the rank's own block" -- the form a CUDA-graph capture
+ * needs, where kernel arguments are frozen between replays): peer_block_host[r] is rank
  * r's block as mapped in THIS process (the rank's own allocation at [rank]).  On return
  * (stream order) this rank's block holds, in rank order and inside a rank in input
  * order, every record whose class this rank owns; info[0] = their count (use it as M_dev

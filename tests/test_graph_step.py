@@ -1,0 +1,123 @@
+"""CapturedHeadStep: the whole head step as one CUDA graph gives the eager step's results, bit for bit,
+also after new data is written into the captured tensors, and across ranks with the peer exchange."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _eager(pred, tgt, conf):
+    from yolo_v1_b200 import YOLOLoss, mAPMetric
+
+    p = pred.detach().clone().requires_grad_(True)
+    total, parts = YOLOLoss()(p, tgt)
+    total.backward()
+    m = mAPMetric(num_classes=20, conf_threshold=conf)
+    m.update(p.detach(), tgt)
+    return parts, {k: float(v) for k, v in m.compute().items()}, p.grad
+
+
+@pytest.mark.parametrize("profile,conf", [("correlated", 0.01), ("uniform", 0.3)])
+def test_replay_equals_eager_and_follows_new_data(profile, conf):
+    from yolo_v1_b200 import CapturedHeadStep, YOLOLoss, mAPMetric, synth
+
+    dev = torch.device("cuda")
+    n = 700
+    sets = []
+    for seed in (1, 2, 3):
+        t = synth.make_targets(n, seed=seed, p_obj=0.055, size_mix=True)
+        sets.append((synth.make_preds(n, profile, seed=seed, targets=t).to(dev), t.to(dev)))
+    pred, tgt = sets[0][0].clone(), sets[0][1].clone()
+    step = CapturedHeadStep(YOLOLoss(), mAPMetric(num_classes=20, conf_threshold=conf), pred, tgt)
+    assert step.launches_per_replay >= 10
+    for p_new, t_new in sets + sets[:1]:
+        pred.copy_(p_new)
+        tgt.copy_(t_new)
+        loss, res = step.replay()
+        want_loss, want_res, want_grad = _eager(p_new, t_new, conf)
+        assert loss == want_loss
+        assert {k: float(v) for k, v in res.items()} == want_res
+        assert torch.equal(step.grad, want_grad)
+
+
+def test_forward_only_capture():
+    from yolo_v1_b200 import CapturedHeadStep, YOLOLoss, mAPMetric, synth
+
+    dev = torch.device("cuda")
+    t = synth.make_targets(300, seed=9, p_obj=0.055, size_mix=True)
+    p = synth.make_preds(300, "correlated", seed=9, targets=t).to(dev)
+    step = CapturedHeadStep(YOLOLoss(), mAPMetric(num_classes=20), p, t.to(dev), backward=False)
+    loss, res = step.replay()
+    want_loss, want_res, _ = _eager(p, t.to(dev), 0.01)
+    assert loss == want_loss and {k: float(v) for k, v in res.items()} == want_res and step.grad is None
+
+
+# ----------------------------------------------------------------------------- two ranks, peer exchange in the graph
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, backend, q):
+    from yolo_v1_b200 import CapturedHeadStep, YOLOLoss, mAPMetric, synth
+    from yolo_v1_b200 import distributed as D
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dev = torch.device("cuda", rank % torch.cuda.device_count())
+    torch.cuda.set_device(dev)
+    kw = {"device_id": dev} if backend == "nccl" else {}
+    dist.init_process_group(backend, rank=rank, world_size=world, **kw)
+    try:
+        n = 640
+        lo, hi = D.shard_range(n, rank, world)
+        data = []
+        for seed in (4, 5):
+            t = synth.make_targets(n, seed=seed, p_obj=0.055, size_mix=True)
+            data.append((synth.make_preds(n, "correlated", seed=seed, targets=t)[lo:hi].to(dev), t[lo:hi].to(dev)))
+        pred, tgt = data[0][0].clone(), data[0][1].clone()
+        dm = D.DistributedMAP(mAPMetric(num_classes=20, conf_threshold=0.01), mode="auto")
+        step = CapturedHeadStep(YOLOLoss(), dm, pred, tgt)
+        out = []
+        for p_new, t_new in data + data[:1]:
+            pred.copy_(p_new)
+            tgt.copy_(t_new)
+            loss, res = step.replay()
+            out.append({k: float(v) for k, v in res.items()})
+        q.put((rank, out, step.launches_per_replay, dm.mode))
+        dm.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_exchange_inside_the_graph():
+    from yolo_v1_b200 import mAPMetric, synth
+
+    two = torch.cuda.device_count() >= 2
+    world, backend = 2, ("nccl" if two else "gloo")       # one GPU: the two ranks time-slice it
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, backend, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {r: (o, l, m) for r, o, l, m in (q.get(timeout=300) for _ in range(world))}
+    for p in procs:
+        p.join(60)
+    want = []
+    for seed in (4, 5):
+        t = synth.make_targets(640, seed=seed, p_obj=0.055, size_mix=True)
+        p = synth.make_preds(640, "correlated", seed=seed, targets=t)
+        m = mAPMetric(num_classes=20, conf_threshold=0.01)
+        m.update(p.cuda(), t.cuda())
+        want.append({k: float(v) for k, v in m.compute().items()})
+    want.append(want[0])
+    for r in range(world):
+        out, launches, mode = got[r]
+        assert mode == "peer" and launches >= 15
+        assert out == want

@@ -5,6 +5,7 @@ Drop-in counterparts of the reference's loss / metrics / inference modules
 hand-written CUDA kernels behind a C ABI (include/yolohead.h, libyolohead.so).
 The conv backbone stays stock PyTorch/cuDNN and is not part of this package.
 """
+from .graph import CapturedHeadStep
 from .inference import YOLOInference
 from .loss import YOLOLoss
 from .metrics import evaluate_model, mAPMetric
@@ -13,5 +14,5 @@ from .targets import encode_target, encode_targets, encode_targets_csr
 
 __version__ = "0.1.0"
 
-__all__ = ["BoundingBox", "Detection", "YOLOInference", "YOLOLoss", "encode_target", "encode_targets",
+__all__ = ["BoundingBox", "CapturedHeadStep", "Detection", "YOLOInference", "YOLOLoss", "encode_target", "encode_targets",
            "encode_targets_csr", "evaluate_model", "mAPMetric"]

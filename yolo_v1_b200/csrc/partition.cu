@@ -195,7 +195,8 @@ struct PeerCtl {
     unsigned ready[kMaxParts];
     unsigned done[kMaxParts];
     unsigned res_ready[kMaxParts];
-    unsigned pad[kMaxParts];
+    unsigned calls;              // exchanges this rank has started: the epoch when the caller passes 0
+    unsigned pad[kMaxParts - 1];
     long long row[kMaxParts][kMaxParts];
     int gt[kMaxParts][kGtWords];
     double res[kMaxParts][kResWords];
@@ -229,6 +230,12 @@ __device__ __forceinline__ unsigned long long now_ns() {
 }
 constexpr unsigned long long kWaitLimitNs = 4000000000ull;
 
+// epoch 0 = "the library's own call counter" (kept in the rank's block, advanced by peer_begin):
+// what a CUDA-graph replay needs, where kernel arguments are frozen
+__device__ __forceinline__ unsigned epoch_of(unsigned epoch, const PeerCtl *mine) {
+    return epoch ? epoch : *reinterpret_cast<const volatile unsigned *>(&mine->calls);
+}
+
 // true once *flag == epoch; false if the limit ran out
 __device__ __forceinline__ bool wait_flag(const unsigned *flag, unsigned epoch) {
     if (ld_acquire_sys(flag) == epoch) return true;
@@ -238,6 +245,16 @@ __device__ __forceinline__ bool wait_flag(const unsigned *flag, unsigned epoch) 
         if (now_ns() - t0 > kWaitLimitNs) return false;
     }
     return true;
+}
+
+// first kernel of an exchange: clears the per-call words and advances the call counter
+__global__ void peer_begin(ExchangeLocal *__restrict__ loc, PeerCtl *__restrict__ mine) {
+    if (threadIdx.x == 0) {
+        loc->finished_ctas = 0;
+        loc->timed_out = 0;
+        loc->overflow = 0;
+        mine->calls = mine->calls + 1;
+    }
 }
 
 // A CTA of the exchange owns a contiguous range of tiles (the same range in the count and in
@@ -327,7 +344,7 @@ peer_scan_publish(unsigned *__restrict__ cta_cnt, int nctas, const __grid_consta
     }
     __threadfence_system();
     __syncthreads();
-    if (tid < world) st_release_sys(&peers.ctl[tid]->ready[me], epoch);
+    if (tid < world) st_release_sys(&peers.ctl[tid]->ready[me], epoch_of(epoch, peers.ctl[me]));
 }
 
 __global__ void __launch_bounds__(kPartThreads)
@@ -343,6 +360,7 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
     const int64_t M = part_count_of(Mcap, Mdev);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const PeerCtl *mine = peers.ctl[me];
+    epoch = epoch_of(epoch, mine);
     if (tid == 0) s_state = 0;
     __syncthreads();
     // persistent CTAs: one wait for the peers' rows per CTA, one system fence at the end
@@ -463,6 +481,7 @@ peer_finish(const __grid_constant__ PeerTable peers, int world, int me, unsigned
     __shared__ int s_bad;
     const int tid = threadIdx.x;
     const PeerCtl *mine = peers.ctl[me];
+    epoch = epoch_of(epoch, mine);
     if (tid == 0) s_bad = 0;
     __syncthreads();
     if (tid < world && !wait_flag(&mine->done[tid], epoch)) s_bad = 1;
@@ -555,6 +574,7 @@ peer_sum_results(const __grid_constant__ PeerTable peers, int world, int me, uns
     __shared__ int s_bad;
     const int tid = threadIdx.x;
     const PeerCtl *mine = peers.ctl[me];
+    epoch = epoch_of(epoch, mine);
     if (tid == 0) s_bad = 0;
     for (int q = tid; q < world * n; q += blockDim.x) {
         const int d = q / n, i = q - d * n;
@@ -578,7 +598,7 @@ peer_sum_results(const __grid_constant__ PeerTable peers, int world, int me, uns
 extern "C" int yh_peer_sum(double *vec, int n, int err_index, int world, int rank, void *const *peer_block_host,
                            unsigned epoch, void *stream) {
     if (!vec || n < 1 || n > kResWords || world < 1 || world > kMaxParts || rank < 0 || rank >= world ||
-        !peer_block_host || epoch == 0) {
+        !peer_block_host) {
         set_error("yh_peer_sum: bad argument (n=%d world=%d rank=%d)", n, world, rank);
         return YH_ERR_BAD_ARG;
     }
@@ -690,7 +710,7 @@ extern "C" int yh_exchange_records(const uint64_t *key, const uint64_t *flags, i
         set_error("yh_exchange_records: C=%d / world=%d outside this build (C<=32, world<=%d)", C, world, kMaxParts);
         return YH_ERR_UNSUPPORTED;
     }
-    if (M < 0 || M >= (1ll << 31) || rank < 0 || rank >= world || capacity < 0 || epoch == 0 ||
+    if (M < 0 || M >= (1ll << 31) || rank < 0 || rank >= world || capacity < 0 ||
         !owner_of_class_host || !peer_block_host || !gt_count_local || !gt_count_global || !info || !workspace ||
         (M > 0 && (!key || !flags))) {
         set_error("yh_exchange_records: bad argument (M=%lld rank=%d world=%d)", (long long)M, rank, world);
@@ -728,16 +748,12 @@ extern "C" int yh_exchange_records(const uint64_t *key, const uint64_t *flags, i
     const int ntiles = (int)((M + kPartTile - 1) / kPartTile);
     int grid = ntiles < kExchangeCtas ? ntiles : kExchangeCtas;  // persistent: a CTA owns a contiguous tile range
     if (grid < 1) grid = 1;
-    cudaError_t e = cudaMemsetAsync(ws, 0, 256, st);
-    if (e != cudaSuccess) {
-        set_error("yh_exchange_records: memset: %s", cudaGetErrorString(e));
-        return (int)e;
-    }
+    peer_begin<<<1, 32, 0, st>>>(loc, peers.ctl[rank]);
     peer_count<<<grid, kPartThreads, 0, st>>>(flags, M, M_dev, tab, cta_cnt);
     peer_scan_publish<<<1, 1024, 0, st>>>(cta_cnt, grid, peers, world, rank, epoch, gt_count_local, 4 * C,
                                           (long long)n_images_local);
     peer_scatter<<<grid, kPartThreads, 0, st>>>(key, flags, M, M_dev, tab, cta_cnt, peers, world, rank, epoch,
                                                 (long long)capacity, loc);
     peer_finish<<<1, 256, 0, st>>>(peers, world, rank, epoch, 4 * C, loc, gt_count_global, info);
-    return check_launch("yh_exchange_records", 4);
+    return check_launch("yh_exchange_records", 5);
 }

@@ -154,14 +154,14 @@ class PeerExchange:
 
     Construction and close() are collective.  exchange() enqueues yh_exchange_records on
     the current stream and returns views of this rank's receive buffer; it never reads
-    anything back."""
+    anything back, and the epoch of the flag protocol is the library's own call counter on the
+    device (epoch argument 0), so an exchange can sit inside a captured CUDA graph."""
 
     def __init__(self, capacity: int, device: torch.device, group=None):
         lib = _lib.lib()
         self.group, self.device = group, device
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.capacity = int(max(capacity, 1024))
-        self.epoch = 0
         self.nbytes = int(lib.yh_peer_block_bytes(self.capacity))
         self._own = _lib.C.c_void_p()
         self._opened: List[int] = []
@@ -207,7 +207,6 @@ class PeerExchange:
     def exchange(self, key, flags, m: int, m_dev, owners: List[int], gt_count: torch.Tensor, n_images: int):
         """Returns (recv_key, recv_flags, gt_count_global int32 [4C], info int64 [4]); see yolohead.h."""
         lib, dev = _lib.lib(), self.device
-        self.epoch += 1
         need = int(lib.yh_exchange_workspace_bytes(int(m))) + 256
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
@@ -217,7 +216,7 @@ class PeerExchange:
         with _lib.on_device(dev):
             rc = lib.yh_exchange_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m),
                                          _lib.ptr(m_dev), tab, len(owners), self.world, self.rank, self._blocks,
-                                         self.capacity, self.epoch, gt_count.data_ptr(), int(n_images),
+                                         self.capacity, 0, gt_count.data_ptr(), int(n_images),
                                          gt_glob.data_ptr(), info.data_ptr(), self._ws.data_ptr(),
                                          self._ws.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "yh_exchange_records")
@@ -227,7 +226,7 @@ class PeerExchange:
         """vec[:n] (float64, in place) summed over the ranks through the peer blocks (yh_peer_sum)."""
         with _lib.on_device(self.device):
             rc = _lib.lib().yh_peer_sum(vec.data_ptr(), int(n), int(err_index), self.world, self.rank, self._blocks,
-                                        self.epoch, _lib.stream_ptr(self.device))
+                                        0, _lib.stream_ptr(self.device))
         _lib.check(rc, "yh_peer_sum")
 
     def close(self):
@@ -332,6 +331,33 @@ class DistributedMAP:
         gt_count = m._gt_count.clone() if m._gt_count is not None else torch.zeros(4 * C, dtype=torch.int32, device=dev)
         return key, flg, cap, running, gt_count
 
+    def enqueue_peer(self, dev, key, flg, cap, running, gt_count, n_images) -> torch.Tensor:
+        """Peer-mode compute() up to, not including, the host read: exchange, sort + AP, sum over
+        the ranks.  Returns the device vector finish_peer() decodes.  Capturable in a CUDA graph."""
+        m = self.metric
+        world = dist.get_world_size(self.group)
+        T, C = len(m.iou_thresholds), m.num_classes
+        px = self._peer_blocks(dev, cap)
+        rk, rf, gt_glob, info = px.exchange(key, flg, cap, running, class_owners(C, world), gt_count, n_images)
+        _, _, packed = head.ap_reduce(rk, rf, px.capacity, gt_glob, C, T, m_dev=info[:1])
+        if world > 1:
+            px.sum_results(packed, 4 * C * T + 3, 4 * C * T + 2)
+        return torch.cat([packed, info.to(torch.float64)])
+
+    def finish_peer(self, vec: torch.Tensor) -> Optional[Dict[str, float]]:
+        """Host side of a peer-mode compute(): the result dict, or None if a receive block overflowed."""
+        m = self.metric
+        T, C = len(m.iou_thresholds), m.num_classes
+        host = vec.cpu()
+        if host[-1] != 0:
+            raise _lib.YoloHeadError("yh_exchange_records: a rank of the group did not show up within 4 s")
+        if host[-2] != 0:
+            return None
+        if int(host[-3]) == 0:
+            return {"mAP50:95": 0.0, "mAP50": 0.0, "mAP75": 0.0, "precision": 0.0, "recall": 0.0}
+        ap, tp_total, n_pred, gtc = head.unpack_ap(host[:-4], C, T)
+        return m._results(ap, tp_total, n_pred, gtc, int(gtc[0].sum()), T, C)
+
     def compute(self) -> Dict[str, float]:
         m, g = self.metric, self.group
         world = dist.get_world_size(g)
@@ -349,19 +375,9 @@ class DistributedMAP:
                 warnings.warn(f"DistributedMAP: peer-memory exchange unavailable ({e}); using the NCCL exchange")
                 self.mode = "class_shard"
         if self.mode == "peer":
-            px = self._peer_blocks(dev, cap)
-            rk, rf, gt_glob, info = px.exchange(key, flg, cap, running, class_owners(C, world), gt_count, n_images)
-            _, _, packed = head.ap_reduce(rk, rf, px.capacity, gt_glob, C, T, m_dev=info[:1])
-            if world > 1:
-                px.sum_results(packed, 4 * C * T + 3, 4 * C * T + 2)
-            host = torch.cat([packed, info.to(torch.float64)]).cpu()
-            if host[-1] != 0:
-                raise _lib.YoloHeadError("yh_exchange_records: a rank of the group did not show up within 4 s")
-            if host[-2] == 0:
-                if int(host[-3]) == 0:
-                    return {"mAP50:95": 0.0, "mAP50": 0.0, "mAP75": 0.0, "precision": 0.0, "recall": 0.0}
-                ap, tp_total, n_pred, gtc = head.unpack_ap(host[:-4], C, T)
-                return m._results(ap, tp_total, n_pred, gtc, int(gtc[0].sum()), T, C)
+            res = self.finish_peer(self.enqueue_peer(dev, key, flg, cap, running, gt_count, n_images))
+            if res is not None:
+                return res
             self.peer_fallbacks += 1           # a receive block was too small: NCCL path now, larger blocks next
         # ground-truth counts and the image count travel in one all-reduce
         glob = torch.cat([gt_count.to(torch.int64),

@@ -1,0 +1,121 @@
+"""CapturedHeadStep -- one CUDA graph for a whole head step on fixed tensors.
+
+A validation / benchmarking loop that runs the same shapes over and over spends a
+visible share of each step (about 0.2 of 1.4 ms at 65,536 images) in Python between
+the ~25 kernel launches of
+
+    loss, parts = criterion(predictions, targets);  loss.backward()
+    metric.reset();  metric.update(predictions, targets);  results = metric.compute()
+
+Every call on that path only enqueues work on the current stream (include/yolohead.h:
+no allocation, no synchronisation, sizes and counts stay on the device), so the whole
+sequence -- loss forward + backward, decode + NMS + TP/FP, compaction, the multi-GPU
+record exchange over peer memory when the metric is a DistributedMAP in "peer" mode,
+sort and AP -- can be captured once and replayed with a single launch.  replay() then
+costs one graph launch and one 7 KB device->host copy.
+
+The tensors are captured by address: write new data INTO `predictions` / `targets`
+(`.copy_()`), or let the model write its output there, and call replay().  The
+reference has no counterpart (its step is Python loops); results are the same dicts
+`YOLOLoss.forward` and `mAPMetric.compute` return.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from .loss import _KEYS, YOLOLoss, _YoloLossFn
+from .metrics import mAPMetric
+
+
+class CapturedHeadStep:
+    def __init__(self, criterion: YOLOLoss, metric, predictions: torch.Tensor, targets: torch.Tensor,
+                 backward: bool = True, warmup: int = 2):
+        _lib.require_cuda(predictions, "predictions")
+        _lib.require_cuda(targets, "targets")
+        self.criterion, self.metric = criterion, metric
+        self.predictions, self.targets = predictions, targets
+        self.backward = backward
+        self.grad: Optional[torch.Tensor] = None        # d loss / d predictions after replay()
+        self._dist = not isinstance(metric, mAPMetric)  # a DistributedMAP wrapping one
+        if self._dist and metric.mode not in ("peer", "auto"):
+            raise _lib.YoloHeadError("CapturedHeadStep needs the peer-memory exchange (mode 'peer' or 'auto'): the "
+                                     "NCCL exchange reads its split sizes on the host")
+        self.recaptures = 0
+        dev = predictions.device
+        # eager runs first: workspaces, peer blocks and lazily created state exist before the capture
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            if self._dist:        # one plain compute() resolves "auto" and sizes the receive blocks
+                metric.reset()
+                metric.update(predictions.detach(), targets)
+                metric.compute()
+                if metric.mode != "peer":
+                    raise _lib.YoloHeadError("peer-memory exchange unavailable on this box: run the step eagerly")
+            for _ in range(max(warmup, 1)):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self._capture()
+
+    def _capture(self):
+        lib = _lib.lib()
+        self.graph = torch.cuda.CUDAGraph()
+        before = lib.yh_launch_count()
+        with torch.cuda.graph(self.graph):
+            self._out = self._enqueue()
+        self.launches_per_replay = int(lib.yh_launch_count() - before)   # this library's kernels in the graph
+
+    # ---------------------------------------------------------------- the step, enqueue only
+    def _inner(self) -> mAPMetric:
+        return self.metric.metric if self._dist else self.metric
+
+    def _enqueue(self) -> torch.Tensor:
+        c = self.criterion
+        p = self.predictions.detach().requires_grad_(self.backward)
+        total, parts = _YoloLossFn.apply(p, self.targets, c.S, c.B, c.C, c.lambda_coord, c.lambda_noobj)
+        if self.backward:
+            total.backward()
+            self.grad = p.grad
+        self.metric.reset()
+        self.metric.update(p.detach(), self.targets)
+        if self._dist:
+            dm, m = self.metric, self._inner()
+            key, flg, cap, running, gt_count = dm._local_records(p.device)
+            n_images = sum(ch.n for ch in m._chunks)
+            vec = dm.enqueue_peer(p.device, key, flg, cap, running, gt_count, n_images)
+        else:
+            vec = self.metric._enqueue_reduce()
+        return torch.cat([vec, parts.to(torch.float64)])
+
+    def _decode(self, host: torch.Tensor):
+        loss = dict(zip(_KEYS, host[-5:].tolist()))
+        if self._dist:
+            return loss, self.metric.finish_peer(host[:-5])
+        return loss, self.metric._results_from_packed(host[:-5])
+
+    def _eager(self):
+        loss, res = self._decode(self._enqueue().cpu())
+        if res is None:           # receive blocks too small for this data: the eager compute() grows them
+            res = self.metric.compute()
+        return loss, res
+
+    # ---------------------------------------------------------------- public
+    def replay(self) -> Tuple[Dict[str, float], Dict[str, float]]:
+        """Run the captured step on whatever `predictions` / `targets` hold now.
+        Returns (loss_dict, metric results), as criterion(...)[1] and metric.compute() would."""
+        self.graph.replay()
+        loss, res = self._decode(self._out.cpu())
+        if res is None:
+            # A skewed class mix overflowed the peer receive blocks (every rank sees it, nothing was
+            # moved).  The metric's chunks are the graph's own tensors, so the eager compute() sees this
+            # step's data: it takes the NCCL exchange and re-creates larger blocks (collective), and the
+            # step is captured again against them.
+            res = self.metric.compute()
+            torch.cuda.synchronize(self.predictions.device)
+            self._capture()
+            self.recaptures += 1
+        return loss, res

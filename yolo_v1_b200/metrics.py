@@ -176,9 +176,9 @@ class mAPMetric:
             n_gt_total = int(gt_count.reshape(4, C)[0].sum())
         return self._results(ap, tp_total, n_pred, gt_count.reshape(4, C), n_gt_total, T, C)
 
-    def _reduce_chunks(self):
-        """Device records -> AP table.  Nothing is read back before the one packed copy at the end:
-        the batches are compacted into one buffer behind a device-side running count, and
+    def _enqueue_reduce(self) -> torch.Tensor:
+        """Device records -> packed AP result, all enqueued, nothing read back (capturable in a CUDA
+        graph): the batches are compacted into one buffer behind a device-side running count, and
         yh_ap_reduce takes that count from the device."""
         T, C = len(self.iou_thresholds), self.num_classes
         dev = self._device
@@ -188,8 +188,17 @@ class mAPMetric:
         running = torch.zeros(1, dtype=torch.int64, device=dev)
         for ch in self._chunks:
             head.compact_records(ch, key, flg, running)
-        _, _, packed = head.ap_reduce(key, flg, cap, self._gt_count, C, T, m_dev=running)
+        return head.ap_reduce(key, flg, cap, self._gt_count, C, T, m_dev=running)[2]
+
+    def _results_from_packed(self, packed: torch.Tensor) -> Dict[str, float]:
+        """The one device->host copy of compute() and the result dict."""
+        T, C = len(self.iou_thresholds), self.num_classes
         ap, tp_total, n_pred, gt_count = head.unpack_ap(packed, C, T)
+        return self._results(ap, tp_total, n_pred, gt_count, int(gt_count[0].sum()), T, C)
+
+    def _reduce_chunks(self):
+        T, C = len(self.iou_thresholds), self.num_classes
+        ap, tp_total, n_pred, gt_count = head.unpack_ap(self._enqueue_reduce(), C, T)
         return ap, tp_total, n_pred, gt_count.reshape(-1)
 
     def _reduce_lists(self):
