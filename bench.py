@@ -251,19 +251,28 @@ def main():
     if not args.no_graph and (world == 1 or metric.mode == "peer"):
         from yolo_v1_b200 import CapturedHeadStep
 
-        captured = CapturedHeadStep(crit, metric, pred_d, tgt_d)
+        captured, why = None, ""
+        try:
+            captured = CapturedHeadStep(crit, metric, pred_d, tgt_d)
+        except Exception as e:  # noqa: BLE001 - the eager figure above stands, and says why
+            why = f"{type(e).__name__}: {e}"
+        ok = torch.tensor([1 if captured is not None else 0], device=dev)
+        if world > 1:   # every rank replays, or none does
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 1:
+            def graph_step():
+                loss, res = captured.replay()
+                return float(loss["total"]), float(res["mAP50:95"])
 
-        def graph_step():
-            loss, res = captured.replay()
-            return float(loss["total"]), float(res["mAP50:95"])
-
-        for _ in range(max(args.warmup, 3)):
-            g_out = graph_step()
-        assert g_out == (loss_total, map5095), (g_out, loss_total, map5095)   # same bits as the eager step
-        with ClockSampler(local) as clk:
-            ms, (loss_total, map5095) = timed(graph_step, args.steps)
-        launches = captured.launches_per_replay
-        step_launch = "cuda_graph (CapturedHeadStep)"
+            for _ in range(max(args.warmup, 3)):
+                g_out = graph_step()
+            assert g_out == (loss_total, map5095), (g_out, loss_total, map5095)   # same bits as the eager step
+            with ClockSampler(local) as clk:
+                ms, (loss_total, map5095) = timed(graph_step, args.steps)
+            launches = captured.launches_per_replay
+            step_launch = "cuda_graph (CapturedHeadStep)"
+        else:
+            step_launch += f"; graph capture unavailable ({why or 'on another rank'})"
     value = world * n / (ms * 1e-3)
 
     # ---- end to end: host buffers in, results out.  The batch arrives from pinned host memory

@@ -374,7 +374,7 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
         long long before = 0, total = 0;
         if (tid < world)
             for (int r = 0; r < world; ++r) {
-                const long long c = mine->row[r][tid];
+                const long long c = __ldcv(&mine->row[r][tid]);  // written by a peer: never from L1
                 if (r < me) before += c;
                 total += c;
             }
@@ -490,15 +490,15 @@ peer_finish(const __grid_constant__ PeerTable peers, int world, int me, unsigned
     const bool overflow = loc->overflow != 0;
     for (int i = tid; i < n_gt; i += blockDim.x) {
         int s = 0;
-        for (int r = 0; r < world; ++r) s += mine->gt[r][i];
+        for (int r = 0; r < world; ++r) s += __ldcv(&mine->gt[r][i]);
         gt_global[i] = s;
     }
     if (tid == 0) {
         long long total = 0, images = 0;
         for (int r = 0; r < world; ++r) {
-            total += mine->row[r][me];
-            images += (long long)(((unsigned long long)(unsigned)mine->gt[r][kGtWords - 1] << 32) |
-                                  (unsigned)mine->gt[r][kGtWords - 2]);
+            total += __ldcv(&mine->row[r][me]);
+            images += (long long)(((unsigned long long)(unsigned)__ldcv(&mine->gt[r][kGtWords - 1]) << 32) |
+                                  (unsigned)__ldcv(&mine->gt[r][kGtWords - 2]));
         }
         info[0] = (bad || overflow) ? 0 : total;
         info[1] = images;
@@ -589,7 +589,7 @@ peer_sum_results(const __grid_constant__ PeerTable peers, int world, int me, uns
     __syncthreads();
     for (int i = tid; i < n; i += blockDim.x) {
         double s = 0.0;
-        for (int r = 0; r < world; ++r) s += mine->res[r][i];
+        for (int r = 0; r < world; ++r) s += __ldcv(&mine->res[r][i]);
         vec[i] = (i == err_index && s_bad) ? 1.0 : s;
     }
 }
