@@ -41,7 +41,9 @@ def test_class_owners_are_contiguous_blocks():
     for world in (1, 2, 3, 4, 8, 32):
         own = D.class_owners(20, world)
         assert len(own) == 20 and own == sorted(own) and max(own) < world
-    assert D.class_owners(20, 8) == [0, 0, 0, 1, 1, 1, 2, 2, 2, 3, 3, 3, 4, 4, 4, 5, 5, 5, 6, 6]
+    own = D.class_owners(20, 8)          # balanced: nobody idle, nobody above ceil(20 / 8)
+    assert own == [0, 0, 0, 1, 1, 2, 2, 2, 3, 3, 4, 4, 4, 5, 5, 6, 6, 6, 7, 7]
+    assert sorted(own.count(r) for r in range(8)) == [2, 2, 2, 2, 3, 3, 3, 3]
 
 
 def _records(rank, n):
