@@ -12,7 +12,7 @@ no allocation, no synchronisation, sizes and counts stay on the device), so the 
 sequence -- loss forward + backward, decode + NMS + TP/FP, compaction, the multi-GPU
 record exchange over peer memory when the metric is a DistributedMAP in "peer" mode,
 sort and AP -- can be captured once and replayed with a single launch.  replay() then
-costs one graph launch and one 7 KB device->host copy.
+costs one graph launch; the 7 KB device->host copy of the results is its last node.
 
 The tensors are captured by address: write new data INTO `predictions` / `targets`
 (`.copy_()`), or let the model write its output there, and call replay().  The
@@ -44,6 +44,7 @@ class CapturedHeadStep:
             raise _lib.YoloHeadError("CapturedHeadStep needs the peer-memory exchange (mode 'peer' or 'auto'): the "
                                      "NCCL exchange reads its split sizes on the host")
         self.recaptures = 0
+        self._host: Optional[torch.Tensor] = None       # pinned landing buffer of the packed results
         dev = predictions.device
         # eager runs first: workspaces, peer blocks and lazily created state exist before the capture
         side = torch.cuda.Stream(device=dev)
@@ -67,6 +68,7 @@ class CapturedHeadStep:
         before = lib.yh_launch_count()
         with torch.cuda.graph(self.graph):
             self._out = self._enqueue()
+            self._host.copy_(self._out, non_blocking=True)   # the read-back is a node of the graph too
         self.launches_per_replay = int(lib.yh_launch_count() - before)   # this library's kernels in the graph
 
     # ---------------------------------------------------------------- the step, enqueue only
@@ -98,7 +100,10 @@ class CapturedHeadStep:
         return loss, self.metric._results_from_packed(host[:-5])
 
     def _eager(self):
-        loss, res = self._decode(self._enqueue().cpu())
+        out = self._enqueue()
+        if self._host is None or self._host.numel() != out.numel():   # allocated outside the capture
+            self._host = torch.empty(out.numel(), dtype=torch.float64, pin_memory=True)
+        loss, res = self._decode(out.cpu())
         if res is None:           # receive blocks too small for this data: the eager compute() grows them
             res = self.metric.compute()
         return loss, res
@@ -108,7 +113,8 @@ class CapturedHeadStep:
         """Run the captured step on whatever `predictions` / `targets` hold now.
         Returns (loss_dict, metric results), as criterion(...)[1] and metric.compute() would."""
         self.graph.replay()
-        loss, res = self._decode(self._out.cpu())
+        torch.cuda.current_stream(self.predictions.device).synchronize()
+        loss, res = self._decode(self._host)
         if res is None:
             # A skewed class mix overflowed the peer receive blocks (every rank sees it, nothing was
             # moved).  The metric's chunks are the graph's own tensors, so the eager compute() sees this
