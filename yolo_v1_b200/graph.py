@@ -46,6 +46,7 @@ class CapturedHeadStep:
         self.recaptures = 0
         self._host: Optional[torch.Tensor] = None       # pinned landing buffer of the packed results
         dev = predictions.device
+        self._side = torch.cuda.Stream(device=dev)      # the loss branch of the step
         # eager runs first: workspaces, peer blocks and lazily created state exist before the capture
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -76,22 +77,33 @@ class CapturedHeadStep:
         return self.metric.metric if self._dist else self.metric
 
     def _enqueue(self) -> torch.Tensor:
+        """The step as two branches that join at the end: the metric chain on the current stream and
+        the loss (which shares nothing with it but its inputs) on a side stream forked after the
+        update kernel.  The loss kernel is bandwidth-bound while compaction, the record exchange
+        (flag waits, NVLink writes) and the small sort-setup kernels are latency-bound, so they
+        overlap instead of queueing behind each other."""
         c = self.criterion
+        dev = self.predictions.device
+        main = torch.cuda.current_stream(dev)
         p = self.predictions.detach().requires_grad_(self.backward)
-        total, parts = _YoloLossFn.apply(p, self.targets, c.S, c.B, c.C, c.lambda_coord, c.lambda_noobj)
-        if self.backward:
-            total.backward()
-            self.grad = p.grad
         self.metric.reset()
         self.metric.update(p.detach(), self.targets)
+        self._side.wait_stream(main)                     # fork (forking before the update kernel measures the same)
+        with torch.cuda.stream(self._side):
+            total, parts = _YoloLossFn.apply(p, self.targets, c.S, c.B, c.C, c.lambda_coord, c.lambda_noobj)
+            if self.backward:
+                total.backward()
+                self.grad = p.grad
+            parts64 = parts.to(torch.float64)
         if self._dist:
             dm, m = self.metric, self._inner()
-            key, flg, cap, running, gt_count = dm._local_records(p.device)
+            key, flg, cap, running, gt_count = dm._local_records(dev)
             n_images = sum(ch.n for ch in m._chunks)
-            vec = dm.enqueue_peer(p.device, key, flg, cap, running, gt_count, n_images)
+            vec = dm.enqueue_peer(dev, key, flg, cap, running, gt_count, n_images)
         else:
             vec = self.metric._enqueue_reduce()
-        return torch.cat([vec, parts.to(torch.float64)])
+        main.wait_stream(self._side)                     # join
+        return torch.cat([vec, parts64])
 
     def _decode(self, host: torch.Tensor):
         loss = dict(zip(_KEYS, host[-5:].tolist()))
