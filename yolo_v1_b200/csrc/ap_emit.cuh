@@ -152,6 +152,29 @@ class_start_bits(const uint64_t *__restrict__ val_a, const uint64_t *__restrict_
     }
 }
 
+constexpr int kEmitQueue = 128;  // queued true positives per warp between two drains
+
+__device__ __forceinline__ void emit_queue(const uint2 *__restrict__ qa, const unsigned short *__restrict__ qb, int n,
+                                           int lane, int C, int T, const int32_t *__restrict__ gt_count,
+                                           ApCtl *__restrict__ ap) {
+    for (int j = lane; j < n; j += 32) {
+        const uint2 it = qa[j];
+        const int c = qb[j] >> 8, b = qb[j] & 0xff;
+        const int s = b / T, t = b - s * T;
+        const unsigned ordinal = it.x;
+        const int ngt = gt_count[s * C + c];
+        const double prec = __ddiv_rn((double)ordinal, __dadd_rn((double)((long long)it.y + 1), 1e-6));
+        const double rec = __ddiv_rn((double)ordinal, (double)ngt);
+        int lvl = 0;
+#pragma unroll
+        for (int r = kLevels - 1; r >= 1; --r) {
+            const double level = (r == kLevels - 1) ? 1.0 : __dmul_rn((double)r, 0.1);
+            if (lvl == 0 && rec >= level) lvl = r;
+        }
+        atomicMax(&ap->binmax[(((size_t)s * C + c) * T + t) * kLevels + lvl],
+                  (unsigned long long)__double_as_longlong(prec));
+    }
+}
 // For every TP: ordinal within its class, rank within its class -> precision, recall
 // -> atomicMax into the highest recall level it reaches.
 __global__ void __launch_bounds__(kSortThreads)
@@ -160,6 +183,8 @@ emit_precisions(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__
                 const unsigned *__restrict__ tile_bits, const int32_t *__restrict__ gt_count,
                 ApCtl *__restrict__ ap) {
     __shared__ unsigned s_acc[kSortWarps][kMaxBits];
+    __shared__ uint2 s_qa[kSortWarps][kEmitQueue];
+    __shared__ unsigned short s_qb[kSortWarps][kEmitQueue];
     const int64_t M = count_of(Mcap, Mdev);
     if ((int64_t)blockIdx.x * kSortTile >= M) return;
     const uint64_t *val = sorted_flags(ctl, val_a, val_b);
@@ -188,6 +213,10 @@ emit_precisions(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__
         run[h] = r;
     }
     const unsigned le = (lane == 31) ? 0xffffffffu : ((2u << lane) - 1u);
+    // True positives are sparse and land on arbitrary lanes: each one is queued (ordinal, rank within its
+    // class, class, bit) and the queue is worked off by all 32 lanes, so the two fp64 divisions and the
+    // recall-level search of a TP never run with one active lane.
+    int queued = 0;
 #pragma unroll
     for (int i = 0; i < kSortItems; ++i) {
         const int64_t idx = first + 32 * i;
@@ -206,25 +235,26 @@ emit_precisions(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__
                 const unsigned m = __ballot_sync(0xffffffffu, (mine >> bb) & 1u);
                 const unsigned before = __shfl_sync(0xffffffffu, run[h], bb);
                 if (lane == bb) run[h] += __popc(m);
-                if ((mine >> bb) & 1u) {
-                    const int b = bb + 32 * h, s = b / T, t = b % T;
-                    const unsigned ordinal = before + __popc(m & le) - ap->seg_bits[c][b];
-                    const int64_t rank = idx - (int64_t)ctl->class_start[c];  // 0-based within class
-                    const int ngt = gt_count[s * C + c];
-                    const double prec = __ddiv_rn((double)ordinal, __dadd_rn((double)(rank + 1), 1e-6));
-                    const double rec = __ddiv_rn((double)ordinal, (double)ngt);
-                    int lvl = 0;
-#pragma unroll
-                    for (int r = kLevels - 1; r >= 1; --r) {
-                        const double level = (r == kLevels - 1) ? 1.0 : __dmul_rn((double)r, 0.1);
-                        if (lvl == 0 && rec >= level) lvl = r;
-                    }
-                    atomicMax(&ap->binmax[(((size_t)s * C + c) * T + t) * kLevels + lvl],
-                              (unsigned long long)__double_as_longlong(prec));
+                if (queued + 32 > kEmitQueue) {  // warp-uniform
+                    __syncwarp();
+                    emit_queue(s_qa[wp], s_qb[wp], queued, lane, C, T, gt_count, ap);
+                    __syncwarp();
+                    queued = 0;
                 }
+                if ((mine >> bb) & 1u) {
+                    const int b = bb + 32 * h;
+                    const unsigned ordinal = before + __popc(m & le) - ap->seg_bits[c][b];
+                    const unsigned rank = (unsigned)(idx - (int64_t)ctl->class_start[c]);  // 0-based within class
+                    const int at = queued + __popc(m & (le >> 1));
+                    s_qa[wp][at] = make_uint2(ordinal, rank);
+                    s_qb[wp][at] = (unsigned short)((c << 8) | b);
+                }
+                queued += __popc(m);
             }
         }
     }
+    __syncwarp();
+    emit_queue(s_qa[wp], s_qb[wp], queued, lane, C, T, gt_count, ap);
 }
 
 // ap[(s*C+c)*T+t]; totals[0] = TP of the overall pass, totals[1] = M
