@@ -226,6 +226,11 @@ __device__ __forceinline__ int64_t count_of(int64_t cap, const int64_t *dev) {
     return m < cap ? m : cap;
 }
 
+__global__ void __launch_bounds__(256) zero_fill(uint4 *__restrict__ p, size_t n16) {
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) p[i] = z;
+}
+
 // which key bits vary
 __global__ void __launch_bounds__(256)
 key_range(const uint64_t *__restrict__ key, int64_t Mcap, const int64_t *__restrict__ Mdev,
@@ -543,12 +548,15 @@ extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int
     unsigned *status = (unsigned *)(ws + L.status);
     unsigned *tile_bits = (unsigned *)(ws + L.tile_bits);
     uint64_t *kb = (uint64_t *)(ws + L.key_alt), *vb = (uint64_t *)(ws + L.val_alt);
-    cudaError_t e = cudaMemsetAsync(ws, 0, L.zero_end, st);
-    if (e != cudaSuccess) {
-        set_error("yh_ap_reduce: memset: %s", cudaGetErrorString(e));
-        return (int)e;
+    // zeroed by a kernel of ours rather than a memset node: inside a captured graph a memset does not
+    // inherit the stream's priority and would queue behind a concurrent lower-priority kernel
+    {
+        const size_t n16 = L.zero_end / 16;  // the zeroed prefix is a multiple of 256 bytes
+        int zb = (int)((n16 + 256 * 8 - 1) / (256 * 8));
+        if (zb > 148 * 8) zb = 148 * 8;
+        zero_fill<<<zb < 1 ? 1 : zb, 256, 0, st>>>(reinterpret_cast<uint4 *>(ws), n16);
     }
-    int launched = 1;
+    int launched = 2;
     if (M > 0) {
         int hb = (int)((M + 256 * 16 - 1) / (256 * 16));
         if (hb > 148 * YH_HIST_CTAS_PER_SM) hb = 148 * YH_HIST_CTAS_PER_SM;  // every CTA ends with global atomics

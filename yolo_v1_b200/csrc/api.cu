@@ -31,11 +31,17 @@ constexpr int kTicketSlots = 256;
 __device__ unsigned g_tickets[kTicketSlots];
 static std::atomic<unsigned> g_ticket_next{0};
 
+__global__ void zero_ticket(unsigned *t) { *t = 0u; }
+
 unsigned *fresh_ticket(cudaStream_t stream) {
     static unsigned *base = nullptr;
     if (base == nullptr) cudaGetSymbolAddress((void **)&base, g_tickets);
     unsigned *t = base + (g_ticket_next.fetch_add(1, std::memory_order_relaxed) % kTicketSlots);
+#ifdef YH_TICKET_MEMSET
     cudaMemsetAsync(t, 0, sizeof(unsigned), stream);
+#else
+    zero_ticket<<<1, 1, 0, stream>>>(t);  // a kernel, not a memset node: see yh_ap_reduce
+#endif
     return t;
 }
 

@@ -46,9 +46,14 @@ class CapturedHeadStep:
         self.recaptures = 0
         self._host: Optional[torch.Tensor] = None       # pinned landing buffer of the packed results
         dev = predictions.device
-        self._side = torch.cuda.Stream(device=dev)      # the loss branch of the step
+        # Two branches: the metric chain is captured on a high-priority stream, the loss on a normal
+        # one.  The loss kernel's 25,088 short CTAs would otherwise sit in front of every kernel of
+        # the metric chain queued after it; with the priorities the chain's CTAs take the slots the
+        # loss CTAs free, and the latency-bound sort passes run inside the bandwidth-bound loss.
+        self._main = torch.cuda.Stream(device=dev, priority=-1)
+        self._side = torch.cuda.Stream(device=dev, priority=0)
         # eager runs first: workspaces, peer blocks and lazily created state exist before the capture
-        side = torch.cuda.Stream(device=dev)
+        side = self._main
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             if self._dist:        # one plain compute() resolves "auto" and sizes the receive blocks
@@ -67,7 +72,7 @@ class CapturedHeadStep:
         lib = _lib.lib()
         self.graph = torch.cuda.CUDAGraph()
         before = lib.yh_launch_count()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.graph(self.graph, stream=self._main):
             self._out = self._enqueue()
             self._host.copy_(self._out, non_blocking=True)   # the read-back is a node of the graph too
         self.launches_per_replay = int(lib.yh_launch_count() - before)   # this library's kernels in the graph
