@@ -1,3 +1,4 @@
-python tools/fuzz_parity.py --rounds 150 2>&1 | tail -8
-python tools/sanitize.py 2>&1 | tail -3
-timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python tools/sanitize.py > gpurun_out/memcheck.log 2>&1; echo "memcheck rc=$?"; grep -c "Invalid\|Error" gpurun_out/memcheck.log; tail -3 gpurun_out/memcheck.log
+python -m pytest tests/test_gpu_edges.py tests/test_gpu_parity.py -x -q -m gpu 2>&1 | tail -2
+python tools/kernel_table.py 2>&1 | grep "radix\|^sum"
+PROFILE=realistic python tools/kernel_table.py 2>&1 | grep "radix\|^sum"
+python tools/time_ap.py 2>&1 | tail -1

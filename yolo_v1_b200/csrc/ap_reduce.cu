@@ -355,14 +355,20 @@ radix_pass(uint64_t *__restrict__ key_a, uint64_t *__restrict__ val_a, uint64_t 
     if (pass >= pl.npasses) return;
     const int64_t M = count_of(Mcap, Mdev);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const uint64_t *kin = (pass & 1) ? key_b : key_a, *vin = (pass & 1) ? val_b : val_a;
+    uint64_t *kout = (pass & 1) ? key_a : key_b, *vout = (pass & 1) ? val_a : val_b;
+    // Persistent CTAs: the grid is sized for the SMs, not for the record capacity (the count is only
+    // known on the device, and a CTA per possible tile means a tail of empty CTAs in every pass).
+    // Tiles are drawn in order from the pass's counter, so a tile's predecessors are always held by
+    // CTAs that are running or done -- what the look-back needs.
+  for (;;) {
+    __syncthreads();  // everybody is done with the previous tile's shared memory
     if (tid == 0) s_tile = atomicAdd(&ctl->tile_counter[pass], 1u);
     for (int i = tid; i < kSortWarps * 256; i += kSortThreads) (&s_hist[0][0])[i] = 0;
     __syncthreads();
     const unsigned tile = s_tile;
     const int64_t tile0 = (int64_t)tile * kSortTile;
     if (tile0 >= M) return;
-    const uint64_t *kin = (pass & 1) ? key_b : key_a, *vin = (pass & 1) ? val_b : val_a;
-    uint64_t *kout = (pass & 1) ? key_a : key_b, *vout = (pass & 1) ? val_a : val_b;
     const int64_t first = tile0 + wp * kWarpSpan + lane;
 
     uint64_t k[kSortItems], v[kSortItems];
@@ -482,6 +488,7 @@ radix_pass(uint64_t *__restrict__ key_a, uint64_t *__restrict__ val_a, uint64_t 
             vout[pos] = vv;
         }
     }
+  }
 }
 
 }  // namespace yh
@@ -564,9 +571,10 @@ extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int
         digit_histograms<<<hb, 256, 0, st>>>(key, flags, M, M_dev, ctl);
         digit_offsets<<<kPasses + 1, 256, 0, st>>>(ctl);
         // passes beyond the plan's count return at once (the count is only known on the device)
+        const int sort_grid = L.ntiles < 148 * YH_SORT_MINBLOCKS ? L.ntiles : 148 * YH_SORT_MINBLOCKS;
         for (int p = 0; p < kPasses; ++p)
-            radix_pass<<<L.ntiles, kSortThreads, 0, st>>>(key, flags, kb, vb, M, M_dev, p, ctl,
-                                                          status + (size_t)p * L.ntiles * 256);
+            radix_pass<<<sort_grid, kSortThreads, 0, st>>>(key, flags, kb, vb, M, M_dev, p, ctl,
+                                                           status + (size_t)p * L.ntiles * 256);
         const int nbits = 4 * T + 1;
         tile_bit_counts<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, ctl, nbits, tile_bits);
         scan_tile_bits<<<kMaxBits / kScanCols, 1024, 0, st>>>(tile_bits, L.ntiles, apc);
