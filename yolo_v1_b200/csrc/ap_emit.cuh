@@ -43,6 +43,7 @@ tile_bit_counts(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__
                 unsigned *__restrict__ tile_bits) {
     __shared__ unsigned s_acc[kSortWarps][kMaxBits];
     const int64_t M = count_of(Mcap, Mdev);
+    if ((int64_t)blockIdx.x * kSortTile >= M) return;  // rows of empty tiles are never read
     const uint64_t *val = sorted_flags(ctl, val_a, val_b);
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const int64_t first = (int64_t)blockIdx.x * kSortTile + wp * kWarpSpan + lane;
@@ -70,8 +71,11 @@ tile_bit_counts(const uint64_t *__restrict__ val_a, const uint64_t *__restrict__
 // consecutive tiles, the CTA scans the 1,024 sums per bit, the thread writes its run back
 constexpr int kScanCols = 8;
 __global__ void __launch_bounds__(1024)
-scan_tile_bits(unsigned *__restrict__ tile_bits, int ntiles, ApCtl *__restrict__ ap) {
+scan_tile_bits(unsigned *__restrict__ tile_bits, int64_t Mcap, const int64_t *__restrict__ Mdev,
+               ApCtl *__restrict__ ap) {
     __shared__ unsigned s_w[kScanCols][32];
+    // only the tiles that hold records (the count lives on the device; the capacity can be much larger)
+    const int ntiles = (int)((count_of(Mcap, Mdev) + kSortTile - 1) / kSortTile);
     const int b0 = blockIdx.x * kScanCols, tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const int per = (ntiles + 1023) / 1024;
     const int t0 = tid * per, t1 = min(ntiles, t0 + per);

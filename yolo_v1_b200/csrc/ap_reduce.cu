@@ -577,7 +577,7 @@ extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int
                                                            status + (size_t)p * L.ntiles * 256);
         const int nbits = 4 * T + 1;
         tile_bit_counts<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, ctl, nbits, tile_bits);
-        scan_tile_bits<<<kMaxBits / kScanCols, 1024, 0, st>>>(tile_bits, L.ntiles, apc);
+        scan_tile_bits<<<kMaxBits / kScanCols, 1024, 0, st>>>(tile_bits, M, M_dev, apc);
         class_start_bits<<<C, kSortThreads, 0, st>>>(flags, vb, M, M_dev, nbits, ctl, tile_bits, apc);
         emit_precisions<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, C, T, ctl, tile_bits, gt_count, apc);
         launched += 3 + kPasses + 4;
