@@ -8,7 +8,7 @@ import pytest
 import torch
 
 from oracle import c_oracle, results
-from yolo_v1_b200 import head, mAPMetric, synth
+from yolo_v1_b200 import _lib, head, mAPMetric, synth
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -180,7 +180,42 @@ def _ap_from_records(key, flags, gt_count, C, T):
     return ap
 
 
-@pytest.mark.parametrize("kind", ["full64", "equal", "narrow", "high_bits", "two_values", "one_record", "tile_edge"])
+def _sort_ctl(dev, m, C, T):
+    """(overflow, queued runs) of the last yh_ap_reduce on this device: SortCtl sits at the head of the
+    workspace (csrc/ap_reduce.cu: tile_counter[16], err, overflow, key_or, key_nand, work_count)."""
+    ws = head._ap_workspace(dev, _lib.lib().yh_ap_workspace_bytes(int(m), C, T))
+    w = ws[:96].cpu().numpy().view(np.uint32)
+    return int(w[17]), int(w[22])
+
+
+# short plan (four passes over the composite's leading 32 bits + fix_runs) and its fallback:
+#   short_sparse    50 varying key bits, no two records agree in the leading bits
+#   short_runs      128 leading values per class, random tails: every run is out of order, all shorter than 32
+#   short_equal     long runs of IDENTICAL keys next to ordinary ones: nothing to fix, no fallback
+#   short_clusters  4 leading values per class, random tails: runs of thousands -> radix_fallback
+#   short_mixed     mostly sparse, one long unordered run -> radix_fallback
+SHORT_KINDS = ["short_sparse", "short_runs", "short_equal", "short_clusters", "short_clusters42", "short_mixed"]
+
+
+def _check_sorted_arrays(key, flags, k_dev, f_dev, fell_back):
+    """The sort ping-pongs between the caller's arrays and the workspace; when the number of passes it ran is
+    even, the caller's arrays hold the result and must equal numpy's stable sort by (class, key) record for
+    record (the AP table alone would forgive a few misplaced neighbours)."""
+    vary = int(np.bitwise_or.reduce(key) & np.bitwise_or.reduce(~key))
+    nb = vary.bit_length() - ((vary & -vary).bit_length() - 1) if vary else 0
+    full = (nb + 5 + 7) // 8
+    passes = full if (nb > 59 or nb + 5 <= 32 or fell_back) else 4
+    if passes % 2:
+        return
+    cls = (flags >> np.uint64(56)).astype(np.int64)
+    order = np.lexsort((np.arange(len(key)), key, cls))
+    got_k, got_f = k_dev.cpu().numpy().view(np.uint64), f_dev.cpu().numpy().view(np.uint64)
+    bad = np.nonzero((got_k != key[order]) | (got_f != flags[order]))[0]
+    assert len(bad) == 0, (len(bad), bad[:8], [hex(int(x)) for x in got_k[bad[:4]]], [hex(int(x)) for x in key[order][bad[:4]]])
+
+
+@pytest.mark.parametrize("kind", ["full64", "equal", "narrow", "high_bits", "two_values", "one_record", "tile_edge"]
+                         + SHORT_KINDS)
 def test_ap_reduce_sort_plans(kind):
     rng = np.random.default_rng(len(kind) * 131 + ord(kind[0]))
     C, T = 20, 3
@@ -195,9 +230,25 @@ def test_ap_reduce_sort_plans(kind):
         key = rng.integers(0, 4, size=m).astype(np.uint64) << np.uint64(62)
     elif kind == "two_values":
         key = np.where(rng.random(m) < 0.5, np.uint64(5), np.uint64(1 << 40)).astype(np.uint64)
+    elif kind == "short_sparse":
+        key = np.uint64(0x3FD0_0000_0000_0000) + rng.integers(0, 1 << 50, size=m).astype(np.uint64)
+    elif kind == "short_runs":
+        key = (rng.integers(0, 128, size=m).astype(np.uint64) << np.uint64(42)) | rng.integers(0, 1 << 20, size=m).astype(np.uint64)
+    elif kind == "short_equal":
+        key = np.uint64(0x3FD0_0000_0000_0000) + rng.integers(0, 1 << 50, size=m).astype(np.uint64)
+        key[rng.random(m) < 0.5] = np.uint64(0x3FD0_0000_0000_0000) + np.uint64(12345 << 20)
+    elif kind == "short_clusters":      # 50 varying bits: the fallback runs 7 passes
+        key = (rng.integers(0, 4, size=m).astype(np.uint64) << np.uint64(48)) | rng.integers(0, 1 << 20, size=m).astype(np.uint64)
+    elif kind == "short_clusters42":    # 42 varying bits: 6 passes, the result lands in the caller's arrays
+        key = (rng.integers(0, 4, size=m).astype(np.uint64) << np.uint64(40)) | rng.integers(0, 1 << 15, size=m).astype(np.uint64)
+    elif kind == "short_mixed":
+        key = np.uint64(0x3FD0_0000_0000_0000) + rng.integers(0, 1 << 42, size=m).astype(np.uint64)
+        key[:200] = np.uint64(0x3FD0_0000_0000_0000) + np.uint64(777 << 15) + rng.integers(0, 1 << 15, size=200).astype(np.uint64)
     else:
         key = rng.integers(0, 2**64, size=m, dtype=np.uint64)
     cls = rng.integers(0, C, size=m).astype(np.uint64)
+    if kind == "short_mixed":
+        cls[:200] = 7
     bits = rng.integers(0, 1 << (4 * T + 1), size=m).astype(np.uint64)
     flags = (cls << np.uint64(56)) | bits
     gt_count = rng.integers(0, 200, size=4 * C).astype(np.int32) + 400
@@ -209,6 +260,14 @@ def test_ap_reduce_sort_plans(kind):
     ap, totals, packed = head.ap_reduce(k, f, m, g, C, T)
     np.testing.assert_allclose(ap.cpu().numpy(), want, rtol=1e-12, atol=0)
     assert int(totals[1]) == m and int(totals[0]) == int(((bits >> np.uint64(4 * T)) & np.uint64(1)).sum())
+    overflow, queued = _sort_ctl(g.device, m, C, T)
+    _check_sorted_arrays(key, flags, k, f, overflow != 0)
+    if kind in SHORT_KINDS:  # the path each case is meant to take
+        assert overflow == (1 if kind in ("short_clusters", "short_clusters42", "short_mixed") else 0), (overflow, queued)
+        if kind == "short_runs":
+            assert queued > 1000
+        if kind in ("short_sparse", "short_equal"):
+            assert queued == 0
     # same records, count supplied from the device with a larger capacity
     cap = m + 5000
     k2 = torch.zeros(cap, dtype=torch.int64, device=DEV); k2[:m] = torch.from_numpy(key.view(np.int64).copy()).to(DEV)

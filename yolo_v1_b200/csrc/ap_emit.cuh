@@ -4,9 +4,9 @@
 
 namespace yh {
 
-// the sorted records sit in buffer (npasses & 1): a = caller's arrays, b = workspace copies
+// the sorted records sit in buffer (passes run & 1): a = caller's arrays, b = workspace copies
 __device__ __forceinline__ const uint64_t *sorted_flags(const SortCtl *ctl, const uint64_t *a, const uint64_t *b) {
-    return (key_plan(ctl).npasses & 1) ? b : a;
+    return final_buffer(ctl) ? b : a;
 }
 
 struct ApCtl {                        // zeroed per call, follows SortCtl in the workspace
