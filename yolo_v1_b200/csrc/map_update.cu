@@ -210,44 +210,37 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         // ---- greedy TP/FP: an item is a TP at threshold t iff its best IoU >= t and no
         // earlier detection of its class claimed the same ground truth with IoU >= t
         // (metrics.py:406-413).  "Earlier" = lower sorted position = lower item index.
+        // One lane per (item, ground-truth subset): an image has few items (kept boxes whose
+        // class has a ground truth), so a lane per item leaves most of the warp idle.
+        const int n_work = 4 * n_items;
 #pragma unroll 1
-        for (int it = lane; it < n_items; it += 32) {
-            const unsigned mine = *reinterpret_cast<const unsigned *>(mo.bgt[it]);
-            if (mine == 0xffffffffu) continue;
-            const int k = mo.ik[it], c = mo.icls[it];
-            double rival[4] = {0.0, 0.0, 0.0, 0.0};  // best IoU an earlier item brought to the same ground truth
-            for (int e = it - 1; e >= 0 && mo.icls[e] == c; --e) {
-                const unsigned theirs = *reinterpret_cast<const unsigned *>(mo.bgt[e]);
-                const unsigned diff = theirs ^ mine;
-                if ((diff & 0xffu) && (diff & 0xff00u) && (diff & 0xff0000u) && (diff & 0xff000000u)) continue;
-                const int ke = mo.ik[e];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const unsigned g = (mine >> (8 * q)) & 0xffu;
-                    if (g == 255u || ((diff >> (8 * q)) & 0xffu)) continue;
-                    // subset 0: e's best over all sizes is g, so its IoU sits in g's bucket table
-                    const int bucket = q ? q : mo.gbucket[g];
-                    rival[q] = fmax(rival[q], bucket_iou(w, bucket)[ke]);
-                }
-            }
-            // best IoU per subset; NaN where the subset has no ground truth for this item (never >= t)
-            double best[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const unsigned g = (mine >> (8 * q)) & 0xffu;
-                const int bucket = q ? q : mo.gbucket[g == 255u ? 0 : g];
-                best[q] = g == 255u ? __longlong_as_double(0x7ff8000000000000ll) : bucket_iou(w, bucket)[k];
-            }
+        for (int base = 0; base < n_work; base += 32) {
+            const int wq = base + lane, q = lane & 3;
+            const bool act = wq < n_work;
+            const int it = act ? wq >> 2 : 0;
             uint64_t flags = 0;
+            const unsigned g = act ? mo.bgt[it][q] : 255u;  // my best ground truth in subset q
+            if (g != 255u) {
+                const int k = mo.ik[it], c = mo.icls[it];
+                // subset 0: the best over all sizes is g, so the IoU sits in g's bucket table
+                const double *tab = bucket_iou(w, q ? q : mo.gbucket[g]);
+                const double best = tab[k];
+                double rival = 0.0;  // best IoU an earlier item brought to the same ground truth
+                for (int e = it - 1; e >= 0 && mo.icls[e] == c; --e)
+                    if (mo.bgt[e][q] == g) rival = fmax(rival, tab[mo.ik[e]]);
+                unsigned bits = 0;
 #pragma unroll 1
-            for (int t = 0; t < T; ++t) {
-                const double th = s_thr[t];
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    if (best[q] >= th && !(rival[q] >= th)) flags |= 1ull << (q * T + t);
+                for (int t = 0; t < T; ++t) {
+                    const double th = s_thr[t];
+                    if (best >= th && !(rival >= th)) bits |= 1u << t;
+                }
+                flags = (uint64_t)bits << (q * T);
+                if (q == 0 && best >= 0.5 && !(rival >= 0.5)) flags |= 1ull << (4 * T);
             }
-            if (best[0] >= 0.5 && !(rival[0] >= 0.5)) flags |= 1ull << (4 * T);
-            mo.flags[mo.ipos[it]] = flags;
+            // the four subsets of an item sit on four neighbouring lanes
+            flags |= __shfl_xor_sync(kFull, flags, 1);
+            flags |= __shfl_xor_sync(kFull, flags, 2);
+            if (act && q == 0) mo.flags[mo.ipos[it]] = flags;
         }
         __syncwarp();
 
