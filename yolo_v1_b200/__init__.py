@@ -9,10 +9,11 @@ from .graph import CapturedHeadStep
 from .inference import YOLOInference
 from .loss import YOLOLoss
 from .metrics import evaluate_model, mAPMetric
+from .report import format_evaluation_report, write_results_file
 from .schemas import BoundingBox, Detection
 from .targets import encode_target, encode_targets, encode_targets_csr
 
 __version__ = "0.1.0"
 
 __all__ = ["BoundingBox", "CapturedHeadStep", "Detection", "YOLOInference", "YOLOLoss", "encode_target", "encode_targets",
-           "encode_targets_csr", "evaluate_model", "mAPMetric"]
+           "encode_targets_csr", "evaluate_model", "format_evaluation_report", "mAPMetric", "write_results_file"]

@@ -751,8 +751,11 @@ static ApLayout ap_layout(int64_t M, int C, int T) {
     size_t o = 0;
     L.ctl = o; o = up256(o + sizeof(SortCtl));
     L.apc = o; o = up256(o + sizeof(ApCtl) + sizeof(unsigned long long) * (size_t)4 * C * T * kLevels);
-    L.status = o; o = up256(o + sizeof(unsigned) * (size_t)kPasses * L.ntiles * 256);
-    L.zero_end = o;
+    // look-back status words, one row per pass; only the short plan's rows are zeroed up front
+    // (radix_fallback clears the rows it uses itself)
+    L.status = o;
+    L.zero_end = up256(o + sizeof(unsigned) * (size_t)kShortPasses * L.ntiles * 256);
+    o = up256(o + sizeof(unsigned) * (size_t)kPasses * L.ntiles * 256);
     L.tile_bits = o; o = up256(o + sizeof(unsigned) * (size_t)L.ntiles * kMaxBits);
     L.work_cap = (unsigned)(M / 8 > 4096 ? M / 8 : 4096);  // out-of-order runs the short plan may leave
     L.work = o; o = up256(o + sizeof(unsigned) * (size_t)L.work_cap);
