@@ -424,12 +424,15 @@ def main():
                                     "gbs": (IMG_BYTES + 128) * n / (t_decm * 1e-3) / 1e9}
     key, flg, off = head.compact_records(chunk)
     M = int(off[-1].item())
-    # radix passes the sort needs for these keys: bits that vary over the input + 5 class bits, 8 per pass
+    # radix passes the sort runs for these keys (csrc/ap_reduce.cu key_plan): bits that vary over the input
+    # + 5 class bits; more than 32 of them -> the short plan: four passes over the leading 32 bits, then one
+    # sweep over the keys (find_runs) that orders the few runs of equal leading bits
     kk = key[:M]
     k_np = kk.cpu().numpy().view(np.uint64)
     v_bits = int(np.bitwise_or.reduce(k_np) & np.bitwise_or.reduce(~k_np)) if M else 0
     nb = (v_bits.bit_length() - ((v_bits & -v_bits).bit_length() - 1)) if v_bits else 0
-    passes = (nb + 5 + 7) // 8
+    short_plan = 32 < nb + 5 <= 64
+    passes = 4 if short_plan else (nb + 5 + 7) // 8
 
     def ap_only():
         k2, f2 = key[:M].clone(), flg[:M].clone()
@@ -437,9 +440,11 @@ def main():
 
     t_clone = time_call(lambda: (key[:M].clone(), flg[:M].clone()))
     t_ap = time_call(ap_only) - t_clone
-    # key-range read 8 + histogram read 16 + passes x (read 16 + write 16) + two flag sweeps 8 + 8
-    ap_bytes = M * (8 + 16 + 32 * passes + 16)
-    stages["ap_reduce"] = {"ms": t_ap, "records": M, "radix_passes": passes, "bytes": ap_bytes,
+    # key-range read 8 + histogram read 16 + passes x (read 16 + write 16) + find_runs read 8 (short plan)
+    # + two flag sweeps 8 + 8
+    ap_bytes = M * (8 + 16 + 32 * passes + (8 if short_plan else 0) + 16)
+    stages["ap_reduce"] = {"ms": t_ap, "records": M, "radix_passes": passes, "key_bits": nb, "short_plan": short_plan,
+                           "bytes": ap_bytes,
                            "gbs": ap_bytes / (t_ap * 1e-3) / 1e9}
     t_cmp = time_call(lambda: head.compact_records(chunk))
     stages["compact_records"] = {"ms": t_cmp, "bytes": M * 32 + n * 4, "gbs": (M * 32 + n * 4) / (t_cmp * 1e-3) / 1e9}
