@@ -755,6 +755,21 @@ struct ApLayout {
     unsigned work_cap;
 };
 
+// CTAs of radix_fallback that are resident at once on the current device (cached per device)
+static int fallback_resident_ctas() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 1;
+    if (cached[dev] == 0) {
+        int sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radix_fallback, kSortThreads, 0);
+        if (per_sm > kFallbackCtasPerSm) per_sm = kFallbackCtasPerSm;
+        cached[dev] = (sms > 0 && per_sm > 0) ? sms * per_sm : 1;
+    }
+    return cached[dev];
+}
+
 static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 static ApLayout ap_layout(int64_t M, int C, int T) {
@@ -840,7 +855,9 @@ extern "C" int yh_ap_reduce(uint64_t *key, uint64_t *flags, int64_t M, const int
         if (fb > 148 * 8) fb = 148 * 8;
         find_runs<<<fb, 256, 0, st>>>(key, flags, M, M_dev, ctl, work, L.work_cap);
         fix_runs<<<148, 128, 0, st>>>(key, flags, M, M_dev, ctl, work, L.work_cap);
-        const int fall_grid = L.ntiles < 148 * kFallbackCtasPerSm ? L.ntiles : 148 * kFallbackCtasPerSm;
+        // the grid barrier needs every CTA resident: size the grid from what this device really holds
+        const int fall_cap = fallback_resident_ctas();
+        const int fall_grid = L.ntiles < fall_cap ? L.ntiles : fall_cap;
         radix_fallback<<<fall_grid, kSortThreads, 0, st>>>(key, flags, kb, vb, M, M_dev, ctl, status, L.ntiles);
         const int nbits = 4 * T + 1;
         tile_bit_counts<<<L.ntiles, kSortThreads, 0, st>>>(flags, vb, M, M_dev, ctl, nbits, tile_bits);
