@@ -214,12 +214,20 @@ def _check_sorted_arrays(key, flags, k_dev, f_dev, fell_back):
     assert len(bad) == 0, (len(bad), bad[:8], [hex(int(x)) for x in got_k[bad[:4]]], [hex(int(x)) for x in key[order][bad[:4]]])
 
 
+# the same at a size where radix_fallback's persistent CTAs each take several tiles per pass and its grid
+# barrier spans every SM (1.5 M records = 733 tiles): the two-cluster keys (6 passes, result in the caller's
+# arrays) and full 64-bit keys (9 passes, everything left to the fallback); and the short plan with ~2,000 runs
+BIG_KINDS = ["big:short_clusters42", "big:full64", "big:short_sparse"]
+
+
 @pytest.mark.parametrize("kind", ["full64", "equal", "narrow", "high_bits", "two_values", "one_record", "tile_edge"]
-                         + SHORT_KINDS)
+                         + SHORT_KINDS + BIG_KINDS)
 def test_ap_reduce_sort_plans(kind):
     rng = np.random.default_rng(len(kind) * 131 + ord(kind[0]))
     C, T = 20, 3
     m = {"one_record": 1, "tile_edge": 2048 * 3, "full64": 70_001}.get(kind, 30_000)
+    if kind.startswith("big:"):
+        kind, m = kind[4:], 1_500_000
     if kind == "full64":
         key = rng.integers(0, 2**64, size=m, dtype=np.uint64)
     elif kind == "equal":
@@ -266,7 +274,7 @@ def test_ap_reduce_sort_plans(kind):
         assert overflow == (1 if kind in ("short_clusters", "short_clusters42", "short_mixed") else 0), (overflow, queued)
         if kind == "short_runs":
             assert queued > 1000
-        if kind in ("short_sparse", "short_equal"):
+        if kind in ("short_sparse", "short_equal") and m <= 30_000:
             assert queued == 0
     # same records, count supplied from the device with a larger capacity
     cap = m + 5000
