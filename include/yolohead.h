@@ -243,6 +243,18 @@ int yh_exchange_records(const uint64_t *key, const uint64_t *flags, int64_t M, c
 int yh_encode_targets(const double *boxes, const int32_t *cls, const int64_t *offsets, int N, int S,
                       int B, int C, float *out, uint8_t *bad, void *stream);
 
+/* ------------------------------------------------ image preprocessing ----
+ * Replaces `self.transform(image)` of YOLOInference (src/yolo/inference.py:57-66, 88-101):
+ * torchvision Resize((out_h, out_w)) on a PIL RGB image (Pillow's bilinear resample: 22-bit
+ * fixed-point taps, horizontal then vertical pass, 8-bit rounding in between), ToTensor
+ * (/ 255) and Normalize((x - mean) / std), all in float32.  rgb = (H, W, 3) uint8 on the
+ * device, out = (3, out_h, out_w) float32, bit-identical to the reference's tensor.
+ * mean3 / std3 are HOST arrays of three floats.  Uses `workspace` (256-byte aligned) of
+ * yh_preprocess_workspace_bytes(H, W, out_h, out_w); 0 = shape not supported. */
+size_t yh_preprocess_workspace_bytes(int H, int W, int out_h, int out_w);
+int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, int out_w, const float *mean3,
+                       const float *std3, float *out, void *workspace, size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------- list-form entry points ----
  * The reference's helpers also accept arbitrary Python lists (tests call
  * _apply_nms / non_max_suppression / _calculate_iou / iou on hand-built boxes,

@@ -47,6 +47,13 @@ class YOLOInference:
         return Image.open(image_path).convert("RGB")
 
     def preprocess_image(self, image) -> torch.Tensor:
+        """(1, 3, 448, 448) float32 on the model's device (inference.py:88-101).  With the model on a GPU the
+        resize / scale / normalise runs there (yh_preprocess_rgb8, bit-identical to `self.transform`); a model
+        kept on the host gets the reference's torchvision transform, as the backbone is its business."""
+        if torch.device(self.device).type == "cuda":
+            from .preprocess import preprocess_pil
+
+            return preprocess_pil(image, self.device).unsqueeze(0)
         return self.transform(image).unsqueeze(0).to(self.device)
 
     # ---------------------------------------------------------------- pipeline
