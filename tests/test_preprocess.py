@@ -78,8 +78,10 @@ def test_cuda_matches_live_torchvision_random_sizes_and_other_targets():
     Image = pytest.importorskip("PIL.Image")
     from yolo_v1_b200 import preprocess
     rng = np.random.default_rng(11)
-    for r in range(40):
+    for r in range(42):
         h, w = int(rng.integers(1, 1500)), int(rng.integers(1, 1500))
+        if r >= 40:   # a span of input pixels too long for the staged horizontal pass: the unstaged kernel
+            h, w = 3, 61_000 + r
         oh, ow = ((448, 448), (224, 224), (300, 517))[r % 3]
         tf = transforms.Compose([transforms.Resize((oh, ow)), transforms.ToTensor(),
                                  transforms.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])])

@@ -91,6 +91,67 @@ pp_horizontal(const uint8_t *__restrict__ in, int H, int W, int OW, int ksize, c
     o[2] = (uint8_t)clip8(a2);
 }
 
+// The same pass with the input staged through shared memory: a CTA owns kHSeg consecutive output pixels of
+// one row, copies the span of input bytes they tap with aligned 4-byte loads (a row starts at an arbitrary
+// byte), and every thread then reads its taps from shared memory.  Used whenever the span fits 48 KB.
+constexpr int kHSeg = 128;
+__global__ void __launch_bounds__(kHSeg)
+pp_horizontal_staged(const uint8_t *__restrict__ in, int H, int W, int OW, int ksize, const int *__restrict__ bounds,
+                     const int *__restrict__ kk, uint8_t *__restrict__ out) {
+    extern __shared__ uint32_t s_words[];
+    const int xx0 = blockIdx.x * kHSeg, y = blockIdx.y, tid = threadIdx.x;
+    const int xlast = min(xx0 + kHSeg, OW) - 1;
+    const int p0 = bounds[2 * xx0], p1 = bounds[2 * xlast] + bounds[2 * xlast + 1];  // input pixels [p0, p1)
+    const uintptr_t first = (uintptr_t)in + ((size_t)y * W + p0) * 3, last = (uintptr_t)in + ((size_t)y * W + p1) * 3;
+    const uintptr_t a0 = first & ~(uintptr_t)3;
+    const uintptr_t buf_end = (uintptr_t)in + (size_t)H * W * 3;
+    const int nwords = (int)((last - a0 + 3) >> 2);
+    if (a0 + 4 * (uintptr_t)nwords <= buf_end) {
+        // four independent loads per thread and round: the copy is latency-bound otherwise
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a0);
+        int i = tid;
+        for (; i + 3 * kHSeg < nwords; i += 4 * kHSeg) {
+            const uint32_t v0 = __ldg(src + i), v1 = __ldg(src + i + kHSeg), v2 = __ldg(src + i + 2 * kHSeg),
+                           v3 = __ldg(src + i + 3 * kHSeg);
+            s_words[i] = v0;
+            s_words[i + kHSeg] = v1;
+            s_words[i + 2 * kHSeg] = v2;
+            s_words[i + 3 * kHSeg] = v3;
+        }
+        for (; i < nwords; i += kHSeg) s_words[i] = __ldg(src + i);
+    } else {  // the last words of the image: the one that would run past its end is read bytewise
+        for (int i = tid; i < nwords; i += kHSeg) {
+            const uintptr_t a = a0 + 4 * (uintptr_t)i;
+            uint32_t v;
+            if (a + 4 <= buf_end) {
+                v = __ldg(reinterpret_cast<const uint32_t *>(a));
+            } else {
+                v = 0;
+                for (int b = 0; b < 4 && a + b < buf_end; ++b)
+                    v |= (uint32_t)__ldg(reinterpret_cast<const uint8_t *>(a + b)) << (8 * b);
+            }
+            s_words[i] = v;
+        }
+    }
+    __syncthreads();
+    const int xx = xx0 + tid;
+    if (xx >= OW) return;
+    const int x0 = bounds[2 * xx], n = bounds[2 * xx + 1];
+    const int *k = kk + (size_t)xx * ksize;
+    const uint8_t *row = reinterpret_cast<const uint8_t *>(s_words) + (first - a0) + (size_t)(x0 - p0) * 3;
+    int a0c = 1 << (kPrecisionBits - 1), a1c = a0c, a2c = a0c;
+    for (int x = 0; x < n; ++x) {
+        const int c = __ldg(k + x);
+        a0c += (int)row[3 * x] * c;
+        a1c += (int)row[3 * x + 1] * c;
+        a2c += (int)row[3 * x + 2] * c;
+    }
+    uint8_t *o = out + ((size_t)y * OW + xx) * 3;
+    o[0] = (uint8_t)clip8(a0c);
+    o[1] = (uint8_t)clip8(a1c);
+    o[2] = (uint8_t)clip8(a2c);
+}
+
 struct Norm3 {
     float mean[3], std[3];
 };
@@ -179,7 +240,15 @@ extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, i
     const uint8_t *vin = rgb;
     if (W != out_w) {  // Pillow skips the horizontal pass when the width already matches
         pp_coeffs<<<(out_w + 127) / 128, 128, 0, st>>>(W, out_w, L.ph.ksize, bounds_h, kk_h);
-        pp_horizontal<<<dim3((out_w + 255) / 256, H), 256, 0, st>>>(rgb, H, W, out_w, L.ph.ksize, bounds_h, kk_h, tmp);
+        // input pixels a segment of kHSeg outputs can tap: its centres span kHSeg * scale, plus the support on both sides
+        const double scale = (double)W / (double)out_w;
+        const size_t span_px = (size_t)ceil(kHSeg * scale) + (size_t)L.ph.ksize + 2;
+        const size_t span_bytes = (span_px * 3 + 8 + 3) & ~(size_t)3;
+        if (span_bytes <= 48 * 1024)
+            pp_horizontal_staged<<<dim3((out_w + kHSeg - 1) / kHSeg, H), kHSeg, span_bytes, st>>>(
+                rgb, H, W, out_w, L.ph.ksize, bounds_h, kk_h, tmp);
+        else
+            pp_horizontal<<<dim3((out_w + 255) / 256, H), 256, 0, st>>>(rgb, H, W, out_w, L.ph.ksize, bounds_h, kk_h, tmp);
         vin = tmp;
         launched += 2;
     }
