@@ -118,3 +118,27 @@ def test_bad_arguments():
         preprocess.preprocess_rgb8(torch.zeros(4, 4, 3, dtype=torch.uint8))          # host tensor: no CPU path
     with pytest.raises(TypeError):
         preprocess.preprocess_rgb8(torch.zeros(4, 4, 3, device="cuda"))               # not uint8
+
+
+@gpu
+def test_predict_images_equals_predict_per_image(tmp_path):
+    Image = pytest.importorskip("PIL.Image")
+    from yolo_v1_b200 import YOLOInference
+
+    class Head(torch.nn.Module):          # a stand-in backbone: predictions are a fixed function of the input tensor
+        S, B = 7, 2
+
+        def forward(self, x):
+            feat = torch.nn.functional.adaptive_avg_pool2d(x, (7, 7)).permute(0, 2, 3, 1)     # (N, 7, 7, 3)
+            return torch.sigmoid(torch.cat([feat * (i + 1) for i in range(10)], dim=-1))      # (N, 7, 7, 30) in (0, 1)
+
+    eng = YOLOInference(Head(), device="cuda")
+    paths = []
+    for i, (h, w) in enumerate([(120, 160), (333, 500), (448, 448), (64, 31), (500, 375)]):
+        p = tmp_path / f"img{i}.png"
+        Image.fromarray(make_image(40 + i, h, w)).save(p)
+        paths.append(str(p))
+    many = eng.predict_images(paths, conf_threshold=0.3, batch_size=2)
+    assert len(many) == len(paths) and sum(len(d) for d in many) > 0
+    for p, dets in zip(paths, many):
+        assert dets == eng.predict(p, conf_threshold=0.3)

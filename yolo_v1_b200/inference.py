@@ -65,6 +65,20 @@ class YOLOInference:
             out = self.model(batch)
         return self.predict_batch(out[:1], conf_threshold, nms_threshold, class_names)[0]
 
+    def predict_images(self, image_paths, conf_threshold: float = 0.5, nms_threshold: float = 0.4,
+                       class_names: list[str] | None = None, batch_size: int = 64) -> list[list[Detection]]:
+        """predict() for many images (the loop of predict.py:128-185): every image is preprocessed to the
+        same (3, 448, 448) tensor, `batch_size` of them go through the model in one forward, and decode + NMS
+        of the whole batch is one launch.  Per image the same result as predict(path)."""
+        out: list[list[Detection]] = []
+        paths = list(image_paths)
+        for lo in range(0, len(paths), max(1, int(batch_size))):
+            batch = torch.cat([self.preprocess_image(self.load_image(p)) for p in paths[lo:lo + batch_size]])
+            with torch.no_grad():
+                pred = self.model(batch)
+            out.extend(self.predict_batch(pred, conf_threshold, nms_threshold, class_names))
+        return out
+
     def predict_batch(self, predictions: torch.Tensor, conf_threshold: float = 0.5, nms_threshold: float = 0.4,
                       class_names: list[str] | None = None) -> list[list[Detection]]:
         """Decode + NMS for a whole (N,S,S,B*5+C) batch in one launch; one list per image.
