@@ -33,8 +33,16 @@ __device__ __forceinline__ double bilinear_filter(double x) {
 
 // precompute_coeffs + normalize_coeffs_8bpc for one axis: thread xx owns output position xx.
 // bounds[2*xx] = first input index, bounds[2*xx + 1] = number of taps; kk[xx * ksize + x] = tap x.
+struct AxisArgs {
+    int in_size, out_size, ksize;
+    int *bounds, *kk;
+};
+// blockIdx.y picks the axis (both tables in one launch; an axis with out_size 0 is skipped)
 __global__ void __launch_bounds__(128)
-pp_coeffs(int in_size, int out_size, int ksize, int *__restrict__ bounds, int *__restrict__ kk) {
+pp_coeffs(const AxisArgs ax0, const AxisArgs ax1) {
+    const AxisArgs &ax = blockIdx.y ? ax1 : ax0;
+    const int in_size = ax.in_size, out_size = ax.out_size, ksize = ax.ksize;
+    int *__restrict__ bounds = ax.bounds, *__restrict__ kk = ax.kk;
     const int xx = blockIdx.x * 128 + threadIdx.x;
     if (xx >= out_size) return;
     const double scale = __ddiv_rn((double)in_size, (double)out_size);
@@ -238,8 +246,15 @@ extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, i
     uint8_t *tmp = (uint8_t *)(ws + L.tmp);
     int launched = 0;
     const uint8_t *vin = rgb;
-    if (W != out_w) {  // Pillow skips the horizontal pass when the width already matches
-        pp_coeffs<<<(out_w + 127) / 128, 128, 0, st>>>(W, out_w, L.ph.ksize, bounds_h, kk_h);
+    // Pillow skips the horizontal pass when the width already matches.  The vertical pass with equal heights is
+    // the identity (taps 1, 0), so it always runs: it carries the normalisation.
+    const bool horiz = W != out_w;
+    const AxisArgs axh = {W, horiz ? out_w : 0, L.ph.ksize, bounds_h, kk_h};
+    const AxisArgs axv = {H, out_h, L.pv.ksize, bounds_v, kk_v};
+    const int widest = (horiz && out_w > out_h) ? out_w : out_h;
+    pp_coeffs<<<dim3((widest + 127) / 128, 2), 128, 0, st>>>(axh, axv);
+    ++launched;
+    if (horiz) {
         // input pixels a segment of kHSeg outputs can tap: its centres span kHSeg * scale, plus the support on both sides
         const double scale = (double)W / (double)out_w;
         const size_t span_px = (size_t)ceil(kHSeg * scale) + (size_t)L.ph.ksize + 2;
@@ -250,10 +265,8 @@ extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, i
         else
             pp_horizontal<<<dim3((out_w + 255) / 256, H), 256, 0, st>>>(rgb, H, W, out_w, L.ph.ksize, bounds_h, kk_h, tmp);
         vin = tmp;
-        launched += 2;
+        ++launched;
     }
-    // the vertical pass with equal heights is the identity (taps 1, 0), so it always runs: it carries the normalisation
-    pp_coeffs<<<(out_h + 127) / 128, 128, 0, st>>>(H, out_h, L.pv.ksize, bounds_v, kk_v);
     Norm3 nm;
     for (int c = 0; c < 3; ++c) {
         nm.mean[c] = mean3[c];
@@ -261,6 +274,6 @@ extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, i
     }
     pp_vertical_normalize<<<dim3((out_w + 255) / 256, out_h), 256, 0, st>>>(vin, H, out_w, out_h, L.pv.ksize, bounds_v,
                                                                            kk_v, nm, out);
-    launched += 2;
+    ++launched;
     return check_launch("yh_preprocess_rgb8", launched);
 }
