@@ -158,7 +158,7 @@ int yh_compact_records(const int32_t *n_keep, const uint64_t *rec_key, const uin
  * reference's stable sorted()).  The class is read from flags >> 56.
  * The sort runs four 8-bit passes over the leading 32 bits of (class, varying key
  * bits) and then orders the few short runs of records that agree in those bits;
- * inputs that does not suit (long unordered runs, > 59 varying key bits) are
+ * inputs this does not suit (long unordered runs, > 59 varying key bits) are
  * re-sorted by all digits inside the same call.
  *   ap[(s*C + c)*T + t]  fp64, bit-exact with the reference's arithmetic
  *   totals[0] = overall TP (bit 4*T), totals[1] = M  (int64)
