@@ -247,12 +247,13 @@ int yh_encode_targets(const double *boxes, const int32_t *cls, const int64_t *of
  * Replaces `self.transform(image)` of YOLOInference (src/yolo/inference.py:57-66, 88-101):
  * torchvision Resize((out_h, out_w)) on a PIL RGB image (Pillow's bilinear resample: 22-bit
  * fixed-point taps, horizontal then vertical pass, 8-bit rounding in between), ToTensor
- * (/ 255) and Normalize((x - mean) / std), all in float32.  rgb = (H, W, 3) uint8 on the
- * device, out = (3, out_h, out_w) float32, bit-identical to the reference's tensor.
+ * (/ 255) and Normalize((x - mean) / std), all in float32.  rgb = (N, H, W, 3) uint8 on the
+ * device (N images of one size, 4-byte aligned), out = (N, 3, out_h, out_w) float32,
+ * bit-identical to the reference's tensor for every image; three launches for the batch.
  * mean3 / std3 are HOST arrays of three floats.  Uses `workspace` (256-byte aligned) of
- * yh_preprocess_workspace_bytes(H, W, out_h, out_w); 0 = shape not supported. */
-size_t yh_preprocess_workspace_bytes(int H, int W, int out_h, int out_w);
-int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, int out_w, const float *mean3,
+ * yh_preprocess_workspace_bytes(N, H, W, out_h, out_w); 0 = shape not supported. */
+size_t yh_preprocess_workspace_bytes(int N, int H, int W, int out_h, int out_w);
+int yh_preprocess_rgb8(const uint8_t *rgb, int N, int H, int W, int out_h, int out_w, const float *mean3,
                        const float *std3, float *out, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------- list-form entry points ----

@@ -142,3 +142,17 @@ def test_predict_images_equals_predict_per_image(tmp_path):
     assert len(many) == len(paths) and sum(len(d) for d in many) > 0
     for p, dets in zip(paths, many):
         assert dets == eng.predict(p, conf_threshold=0.3)
+
+
+@gpu
+@pytest.mark.parametrize("shape", [(5, 375, 500), (3, 448, 448), (4, 37, 1201), (2, 900, 448)])
+def test_batch_of_equal_sized_images_equals_per_image(shape):
+    from yolo_v1_b200 import preprocess
+    n, h, w = shape
+    imgs = np.stack([make_image(60 + i, h, w) for i in range(n)])
+    d = torch.from_numpy(imgs).cuda()
+    batch = preprocess.preprocess_rgb8(d)
+    assert batch.shape == (n, 3, 448, 448)
+    for i in range(n):
+        assert torch.equal(batch[i], preprocess.preprocess_rgb8(d[i]))
+    assert np.array_equal(batch[n - 1].cpu().numpy().view(np.uint32), po.preprocess(imgs[n - 1]).view(np.uint32))

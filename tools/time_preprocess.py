@@ -38,3 +38,18 @@ for h, w in [(375, 500), (768, 1024), (2160, 3840), (6000, 8000)]:
         tf(pil)
     us_cpu = (time.perf_counter() - t0) * 1e6 / n_cpu
     print(f"{h:5d}x{w:<6d} {us:11.1f} {nbytes / us / 1e3:8.1f} {us_pil:12.1f} {us_cpu:19.1f}")
+
+# a batch of equal-sized images: three launches for all of them
+for n, h, w in [(64, 375, 500), (256, 375, 500)]:
+    d = torch.from_numpy(rng.integers(0, 256, size=(n, h, w, 3), dtype=np.uint8)).cuda()
+    for _ in range(3):
+        preprocess.preprocess_rgb8(d)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        preprocess.preprocess_rgb8(d)
+    e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / 20
+    nbytes = n * (h * w * 3 + 2 * h * 448 * 3 + 3 * 448 * 448 * 4)
+    print(f"batch {n} x {h}x{w}: {us:8.1f} us = {us / n:6.2f} us per image, {nbytes / us / 1e3:7.1f} GB/s")

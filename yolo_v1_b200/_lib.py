@@ -38,8 +38,8 @@ SIGNATURES = {
     "yh_compact_records": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_ap_workspace_bytes": (_sz, [_i64, _i, _i]),
     "yh_ap_reduce": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "yh_preprocess_workspace_bytes": (_sz, [_i, _i, _i, _i]),
-    "yh_preprocess_rgb8": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "yh_preprocess_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
+    "yh_preprocess_rgb8": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_partition_workspace_bytes": (_sz, [_i64]),
     "yh_partition_records": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "yh_peer_sum": (_i, [_vp, _i, _i, _i, _i, _vp, C.c_uint, _vp]),

@@ -83,6 +83,8 @@ __device__ __forceinline__ unsigned clip8(int v) {
 __global__ void __launch_bounds__(256)
 pp_horizontal(const uint8_t *__restrict__ in, int H, int W, int OW, int ksize, const int *__restrict__ bounds,
               const int *__restrict__ kk, uint8_t *__restrict__ out) {
+    in += (size_t)blockIdx.z * H * W * 3;
+    out += (size_t)blockIdx.z * H * OW * 3;
     const int xx = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y;
     if (xx >= OW) return;
     const int x0 = bounds[2 * xx], n = bounds[2 * xx + 1];
@@ -109,6 +111,8 @@ __global__ void __launch_bounds__(kHSeg)
 pp_horizontal_staged(const uint8_t *__restrict__ in, int H, int W, int OW, int ksize, const int *__restrict__ bounds,
                      const int *__restrict__ kk, uint8_t *__restrict__ out) {
     extern __shared__ uint32_t s_words[];
+    in += (size_t)blockIdx.z * H * W * 3;    // image blockIdx.z of the batch
+    out += (size_t)blockIdx.z * H * OW * 3;
     const int xx0 = blockIdx.x * kHSeg, y = blockIdx.y, tid = threadIdx.x;
     const int xlast = min(xx0 + kHSeg, OW) - 1;
     const int p0 = bounds[2 * xx0], p1 = bounds[2 * xlast] + bounds[2 * xlast + 1];  // input pixels [p0, p1)
@@ -184,6 +188,8 @@ __global__ void __launch_bounds__(256)
 pp_vertical_normalize(const uint8_t *__restrict__ in, int H, int OW, int OH, int ksize,
                       const int *__restrict__ bounds, const int *__restrict__ kk, const __grid_constant__ Norm3 nm,
                       float *__restrict__ out) {
+    in += (size_t)blockIdx.z * H * OW * 3;
+    out += (size_t)blockIdx.z * 3 * OH * OW;
     const int xx = blockIdx.x * 256 + threadIdx.x, yy = blockIdx.y;
     if (xx >= OW) return;
     const int y0 = bounds[2 * yy], n = bounds[2 * yy + 1];
@@ -208,7 +214,7 @@ struct PpLayout {
     size_t bounds_h, kk_h, bounds_v, kk_v, tmp, total;
     AxisPlan ph, pv;
 };
-static PpLayout pp_layout(int H, int W, int OH, int OW) {
+static PpLayout pp_layout(int N, int H, int W, int OH, int OW) {
     PpLayout L;
     L.ph = axis_plan(W, OW);
     L.pv = axis_plan(H, OH);
@@ -218,7 +224,7 @@ static PpLayout pp_layout(int H, int W, int OH, int OW) {
     L.kk_h = o; o = up(o + sizeof(int) * (size_t)OW * L.ph.ksize);
     L.bounds_v = o; o = up(o + sizeof(int) * 2 * (size_t)OH);
     L.kk_v = o; o = up(o + sizeof(int) * (size_t)OH * L.pv.ksize);
-    L.tmp = o; o = up(o + (size_t)H * OW * 3);
+    L.tmp = o; o = up(o + (size_t)N * H * OW * 3);
     L.total = o;
     return L;
 }
@@ -227,29 +233,29 @@ static PpLayout pp_layout(int H, int W, int OH, int OW) {
 
 using namespace yh;
 
-static bool pp_shape_ok(int H, int W, int OH, int OW) {
-    return H >= 1 && W >= 1 && OH >= 1 && OW >= 1 && H <= 65535 && OH <= 65535 && W <= (1 << 20) && OW <= (1 << 20);
+static bool pp_shape_ok(int N, int H, int W, int OH, int OW) {
+    return N >= 1 && N <= 65535 && H >= 1 && W >= 1 && OH >= 1 && OW >= 1 && H <= 65535 && OH <= 65535 && W <= (1 << 20) && OW <= (1 << 20);
 }
 
-extern "C" size_t yh_preprocess_workspace_bytes(int H, int W, int out_h, int out_w) {
-    if (!pp_shape_ok(H, W, out_h, out_w)) return 0;
-    return pp_layout(H, W, out_h, out_w).total;
+extern "C" size_t yh_preprocess_workspace_bytes(int N, int H, int W, int out_h, int out_w) {
+    if (!pp_shape_ok(N, H, W, out_h, out_w)) return 0;
+    return pp_layout(N, H, W, out_h, out_w).total;
 }
 
-extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, int out_w, const float *mean3,
+extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int N, int H, int W, int out_h, int out_w, const float *mean3,
                                   const float *std3, float *out, void *workspace, size_t workspace_bytes,
                                   void *stream) {
-    if (!rgb || !out || !workspace || !mean3 || !std3 || !pp_shape_ok(H, W, out_h, out_w)) {
-        set_error("yh_preprocess_rgb8: bad argument (H=%d W=%d -> %dx%d)", H, W, out_h, out_w);
+    if (!rgb || !out || !workspace || !mean3 || !std3 || !pp_shape_ok(N, H, W, out_h, out_w)) {
+        set_error("yh_preprocess_rgb8: bad argument (N=%d H=%d W=%d -> %dx%d)", N, H, W, out_h, out_w);
         return YH_ERR_BAD_ARG;
     }
-    const PpLayout L = pp_layout(H, W, out_h, out_w);
+    const PpLayout L = pp_layout(N, H, W, out_h, out_w);
     if (workspace_bytes < L.total) {
         set_error("yh_preprocess_rgb8: workspace too small (%zu < %zu)", workspace_bytes, L.total);
         return YH_ERR_WORKSPACE;
     }
-    if ((uintptr_t)workspace % 256) {
-        set_error("yh_preprocess_rgb8: workspace must be 256-byte aligned");
+    if ((uintptr_t)workspace % 256 || (uintptr_t)rgb % 4) {
+        set_error("yh_preprocess_rgb8: workspace must be 256-byte aligned, rgb 4-byte aligned");
         return YH_ERR_ALIGNMENT;
     }
     cudaStream_t st = (cudaStream_t)stream;
@@ -273,10 +279,10 @@ extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, i
         const size_t span_px = (size_t)ceil(kHSeg * scale) + (size_t)L.ph.ksize + 2;
         const size_t span_bytes = ((span_px * 3 + 8 + 3) & ~(size_t)3) + 32;  // + the words a last group reads past the span
         if (span_bytes <= 48 * 1024)
-            pp_horizontal_staged<<<dim3((out_w + kHSeg - 1) / kHSeg, H), kHSeg, span_bytes, st>>>(
+            pp_horizontal_staged<<<dim3((out_w + kHSeg - 1) / kHSeg, H, N), kHSeg, span_bytes, st>>>(
                 rgb, H, W, out_w, L.ph.ksize, bounds_h, kk_h, tmp);
         else
-            pp_horizontal<<<dim3((out_w + 255) / 256, H), 256, 0, st>>>(rgb, H, W, out_w, L.ph.ksize, bounds_h, kk_h, tmp);
+            pp_horizontal<<<dim3((out_w + 255) / 256, H, N), 256, 0, st>>>(rgb, H, W, out_w, L.ph.ksize, bounds_h, kk_h, tmp);
         vin = tmp;
         ++launched;
     }
@@ -285,7 +291,7 @@ extern "C" int yh_preprocess_rgb8(const uint8_t *rgb, int H, int W, int out_h, i
         nm.mean[c] = mean3[c];
         nm.std[c] = std3[c];
     }
-    pp_vertical_normalize<<<dim3((out_w + 255) / 256, out_h), 256, 0, st>>>(vin, H, out_w, out_h, L.pv.ksize, bounds_v,
+    pp_vertical_normalize<<<dim3((out_w + 255) / 256, out_h, N), 256, 0, st>>>(vin, H, out_w, out_h, L.pv.ksize, bounds_v,
                                                                            kk_v, nm, out);
     ++launched;
     return check_launch("yh_preprocess_rgb8", launched);
