@@ -5,7 +5,7 @@ Run in the build container only (the GPU box has no /root/reference):
     python tests/golden/make_golden.py            # small fixtures (seconds..minutes)
     python tests/golden/make_golden.py --big      # + the 4,952-image compute() case (slow)
 
-Outputs (committed): tests/golden/loss.npz, decode_nms.npz, map_small.npz, map_big.npz, encode.npz.
+Outputs (committed): tests/golden/loss.npz, decode_nms.npz, map_small.npz, map_big.npz, encode.npz, validation.npz.
 The reference is imported, never copied; only its outputs are stored.
 """
 from __future__ import annotations
@@ -278,8 +278,9 @@ def gen_map_small(out):
 
 
 def gen_map_big(out, n, name):
-    tg = synth.make_targets(n, seed=51, p_obj=0.055, size_mix=True)
-    pred = synth.make_preds(n, "correlated", seed=50, targets=tg)
+    # synth.make_exact: integer hash + IEEE-exact operators only, so the GPU box regenerates these
+    # inputs bit for bit whatever its CPU or thread count (the test FAILS on a hash mismatch)
+    pred, tg = synth.make_exact(n, seed=50)
     keep_k, flags, keys, vals = reference_map(pred, tg, 0.01)
     out[f"{name}/n"] = np.int64(n)
     out[f"{name}/input_sha"] = np.array(sha(pred.numpy(), tg.numpy()))
@@ -326,6 +327,74 @@ def gen_encode(out):
     out["names"] = np.asarray(names)
 
 
+def validation_cases():
+    """Images for the pre-NMS validation of YOLOInference.predict (inference.py:133-136, 197-208)."""
+    def blank():
+        return torch.zeros(S, S, 30)
+
+    def put(p, row, col, b, box, conf, cls):
+        p[row, col, b * 5:b * 5 + 4] = torch.tensor(box)
+        p[row, col, b * 5 + 4] = conf
+        p[row, col, 10 + cls] = 1.0
+
+    cases = {}
+    # A (valid, conf 0.9) and B (same class, conf 0.8, centre x = (6 + 1.05) / 7 > 1) overlap with IoU 0.57:
+    # NMS would drop B, but the reference validates B first and raises
+    p = blank()
+    put(p, 3, 6, 0, [0.90, 0.5, 0.30, 0.30], 0.9, 4)
+    put(p, 3, 6, 1, [1.05, 0.5, 0.30, 0.30], 0.8, 4)
+    cases["suppressed_x_gt_1"] = p
+    # the same pair in range: B is suppressed, one detection comes back
+    p = blank()
+    put(p, 3, 6, 0, [0.90, 0.5, 0.30, 0.30], 0.9, 4)
+    put(p, 3, 6, 1, [0.99, 0.5, 0.30, 0.30], 0.8, 4)
+    cases["suppressed_in_range"] = p
+    # two offenders: the EARLIER one in cell / box order raises (negative width at (0,2), conf > 1 at (5,1))
+    p = blank()
+    put(p, 5, 1, 0, [0.5, 0.5, 0.2, 0.2], 1.5, 7)
+    put(p, 0, 2, 1, [0.5, 0.5, -0.1, 0.2], 0.7, 2)
+    put(p, 0, 2, 0, [0.5, 0.5, 0.2, 0.2], 0.6, 2)
+    cases["two_offenders"] = p
+    # an offender below the confidence threshold is never built, so nothing raises
+    p = blank()
+    put(p, 2, 2, 0, [0.5, 0.5, 0.2, 0.2], 0.9, 1)
+    put(p, 4, 4, 0, [0.5, 0.5, 1.7, 0.2], 0.4, 1)
+    cases["offender_below_threshold"] = p
+    # confidence product above 1 (class score 1.2 in a raw head)
+    p = blank()
+    put(p, 1, 1, 0, [0.5, 0.5, 0.2, 0.2], 0.95, 3)
+    p[1, 1, 13] = 1.2
+    cases["confidence_gt_1"] = p
+    return cases
+
+
+def gen_validation(out):
+    """What the reference's parse_predictions + non_max_suppression do at conf 0.5 / nms 0.4."""
+    import json
+
+    inf = YOLOInference(_Shape(), device="cpu")
+    names = []
+    for name, pred in validation_cases().items():
+        rec = {}
+        try:
+            dets = inf.parse_predictions(pred, 0.5)
+            kept = inf.non_max_suppression(dets, 0.4)
+            rec["raises"] = False
+            rec["kept"] = [[d.class_id, d.confidence, d.bbox.x, d.bbox.y, d.bbox.width, d.bbox.height] for d in kept]
+        except ValueError as e:   # pydantic.ValidationError
+            err = e.errors()[0]
+            rec["raises"] = True
+            rec["title"] = e.title
+            rec["type"] = err["type"]
+            rec["loc"] = list(err["loc"])
+            rec["input"] = float(err["input"])
+        out[f"{name}/pred"] = pred.numpy()
+        out[f"{name}/expect"] = np.array(json.dumps(rec))
+        names.append(name)
+        print(name, rec)
+    out["names"] = np.asarray(names)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--big", action="store_true")
@@ -333,7 +402,8 @@ def main():
     a = ap.parse_args()
     warnings.simplefilter("ignore")
     torch.set_num_threads(1)
-    jobs = {"loss": gen_loss, "decode_nms": gen_decode_nms, "map_small": gen_map_small, "encode": gen_encode}
+    jobs = {"loss": gen_loss, "decode_nms": gen_decode_nms, "map_small": gen_map_small, "encode": gen_encode,
+            "validation": gen_validation}
     for name, fn in jobs.items():
         if a.only and a.only != name:
             continue
@@ -343,8 +413,8 @@ def main():
         print("wrote", name, len(out), "arrays")
     if a.big or a.only == "map_big":
         out = {}
-        gen_map_big(out, 512, "corr512")
-        gen_map_big(out, 4952, "corr4952")
+        gen_map_big(out, 512, "exact512")
+        gen_map_big(out, 4952, "exact4952")
         np.savez_compressed(os.path.join(HERE, "map_big.npz"), **out)
         print("wrote map_big")
 

@@ -285,27 +285,45 @@ def test_map_matches_oracle_seeded(n, profile, conf_thr):
 
 
 def test_map_big_golden(golden):
-    try:
-        g = golden("map_big")
-    except FileNotFoundError:
-        pytest.skip("tests/golden/map_big.npz not generated")
-    for name in ("corr512", "corr4952"):
-        if f"{name}/n" not in g.files:
-            continue
-        n = int(g[f"{name}/n"])
-        tgt = synth.make_targets(n, seed=51, p_obj=0.055, size_mix=True)
-        pred = synth.make_preds(n, "correlated", seed=50, targets=tgt)
-        import hashlib
+    """configs[2] size (4,952 images): the reference's own compute() dict, n_keep per image and the
+    hashes of its ordered keep lists and TP flag words.  The inputs come from synth.make_exact
+    (integer hash + IEEE-exact operators), so a hash mismatch is a failure, not a skip."""
+    import hashlib
+
+    def sha(*arrays):
         h = hashlib.sha256()
-        h.update(pred.numpy().tobytes())
-        h.update(tgt.numpy().tobytes())
-        if h.hexdigest()[:16] != str(g[f"{name}/input_sha"]):
-            pytest.skip("torch RNG stream differs from the one the golden inputs were drawn with")
+        for a in arrays:
+            h.update(np.ascontiguousarray(a).tobytes())
+        return h.hexdigest()[:16]
+
+    g = golden("map_big")
+    for name in ("exact512", "exact4952"):
+        n = int(g[f"{name}/n"])
+        pred, tgt = synth.make_exact(n, seed=50)
+        assert sha(pred.numpy(), tgt.numpy()) == str(g[f"{name}/input_sha"]), "synth.make_exact is not bit-reproducible here"
         metric = mAPMetric(num_classes=20, conf_threshold=0.01)
         metric.update(pred.to(DEV), tgt.to(DEV))
-        np.testing.assert_array_equal(metric._chunks[0].n_keep.cpu().numpy(), g[f"{name}/n_keep"])
+        ch = metric._chunks[0]
+        n_keep = ch.n_keep.cpu().numpy()
+        np.testing.assert_array_equal(n_keep, g[f"{name}/n_keep"])
+        # ordered keep lists (the reference's class-grouped order) and the TP flag words in that order,
+        # as make_golden.py stores them (-1 / 0 padded)
+        live = np.arange(98)[None, :] < n_keep[:, None]
+        r = head.decode_nms(pred.to(DEV), 0.01, 0.4, head.IOU_METRICS, head.ORDER_CLASS_GROUPED, want_boxes=False)
+        np.testing.assert_array_equal(r.n_keep.cpu().numpy(), n_keep)
+        keep_k = np.where(live, r.keep_k.cpu().numpy().astype(np.int32), -1).astype(np.int32)
+        assert sha(keep_k) == str(g[f"{name}/keep_k_sha"])
+        by_k = np.zeros((n, 98), np.uint64)          # flag word of candidate k (records are in sorted order)
+        rec_k = ch.rec_k.cpu().numpy().astype(np.int64)
+        fl = ch.rec_flags.cpu().numpy().view(np.uint64) & np.uint64((1 << 40) - 1)
+        rows = np.repeat(np.arange(n), 98).reshape(n, 98)
+        by_k[rows[live], rec_k[live]] = fl[live]
+        ref_order = np.where(live, np.take_along_axis(by_k, np.maximum(keep_k, 0).astype(np.int64), 1), np.uint64(0))
+        assert sha(ref_order.astype(np.uint64)) == str(g[f"{name}/flags_sha"])
         res = metric.compute()
-        for k, v in zip([str(k) for k in g[f"{name}/keys"]], g[f"{name}/vals"]):
+        keys = [str(k) for k in g[f"{name}/keys"]]
+        assert sorted(res) == keys
+        for k, v in zip(keys, g[f"{name}/vals"]):
             assert float(res[k]) == pytest.approx(v, rel=1e-9, abs=1e-12), k
 
 

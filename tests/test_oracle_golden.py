@@ -84,6 +84,37 @@ def test_map_oracle_matches_reference(golden, case):
         np.testing.assert_array_equal(a, b)
 
 
+@pytest.mark.parametrize("name", ["exact512", "exact4952"])
+def test_map_oracle_matches_reference_at_config3_size(golden, name):
+    """tests/golden/map_big.npz: the reference's compute() on 512 / 4,952 regenerated images."""
+    import hashlib
+
+    from yolo_v1_b200 import synth
+
+    def sha(*arrays):
+        h = hashlib.sha256()
+        for a in arrays:
+            h.update(np.ascontiguousarray(a).tobytes())
+        return h.hexdigest()[:16]
+
+    g = golden("map_big")
+    n = int(g[f"{name}/n"])
+    pred, tgt = synth.make_exact(n, seed=50)
+    assert sha(pred.numpy(), tgt.numpy()) == str(g[f"{name}/input_sha"]), "synth.make_exact is not bit-reproducible here"
+    thr = [0.5 + 0.05 * i for i in range(10)]
+    st = c_oracle.update_batch(pred.numpy(), tgt.numpy(), 0.01, 0.4, n_threads=4)
+    np.testing.assert_array_equal(st["n_det"], g[f"{name}/n_keep"])
+    live = np.arange(98)[None, :] < st["n_det"][:, None]
+    assert sha(np.where(live, st["det_k"], -1).astype(np.int32)) == str(g[f"{name}/keep_k_sha"])
+    out = c_oracle.compute(st, thr, n_threads=4)
+    assert sha((out["flags"] & np.uint64((1 << 40) - 1)).astype(np.uint64)) == str(g[f"{name}/flags_sha"])
+    res = results.assemble(out["ap"], out["overall"], out["sizes"], thr, 20, n)
+    keys = [str(k) for k in g[f"{name}/keys"]]
+    assert sorted(res.keys()) == keys
+    for k, v in zip(keys, g[f"{name}/vals"]):
+        assert float(res[k]) == pytest.approx(v, rel=1e-12, abs=1e-15), k
+
+
 def test_iou_known_answers():
     # tests/test_metrics.py:35-55,208-222 and tests/test_yolo.py:196-227 of the reference
     assert c_oracle.iou((0.5, 0.5, 0.2, 0.2), (0.5, 0.5, 0.2, 0.2)) == pytest.approx(1.0, abs=1e-5)

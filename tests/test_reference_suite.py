@@ -250,3 +250,53 @@ def test_detection_string_and_equality():
     assert "class_3" in str(d)
     ranked = sorted([d, _det(1, 0.9, 0.5, 0.5, 0.1, 0.1)], key=lambda x: x.confidence, reverse=True)
     assert ranked[0].class_id == 1
+
+
+# ------------------------------------------------------------------ pre-NMS validation (inference.py:133-136, 197-208)
+class _Fixed(nn.Module):
+    """Stands in for the model: returns one fixed (1, S, S, 30) prediction, whatever the image."""
+
+    def __init__(self, pred):
+        super().__init__()
+        self.S, self.B = 7, 2
+        self.register_buffer("pred", pred.clone())
+
+    def forward(self, x):
+        return self.pred.unsqueeze(0).expand(x.shape[0], -1, -1, -1)
+
+
+@pytest.mark.parametrize("case", ["suppressed_x_gt_1", "suppressed_in_range", "two_offenders",
+                                  "offender_below_threshold", "confidence_gt_1"])
+def test_predict_validates_every_candidate_before_nms(golden, tmp_path, case):
+    """tests/golden/validation.npz: what the reference's parse_predictions + non_max_suppression did
+    (conf 0.5, nms 0.4).  A candidate outside [0, 1] raises pydantic's ValidationError for the same
+    model, field and value even when NMS would have suppressed it -- through predict(), predict_batch()
+    and predict_images()."""
+    import json
+
+    from PIL import Image
+    from pydantic import ValidationError
+
+    g = golden("validation")
+    pred = torch.from_numpy(g[f"{case}/pred"])
+    want = json.loads(str(g[f"{case}/expect"]))
+    eng = YOLOInference(_Fixed(pred), device="cuda")
+    path = tmp_path / "grey.png"
+    Image.new("RGB", (64, 48), color=(90, 90, 90)).save(path)
+    other = torch.zeros(7, 7, 30)
+    other[2, 2, 0:5] = torch.tensor([0.5, 0.5, 0.2, 0.2, 0.9])
+    other[2, 2, 11] = 1.0
+    batch = torch.stack([other, pred, other])
+    calls = [lambda: eng.predict(str(path), 0.5, 0.4), lambda: eng.predict_batch(batch, 0.5, 0.4)[1],
+             lambda: eng.predict_images([str(path), str(path)], 0.5, 0.4)[1]]
+    for call in calls:
+        if want["raises"]:
+            with pytest.raises(ValidationError) as ei:
+                call()
+            err = ei.value.errors()[0]
+            assert ei.value.title == want["title"]
+            assert (err["type"], list(err["loc"]), float(err["input"])) == (want["type"], want["loc"], want["input"])
+        else:
+            kept = call()
+            got = [[d.class_id, d.confidence, d.bbox.x, d.bbox.y, d.bbox.width, d.bbox.height] for d in kept]
+            assert got == want["kept"]

@@ -83,11 +83,23 @@ class YOLOInference:
                       class_names: list[str] | None = None) -> list[list[Detection]]:
         """Decode + NMS for a whole (N,S,S,B*5+C) batch in one launch; one list per image.
 
-        Same result per image as parse_predictions() followed by non_max_suppression()."""
+        Same result per image as parse_predictions() followed by non_max_suppression() -- including
+        the error: the reference builds a validated Detection for EVERY candidate above the confidence
+        threshold before NMS runs (inference.py:133-136, 197-208), so a candidate outside [0, 1] raises
+        pydantic's ValidationError even when NMS would have suppressed it.  The kernel flags such
+        images (`bad_range`); the first flagged image is then decoded without NMS, which builds its
+        Detections in the reference's cell / box order and raises at the same candidate."""
         S, B = self.model.S, self.model.B
         Cn = predictions.shape[-1] - B * 5
-        r = head.decode_nms(self._on_cuda(predictions), conf_threshold, nms_threshold, head.IOU_INFER,
+        predictions = self._on_cuda(predictions)
+        r = head.decode_nms(predictions, conf_threshold, nms_threshold, head.IOU_INFER,
                             head.ORDER_GLOBAL_CONF, S, B, Cn)
+        bad = r.bad_range.cpu()
+        if bool(bad.any()):
+            first = int(torch.nonzero(bad)[0].item())
+            one = predictions[first] if predictions.dim() == 4 else predictions
+            self.parse_predictions(one, conf_threshold, class_names)   # raises ValidationError
+            raise _lib.YoloHeadError("yh_decode_nms flagged an out-of-range candidate that the schema accepted")
         return self._build(r, class_names)
 
     def parse_predictions(self, pred: torch.Tensor, conf_threshold: float,

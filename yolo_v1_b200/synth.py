@@ -103,3 +103,91 @@ def make_preds(n: int, profile: str = "uniform", seed: int = 1234, S: int = 7, B
     else:
         raise ValueError(f"unknown profile {profile!r}; choose from {PROFILES}")
     return p.contiguous()
+
+
+# ---------------------------------------------------------------------------------------------
+# Bit-reproducible inputs.  The torch generators above go through exp / pow / softmax, whose
+# vectorised and scalar-tail code paths differ in the last bit, so their output depends on the
+# ATen thread count and the CPU's vector width.  Fixtures that are REGENERATED on another
+# machine (tests/golden/map_big.npz stores only a hash of its 58 MB of inputs) are drawn here:
+# a counter-based integer hash (splitmix64) turned into k / 2^24 floats, and nothing but
+# IEEE-exact operators (+ - * / sqrt, comparisons) after that.
+_SM_GAMMA = 0x9E3779B97F4A7C15
+_MASK64 = (1 << 64) - 1
+
+
+def _mix64(z):
+    import numpy as np
+
+    with np.errstate(over="ignore"):
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return z ^ (z >> np.uint64(31))
+
+
+def _mix64_int(z: int) -> int:
+    z &= _MASK64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _MASK64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _MASK64
+    return z ^ (z >> 31)
+
+
+def exact_uniform(shape, seed: int, stream: int):
+    """float32 array of k / 2^24, k = top 24 bits of splitmix64(hash(seed, stream) + gamma * index)."""
+    import numpy as np
+
+    count = int(np.prod(shape))
+    base = np.uint64(_mix64_int(int(seed) * 0xD1342543DE82EF95 + int(stream) * 0xA0761D6478BD642F + 1))
+    idx = np.arange(count, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        z = _mix64(base + (idx + np.uint64(1)) * np.uint64(_SM_GAMMA))
+    return ((z >> np.uint64(40)).astype(np.float32) * np.float32(2.0 ** -24)).reshape(shape)
+
+
+def make_exact(n: int, seed: int = 1234, S: int = 7, B: int = 2, C: int = 20, p_obj: float = 0.055):
+    """(pred, targets) in the spirit of the `correlated` profile with VOC's size mix (SURVEY.md
+    section 8d config 3), identical bits on any machine.  Returns torch float32 tensors."""
+    import numpy as np
+
+    f = np.float32
+    u = lambda shape, stream: exact_uniform(shape, seed, stream)  # noqa: E731
+    D = B * 5 + C
+    # ---- targets: slot 0 = (x, y, w, h, 1), one-hot class (dataset.py:516-530)
+    obj = u((n, S, S), 1) < f(p_obj)
+    mix = u((n, S, S), 2)
+    small, medium = mix < f(_SIZE_MIX[0]), mix < f(_SIZE_MIX[0] + _SIZE_MIX[1])
+    lo = np.where(small, f(0.0004), np.where(medium, f(_SMALL_A), f(_MEDIUM_A))).astype(f)
+    hi = np.where(small, f(_SMALL_A), np.where(medium, f(_MEDIUM_A), f(0.81))).astype(f)
+    area = lo + (hi - lo) * u((n, S, S), 3)
+    aspect = (f(0.55) + u((n, S, S), 4)) / (f(0.55) + u((n, S, S), 5))       # 0.35 .. 2.8
+    w = np.minimum(np.sqrt(area * aspect), f(1.0))
+    h = np.minimum(np.sqrt(area / aspect), f(1.0))
+    cls = np.minimum((u((n, S, S), 6) * f(C)).astype(np.int64), C - 1)
+    t = np.zeros((n, S, S, D), f)
+    t[..., 0:2] = u((n, S, S, 2), 7)
+    t[..., 2] = w
+    t[..., 3] = h
+    t[..., 4] = f(1.0)
+    t[..., B * 5:] = (cls[..., None] == np.arange(C)).astype(f)
+    t *= obj[..., None].astype(f)
+    # ---- predictions: low-confidence noise everywhere ...
+    p = np.empty((n, S, S, D), f)
+    for b in range(B):
+        p[..., b * 5:b * 5 + 2] = u((n, S, S, 2), 10 + 3 * b)
+        p[..., b * 5 + 2:b * 5 + 4] = f(0.05) + f(0.75) * u((n, S, S, 2), 11 + 3 * b)
+        c2 = u((n, S, S), 12 + 3 * b)
+        c2 = c2 * c2
+        p[..., b * 5 + 4] = c2 * c2
+    q = u((n, S, S, C), 20)
+    q = q * q
+    p[..., B * 5:] = q * q * f(0.5)
+    # ... and in object cells box 0 = target + noise, confidence 0.3..1, the true class high w.p. 0.8
+    noise = (u((n, S, S, 4), 21) + u((n, S, S, 4), 22) + u((n, S, S, 4), 23) + u((n, S, S, 4), 24) - f(2.0)) * f(0.0866)
+    noisy = np.clip(t[..., 0:4] + noise, f(0.0), f(1.0))
+    conf = f(0.3) + f(0.7) * u((n, S, S), 25)
+    hit = obj & (u((n, S, S), 26) < f(0.8))
+    sharp = f(0.1) * u((n, S, S, C), 27) + f(0.85) * t[..., B * 5:]
+    p[..., 0:4] = np.where(obj[..., None], noisy, p[..., 0:4])
+    p[..., 4] = np.where(obj, conf, p[..., 4])
+    p[..., B * 5:] = np.where(hit[..., None], sharp, p[..., B * 5:])
+    return torch.from_numpy(np.ascontiguousarray(p)), torch.from_numpy(np.ascontiguousarray(t))
