@@ -153,6 +153,52 @@ def test_full_size_invariants():
     assert (cls[:, 1:][valid[:, 1:]] >= cls[:, :-1][valid[:, 1:]]).all()
 
 
+def _by_candidate(n_keep, ks, vals, fill):
+    """(N,98) array indexed by candidate k from per-position arrays (positions >= n_keep ignored)."""
+    n = len(n_keep)
+    live = np.arange(98)[None, :] < n_keep[:, None]
+    out = np.full((n, 98), fill, dtype=vals.dtype)
+    rows = np.repeat(np.arange(n), 98).reshape(n, 98)
+    out[rows[live], ks.astype(np.int64)[live]] = vals[live]
+    return out
+
+
+def test_full_size_oracle_parity_config1():
+    """BASELINE.json configs[1] at its stated size: 65,536 `uniform` images, conf 0.3 / NMS IoU 0.4.
+    Ordered keep lists of both flavours ((metrics IoU, class-grouped) and (inference IoU, global
+    confidence order)) against the C oracle, and the fused update's TP flag words against the oracle's
+    compute(), every image, bit for bit."""
+    import os
+
+    n = 65536
+    th = min(os.cpu_count() or 1, 32)
+    tgt = synth.make_targets(n, seed=1234, p_obj=0.055, size_mix=True)
+    pred = synth.make_preds(n, "uniform", seed=1234, targets=tgt)
+    pd, td = pred.to(DEV), tgt.to(DEV)
+    live_of = lambda nk: np.arange(98)[None, :] < nk[:, None]  # noqa: E731
+    for iou_mode, order, o_iou, o_order in ((head.IOU_METRICS, head.ORDER_CLASS_GROUPED, c_oracle.IOU_METRICS, c_oracle.ORDER_CLASS_GROUPED),
+                                            (head.IOU_INFER, head.ORDER_GLOBAL_CONF, c_oracle.IOU_INFER, c_oracle.ORDER_GLOBAL_CONF)):
+        st = c_oracle.update_batch(pred.numpy(), tgt.numpy(), 0.3, 0.4, o_iou, o_order, n_threads=th)
+        r = head.decode_nms(pd, 0.3, 0.4, iou_mode, order, want_boxes=False)
+        nk = r.n_keep.cpu().numpy()
+        np.testing.assert_array_equal(nk, st["n_det"])
+        live = live_of(nk)
+        assert np.array_equal(np.where(live, r.keep_k.cpu().numpy().astype(np.int32), -1), np.where(live, st["det_k"], -1))
+        assert np.array_equal(np.where(live, r.keep_cls.cpu().numpy().astype(np.int32), -1), np.where(live, st["det_cls"], -1))
+        assert np.where(live, r.keep_conf.cpu().numpy(), 0.0).tobytes() == np.where(live, st["det_conf"], 0.0).tobytes()
+        if order == head.ORDER_CLASS_GROUPED:
+            ref = c_oracle.compute(st, DEFAULT_THR, n_threads=th)
+            gt_count = torch.zeros(80, dtype=torch.int32, device=DEV)
+            ch = head.map_update(pd, td, 0.3, 0.4, DEFAULT_THR, gt_count)
+            np.testing.assert_array_equal(ch.n_keep.cpu().numpy(), st["n_det"])
+            np.testing.assert_array_equal(ch.n_gt.cpu().numpy(), st["n_gt"])
+            fl = ch.rec_flags.cpu().numpy().view(np.uint64) & np.uint64((1 << 56) - 1)
+            mine = _by_candidate(nk, ch.rec_k.cpu().numpy(), fl, np.uint64(0))
+            want = _by_candidate(nk, st["det_k"], ref["flags"].astype(np.uint64), np.uint64(0))
+            assert np.array_equal(mine, want)
+            assert int((mine & np.uint64(1)).sum()) > 0            # some true positives exist at IoU 0.5
+
+
 # ----------------------------------------------------------------------------- sort plan / AP reduce on raw records
 def _ap_from_records(key, flags, gt_count, C, T):
     """numpy restatement of metrics.py:382-436 over (key, flags) records: stable sort per class by key
@@ -284,3 +330,82 @@ def test_ap_reduce_sort_plans(kind):
     assert torch.equal(ap2, ap)
     a, tp, n, gc = head.unpack_ap(packed2, C, T)
     assert n == m and np.array_equal(gc.reshape(-1), gt_count) and np.array_equal(a, ap.cpu().numpy())
+
+
+# ----------------------------------------------------------------------------- round-2 regressions
+def test_second_backward_over_a_retained_graph_recomputes_the_gradient():
+    """The reference's autograd graph can be walked twice with retain_graph=True; the fused loss gives its
+    gradient buffer away on the first backward and re-runs the kernel for any further one."""
+    from oracle import loss_oracle
+    from yolo_v1_b200 import YOLOLoss
+
+    tgt = synth.make_targets(8, seed=3, p_obj=0.2)
+    pred = synth.make_preds(8, "uniform", seed=4)
+    p = pred.to(DEV).requires_grad_(True)
+    total, _ = YOLOLoss()(p, tgt.to(DEV))
+    total.backward(retain_graph=True)
+    g1 = p.grad.clone()
+    p.grad = None
+    (total * 3.0).backward()
+    _, ref = loss_oracle.yolo_loss_and_grad(pred, tgt)
+    np.testing.assert_allclose(g1.cpu().numpy(), ref.numpy(), rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(p.grad.cpu().numpy(), 3.0 * ref.numpy(), rtol=1e-5, atol=1e-7)
+
+
+def test_encode_target_without_a_device_argument():
+    from oracle import encode_oracle
+    from yolo_v1_b200 import targets
+
+    boxes, cls = [[0.3, 0.4, 0.2, 0.1], [0.8, 0.1, 0.05, 0.3]], [3, 17]
+    got = targets.encode_target(boxes, cls)
+    assert got.is_cuda and got.cpu().numpy().tobytes() == encode_oracle.encode_target(boxes, cls).tobytes()
+    assert targets.encode_targets([boxes, []], [cls, []]).shape == (2, 7, 7, 30)
+
+
+def test_concurrent_streams_do_not_share_scratch():
+    """Two streams run loss + update + compute at the same time on different data (stream-keyed workspaces,
+    ticket ring): each must give the result it gives alone."""
+    from yolo_v1_b200 import YOLOLoss
+
+    sets = []
+    for seed in (11, 12):
+        tgt = synth.make_targets(6000, seed=seed, p_obj=0.055, size_mix=True)
+        pred = synth.make_preds(6000, "correlated", seed=seed, targets=tgt)
+        sets.append((pred.to(DEV), tgt.to(DEV)))
+
+    def run(p, t):
+        total, parts = YOLOLoss(defer_loss_dict=True)(p.clone().requires_grad_(True), t)
+        m = mAPMetric(num_classes=20, conf_threshold=0.05)
+        m.update(p, t)
+        packed = m._enqueue_reduce()
+        return parts._parts, packed
+
+    alone = [tuple(x.clone() for x in run(p, t)) for p, t in sets]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    for _ in range(5):
+        outs = []
+        for st, (p, t) in zip(streams, sets):
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                outs.append(run(p, t))
+        torch.cuda.synchronize()
+        for (a_parts, a_packed), (b_parts, b_packed) in zip(alone, outs):
+            assert torch.equal(a_parts, b_parts) and torch.equal(a_packed, b_packed)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_one_process_two_devices():
+    """The ticket array is a __device__ symbol with one address per device, and kernel attributes are per
+    device: a process that uses cuda:0 and then cuda:1 must get the same answer on both."""
+    tgt = synth.make_targets(3000, seed=21, p_obj=0.055, size_mix=True)
+    pred = synth.make_preds(3000, "correlated", seed=21, targets=tgt)
+    res = []
+    for d in ("cuda:0", "cuda:1", "cuda:0"):
+        m = mAPMetric(num_classes=20, conf_threshold=0.05)
+        m.update(pred.to(d), tgt.to(d))
+        res.append(m.compute())
+        r = head.decode_nms(pred.to(d), 0.3, 0.4, head.IOU_INFER, head.ORDER_GLOBAL_CONF, want_boxes=False)
+        res.append(r.keep_k.cpu())
+    assert res[0] == res[2] == res[4]
+    assert torch.equal(res[1], res[3]) and torch.equal(res[1], res[5])

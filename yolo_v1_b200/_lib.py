@@ -139,3 +139,52 @@ def on_device(device):
 
 def ptr(t):
     return None if t is None else t.data_ptr()
+
+
+class Workspace:
+    """Scratch buffers for kernels that need one, one per (device, stream), grown on demand.
+
+    Keyed by stream because a workspace carries per-launch state (sort control words, the loss
+    kernel's partials, exchange staging): two calls in flight on different streams -- or an eager
+    call next to a replaying CUDA graph, which owns a private stream -- must not share one.
+    While a `holding()` context is open every buffer handed out is also appended to the holder's
+    list: CapturedHeadStep keeps the buffers whose addresses its graph has baked in alive that way,
+    whatever later calls do to this cache."""
+
+    _holders: list = []
+
+    def __init__(self, zeroed: bool = False, align: int = 256):
+        self._buf: dict = {}
+        self._zeroed, self._align = zeroed, align
+
+    def get(self, device, nbytes: int, stream: int | None = None) -> torch.Tensor:
+        device = torch.device(device)
+        if device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        key = (device.index, stream_ptr(device) if stream is None else stream)
+        buf = self._buf.get(key)
+        if buf is None or buf.numel() < nbytes + self._align:
+            make = torch.zeros if self._zeroed else torch.empty
+            buf = make(max(nbytes, 1 << 16) + self._align, dtype=torch.uint8, device=device)
+            self._buf[key] = buf
+        for h in Workspace._holders:
+            h.append(buf)
+        pad = (-buf.data_ptr()) % self._align
+        return buf[pad:pad + nbytes]
+
+    @staticmethod
+    def holding(refs: list):
+        return _Holding(refs)
+
+
+class _Holding:
+    def __init__(self, refs):
+        self.refs = refs
+
+    def __enter__(self):
+        Workspace._holders.append(self.refs)
+        return self.refs
+
+    def __exit__(self, *a):
+        Workspace._holders.remove(self.refs)
+        return False

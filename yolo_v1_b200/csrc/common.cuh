@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/yolohead.h"
 
 namespace yh {
@@ -25,7 +27,12 @@ void set_error(const char *fmt, ...);
 // A zeroed device counter for one launch's dynamic image schedule (api.cu): slots are handed
 // out round-robin from a ring, so launches in flight on different streams never share one,
 // and the slot is cleared on the launch's own stream.
+// Returns nullptr (error set) when a graph capture has used up its never-recycled slots.
 unsigned *fresh_ticket(cudaStream_t stream);
+constexpr int kMaxDevices = 64;
+// true the first time it is called for (flag array of kMaxDevices, current device)
+bool first_use_on_device(std::atomic<bool> *seen);
+int current_device();
 int check_launch(const char *what, int kernels_launched = 1);
 
 inline bool shape_ok(int S, int B, int C) { return S == kS && B == kB && C == kC; }

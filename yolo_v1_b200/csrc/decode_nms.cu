@@ -125,17 +125,18 @@ static int launch(const float *pred, int N, double conf_thr, double nms_thr, int
                   uint8_t *keep_k, uint8_t *keep_cls, double *keep_conf, double *keep_box,
                   int32_t *n_cand, uint8_t *bad_range, cudaStream_t st) {
     const size_t smem = sizeof(WarpWindow) * kWarpsPerCta;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static std::atomic<bool> attr_done[kMaxDevices];
+    if (first_use_on_device(attr_done)) {
         cudaFuncSetAttribute(decode_nms_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_done = true;
     }
     int ctas = (N + kWarpsPerCta - 1) / kWarpsPerCta;
     const int cap = 148 * kCtasPerSm;
     if (ctas > cap) ctas = cap;
+    unsigned *ticket = fresh_ticket(st);
+    if (ticket == nullptr) return YH_ERR_UNSUPPORTED;
     decode_nms_kernel<MODE><<<ctas, kWarpsPerCta * 32, smem, st>>>(
         pred, N, conf_thr, nms_thr, order, n_keep, keep_k, keep_cls, keep_conf, keep_box, n_cand, bad_range,
-        fresh_ticket(st));
+        ticket);
     return check_launch("yh_decode_nms");
 }
 

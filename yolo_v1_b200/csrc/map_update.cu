@@ -335,15 +335,15 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
     th.n = T;
     for (int i = 0; i < YH_MAX_THRESHOLDS; ++i) th.t[i] = i < T ? thresholds_host[i] : 2.0;
     const size_t smem = sizeof(WarpWindow) * kWarpsPerCtaM;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static std::atomic<bool> attr_done[kMaxDevices];
+    if (first_use_on_device(attr_done)) {
         cudaFuncSetAttribute(map_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_done = true;
     }
     int ctas = (N + kWarpsPerCtaM - 1) / kWarpsPerCtaM;
     const int cap = 148 * kCtasPerSmM;
     if (ctas > cap) ctas = cap;
     unsigned *ticket = fresh_ticket((cudaStream_t)stream);
+    if (ticket == nullptr) return YH_ERR_UNSUPPORTED;
     map_update_kernel<<<ctas, kWarpsPerCtaM * 32, smem, (cudaStream_t)stream>>>(
         pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, (uint64_t *)rec_box, n_gt, gt_cell,
         gt_cls, (float4 *)gt_raw, gt_count, ticket);

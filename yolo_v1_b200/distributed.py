@@ -202,14 +202,12 @@ class PeerExchange:
         ko, fo = int(lib.yh_peer_key_offset(self.capacity)), int(lib.yh_peer_flags_offset(self.capacity))
         self.recv_key = raw[ko:ko + 8 * self.capacity].view(torch.int64)
         self.recv_flags = raw[fo:fo + 8 * self.capacity].view(torch.int64)
-        self._ws = None
+        self._ws = _lib.Workspace()
 
     def exchange(self, key, flags, m: int, m_dev, owners: List[int], gt_count: torch.Tensor, n_images: int):
         """Returns (recv_key, recv_flags, gt_count_global int32 [4C], info int64 [4]); see yolohead.h."""
         lib, dev = _lib.lib(), self.device
-        need = int(lib.yh_exchange_workspace_bytes(int(m))) + 256
-        if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        ws = self._ws.get(dev, int(lib.yh_exchange_workspace_bytes(int(m))))
         gt_glob = torch.empty_like(gt_count)
         info = torch.empty(4, dtype=torch.int64, device=dev)
         tab = (_lib.C.c_uint8 * len(owners))(*owners)
@@ -217,8 +215,8 @@ class PeerExchange:
             rc = lib.yh_exchange_records(key.data_ptr() if m else None, flags.data_ptr() if m else None, int(m),
                                          _lib.ptr(m_dev), tab, len(owners), self.world, self.rank, self._blocks,
                                          self.capacity, 0, gt_count.data_ptr(), int(n_images),
-                                         gt_glob.data_ptr(), info.data_ptr(), self._ws.data_ptr(),
-                                         self._ws.numel(), _lib.stream_ptr(dev))
+                                         gt_glob.data_ptr(), info.data_ptr(), ws.data_ptr(),
+                                         ws.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "yh_exchange_records")
         return self.recv_key, self.recv_flags, gt_glob, info
 

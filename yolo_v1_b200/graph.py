@@ -72,7 +72,11 @@ class CapturedHeadStep:
         lib = _lib.lib()
         self.graph = torch.cuda.CUDAGraph()
         before = lib.yh_launch_count()
-        with torch.cuda.graph(self.graph, stream=self._main):
+        # every workspace handed out during the capture has its address baked into the graph: hold them
+        # (the caches in _lib.Workspace are per stream, and these two streams are private to this object,
+        # so nothing else regrows them; the references make that independent of the caches' lifetime)
+        self._held: list = []
+        with _lib.Workspace.holding(self._held), torch.cuda.graph(self.graph, stream=self._main):
             self._out = self._enqueue()
             self._host.copy_(self._out, non_blocking=True)   # the read-back is a node of the graph too
         self.launches_per_replay = int(lib.yh_launch_count() - before)   # this library's kernels in the graph

@@ -156,7 +156,7 @@ def compact_records(chunk: UpdateChunk, out_key: torch.Tensor | None = None, out
     if out_key is None:
         out_key = torch.empty(N * K, dtype=torch.int64, device=dev)
         out_flags = torch.empty(N * K, dtype=torch.int64, device=dev)
-    ws = torch.empty(lib.yh_compact_workspace_bytes(N), dtype=torch.uint8, device=dev)
+    ws = _COMPACT_WS.get(dev, lib.yh_compact_workspace_bytes(N))
     with _lib.on_device(dev):
         rc = lib.yh_compact_records(chunk.n_keep.data_ptr(), chunk.rec_key.data_ptr(), chunk.rec_flags.data_ptr(),
                                     N, K, offsets.data_ptr(), out_key.data_ptr(), out_flags.data_ptr(),
@@ -165,17 +165,8 @@ def compact_records(chunk: UpdateChunk, out_key: torch.Tensor | None = None, out
     return out_key, out_flags, offsets
 
 
-_AP_WS: dict = {}
-
-
-def _ap_workspace(dev, nbytes: int) -> torch.Tensor:
-    """Per-device scratch for yh_ap_reduce, grown on demand and reused (256-byte aligned view)."""
-    buf = _AP_WS.get(dev)
-    if buf is None or buf.numel() < nbytes + 256:
-        buf = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
-        _AP_WS[dev] = buf
-    pad = (-buf.data_ptr()) % 256
-    return buf[pad:pad + nbytes]
+_AP_WS = _lib.Workspace()
+_COMPACT_WS = _lib.Workspace()
 
 
 def ap_reduce(key: torch.Tensor, flags: torch.Tensor, M: int, gt_count: torch.Tensor, Cn: int, T: int,
@@ -190,7 +181,7 @@ def ap_reduce(key: torch.Tensor, flags: torch.Tensor, M: int, gt_count: torch.Te
     nbytes = lib.yh_ap_workspace_bytes(int(M), Cn, T)
     if nbytes == 0:
         raise NotImplementedError(f"yh_ap_reduce: C={Cn}, T={T} outside this build")
-    ws = _ap_workspace(dev, nbytes)
+    ws = _AP_WS.get(dev, nbytes)
     ap = torch.empty(4, Cn, T, dtype=torch.float64, device=dev)
     totals = torch.empty(2, dtype=torch.int64, device=dev)
     packed = torch.empty(4 * Cn * T + 3 + 4 * Cn, dtype=torch.float64, device=dev)

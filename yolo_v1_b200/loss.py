@@ -18,21 +18,7 @@ from . import _lib
 _KEYS = ("total", "coord", "conf_obj", "conf_noobj", "class")
 
 
-class _Workspace:
-    """Per-device scratch for the loss kernel, grown on demand, reused across calls."""
-
-    def __init__(self):
-        self.buf = {}
-
-    def get(self, device, nbytes: int) -> torch.Tensor:
-        b = self.buf.get(device)
-        if b is None or b.numel() < nbytes:
-            b = torch.zeros(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
-            self.buf[device] = b
-        return b
-
-
-_WS = _Workspace()
+_WS = _lib.Workspace(zeroed=True)
 
 
 def loss_fwd_bwd(pred: torch.Tensor, tgt: torch.Tensor, S: int, B: int, C: int, lambda_coord: float,
@@ -114,20 +100,32 @@ class LossDict(dict):
 
 
 class _YoloLossFn(torch.autograd.Function):
+    """forward runs the fused kernel once (loss parts + d loss / d predictions); backward hands that
+    gradient to autograd scaled by the upstream scalar.  The buffer is given away on the first
+    backward (so autograd can adopt it without a copy); a further backward over a retained graph
+    (`retain_graph=True`) re-runs the kernel on the saved inputs, as the reference's graph would
+    recompute its gradient."""
+
     @staticmethod
     def forward(ctx, pred, tgt, S, B, C, lc, ln):
         need = pred.requires_grad
         parts, grad = loss_fwd_bwd(pred, tgt, S, B, C, lc, ln, want_grad=need)
         ctx.saved_grad = grad
+        ctx.cfg = (S, B, C, lc, ln)
+        if need:
+            ctx.save_for_backward(pred, tgt)    # references only; autograd checks their versions
         ctx.mark_non_differentiable(parts)
         return parts[0].clone(), parts
 
     @staticmethod
     def backward(ctx, g_total, _g_parts):
-        grad = ctx.saved_grad
-        if grad is None:
+        if not ctx.needs_input_grad[0]:
             return (None,) * 7
+        grad = ctx.saved_grad
         ctx.saved_grad = None
+        if grad is None:                        # second backward: the first one gave the buffer away
+            pred, tgt = ctx.saved_tensors
+            grad = loss_fwd_bwd(pred, tgt, *ctx.cfg, want_grad=True)[1]
         scale = g_total.detach().to(torch.float32).reshape(1).contiguous()
         with _lib.on_device(grad.device):
             rc = _lib.lib().yh_scale_inplace(grad.data_ptr(), _lib.dtype_code(grad), grad.numel(),

@@ -17,16 +17,11 @@ from . import _lib
 
 IMAGENET_MEAN = (0.485, 0.456, 0.406)
 IMAGENET_STD = (0.229, 0.224, 0.225)
-_WS: dict = {}
+_WS = _lib.Workspace()
 
 
 def _workspace(dev: torch.device, nbytes: int) -> torch.Tensor:
-    buf = _WS.get(dev)
-    if buf is None or buf.numel() < nbytes + 256:
-        buf = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
-        _WS[dev] = buf
-    pad = (-buf.data_ptr()) % 256
-    return buf[pad:pad + nbytes]
+    return _WS.get(dev, nbytes)
 
 
 def preprocess_rgb8(image: torch.Tensor, size: Sequence[int] = (448, 448), mean: Sequence[float] = IMAGENET_MEAN,

@@ -26,7 +26,7 @@ def encode_targets(bboxes: Sequence[Sequence[Sequence[float]]], class_ids: Seque
     outside the one-hot range)."""
     if len(bboxes) != len(class_ids):
         raise ValueError("bboxes and class_ids differ in length")
-    dev = torch.device(device if device is not None else ("cuda", torch.cuda.current_device()))
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
     if dev.type != "cuda":
         raise _lib.YoloHeadError("encode_targets runs on CUDA only (no CPU fallback)")
     n = len(bboxes)
