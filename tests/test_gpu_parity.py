@@ -240,11 +240,12 @@ def test_map_matches_reference_golden(golden, case):
         assert float(res2[k]) == pytest.approx(v, rel=1e-9, abs=1e-12), f"list path {k}"
 
 
-def test_map_lists_match_reference_order(golden):
+@pytest.mark.parametrize("lists", ["lazy", "eager"])
+def test_map_lists_match_reference_order(golden, lists):
     g = golden("decode_nms")
     for profile in ("correlated", "ties"):
         pred = torch.from_numpy(g[f"{profile}/pred"]).to(DEV)
-        metric = mAPMetric(num_classes=20, conf_threshold=0.01)
+        metric = mAPMetric(num_classes=20, conf_threshold=0.01, lists=lists)
         metric.update(pred, torch.zeros_like(pred))
         tag = f"{profile}/c0.01"
         gk = g[f"{tag}/metrics_keep_k"]
@@ -255,6 +256,32 @@ def test_map_lists_match_reference_order(golden):
             assert [d[1] for d in dets] == g[f"{tag}/metrics_conf"][i, :n].tolist()
             assert np.array([d[2] for d in dets]).reshape(n, 4).tobytes() == g[f"{tag}/metrics_box"][i, :n].tobytes()
         assert all(len(gts) == 0 for gts in metric.all_ground_truths)
+
+
+def test_list_modes_agree_and_lazy_mode_guards_against_inplace_edits(golden):
+    """lists="lazy" rebuilds all_predictions / all_ground_truths from the retained batch, lists="eager" from what
+    the update kernel stored: same lists.  A batch edited in place after update() makes the lazy rebuild raise."""
+    from yolo_v1_b200 import _lib
+
+    g = golden("map_small")
+    pred, tgt = torch.from_numpy(g["corr64/pred"]).to(DEV), torch.from_numpy(g["corr64/tgt"]).to(DEV)
+    a, b = mAPMetric(num_classes=20, lists="lazy"), mAPMetric(num_classes=20, lists="eager")
+    for m in (a, b):
+        m.update(pred[:40], tgt[:40])
+        m.update(pred[40:], tgt[40:])
+    assert a._chunks[0].rec_raw is None and b._chunks[0].rec_raw is not None
+    assert a.all_predictions == b.all_predictions and a.all_ground_truths == b.all_ground_truths
+    assert len(a.all_predictions) == 64 and sum(len(x) for x in a.all_ground_truths) > 0
+    assert a.compute() == b.compute()
+    c = mAPMetric(num_classes=20)
+    p2 = pred.clone()
+    c.update(p2, tgt)
+    p2.mul_(0.5)
+    with pytest.raises(_lib.YoloHeadError):
+        c.all_predictions
+    d = mAPMetric(num_classes=20)
+    d.update(pred.cpu(), tgt.cpu())          # host tensors: the metric's own device copy is retained
+    assert d.all_predictions == a.all_predictions
 
 
 @pytest.mark.parametrize("n,profile,conf_thr", [(4952, "correlated", 0.01), (3000, "uniform", 0.3),

@@ -3,17 +3,24 @@
 //
 // The 98 candidate boxes of an image never leave the SM: the 5,880-byte image is
 // staged into the warp's shared-memory window with coalesced 8-byte loads (an
-// image start is only 8-byte aligned), decoded into a per-candidate table
-// (corners, area, confidence as fp64), ordered by (class, confidence desc,
-// candidate asc) with a per-class counting rank, and suppressed by a bitmask NMS
-// whose rounds advance every class at once.
+// image start is only 8-byte aligned), decoded into a per-candidate table, ordered
+// by (class, confidence desc, candidate asc) with a per-class counting rank, and
+// suppressed by a bitmask NMS.
+//
+// Round 2: the candidate table is fp32.  It holds the corners and the area of every
+// candidate rounded to float, plus the exact confidence as an orderable 64-bit key.
+// Every "IoU < threshold" test is first made on fp32 intervals (iou_filter.cuh) that
+// provably contain the reference's fp64 values; the exact fp64 sequence (one rounding per
+// operator, as the reference's Python doubles) runs only for the few pairs the intervals
+// cannot separate from the threshold, on the raw values re-read from global memory.  The
+// absolute centre (col + x) / S is no longer computed in fp64 per candidate -- only for
+// those rare pairs and for box outputs.
 //
 // Code-size discipline: the first version of this file unrolled every 4-slot loop
 // and inlined every fp64 division; the kernels grew past 64 KB of SASS and ncu
 // showed 85% of stall samples in `no_inst` (instruction-cache misses with ~20
 // unsynchronised warps per SM; profiles/r01_map_update_v1_lines.txt).  Slot loops
-// are therefore kept rolled, divisions by S use a 3-instruction FMA sequence and
-// the rare exact-quotient path is a call.
+// are therefore kept rolled and the rare exact paths are calls.
 //
 // Reference semantics reproduced here (paths relative to the reference repo):
 //   decode            src/yolo/metrics.py:187-216, src/yolo/inference.py:174-208
@@ -22,6 +29,7 @@
 #pragma once
 
 #include "common.cuh"
+#include "iou_filter.cuh"
 
 namespace yh {
 
@@ -33,19 +41,18 @@ constexpr int kSlots = 4;                     // candidates a lane can own
 constexpr int kPad = 104;                     // 98 rounded up to a multiple of 8
 
 // Candidate table, indexed by candidate k = 2*cell + b.  Only entries whose
-// confidence passed the threshold are written / read.  Centre in fp64 (it is the
-// quotient (col + x) / S), width / height as the raw floats: corners and area are
-// rebuilt on demand (9 fp64 operations) instead of being stored (40 B -> 24 B).
+// confidence passed the threshold are written / read.
 struct CandTable {
-    double xa[kCand], ya[kCand], conf[kCand];
-    float2 wh[kCand];
+    float4 box[kCand];      // fp32 corners (x1, y1, x2, y2), see iou_filter.cuh for their error bound
+    uint64_t key[kCand];    // ~orderable(conf): ascending key = descending fp64 confidence (exact, invertible)
+    float area[kCand];      // RN32(w * h)
     uint8_t cls[kPad];
 };
 
-// Shared-memory window of one warp: 7.4 KB, so 28 warps (7 CTAs of 4) fit an SM.
+// Shared-memory window of one warp: 7.0 KB, so 28 warps (7 CTAs of 4) fit an SM.
 struct __align__(16) WarpWindow {
     float2 stage[kHalfPairs];       // 3,840 B: half an image; reused as NmsOverlay / MatchOverlay
-    CandTable cand;                 // 3,240 B
+    CandTable cand;                 // 2,848 B
     uint8_t order[kPad];            // sorted position p -> candidate k
     uint8_t member[kPad];           // class-segmented member lists (scratch of the ordering)
     int count[kC];                  // class histogram, then running cursor
@@ -55,6 +62,13 @@ struct __align__(16) WarpWindow {
     unsigned validw[4];             // candidates above the threshold, by candidate index
     unsigned keepw[4];              // kept after NMS, by sorted position
     uint8_t keepbase[4];            // kept detections in the words before word s
+};
+
+// What the fp32 prefilter needs to know about the image in hand (warp-uniform).
+struct ImageFilter {
+    float M;       // bound on the magnitude of every fp32 corner of the image's candidates (NaN if one is NaN)
+    float E;       // half-width of the interval around an fp32 intersection side
+    bool ok;       // no NaN / infinite / huge coordinate among the candidates (and the threshold in range)
 };
 
 // ---- exact (j + v) / 7 ----------------------------------------------------------
@@ -72,6 +86,15 @@ __device__ __forceinline__ double div_by_S(double x) {
 // x_abs = (col + x) / S, y_abs = (row + y) / S in doubles (metrics.py:200-201).
 __device__ __forceinline__ double abs_coord(int cell_coord, float v) {
     return div_by_S(__dadd_rn((double)cell_coord, (double)v));
+}
+
+// The reference's fp64 corners of candidate k (or of the box in slot 0 of cell `k >> 1` of a
+// target image when k is even), rebuilt from the raw values in global memory.  Rare path.
+static __device__ __noinline__ Corners exact_corners(const float *__restrict__ img, int k) {
+    const int cell = k >> 1;
+    const float *b = img + cell * kD + (k & 1) * 5;
+    const float x = __ldg(b), y = __ldg(b + 1), w = __ldg(b + 2), h = __ldg(b + 3);
+    return corners_of(abs_coord(cell % kS, x), abs_coord(cell / kS, y), (double)w, (double)h);
 }
 
 // ---- staging ------------------------------------------------------------------
@@ -147,16 +170,19 @@ __device__ __forceinline__ unsigned spread16(unsigned x) {
 // Each lane decodes cells `lane` and `lane + 32` (one per staged half); candidate
 // k = 2*cell + b.  Fills w.cand for every candidate above conf_thr and returns the
 // validity mask (indexed by k).  bad (optional) reports a kept candidate outside
-// [0,1] (schemas.py:9-16,88).
+// [0,1] (schemas.py:9-16,88).  filt receives the image's prefilter margin.
 // tgt_img / tconf0 / tconf1 (optional): the target image and the slot-0 confidences of this
 // lane's two target cells; object cells get their lines prefetched towards L2 between the
 // two halves, a good while before the caller parses them.
 __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__restrict__ img, int lane,
-                                                double conf_thr, bool *bad, const float *__restrict__ tgt_img = nullptr,
+                                                double conf_thr, bool *bad, ImageFilter &filt,
+                                                const float *__restrict__ tgt_img = nullptr,
                                                 float tconf0 = 0.f, float tconf1 = 0.f) {
     const float *st = reinterpret_cast<const float *>(w.stage);
     Mask128 valid = {0, 0, 0, 0};
     bool any_bad = false;
+    float mag = 0.f;
+    const float inv_s = 1.0f / (float)kS;
 #pragma unroll 1
     for (int cs = 0; cs < 2; ++cs) {
         stage_half(w, img, cs, lane);
@@ -167,6 +193,7 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
         const int cls = cell_class_shared(c, conf_thr, pv);
         const double prob = (double)pv;
         const int col = cell % kS, row = cell / kS;
+        const float colf = (float)col, rowf = (float)row;
         bool ok[kB];
 #pragma unroll
         for (int b = 0; b < kB; ++b) {
@@ -175,16 +202,19 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
             ok[b] = live && conf > conf_thr;
             if (ok[b]) {
                 const int k = cell * kB + b;
-                const double xa = abs_coord(col, bx[0]), ya = abs_coord(row, bx[1]);
-                w.cand.xa[k] = xa;
-                w.cand.ya[k] = ya;
-                w.cand.wh[k] = make_float2(bx[2], bx[3]);
-                w.cand.conf[k] = conf;
+                const float x = bx[0], y = bx[1], bw = bx[2], bh = bx[3];
+                const BoxF f = make_box_f((colf + x) * inv_s, (rowf + y) * inv_s, bw, bh);
+                w.cand.box[k] = make_float4(f.x1, f.y1, f.x2, f.y2);
+                w.cand.area[k] = f.area;
+                w.cand.key[k] = ~orderable(conf == 0.0 ? 0.0 : conf);
                 w.cand.cls[k] = (uint8_t)cls;
+                const float m = box_magnitude(f);
+                mag = (m > mag || m != m) ? m : mag;   // NaN sticks
                 if (bad != nullptr) {
-                    const double ww = (double)bx[2], hh = (double)bx[3];
-                    any_bad |= !(xa >= 0.0 && xa <= 1.0 && ya >= 0.0 && ya <= 1.0 && ww >= 0.0 && ww <= 1.0 &&
-                                 hh >= 0.0 && hh <= 1.0 && conf >= 0.0 && conf <= 1.0);
+                    // (col + x) / S in [0, 1] <=> col + x in [0, S] <=> x in [-col, S - col]: exact in fp32
+                    // (the reference's doubles: col + x is exact, the quotient is monotone, S / S == 1)
+                    any_bad |= !(x >= -colf && x <= (float)kS - colf && y >= -rowf && y <= (float)kS - rowf &&
+                                 bw >= 0.f && bw <= 1.f && bh >= 0.f && bh <= 1.f && conf >= 0.0 && conf <= 1.0);
                 }
             }
         }
@@ -203,6 +233,12 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
         }
     }
     if (bad != nullptr) *bad = any_bad;
+    // image-wide magnitude bound: non-negative floats (and NaN, whose pattern is the largest) order like
+    // their bit patterns, so one integer max reduction does it
+    const float M = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(mag)));
+    filt.M = M;
+    filt.ok = M < kFilterMaxCoord;
+    filt.E = filter_margin(M);
     __syncwarp();
     return valid;
 }

@@ -6,10 +6,32 @@
 
 namespace yh {
 
-// corners and area of candidate k, built as the reference does (x - w / 2, ..., w * h)
-__device__ __forceinline__ Corners cand_corners(const WarpWindow &w, int k) {
-    const float2 wh = w.cand.wh[k];
-    return corners_of(w.cand.xa[k], w.cand.ya[k], (double)wh.x, (double)wh.y);
+// fp32 corners / area of candidate k from the table
+__device__ __forceinline__ BoxF cand_box(const WarpWindow &w, int k) {
+    const float4 b = w.cand.box[k];
+    BoxF f;
+    f.x1 = b.x; f.y1 = b.y; f.x2 = b.z; f.y2 = b.w;
+    f.area = w.cand.area[k];
+    return f;
+}
+
+// "IoU(first, second) < thr" with the reference's fp64 arithmetic and argument order, the two boxes
+// rebuilt from the raw image in global memory.  The rare path behind the prefilter.
+template <int MODE>
+static __device__ __noinline__ bool pair_below_exact(const float *__restrict__ img, int k_first, int k_second,
+                                                     double thr) {
+    return iou_below<MODE>(exact_corners(img, k_first), exact_corners(img, k_second), thr);
+}
+
+// The keep test of NMS for two candidates of one image: the fp32 interval verdict when there is one,
+// else the exact sequence.
+template <int MODE>
+__device__ __forceinline__ bool pair_below(const WarpWindow &w, const float *__restrict__ img, int k_first,
+                                           int k_second, double thr, const FilterParams &fp, const ImageFilter &filt) {
+    int verdict = 0;
+    if (filt.ok) verdict = iou_below_fast<MODE == YH_IOU_INFER>(cand_box(w, k_first), cand_box(w, k_second), filt.E, fp);
+    if (verdict == 0) return pair_below_exact<MODE>(img, k_first, k_second, thr);
+    return verdict > 0;
 }
 
 // ---- class segments -------------------------------------------------------------------
@@ -64,12 +86,12 @@ static __device__ __noinline__ void rank_members(WarpWindow &w, int lane) {
             const int k = lane + 32 * s;
             const int c = w.cand.cls[k];
             const int lo = w.cls_start[c], hi = w.cls_start[c + 1];
-            const double mine = w.cand.conf[k];
+            const uint64_t mine = w.cand.key[k];
             int r = 0;
             for (int q = lo; q < hi; ++q) {
                 const int m = w.member[q];
-                const double other = w.cand.conf[m];
-                r += (other > mine) || (other == mine && m < k);
+                const uint64_t other = w.cand.key[m];
+                r += (other < mine) || (other == mine && m < k);
             }
             w.order[lo + r] = (uint8_t)k;
         }
@@ -83,7 +105,9 @@ static __device__ __noinline__ void rank_members(WarpWindow &w, int lane) {
 // nms_pairwise (a class with more than 64 members) and for "decode only" (NaN
 // threshold: keep everything).
 template <int MODE>
-static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, int n, double nms_thr, int lane) {
+static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, const float *__restrict__ img, int n,
+                                                  double nms_thr, const FilterParams &fp, const ImageFilter &filt,
+                                                  int lane) {
     Mask128 rem, keep = {0, 0, 0, 0};
 #pragma unroll
     for (int s = 0; s < kSlots; ++s) {
@@ -107,7 +131,7 @@ static __device__ __noinline__ Mask128 nms_rounds(const WarpWindow &w, int n, do
                     mine = false;
                 } else {
                     // reference argument order: iou(current, other)
-                    mine = iou_below<MODE>(cand_corners(w, w.order[head]), cand_corners(w, k), nms_thr);
+                    mine = pair_below<MODE>(w, img, w.order[head], k, nms_thr, fp, filt);
                 }
             }
             still.set_word(s, __ballot_sync(kFull, mine));
@@ -141,8 +165,9 @@ static_assert(sizeof(NmsOverlay) <= sizeof(float2) * kHalfPairs, "overlay too la
 // Returns n and the keep mask by sorted position.  A class with more than 64 members,
 // or a NaN threshold ("decode only": keep everything), takes rank_members + nms_rounds.
 template <int MODE, bool PAIR_TABLE>
-__device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const Mask128 &valid, double nms_thr, int lane,
-                                                 int &n_out) {
+__device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const float *__restrict__ img, const Mask128 &valid,
+                                                 double nms_thr, const FilterParams &fp, const ImageFilter &filt,
+                                                 int lane, int &n_out) {
     const int n = build_members(w, valid, lane);
     n_out = n;
     const int cc = lane < kC ? lane : 0;
@@ -150,7 +175,7 @@ __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const Mask128 &v
     const int m = lane < kC ? chi - clo : 0;
     if (__any_sync(kFull, m > 64) || nms_thr != nms_thr) {
         rank_members(w, lane);
-        return nms_rounds<MODE>(w, n, nms_thr, lane);
+        return nms_rounds<MODE>(w, img, n, nms_thr, fp, filt, lane);
     }
     NmsOverlay &no = *reinterpret_cast<NmsOverlay *>(w.stage);
     const int np = m * (m - 1) / 2;
@@ -185,12 +210,12 @@ __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const Mask128 &v
         const int i = u - j * (j - 1) / 2;                           // i < j, member indices
         const int lo = w.cls_start[c];
         const int ki = w.member[lo + i], kj = w.member[lo + j];
-        const double ci = w.cand.conf[ki], cj = w.cand.conf[kj];
-        const bool i_first = (ci > cj) || (ci == cj && ki < kj);
+        const uint64_t ci = w.cand.key[ki], cj = w.cand.key[kj];     // ascending key = descending confidence
+        const bool i_first = (ci < cj) || (ci == cj && ki < kj);
         const int e = i_first ? i : j, l = i_first ? j : i;          // earlier / later member
         atomicAdd(&no.beaten[lo + l], 1);
         // reference argument order: iou(current = earlier, other = later)
-        if (!iou_below<MODE>(cand_corners(w, i_first ? ki : kj), cand_corners(w, i_first ? kj : ki), nms_thr))
+        if (!pair_below<MODE>(w, img, i_first ? ki : kj, i_first ? kj : ki, nms_thr, fp, filt))
             atomicOr(&no.sup[lo + l], 1ull << e);
     }
     __syncwarp();
@@ -241,17 +266,17 @@ __device__ __forceinline__ void class_group_offsets(WarpWindow &w, const Mask128
     const int lo = w.cls_start[c], hi = w.cls_start[c + 1];
     const bool present = (lane < kC) && hi > lo;
     const int hk = present ? w.order[lo] : 0;
-    const double hc = present ? w.cand.conf[hk] : 0.0;
+    const uint64_t hc = present ? w.cand.key[hk] : 0ull;
     const int kbase = present ? count_below(keep, lo) : 0;
     const int kc = present ? count_below(keep, hi) - kbase : 0;
     const unsigned have = __ballot_sync(kFull, present);
     int off = 0;
     for (unsigned m = have; m; m &= m - 1) {
         const int o = __ffs(m) - 1;
-        const double oc = __shfl_sync(kFull, hc, o);
+        const uint64_t oc = __shfl_sync(kFull, hc, o);
         const int ok = __shfl_sync(kFull, hk, o);
         const int on = __shfl_sync(kFull, kc, o);
-        if ((oc > hc) || (oc == hc && ok < hk)) off += on;
+        if ((oc < hc) || (oc == hc && ok < hk)) off += on;
     }
     if (lane < kC) {
         w.cls_off[lane] = (uint8_t)off;

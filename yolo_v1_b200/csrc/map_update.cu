@@ -21,42 +21,48 @@ struct Thresholds {
     int n;
 };
 
-// Overlay of `stage` once the target image has been parsed into registers.
+// Overlay of `stage` once the predictions have been decoded: ground truths and per-item match results.
 struct MatchOverlay {
-    double gx1[kCells], gy1[kCells], gx2[kCells], gy2[kCells], garea[kCells];  // 1,960 B, compact, cell order
-    uint8_t gcls[kCells + 7], gbucket[kCells + 7];                              // 112 B
-    unsigned long long flags[kCand];  // TP bits by sorted position                 784 B
-    uint8_t bgt[kCand][4];            // by item: best ground truth per subset (255 = none)
-    uint8_t ik[kPad], icls[kPad], ipos[kPad];  // by item: candidate, class, sorted position
+    float4 gbox[kCells];               // fp32 corners of the ground truths, compact, in cell order      784 B
+    float garea[kCells];               //                                                                 196 B
+    uint8_t gcell[kCells + 7], gcls[kCells + 7], gbucket[kCells + 7];          //                         168 B
+    unsigned long long flags[kCand];   // TP bits by sorted position                                      784 B
+    // by item and ground-truth subset (0 all, 1 small, 2 medium, 3 large):
+    unsigned short imask[kCand][4];    // bit t: best IoU >= threshold t; bit T (subset 0): best IoU >= 0.5  784 B
+    uint8_t bgt[kCand][4];             // best ground truth (255 = none)                                  392 B
+    uint8_t ik[kPad], icls[kPad], ipos[kPad];  // by item: candidate, class, sorted position              312 B
 };
 static_assert(sizeof(MatchOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
 
-// Best IoU of a matched detection against the ground truths of one size bucket
-// (1 small / 2 medium / 3 large), indexed by candidate k.  The three tables reuse
-// the candidate's geometry slots (xa, ya, wh): a lane overwrites them only after it
-// has finished with its own candidate's corners, and nobody else reads them.
-__device__ __forceinline__ double *bucket_iou(WarpWindow &w, int bucket) {
-    return bucket == 1 ? w.cand.xa : (bucket == 2 ? w.cand.ya : reinterpret_cast<double *>(w.cand.wh));
-}
+// Thresholds in shared memory: the doubles the reference compares with, and for each the largest float not above
+// and the smallest float not below it (the fp32 interval tests).  Entry T is the 0.5 of the overall
+// precision / recall pass (metrics.py:477).
+struct ThresholdTable {
+    double t[YH_MAX_THRESHOLDS + 1];
+    float lo[YH_MAX_THRESHOLDS + 1], hi[YH_MAX_THRESHOLDS + 1];
+};
 
 // Ground truths of one target image -> MatchOverlay (compact, in cell order).
 // The target tensor is almost empty (an object in about 1 cell of 18), so it is not
 // staged: tconf0/tconf1 are the slot-0 confidences of cells `lane` and `lane + 32`
 // (loaded by the caller long before, 49 sectors per image), and only object cells
 // fetch their box and class scores.  Returns the number of ground truths; cls_mask
-// gets bit c for every class present.  gt_hist (shared, 4*kC ints) accumulates the
-// per-(subset, class) counts of this CTA.
+// gets bit c for every class present; gmag the largest fp32 corner magnitude (for the
+// prefilter margin).  gt_hist (shared, 4*kC ints) accumulates the per-(subset, class)
+// counts of this CTA.
 __device__ __forceinline__ int parse_targets(WarpWindow &w, const float *__restrict__ img, int lane,
                                              float tconf0, float tconf1, int *gt_hist, unsigned &cls_mask,
-                                             uint8_t *__restrict__ out_cell, uint8_t *__restrict__ out_cls,
-                                             float4 *__restrict__ out_raw) {
+                                             float &gmag, uint8_t *__restrict__ out_cell,
+                                             uint8_t *__restrict__ out_cls, float4 *__restrict__ out_raw) {
     const bool gt0 = tconf0 > 0.f, gt1 = (lane + 32 < kCells) && tconf1 > 0.f;  // metrics.py:239
     const unsigned m0 = __ballot_sync(kFull, gt0), m1 = __ballot_sync(kFull, gt1);
     const unsigned lt = (1u << lane) - 1u;
     MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
     const double small_a = __dmul_rn(__ddiv_rn(32.0, 448.0), __ddiv_rn(32.0, 448.0));   // metrics.py:511
     const double medium_a = __dmul_rn(__ddiv_rn(96.0, 448.0), __ddiv_rn(96.0, 448.0));  // metrics.py:512
+    const float inv_s = 1.0f / (float)kS;
     unsigned mine = 0;
+    float mag = 0.f;
     __syncwarp();  // every lane is done with what the overlay region held before
 #pragma unroll 1
     for (int cs = 0; cs < 2; ++cs) {
@@ -67,12 +73,15 @@ __device__ __forceinline__ int parse_targets(WarpWindow &w, const float *__restr
         const float2 wh = __ldg(reinterpret_cast<const float2 *>(c) + 1);
         const int cls = cell_class_global(c);
         const int g = cs ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
-        const double xa = abs_coord(cell % kS, xy.x), ya = abs_coord(cell / kS, xy.y);
-        const Corners cr = corners_of(xa, ya, (double)wh.x, (double)wh.y);
-        mo.gx1[g] = cr.x1; mo.gy1[g] = cr.y1; mo.gx2[g] = cr.x2; mo.gy2[g] = cr.y2;
-        mo.garea[g] = cr.area;
+        const BoxF f = make_box_f(((float)(cell % kS) + xy.x) * inv_s, ((float)(cell / kS) + xy.y) * inv_s, wh.x, wh.y);
+        mo.gbox[g] = make_float4(f.x1, f.y1, f.x2, f.y2);
+        mo.garea[g] = f.area;
+        const float m = box_magnitude(f);
+        mag = (m > mag || m != m) ? m : mag;
+        mo.gcell[g] = (uint8_t)cell;
         mo.gcls[g] = (uint8_t)cls;
-        const int bucket = (cr.area < small_a) ? 1 : ((cr.area < medium_a) ? 2 : 3);
+        const double area = __dmul_rn((double)wh.x, (double)wh.y);            // exact, as metrics.py:519
+        const int bucket = (area < small_a) ? 1 : ((area < medium_a) ? 2 : 3);
         mo.gbucket[g] = (uint8_t)bucket;
         if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
             out_cell[g] = (uint8_t)cell;
@@ -84,8 +93,33 @@ __device__ __forceinline__ int parse_targets(WarpWindow &w, const float *__restr
         mine |= 1u << cls;
     }
     cls_mask = __reduce_or_sync(kFull, mine);
+    gmag = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(mag)));
     __syncwarp();
     return __popc(m0) + __popc(m1);
+}
+
+// Best ground truth of detection k within subset q and the thresholds its IoU reaches, with the reference's
+// own fp64 arithmetic (metrics.py:391-403, 613-623): both boxes rebuilt from the raw tensors.  The rare path
+// behind the fp32 intervals.  Returns the ground truth (255 = none); mask as MatchOverlay::imask.
+static __device__ __noinline__ int match_exact(const MatchOverlay &mo, const float *__restrict__ pimg,
+                                               const float *__restrict__ timg, int k, int c, int q, int ngt,
+                                               const ThresholdTable &th, int T, unsigned &mask) {
+    const Corners dc = exact_corners(pimg, k);
+    double best = 0.0;
+    int bg = 255;
+    for (int g = 0; g < ngt; ++g) {
+        if (mo.gcls[g] != c || (q != 0 && mo.gbucket[g] != q)) continue;
+        const double iou = iou_exact<YH_IOU_METRICS>(dc, exact_corners(timg, 2 * mo.gcell[g]));
+        if (iou > best) {  // strict: the first ground truth wins ties, IoU 0 never matches
+            best = iou;
+            bg = g;
+        }
+    }
+    unsigned m = 0;
+    if (bg != 255)
+        for (int t = 0; t <= T; ++t) m |= (best >= th.t[t] ? 1u : 0u) << t;
+    mask = m;
+    return bg;
 }
 
 __global__ void __launch_bounds__(kWarpsPerCtaM * 32, kCtasPerSmM)
@@ -99,14 +133,20 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WarpWindow *windows = reinterpret_cast<WarpWindow *>(smem_raw);
     __shared__ int gt_hist[4 * kC];
-    __shared__ double s_thr[YH_MAX_THRESHOLDS];
+    __shared__ ThresholdTable th;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     WarpWindow &w = windows[wib];
     const int warps_total = gridDim.x * kWarpsPerCtaM;
     const int T = thr.n;
     const unsigned lt = (1u << lane) - 1u;
+    const FilterParams fp = filter_params(nms_thr);
     for (int i = threadIdx.x; i < 4 * kC; i += blockDim.x) gt_hist[i] = 0;
-    if (threadIdx.x < YH_MAX_THRESHOLDS) s_thr[threadIdx.x] = thr.t[threadIdx.x];
+    if (threadIdx.x <= YH_MAX_THRESHOLDS) {
+        const double v = threadIdx.x < T ? thr.t[threadIdx.x] : (threadIdx.x == T ? 0.5 : 2.0);
+        th.t[threadIdx.x] = v;
+        th.lo[threadIdx.x] = __double2float_rd(v);
+        th.hi[threadIdx.x] = __double2float_ru(v);
+    }
     __syncthreads();
 
     // A warp's first image is fixed by its position; every further one is taken from a
@@ -120,28 +160,33 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         const float tconf0 = __ldg(timg + lane * kD + 4);
         const float tconf1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 4);
         // ---- predictions: decode, order, NMS
-        const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr, timg, tconf0, tconf1);
+        ImageFilter filt;
+        const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr, filt, timg, tconf0, tconf1);
+        ImageFilter nfilt = filt;
+        nfilt.ok = filt.ok && fp.thr_ok;
         int n;
-        const Mask128 keep = order_and_nms<YH_IOU_METRICS, false>(w, valid, nms_thr, lane, n);
+        const Mask128 keep = order_and_nms<YH_IOU_METRICS, false>(w, pimg, valid, nms_thr, fp, nfilt, lane, n);
         publish_keep(w, keep, lane);
         const bool lists = gt_raw != nullptr;
         if (rec_box != nullptr) {
-            // the kept boxes as the reference stores them: (x_abs, y_abs) fp64, (w, h) fp32.
-            // Written now: the matching below reuses the geometry slots of the table.
+            // the kept boxes as the reference stores them: (x_abs, y_abs) fp64, (w, h) fp32 (optional list data)
 #pragma unroll 1
             for (int s = 0; s < kSlots; ++s) {
                 if (!((w.keepw[s] >> lane) & 1u)) continue;
                 const int k = w.order[lane + 32 * s];
                 uint64_t *o = rec_box + 3 * ((size_t)img * kCand + w.keepbase[s] + __popc(w.keepw[s] & lt));
-                o[0] = (uint64_t)__double_as_longlong(w.cand.xa[k]);
-                o[1] = (uint64_t)__double_as_longlong(w.cand.ya[k]);
-                o[2] = *reinterpret_cast<const uint64_t *>(&w.cand.wh[k]);
+                const int cell = k >> 1;
+                const float *b = pimg + cell * kD + (k & 1) * 5;
+                o[0] = (uint64_t)__double_as_longlong(abs_coord(cell % kS, __ldg(b)));
+                o[1] = (uint64_t)__double_as_longlong(abs_coord(cell / kS, __ldg(b + 1)));
+                o[2] = (uint64_t)__float_as_uint(__ldg(b + 2)) | ((uint64_t)__float_as_uint(__ldg(b + 3)) << 32);
             }
         }
 
         // ---- targets: parse into the overlay
         unsigned cls_mask;
-        const int ngt = parse_targets(w, timg, lane, tconf0, tconf1, gt_hist, cls_mask,
+        float gmag;
+        const int ngt = parse_targets(w, timg, lane, tconf0, tconf1, gt_hist, cls_mask, gmag,
                                       lists ? gt_cell + (size_t)img * kCells : nullptr,
                                       lists ? gt_cls + (size_t)img * kCells : nullptr,
                                       lists ? gt_raw + (size_t)img * kCells : nullptr);
@@ -150,6 +195,10 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             n_keep[img] = keep.count();
             n_gt[img] = ngt;
         }
+        // prefilter margin for detection-vs-ground-truth pairs: both sets of corners count
+        const float mM = fmaxf(filt.M, gmag);
+        const bool mok = filt.ok && gmag < kFilterMaxCoord;
+        const float mE = filter_margin(mM);
 
         // ---- items: kept detections whose class has a ground truth, in sorted order
         int n_items = 0;
@@ -175,44 +224,52 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         }
         __syncwarp();
 
-        // ---- best ground truth of every item per size bucket; "all sizes" follows from the three
+        // ---- best ground truth and threshold mask of every (item, subset): one lane each, the reference's loop
+        // per subset (metrics.py:391-403 over all ground truths of the class, :613-623 over one size bucket).
+        // IoUs are fp32 intervals; a comparison the intervals cannot settle sends that (item, subset) to the
+        // exact fp64 loop.
+        const int n_work = 4 * n_items;
 #pragma unroll 1
-        for (int it = lane; it < n_items; it += 32) {
+        for (int base = 0; base < n_work; base += 32) {
+            const int wq = base + lane, q = lane & 3;
+            if (wq >= n_work) continue;
+            const int it = wq >> 2;
             const int k = mo.ik[it], c = mo.icls[it];
-            const Corners dc = cand_corners(w, k);
-            double b1 = 0.0, b2 = 0.0, b3 = 0.0;
-            int g1 = 255, g2 = 255, g3 = 255;
-            for (int g = 0; g < ngt; ++g) {
-                if (mo.gcls[g] != c) continue;
-                Corners gc;
-                gc.x1 = mo.gx1[g]; gc.y1 = mo.gy1[g]; gc.x2 = mo.gx2[g]; gc.y2 = mo.gy2[g];
-                gc.area = mo.garea[g];
-                const double iou = iou_exact<YH_IOU_METRICS>(dc, gc);
-                const int b = mo.gbucket[g];
-                // strict: the first ground truth wins ties, IoU 0 never matches (metrics.py:393-403)
-                if (b == 1 && iou > b1) { b1 = iou; g1 = g; }
-                if (b == 2 && iou > b2) { b2 = iou; g2 = g; }
-                if (b == 3 && iou > b3) { b3 = iou; g3 = g; }
+            const BoxF d = cand_box(w, k);
+            float blo = 0.f, bhi = 0.f;
+            int bg = 255;
+            bool amb = !mok;
+            for (int g = 0; g < ngt && !amb; ++g) {
+                if (mo.gcls[g] != c || (q != 0 && mo.gbucket[g] != q)) continue;
+                const float4 gb4 = mo.gbox[g];
+                BoxF gb;
+                gb.x1 = gb4.x; gb.y1 = gb4.y; gb.x2 = gb4.z; gb.y2 = gb4.w;
+                gb.area = mo.garea[g];
+                float lo, hi;
+                const int r = iou_interval(d, gb, mE, lo, hi);
+                if (r == 2) continue;                         // IoU exactly 0: never matches
+                if (r == 0 || !(lo > 0.f)) { amb = true; break; }   // cannot tell IoU from 0
+                if (bg == 255 || lo > bhi) { blo = lo; bhi = hi; bg = g; }   // certainly greater (strict)
+                else if (!(hi < blo)) amb = true;             // cannot order it against the best so far
             }
-            // over all sizes: the largest of the three, the earliest ground truth on a tie
-            double b0 = b1;
-            int g0 = g1;
-            if (b2 > b0 || (b2 == b0 && g2 < g0)) { b0 = b2; g0 = g2; }
-            if (b3 > b0 || (b3 == b0 && g3 < g0)) { b0 = b3; g0 = g3; }
-            w.cand.xa[k] = b1;  // bucket_iou(w, 1..3)[k]: this candidate's geometry is no longer needed
-            w.cand.ya[k] = b2;
-            reinterpret_cast<double *>(w.cand.wh)[k] = b3;
-            *reinterpret_cast<unsigned *>(mo.bgt[it]) =
-                (unsigned)g0 | ((unsigned)g1 << 8) | ((unsigned)g2 << 16) | ((unsigned)g3 << 24);
+            unsigned mask = 0;
+            if (!amb && bg != 255) {
+#pragma unroll 1
+                for (int t = 0; t <= T; ++t) {
+                    const bool ge = blo >= th.hi[t];
+                    amb |= !ge && !(bhi < th.lo[t]);
+                    mask |= (ge ? 1u : 0u) << t;
+                }
+            }
+            if (amb) bg = match_exact(mo, pimg, timg, k, c, q, ngt, th, T, mask);
+            mo.bgt[it][q] = (uint8_t)bg;
+            mo.imask[it][q] = (unsigned short)mask;
         }
         __syncwarp();
 
-        // ---- greedy TP/FP: an item is a TP at threshold t iff its best IoU >= t and no
-        // earlier detection of its class claimed the same ground truth with IoU >= t
-        // (metrics.py:406-413).  "Earlier" = lower sorted position = lower item index.
-        // One lane per (item, ground-truth subset): an image has few items (kept boxes whose
-        // class has a ground truth), so a lane per item leaves most of the warp idle.
-        const int n_work = 4 * n_items;
+        // ---- greedy TP/FP: an item is a TP at threshold t iff its best IoU >= t and no earlier detection of
+        // its class claimed the same ground truth with IoU >= t (metrics.py:406-413).  "Earlier" = lower sorted
+        // position = lower item index.
 #pragma unroll 1
         for (int base = 0; base < n_work; base += 32) {
             const int wq = base + lane, q = lane & 3;
@@ -221,21 +278,13 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             uint64_t flags = 0;
             const unsigned g = act ? mo.bgt[it][q] : 255u;  // my best ground truth in subset q
             if (g != 255u) {
-                const int k = mo.ik[it], c = mo.icls[it];
-                // subset 0: the best over all sizes is g, so the IoU sits in g's bucket table
-                const double *tab = bucket_iou(w, q ? q : mo.gbucket[g]);
-                const double best = tab[k];
-                double rival = 0.0;  // best IoU an earlier item brought to the same ground truth
+                const int c = mo.icls[it];
+                unsigned claimed = 0;   // thresholds at which an earlier item took the same ground truth
                 for (int e = it - 1; e >= 0 && mo.icls[e] == c; --e)
-                    if (mo.bgt[e][q] == g) rival = fmax(rival, tab[mo.ik[e]]);
-                unsigned bits = 0;
-#pragma unroll 1
-                for (int t = 0; t < T; ++t) {
-                    const double th = s_thr[t];
-                    if (best >= th && !(rival >= th)) bits |= 1u << t;
-                }
-                flags = (uint64_t)bits << (q * T);
-                if (q == 0 && best >= 0.5 && !(rival >= 0.5)) flags |= 1ull << (4 * T);
+                    if (mo.bgt[e][q] == g) claimed |= mo.imask[e][q];
+                const unsigned bits = mo.imask[it][q] & ~claimed;
+                flags = (uint64_t)(bits & ((1u << T) - 1u)) << (q * T);
+                if (q == 0 && ((bits >> T) & 1u)) flags |= 1ull << (4 * T);
             }
             // the four subsets of an item sit on four neighbouring lanes
             flags |= __shfl_xor_sync(kFull, flags, 1);
@@ -251,10 +300,9 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             const int p = lane + 32 * s;
             const int k = w.order[p], c = w.cand.cls[k];
             const size_t o = (size_t)img * kCand + w.keepbase[s] + __popc(w.keepw[s] & lt);
-            const double cf = w.cand.conf[k];
-            rec_key[o] = ~orderable(cf == 0.0 ? 0.0 : cf);
+            rec_key[o] = w.cand.key[k];
             rec_flags[o] = mo.flags[p] | ((uint64_t)c << 56);
-            rec_k[o] = (uint8_t)k;
+            if (rec_k != nullptr) rec_k[o] = (uint8_t)k;
         }
         asm volatile("" : "+r"(next_ticket)::"memory");  // keep the (slow) ticket read down here
         const unsigned drawn = __shfl_sync(kFull, next_ticket, 0);
@@ -320,7 +368,7 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
         set_error("yh_map_update: T=%d thresholds; this build carries 1..%d", T, YH_MAX_THRESHOLDS);
         return YH_ERR_UNSUPPORTED;
     }
-    if (N < 0 || !pred || !tgt || !thresholds_host || !n_keep || !rec_key || !rec_flags || !rec_k ||
+    if (N < 0 || !pred || !tgt || !thresholds_host || !n_keep || !rec_key || !rec_flags ||
         !n_gt || !gt_count || ((gt_raw != nullptr) != (gt_cell != nullptr)) ||
         ((gt_raw != nullptr) != (gt_cls != nullptr))) {
         set_error("yh_map_update: bad argument");

@@ -89,12 +89,17 @@ class UpdateChunk:
     gt_cls: torch.Tensor | None   # (N,S*S) uint8
     gt_raw: torch.Tensor | None   # (N,S*S,4) float32
     shape: tuple = (S_, B_, C_)
+    # without list data: the batch itself (device tensors + their version counters at update time), from which
+    # the reference's list form can be rebuilt on demand
+    src: tuple | None = None
 
 
 def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: float, thresholds,
                gt_count: torch.Tensor, S: int = S_, B: int = B_, Cn: int = C_,
-               want_lists: bool = True) -> UpdateChunk:
-    """yh_map_update: fused decode + NMS + GT parse + TP/FP flags; adds into gt_count (4*C int32)."""
+               want_lists: bool = False) -> UpdateChunk:
+    """yh_map_update: fused decode + NMS + GT parse + TP/FP flags; adds into gt_count (4*C int32).
+    want_lists: also write the optional list-form side data (24-byte boxes, ground-truth cells / classes /
+    raw boxes) that yh_list_form expands; without it the chunk keeps a reference to the batch instead."""
     p = _check_pred(pred, "predictions", S, B, Cn)
     t = _check_pred(tgt, "targets", S, B, Cn)
     if p.shape != t.shape:
@@ -119,7 +124,22 @@ def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: 
                                       _lib.ptr(gt_cell), _lib.ptr(gt_cls), _lib.ptr(gt_raw), gt_count.data_ptr(),
                                       _lib.stream_ptr(dev))
     _lib.check(rc, "yh_map_update")
-    return UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, rec_raw, n_gt, gt_cell, gt_cls, gt_raw, (S, B, Cn))
+    src = None if want_lists else (p, t, p._version, t._version)
+    return UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, rec_raw, n_gt, gt_cell, gt_cls, gt_raw, (S, B, Cn), src)
+
+
+def parse_gt(tgt: torch.Tensor, S: int = S_, B: int = B_, Cn: int = C_):
+    """yh_parse_gt over a batch: (n_gt int32 (N,), gt_cls uint8 (N,S*S), gt_box float64 (N,S*S,4))."""
+    t = _check_pred(tgt, "targets", S, B, Cn)
+    N, G, dev = t.shape[0], S * S, t.device
+    n_gt = torch.zeros(N, dtype=torch.int32, device=dev)
+    gt_cls = torch.empty(N, G, dtype=torch.uint8, device=dev)
+    gt_box = torch.empty(N, G, 4, dtype=torch.float64, device=dev)
+    with _lib.on_device(dev):
+        rc = _lib.lib().yh_parse_gt(t.data_ptr(), N, S, B, Cn, n_gt.data_ptr(), gt_cls.data_ptr(), gt_box.data_ptr(),
+                                    _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_parse_gt")
+    return n_gt, gt_cls, gt_box
 
 
 def list_form(ch: UpdateChunk):

@@ -13,9 +13,13 @@ kernels behind include/yolohead.h:
              table are taken with numpy exactly where the reference takes them.
 
 ``all_predictions`` / ``all_ground_truths`` are real Python lists, built lazily
-from the device records the first time they are touched (the reference's tests
-append to them by hand).  Once touched they are authoritative: compute() then
-uploads them and runs the list-form kernels (yh_match_lists), so hand-edited
+the first time they are touched (the reference's tests append to them by hand).
+By default (``lists="lazy"``) update() only keeps a reference to the batch it was
+given and the lists are rebuilt from it by yh_decode_nms + yh_parse_gt, so the
+update kernel writes nothing but the 16-byte records; ``lists="eager"`` makes the
+update kernel write the list data next to the records instead (no reference to the
+caller's tensors is kept).  Once touched the lists are authoritative: compute()
+then uploads them and runs the list-form kernels (yh_match_lists), so hand-edited
 state gives the reference's answer too.
 """
 from __future__ import annotations
@@ -65,7 +69,11 @@ class mAPMetric:
     """Mean average precision (PASCAL VOC 11-point) at one or more IoU thresholds."""
 
     def __init__(self, num_classes: int, iou_thresholds: List[float] = None, conf_threshold: float = 0.01,
-                 nms_threshold: float = 0.4, S: int = 7, B: int = 2):
+                 nms_threshold: float = 0.4, S: int = 7, B: int = 2, *, lists: str = "lazy"):
+        if lists not in ("lazy", "eager"):
+            raise ValueError("lists must be 'lazy' or 'eager'")
+        # extension (keyword-only): where all_predictions / all_ground_truths come from, see the module docstring
+        self.lists = lists
         self.num_classes = num_classes
         if iou_thresholds is None:
             self.iou_thresholds = [0.5 + 0.05 * i for i in range(10)]
@@ -95,25 +103,55 @@ class mAPMetric:
     def _materialise(self):
         """Turn pending device batches into the reference's list-of-tuples form."""
         for ch in self._chunks:
-            n_keep = ch.n_keep.cpu().numpy()
-            n_gt = ch.n_gt.cpu().numpy()
-            conf = _conf_from_key(ch.rec_key.cpu().numpy())
-            cls = (ch.rec_flags.cpu().numpy().view(np.uint64) >> np.uint64(56)).astype(np.int64)
-            rec_pos, rec_box, gt_box = head.list_form(ch)
-            pos = rec_pos.cpu().numpy()
-            box = rec_box.cpu().numpy()
-            gcls = ch.gt_cls.cpu().numpy()
-            gbox = gt_box.cpu().numpy()
-            for i in range(ch.n):
-                k = int(n_keep[i])
-                dets = [None] * k
-                for q in range(k):
-                    dets[int(pos[i, q])] = (int(cls[i, q]), float(conf[i, q]), tuple(float(v) for v in box[i, q]))
-                self._pred_lists.append(dets)
-                self._gt_lists.append([(int(gcls[i, g]), tuple(float(v) for v in gbox[i, g]))
-                                       for g in range(int(n_gt[i]))])
+            if ch.src is not None:
+                dets, gts = self._lists_from_batch(ch)
+            else:
+                dets, gts = self._lists_from_records(ch)
+            self._pred_lists.extend(dets)
+            self._gt_lists.extend(gts)
         self._chunks = []
         self._gt_count = None
+
+    def _lists_from_batch(self, ch):
+        """lists="lazy": decode + NMS (reference order) and ground-truth parse of the retained batch."""
+        p, t, vp, vt = ch.src
+        if p._version != vp or t._version != vt:
+            raise _lib.YoloHeadError(
+                "all_predictions / all_ground_truths: a tensor passed to update() was modified in place afterwards, "
+                "so the lists can no longer be rebuilt from it; construct mAPMetric(..., lists='eager') to have "
+                "update() store the list data itself")
+        S, B, C = ch.shape
+        r = head.decode_nms(p, self.conf_threshold, self.nms_threshold, head.IOU_METRICS, head.ORDER_CLASS_GROUPED,
+                            S, B, C, want_boxes=True)
+        n_gt, gt_cls, gt_box = head.parse_gt(t, S, B, C)
+        n_keep = r.n_keep.cpu().tolist()
+        cls, conf, box = r.keep_cls.cpu().numpy(), r.keep_conf.cpu().numpy(), r.keep_box.cpu().numpy()
+        n_gt, gcls, gbox = n_gt.cpu().tolist(), gt_cls.cpu().numpy(), gt_box.cpu().numpy()
+        dets = [[(int(cls[i, q]), float(conf[i, q]), tuple(float(v) for v in box[i, q])) for q in range(n_keep[i])]
+                for i in range(ch.n)]
+        gts = [[(int(gcls[i, g]), tuple(float(v) for v in gbox[i, g])) for g in range(n_gt[i])] for i in range(ch.n)]
+        return dets, gts
+
+    def _lists_from_records(self, ch):
+        """lists="eager": the records and side arrays the update kernel wrote (yh_list_form)."""
+        n_keep = ch.n_keep.cpu().numpy()
+        n_gt = ch.n_gt.cpu().numpy()
+        conf = _conf_from_key(ch.rec_key.cpu().numpy())
+        cls = (ch.rec_flags.cpu().numpy().view(np.uint64) >> np.uint64(56)).astype(np.int64)
+        rec_pos, rec_box, gt_box = head.list_form(ch)
+        pos = rec_pos.cpu().numpy()
+        box = rec_box.cpu().numpy()
+        gcls = ch.gt_cls.cpu().numpy()
+        gbox = gt_box.cpu().numpy()
+        all_dets, all_gts = [], []
+        for i in range(ch.n):
+            k = int(n_keep[i])
+            dets = [None] * k
+            for q in range(k):
+                dets[int(pos[i, q])] = (int(cls[i, q]), float(conf[i, q]), tuple(float(v) for v in box[i, q]))
+            all_dets.append(dets)
+            all_gts.append([(int(gcls[i, g]), tuple(float(v) for v in gbox[i, g])) for g in range(int(n_gt[i]))])
+        return all_dets, all_gts
 
     @property
     def all_predictions(self) -> list:
@@ -156,7 +194,7 @@ class mAPMetric:
             self._device = dev
         chunk = head.map_update(predictions, targets, self.conf_threshold, self.nms_threshold,
                                 self.iou_thresholds, self._gt_count, self.S, self.B, self.num_classes,
-                                want_lists=True)
+                                want_lists=self.lists == "eager")
         self._chunks.append(chunk)
         if self._lists_live:
             self._materialise()
@@ -342,15 +380,7 @@ class mAPMetric:
         """(S,S,B*5+C) target -> [(class_id, (x, y, w, h))] (metrics.py:220-256)."""
         if not target.is_cuda:
             target = target.to(_cuda_device(self._device))
-        t = head._check_pred(target, "target", self.S, self.B, self.num_classes)
-        dev, G = t.device, self.S * self.S
-        n_gt = torch.zeros(1, dtype=torch.int32, device=dev)
-        gt_cls = torch.empty(1, G, dtype=torch.uint8, device=dev)
-        gt_box = torch.empty(1, G, 4, dtype=torch.float64, device=dev)
-        with _lib.on_device(dev):
-            rc = _lib.lib().yh_parse_gt(t.data_ptr(), 1, self.S, self.B, self.num_classes, n_gt.data_ptr(),
-                                        gt_cls.data_ptr(), gt_box.data_ptr(), _lib.stream_ptr(dev))
-        _lib.check(rc, "yh_parse_gt")
+        n_gt, gt_cls, gt_box = head.parse_gt(target, self.S, self.B, self.num_classes)
         n = int(n_gt.item())
         return [(int(c), tuple(b)) for c, b in zip(gt_cls[0, :n].cpu().tolist(), gt_box[0, :n].cpu().tolist())]
 
