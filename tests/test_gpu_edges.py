@@ -229,7 +229,7 @@ def _ap_from_records(key, flags, gt_count, C, T):
 def _sort_ctl(dev, m, C, T):
     """(overflow, queued runs) of the last yh_ap_reduce on this device: SortCtl sits at the head of the
     workspace (csrc/ap_reduce.cu: tile_counter[16], err, overflow, key_or, key_nand, work_count)."""
-    ws = head._ap_workspace(dev, _lib.lib().yh_ap_workspace_bytes(int(m), C, T))
+    ws = head._AP_WS.get(torch.device(dev), _lib.lib().yh_ap_workspace_bytes(int(m), C, T))
     w = ws[:96].cpu().numpy().view(np.uint32)
     return int(w[17]), int(w[22])
 

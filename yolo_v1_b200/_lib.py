@@ -11,7 +11,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libyolohead.so")
+LIB_PATH = os.environ.get("YH_LIB") or os.path.join(_HERE, "libyolohead.so")   # YH_LIB: an experiment build
 
 F32, F16, BF16 = 0, 1, 2
 IOU_METRICS, IOU_INFER = 0, 1

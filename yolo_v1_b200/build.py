@@ -38,23 +38,31 @@ def is_stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
+def build_library(force: bool = False, verbose: bool = False, out: str | None = None) -> str:
     extra = os.environ.get("YH_NVCC_EXTRA", "").split()  # experiments only, e.g. -DYH_SORT_LOOK=2
+    if out is not None:                                  # an experiment build next to the product library
+        return _compile(out, extra, verbose)
     flags_file = LIB + ".flags"                          # a change of experiment flags is a rebuild too
     last = open(flags_file).read() if os.path.exists(flags_file) else ""
     if not force and not is_stale() and last == " ".join(extra):
         return LIB
-    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources()
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if verbose or res.returncode != 0:
-        sys.stderr.write(res.stdout + res.stderr)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed building libyolohead.so")
+    _compile(LIB, extra, verbose)
     with open(flags_file, "w") as f:
         f.write(" ".join(extra))
     return LIB
 
 
+def _compile(target: str, extra, verbose: bool) -> str:
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + list(extra) + (["-Xptxas", "-v"] if verbose else []) + ["-o", target] + sources()
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed building {os.path.basename(target)}")
+    return target
+
+
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    _out = sys.argv[sys.argv.index("--out") + 1] if "--out" in sys.argv else None
+    print(build_library(force="--force" in sys.argv, verbose="--verbose" in sys.argv, out=_out))

@@ -49,7 +49,7 @@ struct CandTable {
     uint8_t cls[kPad];
 };
 
-// Shared-memory window of one warp: 7.0 KB, so 28 warps (7 CTAs of 4) fit an SM.
+// Shared-memory window of one warp: 7,088 B, so 32 warps (4 CTAs of 8) fit an SM.
 struct __align__(16) WarpWindow {
     float2 stage[kHalfPairs];       // 3,840 B: half an image; reused as NmsOverlay / MatchOverlay
     CandTable cand;                 // 2,848 B

@@ -146,12 +146,12 @@ constexpr int kPairTable = 256;
 
 // Overlay of `stage` between decode and the next staging: NMS scratch.
 struct NmsOverlay {
-    unsigned long long sup[kCand];  // by member position: bit i = member i of my class is earlier and overlaps me
+    unsigned sup[kCand][2];         // by member position: bit i = member i of my class is earlier and overlaps me
     int beaten[kPad];               // by member position: members of my class that come before me
     uint8_t kept[kPad];             // by sorted position
     uint8_t ordm[kPad];             // sorted position -> member index inside its class
     unsigned short pair_base[kC + 4];  // pairs of all classes before c
-    uint8_t pair_cls[kPairTable];      // class of pair t, when the image has at most kPairTable pairs
+    uint8_t pair_mark[kPairTable];     // class + 1 at the first pair of every class that has pairs, else 0
 };
 static_assert(sizeof(NmsOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
 
@@ -164,7 +164,7 @@ static_assert(sizeof(NmsOverlay) <= sizeof(float2) * kHalfPairs, "overlay too la
 //   3. one lane per class replays the greedy scan over the bitmasks in rank order.
 // Returns n and the keep mask by sorted position.  A class with more than 64 members,
 // or a NaN threshold ("decode only": keep everything), takes rank_members + nms_rounds.
-template <int MODE, bool PAIR_TABLE>
+template <int MODE>
 __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const float *__restrict__ img, const Mask128 &valid,
                                                  double nms_thr, const FilterParams &fp, const ImageFilter &filt,
                                                  int lane, int &n_out) {
@@ -188,23 +188,44 @@ __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const float *__r
     const int total = __shfl_sync(kFull, inc, 31);
     if (lane <= kC) no.pair_base[lane] = (unsigned short)(inc - np);  // [kC] = total
     for (int p = lane; p < n; p += 32) {
-        no.sup[p] = 0;
+        no.sup[p][0] = 0;
+        no.sup[p][1] = 0;
         no.beaten[p] = 0;
     }
-    // class of every pair: with few pairs (the usual case) each class lane labels its own
-    // range; otherwise a lane walks the class boundaries as its pair index grows
-    const bool table = PAIR_TABLE && total <= kPairTable;  // measured: helps decode_nms, not map_update
-    if (table)
-        for (int u = 0, base = inc - np; u < np; ++u) no.pair_cls[base + u] = (uint8_t)lane;
+    // Class of every pair.  With few pairs (the usual case) every class that has pairs marks its first one, and a
+    // lane reads off "the last mark at or before my pair" with a max-scan across the warp (marks ascend with the
+    // pair index); otherwise a lane walks the class boundaries as its pair index grows.
+    const bool table = total <= kPairTable;
+    if (table) {
+        reinterpret_cast<uint2 *>(no.pair_mark)[lane] = make_uint2(0u, 0u);   // 32 x 8 B = kPairTable
+        __syncwarp();
+        if (np > 0) no.pair_mark[inc - np] = (uint8_t)(lane + 1);
+    }
     __syncwarp();
-    int c = 0;
+    int c = 0, carry = 0;
 #pragma unroll 1
-    for (int t = lane; t < total; t += 32) {
-        if (table) c = no.pair_cls[t];
-        else
+    for (int t0 = 0; t0 < total; t0 += 32) {
+        const int t = t0 + lane;
+        const bool act = t < total;
+        if (table) {
+            int v = act ? no.pair_mark[t] : 0;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int o = __shfl_up_sync(kFull, v, off);
+                if (lane >= off) v = max(v, o);
+            }
+            v = max(v, carry);
+            carry = __shfl_sync(kFull, v, 31);
+            c = v - 1;
+        }
+        if (!act) continue;
+        if (!table)
             while (t >= no.pair_base[c + 1]) ++c;
         const int u = t - no.pair_base[c];
-        int j = (int)((1.0f + sqrtf((float)(8 * u + 1))) * 0.5f);  // row of the strict lower triangle
+        // row j of the strict lower triangle that holds pair u: an approximate root, put right by one step either way
+        float root;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(root) : "f"((float)(8 * u + 1)));
+        int j = (int)((1.0f + root) * 0.5f);
         j -= (j * (j - 1) / 2 > u);
         j += ((j + 1) * j / 2 <= u);
         const int i = u - j * (j - 1) / 2;                           // i < j, member indices
@@ -216,7 +237,7 @@ __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const float *__r
         atomicAdd(&no.beaten[lo + l], 1);
         // reference argument order: iou(current = earlier, other = later)
         if (!pair_below<MODE>(w, img, i_first ? ki : kj, i_first ? kj : ki, nms_thr, fp, filt))
-            atomicOr(&no.sup[lo + l], 1ull << e);
+            atomicOr(&no.sup[lo + l][e >> 5], 1u << (e & 31));
     }
     __syncwarp();
     for (int p = lane; p < n; p += 32) {
@@ -228,11 +249,13 @@ __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const float *__r
     }
     __syncwarp();
     if (lane < kC) {
-        unsigned long long km = 0;
+        unsigned km0 = 0, km1 = 0;   // kept members of my class, by member index
         for (int r = 0; r < m; ++r) {
             const int mi = no.ordm[clo + r];
-            const bool kp = (no.sup[clo + mi] & km) == 0;
-            km |= (unsigned long long)kp << mi;
+            const uint2 sp = *reinterpret_cast<const uint2 *>(no.sup[clo + mi]);
+            const bool kp = ((sp.x & km0) | (sp.y & km1)) == 0;
+            const unsigned bit = (kp ? 1u : 0u) << (mi & 31);
+            if (mi < 32) km0 |= bit; else km1 |= bit;
             no.kept[clo + r] = kp;
         }
     }

@@ -13,8 +13,14 @@
 
 namespace yh {
 
-constexpr int kWarpsPerCtaM = 4;
-constexpr int kCtasPerSmM = 7;
+#ifndef YH_WARPS_PER_CTA
+// 8 warps x 4 CTAs = 32 images in flight per SM (64 registers per thread; 4 x (8 x 7,088 B + static + 1 KB) of
+// the SM's 228 KB).  4 x 7 = 28 warps measured 1.5-2 % slower (r02: 0.319 vs 0.314 ms for map_update).
+#define YH_WARPS_PER_CTA 8
+#define YH_CTAS_PER_SM 4
+#endif
+constexpr int kWarpsPerCtaM = YH_WARPS_PER_CTA;   // warps (= images in flight) per CTA
+constexpr int kCtasPerSmM = YH_CTAS_PER_SM;     // resident CTAs per SM the kernel is built for (registers, shared memory)
 
 struct Thresholds {
     double t[YH_MAX_THRESHOLDS];
@@ -39,8 +45,19 @@ static_assert(sizeof(MatchOverlay) <= sizeof(float2) * kHalfPairs, "overlay too 
 // precision / recall pass (metrics.py:477).
 struct ThresholdTable {
     double t[YH_MAX_THRESHOLDS + 1];
-    float lo[YH_MAX_THRESHOLDS + 1], hi[YH_MAX_THRESHOLDS + 1];
+    float lo[16], hi[16];     // entries >= T are +inf (the sorted fast path counts with a 16-entry binary search)
+    float half_lo, half_hi;   // the overall pass's 0.5
+    int ascending;            // thresholds are non-decreasing: "IoU >= t" holds for a prefix of them
 };
+
+// number of entries of the ascending 16-entry table `tab` that are <= v
+__device__ __forceinline__ int count_le(const float *tab, float v) {
+    int c = 0;
+#pragma unroll
+    for (int step = 8; step >= 1; step >>= 1)
+        if (v >= tab[c + step - 1]) c += step;
+    return c;
+}
 
 // Ground truths of one target image -> MatchOverlay (compact, in cell order).
 // The target tensor is almost empty (an object in about 1 cell of 18), so it is not
@@ -56,46 +73,57 @@ __device__ __forceinline__ int parse_targets(WarpWindow &w, const float *__restr
                                              uint8_t *__restrict__ out_cls, float4 *__restrict__ out_raw) {
     const bool gt0 = tconf0 > 0.f, gt1 = (lane + 32 < kCells) && tconf1 > 0.f;  // metrics.py:239
     const unsigned m0 = __ballot_sync(kFull, gt0), m1 = __ballot_sync(kFull, gt1);
-    const unsigned lt = (1u << lane) - 1u;
     MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
     const double small_a = __dmul_rn(__ddiv_rn(32.0, 448.0), __ddiv_rn(32.0, 448.0));   // metrics.py:511
     const double medium_a = __dmul_rn(__ddiv_rn(96.0, 448.0), __ddiv_rn(96.0, 448.0));  // metrics.py:512
     const float inv_s = 1.0f / (float)kS;
-    unsigned mine = 0;
+    unsigned classes = 0;
     float mag = 0.f;
+    int g = 0;
     __syncwarp();  // every lane is done with what the overlay region held before
+    // One object cell at a time, the whole warp on it (an image has two or three): lanes 0..19 fetch one class score
+    // each and the arg-max is a max reduction over order-preserving integer keys plus a ballot (first maximum, NaN
+    // maximal, as torch.argmax); the box is the same broadcast load in every lane.
 #pragma unroll 1
-    for (int cs = 0; cs < 2; ++cs) {
-        if (!(cs ? gt1 : gt0)) continue;
-        const int cell = lane + 32 * cs;
-        const float *c = img + cell * kD;
-        const float2 xy = __ldg(reinterpret_cast<const float2 *>(c));
-        const float2 wh = __ldg(reinterpret_cast<const float2 *>(c) + 1);
-        const int cls = cell_class_global(c);
-        const int g = cs ? __popc(m0) + __popc(m1 & lt) : __popc(m0 & lt);
-        const BoxF f = make_box_f(((float)(cell % kS) + xy.x) * inv_s, ((float)(cell / kS) + xy.y) * inv_s, wh.x, wh.y);
-        mo.gbox[g] = make_float4(f.x1, f.y1, f.x2, f.y2);
-        mo.garea[g] = f.area;
-        const float m = box_magnitude(f);
-        mag = (m > mag || m != m) ? m : mag;
-        mo.gcell[g] = (uint8_t)cell;
-        mo.gcls[g] = (uint8_t)cls;
-        const double area = __dmul_rn((double)wh.x, (double)wh.y);            // exact, as metrics.py:519
-        const int bucket = (area < small_a) ? 1 : ((area < medium_a) ? 2 : 3);
-        mo.gbucket[g] = (uint8_t)bucket;
-        if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
-            out_cell[g] = (uint8_t)cell;
-            out_cls[g] = (uint8_t)cls;
-            out_raw[g] = make_float4(xy.x, xy.y, wh.x, wh.y);
+    for (int half = 0; half < 2; ++half)
+        for (unsigned bits = half ? m1 : m0; bits; bits &= bits - 1, ++g) {
+            const int cell = __ffs(bits) - 1 + 32 * half;
+            const float *c = img + cell * kD;
+            unsigned key = 0;
+            if (lane < kC) {
+                const float v = __fadd_rn(__ldg(c + kB * 5 + lane), 0.f);    // -0 -> +0: they compare equal
+                const unsigned b = __float_as_uint(v);
+                key = (v != v) ? 0xffffffffu : ((b & 0x80000000u) ? ~b : (b | 0x80000000u));
+            }
+            const unsigned mx = __reduce_max_sync(kFull, key);
+            const int cls = __ffs(__ballot_sync(kFull, lane < kC && key == mx)) - 1;
+            const float2 xy = __ldg(reinterpret_cast<const float2 *>(c));
+            const float2 wh = __ldg(reinterpret_cast<const float2 *>(c) + 1);
+            const BoxF f = make_box_f(((float)(cell % kS) + xy.x) * inv_s, ((float)(cell / kS) + xy.y) * inv_s, wh.x, wh.y);
+            const float m = box_magnitude(f);
+            mag = (m > mag || m != m) ? m : mag;
+            const double area = __dmul_rn((double)wh.x, (double)wh.y);            // exact, as metrics.py:519
+            const int bucket = (area < small_a) ? 1 : ((area < medium_a) ? 2 : 3);
+            classes |= 1u << cls;
+            if (lane == 0) {
+                mo.gbox[g] = make_float4(f.x1, f.y1, f.x2, f.y2);
+                mo.garea[g] = f.area;
+                mo.gcell[g] = (uint8_t)cell;
+                mo.gcls[g] = (uint8_t)cls;
+                mo.gbucket[g] = (uint8_t)bucket;
+                if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
+                    out_cell[g] = (uint8_t)cell;
+                    out_cls[g] = (uint8_t)cls;
+                    out_raw[g] = make_float4(xy.x, xy.y, wh.x, wh.y);
+                }
+                atomicAdd(&gt_hist[cls], 1);
+                atomicAdd(&gt_hist[bucket * kC + cls], 1);
+            }
         }
-        atomicAdd(&gt_hist[cls], 1);
-        atomicAdd(&gt_hist[bucket * kC + cls], 1);
-        mine |= 1u << cls;
-    }
-    cls_mask = __reduce_or_sync(kFull, mine);
-    gmag = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(mag)));
+    cls_mask = classes;
+    gmag = mag;
     __syncwarp();
-    return __popc(m0) + __popc(m1);
+    return g;
 }
 
 // Best ground truth of detection k within subset q and the thresholds its IoU reaches, with the reference's
@@ -141,11 +169,18 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
     const unsigned lt = (1u << lane) - 1u;
     const FilterParams fp = filter_params(nms_thr);
     for (int i = threadIdx.x; i < 4 * kC; i += blockDim.x) gt_hist[i] = 0;
-    if (threadIdx.x <= YH_MAX_THRESHOLDS) {
-        const double v = threadIdx.x < T ? thr.t[threadIdx.x] : (threadIdx.x == T ? 0.5 : 2.0);
-        th.t[threadIdx.x] = v;
-        th.lo[threadIdx.x] = __double2float_rd(v);
-        th.hi[threadIdx.x] = __double2float_ru(v);
+    if (threadIdx.x < 16) {
+        const double v = threadIdx.x < T ? thr.t[threadIdx.x] : 0.0;
+        if (threadIdx.x <= YH_MAX_THRESHOLDS) th.t[threadIdx.x] = threadIdx.x < T ? v : (threadIdx.x == T ? 0.5 : 2.0);
+        const float inf = __uint_as_float(0x7f800000u);
+        th.lo[threadIdx.x] = threadIdx.x < T ? __double2float_rd(v) : inf;
+        th.hi[threadIdx.x] = threadIdx.x < T ? __double2float_ru(v) : inf;
+    }
+    if (threadIdx.x == 32) {
+        th.half_lo = th.half_hi = 0.5f;
+        bool asc = true;
+        for (int t = 1; t < T; ++t) asc = asc && thr.t[t] >= thr.t[t - 1];   // false if a NaN is involved
+        th.ascending = asc ? 1 : 0;
     }
     __syncthreads();
 
@@ -165,7 +200,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         ImageFilter nfilt = filt;
         nfilt.ok = filt.ok && fp.thr_ok;
         int n;
-        const Mask128 keep = order_and_nms<YH_IOU_METRICS, false>(w, pimg, valid, nms_thr, fp, nfilt, lane, n);
+        const Mask128 keep = order_and_nms<YH_IOU_METRICS>(w, pimg, valid, nms_thr, fp, nfilt, lane, n);
         publish_keep(w, keep, lane);
         const bool lists = gt_raw != nullptr;
         if (rec_box != nullptr) {
@@ -254,12 +289,22 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             }
             unsigned mask = 0;
             if (!amb && bg != 255) {
+                const bool ge5 = blo >= th.half_hi;              // the overall pass's IoU >= 0.5 (bit T, read for subset 0)
+                amb = !ge5 && !(bhi < th.half_lo);
+                if (th.ascending) {
+                    // "IoU >= t" holds for a prefix of the thresholds: count it from below and from above
+                    const int c_lo = count_le(th.hi, blo), c_hi = count_le(th.lo, bhi);
+                    amb |= c_lo != c_hi;
+                    mask = (1u << c_lo) - 1u;
+                } else {
 #pragma unroll 1
-                for (int t = 0; t <= T; ++t) {
-                    const bool ge = blo >= th.hi[t];
-                    amb |= !ge && !(bhi < th.lo[t]);
-                    mask |= (ge ? 1u : 0u) << t;
+                    for (int t = 0; t < T; ++t) {
+                        const bool ge = blo >= th.hi[t];
+                        amb |= !ge && !(bhi < th.lo[t]);
+                        mask |= (ge ? 1u : 0u) << t;
+                    }
                 }
+                mask |= (ge5 ? 1u : 0u) << T;
             }
             if (amb) bg = match_exact(mo, pimg, timg, k, c, q, ngt, th, T, mask);
             mo.bgt[it][q] = (uint8_t)bg;
