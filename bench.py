@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunks", type=int, default=8, help="mini-batches the e2e step streams from the host")
     ap.add_argument("--no-graph", action="store_true", help="time the eager step only (no CapturedHeadStep)")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the BASELINE.json configs[2] / [4] records")
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "class_shard", "gather"],
                     help="N>1: how compute() makes the per-class order global (yolo_v1_b200/distributed.py)")
     return ap.parse_args()
@@ -172,6 +173,78 @@ def workload_config(args, images_per_gpu):
             "l2": "inputs (770 MB at 65,536 images) exceed the 126 MB L2; no explicit flush"}
 
 
+# ------------------------------------------------------------------ BASELINE.json configs[2] and configs[4]
+def other_configs(args, world, rank, dev, timed, barrier):
+    """configs[2]: mAP@50:95 over a VOC2007-test-sized set (4,952 correlated images, conf 0.01), STRONG scaling:
+    the set is split over the ranks (contiguous ranges) and every rank gets the global result.
+    configs[4]: the 1M-image sweep = 131,072 images per GPU on 8 GPUs (decode + NMS + mAP, weak scaling);
+    run with whatever N this job has and labelled with the total."""
+    import torch.distributed as dist
+
+    from yolo_v1_b200 import mAPMetric, synth
+    from yolo_v1_b200.distributed import DistributedMAP, shard_range
+
+    out = {}
+    # -- configs[2]
+    n_voc = 4952
+    pred, tgt = synth.make_exact(n_voc, seed=50)           # the inputs of tests/golden/map_big.npz
+    lo, hi = shard_range(n_voc, rank, world)
+    p_d, t_d = pred[lo:hi].to(dev), tgt[lo:hi].to(dev)
+    m = mAPMetric(num_classes=C, conf_threshold=0.01, nms_threshold=0.4)
+    if world > 1:
+        m = DistributedMAP(m, mode=args.exchange)
+
+    def voc_step():
+        m.reset()
+        if hi > lo:
+            m.update(p_d, t_d)
+        return m.compute()
+
+    for _ in range(3):
+        res = voc_step()
+    ms, res = timed(voc_step, 10)
+    inner = m.metric if world > 1 else m
+    out["configs[2]"] = {"workload": "mAP@50:95 over 4,952 synthetic images (synth.make_exact, conf 0.01, NMS IoU 0.4, "
+                                     "10 thresholds), reset + update + compute per evaluation",
+                         "scaling": "strong", "n_gpus": world, "ms_per_evaluation": ms,
+                         "images_per_s": n_voc / (ms * 1e-3), "mAP50:95": float(res["mAP50:95"]),
+                         "mAP50": float(res["mAP50"]), "sha256": inner.result_digest(),
+                         "golden": "tests/golden/map_big.npz exact4952 (the reference's own compute() on these inputs: "
+                                   "mAP50:95 0.2713631647915797)"}
+    if world > 1:
+        m.close()
+    # -- configs[4]
+    n_big = 131072
+    sweep = {}
+    for prof in ("uniform", "realistic"):
+        t_h = synth.make_targets(n_big, seed=77 + rank, p_obj=0.055, size_mix=True)
+        p_h = synth.make_preds(n_big, prof, seed=77 + rank, targets=t_h)
+        p_b, t_b = p_h.to(dev), t_h.to(dev)
+        del p_h, t_h
+        mb = mAPMetric(num_classes=C, conf_threshold=args.conf, nms_threshold=args.nms)
+        if world > 1:
+            mb = DistributedMAP(mb, mode=args.exchange)
+
+        def big_step():
+            mb.reset()
+            mb.update(p_b, t_b)
+            return mb.compute()
+
+        for _ in range(2):
+            big_step()
+        ms_b, res_b = timed(big_step, 5)
+        sweep[prof] = {"ms_per_sweep": ms_b, "images_per_s": world * n_big / (ms_b * 1e-3),
+                       "mAP50:95": float(res_b["mAP50:95"])}
+        if world > 1:
+            mb.close()
+        del p_b, t_b, mb
+        torch.cuda.empty_cache()
+    out["configs[4]"] = {"workload": f"decode + NMS + TP/FP + mAP@50:95 sweep, 131,072 images per GPU x {world} GPU(s) = "
+                                     f"{world * n_big} images (1,048,576 on 8 GPUs), conf {args.conf}, eager calls",
+                         "scaling": "weak", "n_gpus": world, "total_images": world * n_big, "profiles": sweep}
+    return out
+
+
 # ------------------------------------------------------------------ our arm
 def main():
     args = parse_args()
@@ -275,6 +348,47 @@ def main():
             step_launch += f"; graph capture unavailable ({why or 'on another rank'})"
     value = world * n / (ms * 1e-3)
 
+    # ---- result check that can see a wrong sort / exchange / flag.  On the `uniform` workload no class reaches
+    # recall 0.1, so every AP is the t=0 sentinel 1/11 whatever the record order.  The `correlated` profile has
+    # true positives: one step of it is run eagerly, through the captured graph and -- with N > 1 -- on rank 0
+    # alone over all ranks' images; the sha256 over the full AP table, TP total, record count and ground-truth
+    # counts (mAPMetric.result_digest) must be the same everywhere.
+    chk_n = min(n, 8192)
+    chk_pred_h, chk_tgt_h = make_batch(chk_n, "correlated", 4321 + rank)
+    chk_pred, chk_tgt = chk_pred_h.to(dev), chk_tgt_h.to(dev)
+    inner = metric.metric if world > 1 else metric
+    conf_saved = inner.conf_threshold
+    inner.conf_threshold = 0.01
+    chk_loss, chk_map = step(chk_pred.detach(), chk_tgt)
+    check = {"profile": "correlated", "images_per_gpu": chk_n, "conf": 0.01, "loss_total": chk_loss, "mAP50:95": chk_map,
+             "sha256": inner.result_digest(), "agree": {}}
+    if step_launch.startswith("cuda_graph"):
+        chk_step = None
+        try:
+            chk_step = CapturedHeadStep(crit, metric, chk_pred, chk_tgt)
+        except Exception as e:  # noqa: BLE001
+            check["agree"]["graph_vs_eager"] = f"capture failed: {type(e).__name__}"
+        if chk_step is not None:
+            g_loss, g_res = chk_step.replay()
+            check["agree"]["graph_vs_eager"] = bool(inner.result_digest() == check["sha256"] and
+                                                    float(g_loss["total"]) == chk_loss)
+            del chk_step
+    if world > 1:   # rank 0 repeats the step alone on the concatenated images of all ranks
+        allp = [torch.empty_like(chk_pred) for _ in range(world)] if rank == 0 else None
+        allt = [torch.empty_like(chk_tgt) for _ in range(world)] if rank == 0 else None
+        dist.gather(chk_pred, allp, dst=0)
+        dist.gather(chk_tgt, allt, dst=0)
+        if rank == 0:
+            solo = mAPMetric(num_classes=C, conf_threshold=0.01, nms_threshold=args.nms)
+            for p_r, t_r in zip(allp, allt):
+                solo.update(p_r, t_r)
+            solo.compute()
+            check["agree"]["sharded_vs_one_gpu"] = bool(solo.result_digest() == check["sha256"])
+            del solo, allp, allt
+    inner.conf_threshold = conf_saved
+    del chk_pred, chk_tgt
+    assert all(v is True for v in check["agree"].values()), check
+
     # ---- end to end: host buffers in, results out.  The batch arrives from pinned host memory
     # in `e2e_chunks` mini-batches on a copy stream; each is consumed (loss fwd+bwd, update) as
     # soon as it lands, so the head overlaps the PCIe transfer of the next mini-batch.
@@ -349,23 +463,32 @@ def main():
         e2e_pf = {"ms_per_step": pf_total_ms / k_pf, "steps": k_pf}
     except Exception as exc:  # the strict one-step-at-a-time figure below stays the e2e value
         e2e_pf = {"error": f"{type(exc).__name__}: {exc}"[:200]}
+    # The PCIe floor of the same transfer: every rank copies its 770 MB AT THE SAME TIME (the host side -- one
+    # NUMA node feeding all GPUs -- is what limits e2e at N > 1), max over ranks; rank 0 alone beside it.
+    def h2d_only():
+        pred_h.to(dev, non_blocking=True)
+        tgt_h.to(dev, non_blocking=True)
+
+    h2d_only()
+    h2d_concurrent_ms, _ = timed(h2d_only, 3)
     h2d_ms = None
-    if rank == 0:  # the PCIe floor of the same transfer, for reference
-        def h2d_only():
-            pred_h.to(dev, non_blocking=True)
-            tgt_h.to(dev, non_blocking=True)
-        h2d_only()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(3):
-            h2d_only()
-        e1.record()
-        torch.cuda.synchronize()
-        h2d_ms = e0.elapsed_time(e1) / 3
+    if world == 1:
+        h2d_ms = h2d_concurrent_ms
+    else:
+        if rank == 0:
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(3):
+                h2d_only()
+            e1.record()
+            torch.cuda.synchronize()
+            h2d_ms = e0.elapsed_time(e1) / 3
+        barrier()
     e2e = {"value": world * n / (e2e_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": 2 * n * IMG_BYTES,
            "d2h_bytes_per_step": n_chunks * 5 * 4 + (4 * C * 10 + 3 + 4 * C) * 8, "ms_per_step": e2e_ms,
-           "mini_batches": n_chunks, "h2d_only_ms": h2d_ms,
+           "mini_batches": n_chunks, "h2d_only_ms": h2d_ms, "h2d_concurrent_ms": h2d_concurrent_ms,
+           "share_of_concurrent_copy_floor": h2d_concurrent_ms / e2e_ms,
            "result_check": {"loss_total": e2e_loss, "mAP50:95": e2e_map}}
     if e2e_pf is not None and "ms_per_step" in e2e_pf:
         # secondary figure; `value` above stays the strict one (a step's copies start after the previous step's read)
@@ -458,10 +581,11 @@ def main():
     chunk = head.map_update(pred_d, tgt_d, args.conf, args.nms, thr, gt_count.zero_())
     kbar = float(chunk.n_keep.float().mean().item())
     gbar = float(chunk.n_gt.float().mean().item())
-    # read pred + tgt, write per image: 2 counters; per kept box: key 8 + flags 8 + candidate 1 + box 24;
-    # per ground truth: cell 1 + class 1 + raw box 16
-    upd_bytes = 2 * IMG_BYTES + 8 + kbar * (8 + 8 + 1 + 24) + gbar * 18
+    # read pred + tgt + a 128-byte per-image result, + 24 B per kept detection.  (What the kernel
+    # writes is a little less: 8 B of counters per image, 16-byte records + 1 candidate byte per kept box.)
+    upd_bytes = 2 * IMG_BYTES + 128 + 24 * kbar
     stages["map_update"] = {"ms": t_upd, "bytes_per_image": upd_bytes, "kept_per_image": kbar, "gt_per_image": gbar,
+                            "written_bytes_per_image": 8 + 17 * kbar,
                             "gbs": upd_bytes * n / (t_upd * 1e-3) / 1e9}
     t_dec = time_call(lambda: head.decode_nms(pred_d, args.conf, args.nms, head.IOU_INFER, head.ORDER_GLOBAL_CONF,
                                               want_boxes=False))
@@ -514,9 +638,29 @@ def main():
             "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": stages[dom]["gbs"] / peak,
             "traffic": traffic, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": stages[dom]["bytes_per_image"] * n,
+            "algorithmic_bytes": "SURVEY.md 8(d): 11,888 B per image + 24 B per kept detection (map_update); "
+                                 "17,640 B per image (loss fwd+bwd); 6,008 B per image (decode + NMS)",
             "launch_ms": stages[dom]["ms"], "share_of_step_kernel_time": stages[dom]["ms"] / step_kernel_ms,
             "all": {k: {"gbs": v.get("gbs"), "frac": (v["gbs"] / peak) if v.get("gbs") else None, "ms": v["ms"]}
                     for k, v in stages.items()}}
+    # the two halves BASELINE.json's metric names, each timed alone on this rank (kernels only, inputs in HBM)
+    map_ms = stages["map_update"]["ms"] + stages["compact_records"]["ms"] + stages["ap_reduce"]["ms"]
+    map_bytes = stages["map_update"]["bytes_per_image"] * n + stages["compact_records"]["bytes"] + stages["ap_reduce"]["bytes"]
+    halves = {
+        "value_loss": {"what": "loss fwd+bwd", "value": n / (stages["loss_fwd_bwd"]["ms"] * 1e-3), "unit": "images/s per GPU",
+                       "ms": stages["loss_fwd_bwd"]["ms"], "frac": stages["loss_fwd_bwd"]["gbs"] / peak},
+        "value_map": {"what": "decode + NMS + TP/FP (map_update) + compact + sort / AP (ap_reduce)",
+                      "value": n / (map_ms * 1e-3), "unit": "images/s per GPU", "ms": map_ms,
+                      "frac": map_bytes / (map_ms * 1e-3) / 1e9 / peak},
+    }
+
+    # ---- the other BASELINE.json configs, after the timed region (records, not the headline)
+    other = {}
+    if not args.no_other_configs:
+        try:
+            other = other_configs(args, world, rank, dev, timed, barrier)
+        except Exception as exc:  # noqa: BLE001 - the headline line must still print
+            other = {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
     if rank == 0:
         cpu = None
@@ -528,7 +672,8 @@ def main():
             "vs_baseline": None, "dtype": "f32 loss / f64 geometry", "data": "synthetic",
             "config": workload_config(args, n), "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cpu, "stages": stages,
-            "result_check": {"loss_total": loss_total, "mAP50:95": map5095},
+            "result_check": {"loss_total": loss_total, "mAP50:95": map5095, "sensitive": check},
+            "value_loss": halves["value_loss"], "value_map": halves["value_map"], "other_configs": other,
         }
         line["step_launch"] = step_launch
         line["eager"] = {"value": world * n / (eager_ms * 1e-3), "ms_per_step": eager_ms}

@@ -300,3 +300,60 @@ def test_predict_validates_every_candidate_before_nms(golden, tmp_path, case):
             kept = call()
             got = [[d.class_id, d.confidence, d.bbox.x, d.bbox.y, d.bbox.width, d.bbox.height] for d in kept]
             assert got == want["kept"]
+
+
+# ------------------------------------------------------------------ evaluate_model (metrics.py:654-714)
+def test_evaluate_model_over_a_dataloader_equals_the_metric_fed_the_same_batches():
+    """model + DataLoader of HOST tensors + device string in, compute() dict out: the same dict as an mAPMetric
+    fed model(images) batch by batch, and as the oracle on the concatenated predictions; model left in eval mode."""
+    import numpy as np
+    from torch.utils.data import DataLoader, TensorDataset
+
+    from oracle import c_oracle, results
+    from yolo_v1_b200 import evaluate_model, synth
+
+    torch.manual_seed(7)
+    n = 50                                                  # 4 batches: 16 + 16 + 16 + 2
+    tgt = synth.make_targets(n, seed=31, p_obj=0.08, size_mix=True)
+    images = torch.randn(n, 3, 32, 32)
+
+    class TinyYolo(nn.Module):
+        """A conv stem whose output is mixed with a per-image table so that true positives exist."""
+
+        def __init__(self, table):
+            super().__init__()
+            self.S, self.B = 7, 2
+            self.conv = nn.Conv2d(3, 30, 3, padding=1)
+            self.pool = nn.AdaptiveAvgPool2d(7)
+            self.drop = nn.Dropout(0.5)                    # would change the output if eval() were not called
+            self.register_buffer("table", table)
+            self.register_buffer("keys", images.flatten(1).sum(1))
+
+        def forward(self, x):
+            idx = (x.flatten(1).sum(1)[:, None] - self.keys[None, :]).abs().argmin(1)
+            noise = torch.sigmoid(self.drop(self.pool(self.conv(x)))).permute(0, 2, 3, 1)
+            return (0.15 * noise + 0.85 * self.table[idx]).contiguous()
+
+    pred_table = synth.make_preds(n, "correlated", seed=32, targets=tgt)
+    model = TinyYolo(pred_table).cuda()
+    model.train()
+    loader = DataLoader(TensorDataset(images, tgt), batch_size=16, shuffle=False)
+    got = evaluate_model(model, loader, "cuda", num_classes=20, conf_threshold=0.05, nms_threshold=0.4)
+    assert not model.training                               # metrics.py:697 calls model.eval()
+
+    metric = mAPMetric(num_classes=20, conf_threshold=0.05, nms_threshold=0.4)
+    outs = []
+    with torch.no_grad():
+        for x, t in loader:
+            out = model(x.cuda())
+            outs.append(out.cpu())
+            metric.update(out, t.cuda())
+    want = metric.compute()
+    assert got == want and float(got["mAP50"]) > 0.0
+    allp = torch.cat(outs)
+    st = c_oracle.update_batch(allp.numpy(), tgt.numpy(), 0.05, 0.4)
+    ref = c_oracle.compute(st, metric.iou_thresholds)
+    exp = results.assemble(ref["ap"], ref["overall"], ref["sizes"], metric.iou_thresholds, 20, n)
+    assert sorted(got) == sorted(exp)
+    for k in exp:
+        assert float(got[k]) == pytest.approx(float(exp[k]), rel=1e-9, abs=1e-12), k

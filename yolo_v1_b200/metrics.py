@@ -266,6 +266,7 @@ class mAPMetric:
 
     def _results(self, ap, tp_total, n_pred, gt_count, n_gt_total, T, C) -> Dict[str, float]:  # noqa: C901
         """Result dict with the reference's keys and its np.mean call sites (metrics.py:126-171, 531-564)."""
+        self._last_raw = (ap, tp_total, n_pred, gt_count)      # what result_digest() hashes
         thr = self.iou_thresholds
         if len(set(thr)) == len(thr):
             return self._results_fast(ap, tp_total, n_pred, gt_count, n_gt_total, T, C)
@@ -360,6 +361,19 @@ class mAPMetric:
         for name, cnt in zip(_SIZES, counts):
             out[f"num_{name}_objects"] = cnt
         return out
+
+    def result_digest(self) -> str:
+        """sha256 over everything the last compute() read back: the full 4 x C x T AP table (every size subset and
+        threshold, not only the entries that reach the result dict), the TP total, the record count and the
+        ground-truth counts.  Two runs that order, exchange or flag a single record differently disagree here."""
+        import hashlib
+
+        ap, tp_total, n_pred, gt_count = self._last_raw
+        h = hashlib.sha256()
+        h.update(np.ascontiguousarray(ap, dtype=np.float64).tobytes())
+        h.update(np.asarray([tp_total, n_pred], dtype=np.int64).tobytes())
+        h.update(np.ascontiguousarray(gt_count, dtype=np.int64).tobytes())
+        return h.hexdigest()[:16]
 
     # --------------------------------------------------- helpers the reference exposes
     def _parse_predictions(self, pred: torch.Tensor) -> List[Tuple[int, float, Tuple[float, float, float, float]]]:
