@@ -151,12 +151,13 @@ __device__ __forceinline__ int argmax_first(const float *v, int n, float &best_v
 }
 
 // Class of one staged prediction cell (cell = pointer to its kD floats in shared memory,
-// 8-byte aligned): best_v = the largest class score; the return value is its first index
+// 8-byte aligned; conf0 / conf1 = its two box confidences): best_v = the largest class score; the return value is its first index
 // -- but only when a box of the cell can pass the confidence threshold (otherwise the
 // class is never looked at and the index search is skipped; a NaN maximum makes both
 // confidences NaN, which never pass).  Out of line: one copy for all call sites keeps
 // the per-image kernels inside the instruction cache.
-static __device__ __noinline__ int cell_class_shared(const float *cell, double conf_thr, float &best_v) {
+static __device__ __noinline__ int cell_class_shared(const float *cell, double conf_thr, float conf0, float conf1,
+                                                     float &best_v) {
     const unsigned addr = (unsigned)__cvta_generic_to_shared(cell + kB * 5);
     float v[kC];
 #pragma unroll
@@ -167,9 +168,7 @@ static __device__ __noinline__ int cell_class_shared(const float *cell, double c
     for (int i = 1; i < kC; ++i) m = max_nan(m, v[i]);
     best_v = m;
     const double prob = (double)m;
-    bool need = false;
-#pragma unroll
-    for (int b = 0; b < kB; ++b) need |= __dmul_rn((double)cell[b * 5 + 4], prob) > conf_thr;
+    const bool need = __dmul_rn((double)conf0, prob) > conf_thr || __dmul_rn((double)conf1, prob) > conf_thr;
     int best = 0;
     if (need) {
 #pragma unroll

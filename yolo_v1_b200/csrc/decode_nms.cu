@@ -143,6 +143,10 @@ decode_nms_kernel(const float *__restrict__ pred, int N, double conf_thr, double
         unsigned next_ticket = 0;
         if (lane == 0) next_ticket = atomicAdd(ticket, 1u);
         const float *pimg = pred + (size_t)img * kImgFloats;
+#ifdef YH_PREFETCH_AHEAD
+        if (img + YH_PREFETCH_AHEAD * warps_total < N)   // see map_update.cu
+            prefetch_image(pimg + (size_t)YH_PREFETCH_AHEAD * warps_total * kImgFloats, lane);
+#endif
         bool bad = false;
         ImageFilter filt;
         const Mask128 valid = decode_image(w, pimg, lane, conf_thr, bad_range != nullptr ? &bad : nullptr, filt);

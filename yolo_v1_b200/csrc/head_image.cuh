@@ -189,20 +189,25 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
         const int cell = lane + 32 * cs;
         const bool live = cell < kCells;
         const float *c = st + (live ? lane : 0) * kD;
+        // the ten box values of the cell as five 8-byte loads (conflict-free at the 120-byte cell stride; scalar
+        // loads of the same words collide two ways)
+        const float2 *c2 = reinterpret_cast<const float2 *>(c);
+        const float2 q0 = c2[0], q1 = c2[1], q2 = c2[2], q3 = c2[3], q4 = c2[4];
+        const float bxs[kB][5] = {{q0.x, q0.y, q1.x, q1.y, q2.x}, {q2.y, q3.x, q3.y, q4.x, q4.y}};
+        static_assert(kB == 2, "the unpacking above is for two boxes per cell");
         float pv;
-        const int cls = cell_class_shared(c, conf_thr, pv);
+        const int cls = cell_class_shared(c, conf_thr, bxs[0][4], bxs[1][4], pv);
         const double prob = (double)pv;
         const int col = cell % kS, row = cell / kS;
         const float colf = (float)col, rowf = (float)row;
         bool ok[kB];
 #pragma unroll
         for (int b = 0; b < kB; ++b) {
-            const float *bx = c + b * 5;
-            const double conf = __dmul_rn((double)bx[4], prob);  // exact: 24b x 24b
+            const double conf = __dmul_rn((double)bxs[b][4], prob);  // exact: 24b x 24b
             ok[b] = live && conf > conf_thr;
             if (ok[b]) {
                 const int k = cell * kB + b;
-                const float x = bx[0], y = bx[1], bw = bx[2], bh = bx[3];
+                const float x = bxs[b][0], y = bxs[b][1], bw = bxs[b][2], bh = bxs[b][3];
                 const BoxF f = make_box_f((colf + x) * inv_s, (rowf + y) * inv_s, bw, bh);
                 w.cand.box[k] = make_float4(f.x1, f.y1, f.x2, f.y2);
                 w.cand.area[k] = f.area;

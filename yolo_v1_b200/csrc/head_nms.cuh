@@ -231,8 +231,15 @@ __device__ __forceinline__ Mask128 order_and_nms(WarpWindow &w, const float *__r
         const int i = u - j * (j - 1) / 2;                           // i < j, member indices
         const int lo = w.cls_start[c];
         const int ki = w.member[lo + i], kj = w.member[lo + j];
-        const uint64_t ci = w.cand.key[ki], cj = w.cand.key[kj];     // ascending key = descending confidence
-        const bool i_first = (ci < cj) || (ci == cj && ki < kj);
+        // ascending key = descending confidence.  The leading words decide almost every pair; equal ones read the
+        // whole keys (little-endian: word 1 of a key is its upper half)
+        const unsigned *kw32 = reinterpret_cast<const unsigned *>(w.cand.key);
+        const unsigned hi_i = kw32[2 * ki + 1], hi_j = kw32[2 * kj + 1];
+        bool i_first = hi_i < hi_j;
+        if (hi_i == hi_j) {
+            const uint64_t ci = w.cand.key[ki], cj = w.cand.key[kj];
+            i_first = (ci < cj) || (ci == cj && ki < kj);
+        }
         const int e = i_first ? i : j, l = i_first ? j : i;          // earlier / later member
         atomicAdd(&no.beaten[lo + l], 1);
         // reference argument order: iou(current = earlier, other = later)

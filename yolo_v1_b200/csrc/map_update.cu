@@ -27,16 +27,21 @@ struct Thresholds {
     int n;
 };
 
-// Overlay of `stage` once the predictions have been decoded: ground truths and per-item match results.
+// Overlay of `stage` once the predictions have been decoded: ground truths, the (detection, ground truth)
+// pairs of equal class with their IoU intervals, and the per-item match results.
+constexpr int kPairCap = 96;           // images with more such pairs compute the intervals inside the item loop
 struct MatchOverlay {
     float4 gbox[kCells];               // fp32 corners of the ground truths, compact, in cell order      784 B
     float garea[kCells];               //                                                                 196 B
     uint8_t gcell[kCells + 7], gcls[kCells + 7], gbucket[kCells + 7];          //                         168 B
-    unsigned long long flags[kCand];   // TP bits by sorted position                                      784 B
+    unsigned short pbase[kCells + 7];  // first pair of ground truth g (pairs: its class's sorted range)   112 B
+    float plo[kPairCap], phi[kPairCap];  // IoU interval of pair t; (0, 0) = no match possible, (-1, -1) = unknown  768 B
+    uint8_t pmark[kPairCap];           // g + 1 at pbase[g] for every ground truth that has pairs, else 0     96 B
     // by item and ground-truth subset (0 all, 1 small, 2 medium, 3 large):
     unsigned short imask[kCand][4];    // bit t: best IoU >= threshold t; bit T (subset 0): best IoU >= 0.5  784 B
     uint8_t bgt[kCand][4];             // best ground truth (255 = none)                                  392 B
-    uint8_t ik[kPad], icls[kPad], ipos[kPad];  // by item: candidate, class, sorted position              312 B
+    // by item: candidate, class, sorted position, record slot within the image                            416 B
+    uint8_t ik[kPad], icls[kPad], ipos[kPad], irec[kPad];
 };
 static_assert(sizeof(MatchOverlay) <= sizeof(float2) * kHalfPairs, "overlay too large");
 
@@ -63,67 +68,78 @@ __device__ __forceinline__ int count_le(const float *tab, float v) {
 // The target tensor is almost empty (an object in about 1 cell of 18), so it is not
 // staged: tconf0/tconf1 are the slot-0 confidences of cells `lane` and `lane + 32`
 // (loaded by the caller long before, 49 sectors per image), and only object cells
-// fetch their box and class scores.  Returns the number of ground truths; cls_mask
-// gets bit c for every class present; gmag the largest fp32 corner magnitude (for the
-// prefilter margin).  gt_hist (shared, 4*kC ints) accumulates the per-(subset, class)
-// counts of this CTA.
+// fetch their box and class scores, one lane per ground truth.  Returns the number of
+// ground truths; cls_mask gets bit c for every class present; gmag the largest fp32
+// corner magnitude (for the prefilter margin); n_pairs the number of (sorted position,
+// ground truth) pairs of equal class, whose layout goes to pbase / pmark.  gt_hist
+// (shared, 4*kC ints) accumulates the per-(subset, class) counts of this CTA.
 __device__ __forceinline__ int parse_targets(WarpWindow &w, const float *__restrict__ img, int lane,
                                              float tconf0, float tconf1, int *gt_hist, unsigned &cls_mask,
-                                             float &gmag, uint8_t *__restrict__ out_cell,
+                                             float &gmag, int &n_pairs, uint8_t *__restrict__ out_cell,
                                              uint8_t *__restrict__ out_cls, float4 *__restrict__ out_raw) {
     const bool gt0 = tconf0 > 0.f, gt1 = (lane + 32 < kCells) && tconf1 > 0.f;  // metrics.py:239
     const unsigned m0 = __ballot_sync(kFull, gt0), m1 = __ballot_sync(kFull, gt1);
+    const unsigned lt = (1u << lane) - 1u;
+    const int ngt = __popc(m0) + __popc(m1);
     MatchOverlay &mo = *reinterpret_cast<MatchOverlay *>(w.stage);
     const double small_a = __dmul_rn(__ddiv_rn(32.0, 448.0), __ddiv_rn(32.0, 448.0));   // metrics.py:511
     const double medium_a = __dmul_rn(__ddiv_rn(96.0, 448.0), __ddiv_rn(96.0, 448.0));  // metrics.py:512
     const float inv_s = 1.0f / (float)kS;
+    __syncwarp();  // every lane is done with what the overlay region held before
+    if (gt0) mo.gcell[__popc(m0 & lt)] = (uint8_t)lane;
+    if (gt1) mo.gcell[__popc(m0) + __popc(m1 & lt)] = (uint8_t)(lane + 32);
+    if (lane < kPairCap / 4) reinterpret_cast<unsigned *>(mo.pmark)[lane] = 0u;
+    __syncwarp();
     unsigned classes = 0;
     float mag = 0.f;
-    int g = 0;
-    __syncwarp();  // every lane is done with what the overlay region held before
-    // One object cell at a time, the whole warp on it (an image has two or three): lanes 0..19 fetch one class score
-    // each and the arg-max is a max reduction over order-preserving integer keys plus a ballot (first maximum, NaN
-    // maximal, as torch.argmax); the box is the same broadcast load in every lane.
+    int carry = 0;
 #pragma unroll 1
-    for (int half = 0; half < 2; ++half)
-        for (unsigned bits = half ? m1 : m0; bits; bits &= bits - 1, ++g) {
-            const int cell = __ffs(bits) - 1 + 32 * half;
+    for (int g0 = 0; g0 < ngt; g0 += 32) {
+        const int g = g0 + lane;
+        int cnt = 0;
+        if (g < ngt) {
+            const int cell = mo.gcell[g];
             const float *c = img + cell * kD;
-            unsigned key = 0;
-            if (lane < kC) {
-                const float v = __fadd_rn(__ldg(c + kB * 5 + lane), 0.f);    // -0 -> +0: they compare equal
-                const unsigned b = __float_as_uint(v);
-                key = (v != v) ? 0xffffffffu : ((b & 0x80000000u) ? ~b : (b | 0x80000000u));
-            }
-            const unsigned mx = __reduce_max_sync(kFull, key);
-            const int cls = __ffs(__ballot_sync(kFull, lane < kC && key == mx)) - 1;
             const float2 xy = __ldg(reinterpret_cast<const float2 *>(c));
             const float2 wh = __ldg(reinterpret_cast<const float2 *>(c) + 1);
+            const int cls = cell_class_global(c);
             const BoxF f = make_box_f(((float)(cell % kS) + xy.x) * inv_s, ((float)(cell / kS) + xy.y) * inv_s, wh.x, wh.y);
+            mo.gbox[g] = make_float4(f.x1, f.y1, f.x2, f.y2);
+            mo.garea[g] = f.area;
             const float m = box_magnitude(f);
             mag = (m > mag || m != m) ? m : mag;
+            mo.gcls[g] = (uint8_t)cls;
             const double area = __dmul_rn((double)wh.x, (double)wh.y);            // exact, as metrics.py:519
             const int bucket = (area < small_a) ? 1 : ((area < medium_a) ? 2 : 3);
-            classes |= 1u << cls;
-            if (lane == 0) {
-                mo.gbox[g] = make_float4(f.x1, f.y1, f.x2, f.y2);
-                mo.garea[g] = f.area;
-                mo.gcell[g] = (uint8_t)cell;
-                mo.gcls[g] = (uint8_t)cls;
-                mo.gbucket[g] = (uint8_t)bucket;
-                if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
-                    out_cell[g] = (uint8_t)cell;
-                    out_cls[g] = (uint8_t)cls;
-                    out_raw[g] = make_float4(xy.x, xy.y, wh.x, wh.y);
-                }
-                atomicAdd(&gt_hist[cls], 1);
-                atomicAdd(&gt_hist[bucket * kC + cls], 1);
+            mo.gbucket[g] = (uint8_t)bucket;
+            if (out_raw != nullptr) {  // enough to rebuild the reference's tuple later (yh_list_form)
+                out_cell[g] = (uint8_t)cell;
+                out_cls[g] = (uint8_t)cls;
+                out_raw[g] = make_float4(xy.x, xy.y, wh.x, wh.y);
             }
+            atomicAdd(&gt_hist[cls], 1);
+            atomicAdd(&gt_hist[bucket * kC + cls], 1);
+            classes |= 1u << cls;
+            cnt = w.cls_start[cls + 1] - w.cls_start[cls];   // candidates of its class, kept or not
         }
-    cls_mask = classes;
-    gmag = mag;
+        int inc = cnt;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int v = __shfl_up_sync(kFull, inc, off);
+            if (lane >= off) inc += v;
+        }
+        const int first = carry + inc - cnt;
+        if (g < ngt) {
+            mo.pbase[g] = (unsigned short)first;
+            if (cnt > 0 && first < kPairCap) mo.pmark[first] = (uint8_t)(g + 1);
+        }
+        carry += __shfl_sync(kFull, inc, 31);
+    }
+    n_pairs = carry;
+    cls_mask = __reduce_or_sync(kFull, classes);
+    gmag = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(mag)));
     __syncwarp();
-    return g;
+    return ngt;
 }
 
 // Best ground truth of detection k within subset q and the thresholds its IoU reaches, with the reference's
@@ -191,6 +207,15 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         unsigned next_ticket = 0;
         if (lane == 0) next_ticket = atomicAdd(ticket, 1u);
         const float *pimg = pred + (size_t)img * kImgFloats, *timg = tgt + (size_t)img * kImgFloats;
+#ifdef YH_PREFETCH_AHEAD
+        // Experiment (off): tickets are handed out in order, so image img + warps_total is drawn by some warp about
+        // one image time from now; pulling it towards L2 measured no gain for decode_nms (0.229 vs 0.233 ms) and a
+        // loss here (0.343 vs 0.325 ms: the target image is read sparsely, prefetching all of it adds DRAM traffic).
+        if (img + YH_PREFETCH_AHEAD * warps_total < N) {
+            prefetch_image(pimg + (size_t)YH_PREFETCH_AHEAD * warps_total * kImgFloats, lane);
+            prefetch_image(timg + (size_t)YH_PREFETCH_AHEAD * warps_total * kImgFloats, lane);
+        }
+#endif
         // slot-0 confidence of my two target cells: in flight while the predictions are decoded
         const float tconf0 = __ldg(timg + lane * kD + 4);
         const float tconf1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 4);
@@ -221,7 +246,8 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         // ---- targets: parse into the overlay
         unsigned cls_mask;
         float gmag;
-        const int ngt = parse_targets(w, timg, lane, tconf0, tconf1, gt_hist, cls_mask, gmag,
+        int n_pairs;
+        const int ngt = parse_targets(w, timg, lane, tconf0, tconf1, gt_hist, cls_mask, gmag, n_pairs,
                                       lists ? gt_cell + (size_t)img * kCells : nullptr,
                                       lists ? gt_cls + (size_t)img * kCells : nullptr,
                                       lists ? gt_raw + (size_t)img * kCells : nullptr);
@@ -234,18 +260,26 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         const float mM = fmaxf(filt.M, gmag);
         const bool mok = filt.ok && gmag < kFilterMaxCoord;
         const float mE = filter_margin(mM);
+        const bool pairs_ok = mok && n_pairs <= kPairCap;
 
-        // ---- items: kept detections whose class has a ground truth, in sorted order
+        // ---- records, in sorted order among the kept (flags = class only: true positives are patched in below),
+        // and the items: kept detections whose class has a ground truth
         int n_items = 0;
+        const size_t rec0 = (size_t)img * kCand;
 #pragma unroll 1
         for (int s = 0; s < kSlots; ++s) {
+            const unsigned kw = w.keepw[s];
+            if (kw == 0) continue;   // warp-uniform
             const int p = lane + 32 * s;
-            const bool kept = (w.keepw[s] >> lane) & 1u;
-            int k = 0, c = 0;
+            const bool kept = (kw >> lane) & 1u;
+            int k = 0, c = 0, slot = 0;
             if (kept) {
                 k = w.order[p];
                 c = w.cand.cls[k];
-                mo.flags[p] = 0;
+                slot = w.keepbase[s] + __popc(kw & lt);
+                rec_key[rec0 + slot] = w.cand.key[k];
+                rec_flags[rec0 + slot] = (uint64_t)c << 56;
+                if (rec_k != nullptr) rec_k[rec0 + slot] = (uint8_t)k;
             }
             const bool is_item = kept && ((cls_mask >> c) & 1u);
             const unsigned im = __ballot_sync(kFull, is_item);
@@ -254,8 +288,43 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                 mo.ik[it] = (uint8_t)k;
                 mo.icls[it] = (uint8_t)c;
                 mo.ipos[it] = (uint8_t)p;
+                mo.irec[it] = (uint8_t)slot;
             }
             n_items += __popc(im);
+        }
+
+        // ---- IoU intervals of all (detection, ground truth) pairs of equal class, one lane per pair: pair t of
+        // ground truth g is sorted position cls_start[class] + (t - pbase[g]).  An image has a handful of them.
+        if (pairs_ok && n_items > 0) {
+            int carry = 0;
+#pragma unroll 1
+            for (int t0 = 0; t0 < n_pairs; t0 += 32) {
+                const int t = t0 + lane;
+                const bool act = t < n_pairs;
+                int v = act ? mo.pmark[t] : 0;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const int o = __shfl_up_sync(kFull, v, off);
+                    if (lane >= off) v = max(v, o);
+                }
+                v = max(v, carry);
+                carry = __shfl_sync(kFull, v, 31);
+                if (!act) continue;
+                const int g = v - 1;
+                const int p = w.cls_start[mo.gcls[g]] + (t - mo.pbase[g]);
+                float lo = 0.f, hi = 0.f;
+                if ((w.keepw[p >> 5] >> (p & 31)) & 1u) {
+                    const float4 gb4 = mo.gbox[g];
+                    BoxF gb;
+                    gb.x1 = gb4.x; gb.y1 = gb4.y; gb.x2 = gb4.z; gb.y2 = gb4.w;
+                    gb.area = mo.garea[g];
+                    const int r = iou_interval(cand_box(w, w.order[p]), gb, mE, lo, hi);
+                    if (r == 2) lo = hi = 0.f;                          // IoU exactly 0: never matches
+                    else if (r == 0 || !(lo > 0.f)) lo = hi = -1.f;     // cannot tell (or cannot tell from 0)
+                }
+                mo.plo[t] = lo;
+                mo.phi[t] = hi;
+            }
         }
         __syncwarp();
 
@@ -270,20 +339,27 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             if (wq >= n_work) continue;
             const int it = wq >> 2;
             const int k = mo.ik[it], c = mo.icls[it];
-            const BoxF d = cand_box(w, k);
+            const int rel = mo.ipos[it] - w.cls_start[c];     // my place inside every pair run of my class
             float blo = 0.f, bhi = 0.f;
             int bg = 255;
             bool amb = !mok;
             for (int g = 0; g < ngt && !amb; ++g) {
                 if (mo.gcls[g] != c || (q != 0 && mo.gbucket[g] != q)) continue;
-                const float4 gb4 = mo.gbox[g];
-                BoxF gb;
-                gb.x1 = gb4.x; gb.y1 = gb4.y; gb.x2 = gb4.z; gb.y2 = gb4.w;
-                gb.area = mo.garea[g];
                 float lo, hi;
-                const int r = iou_interval(d, gb, mE, lo, hi);
-                if (r == 2) continue;                         // IoU exactly 0: never matches
-                if (r == 0 || !(lo > 0.f)) { amb = true; break; }   // cannot tell IoU from 0
+                if (pairs_ok) {
+                    lo = mo.plo[mo.pbase[g] + rel];
+                    hi = mo.phi[mo.pbase[g] + rel];
+                    if (hi == 0.f) continue;
+                    if (lo < 0.f) { amb = true; break; }
+                } else {
+                    const float4 gb4 = mo.gbox[g];
+                    BoxF gb;
+                    gb.x1 = gb4.x; gb.y1 = gb4.y; gb.x2 = gb4.z; gb.y2 = gb4.w;
+                    gb.area = mo.garea[g];
+                    const int r = iou_interval(cand_box(w, k), gb, mE, lo, hi);
+                    if (r == 2) continue;                         // IoU exactly 0: never matches
+                    if (r == 0 || !(lo > 0.f)) { amb = true; break; }   // cannot tell IoU from 0
+                }
                 if (bg == 255 || lo > bhi) { blo = lo; bhi = hi; bg = g; }   // certainly greater (strict)
                 else if (!(hi < blo)) amb = true;             // cannot order it against the best so far
             }
@@ -314,7 +390,8 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
 
         // ---- greedy TP/FP: an item is a TP at threshold t iff its best IoU >= t and no earlier detection of
         // its class claimed the same ground truth with IoU >= t (metrics.py:406-413).  "Earlier" = lower sorted
-        // position = lower item index.
+        // position = lower item index.  The flag word of an item that is a true positive somewhere replaces the
+        // class-only word written above (the __syncwarp orders the two stores).
 #pragma unroll 1
         for (int base = 0; base < n_work; base += 32) {
             const int wq = base + lane, q = lane & 3;
@@ -322,8 +399,8 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             const int it = act ? wq >> 2 : 0;
             uint64_t flags = 0;
             const unsigned g = act ? mo.bgt[it][q] : 255u;  // my best ground truth in subset q
+            const int c = mo.icls[it];
             if (g != 255u) {
-                const int c = mo.icls[it];
                 unsigned claimed = 0;   // thresholds at which an earlier item took the same ground truth
                 for (int e = it - 1; e >= 0 && mo.icls[e] == c; --e)
                     if (mo.bgt[e][q] == g) claimed |= mo.imask[e][q];
@@ -334,21 +411,9 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
             // the four subsets of an item sit on four neighbouring lanes
             flags |= __shfl_xor_sync(kFull, flags, 1);
             flags |= __shfl_xor_sync(kFull, flags, 2);
-            if (act && q == 0) mo.flags[mo.ipos[it]] = flags;
+            if (act && q == 0 && flags != 0) rec_flags[rec0 + mo.irec[it]] = flags | ((uint64_t)c << 56);
         }
         __syncwarp();
-
-        // ---- records, in sorted order among the kept
-#pragma unroll 1
-        for (int s = 0; s < kSlots; ++s) {
-            if (!((w.keepw[s] >> lane) & 1u)) continue;
-            const int p = lane + 32 * s;
-            const int k = w.order[p], c = w.cand.cls[k];
-            const size_t o = (size_t)img * kCand + w.keepbase[s] + __popc(w.keepw[s] & lt);
-            rec_key[o] = w.cand.key[k];
-            rec_flags[o] = mo.flags[p] | ((uint64_t)c << 56);
-            if (rec_k != nullptr) rec_k[o] = (uint8_t)k;
-        }
         asm volatile("" : "+r"(next_ticket)::"memory");  // keep the (slow) ticket read down here
         const unsigned drawn = __shfl_sync(kFull, next_ticket, 0);
         img = drawn < (unsigned)N ? warps_total + (int)drawn : N;
