@@ -212,6 +212,24 @@ int yh_partition_records(const uint64_t *key, const uint64_t *flags, int64_t M, 
  * on a peer gave up after 4 s.  gt_count_global[4*C] = the ranks' gt_count_local summed.
  * Between two calls the ranks must be ordered by some collective that completes after the
  * receive buffer was consumed (yh_peer_sum of the AP table is one). */
+/* yh_exchange_images (collective, same blocks / epoch / info / gt_count conventions as
+ * yh_exchange_records): compaction, partition by class owner and the all-to-all in ONE pass over
+ * the fixed-stride records of yh_map_update -- n_chunks batches in update() order, batch c holding
+ * n_images[c] images with n_keep[c][i] records at rec_key[c][i*K ..] / rec_flags[c][i*K ..]
+ * (host arrays of device pointers).  The records of an image are sorted by class, so they already
+ * are one contiguous run per owner: the call counts those runs (8 counters per image), scans them
+ * and copies every run once, straight into its owner's receive buffer.  Replaces
+ * yh_compact_records + yh_exchange_records (three reads and writes of every record) for
+ * world <= 8; the receive buffers end up with the same contents in the same order.  No reference
+ * counterpart (single-process). */
+size_t yh_exchange_images_workspace_bytes(int64_t n_images_total, int n_chunks);
+int yh_exchange_images(int n_chunks, const int32_t *const *n_keep, const uint64_t *const *rec_key,
+                       const uint64_t *const *rec_flags, const int *n_images, int K,
+                       const uint8_t *owner_of_class_host, int C, int world, int rank,
+                       void *const *peer_block_host, int64_t capacity, unsigned epoch,
+                       const int32_t *gt_count_local, int32_t *gt_count_global, int64_t *info,
+                       void *workspace, size_t workspace_bytes, void *stream);
+
 /* yh_peer_sum (collective, same epoch rule): vec[n] (device doubles, n <= 4*32*13 + 4) becomes
  * the sum over the ranks, in rank order, through the peer blocks -- the all-reduce of the
  * packed AP table without a second library.  vec[err_index] is set to 1 if a peer did not
@@ -221,6 +239,8 @@ int yh_peer_sum(double *vec, int n, int err_index, int world, int rank, void *co
                 unsigned epoch, void *stream);
 int yh_peer_alloc(size_t bytes, void **ptr, void *handle64);
 int yh_peer_open(const void *handle64, void **ptr);
+/* Waits on a peer's flag give up after wait_ms milliseconds of device time (default 4000; a rank's own block). */
+int yh_peer_set_wait_ms(void *own_block, unsigned wait_ms);
 int yh_peer_close(void *ptr);
 int yh_peer_free(void *ptr);
 size_t yh_peer_block_bytes(int64_t capacity);

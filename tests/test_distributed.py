@@ -152,7 +152,7 @@ def test_sharded_metric_equals_single_gpu_and_oracle(mode):
             assert abs(got[r][k] - float(orc[k])) <= 1e-12 * max(1.0, abs(float(orc[k]))), (k, got[r][k], orc[k])
 
 
-def _peer_growth_worker(rank, world, port, backend, sizes, q):
+def _peer_growth_worker(rank, world, port, backend, sizes, q, image_exchange=True, late_rank=-1):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dev = torch.device("cuda", rank % torch.cuda.device_count())
     torch.cuda.set_device(dev)
@@ -162,6 +162,7 @@ def _peer_growth_worker(rank, world, port, backend, sizes, q):
         from yolo_v1_b200 import mAPMetric, synth
 
         dm = D.DistributedMAP(mAPMetric(num_classes=20, conf_threshold=0.01), mode="peer")
+        dm.image_exchange = image_exchange
         out = []
         for n in sizes:
             tgt = synth.make_targets(n, seed=n, p_obj=0.055, size_mix=True)
@@ -170,6 +171,10 @@ def _peer_growth_worker(rank, world, port, backend, sizes, q):
             dm.reset()
             for s in range(lo, hi, 128):
                 dm.update(pred[s:min(hi, s + 128)].to(dev), tgt[s:min(hi, s + 128)].to(dev))
+            if rank == late_rank:
+                import time
+
+                time.sleep(5.5)      # longer than the 4 s a flag wait lasts
             res = dm.compute()
             out.append(({k: float(v) for k, v in res.items()}, dm.peer_fallbacks, dm._peer.capacity))
         dm.close()
@@ -178,13 +183,13 @@ def _peer_growth_worker(rank, world, port, backend, sizes, q):
         dist.destroy_process_group()
 
 
-def _run_peer_growth(world, backend, sizes):
+def _run_peer_growth(world, backend, sizes, image_exchange=True, late_rank=-1):
     from yolo_v1_b200 import mAPMetric, synth
 
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_peer_growth_worker, args=(r, world, port, backend, sizes, q)) for r in range(world)]
+    procs = [ctx.Process(target=_peer_growth_worker, args=(r, world, port, backend, sizes, q, image_exchange, late_rank)) for r in range(world)]
     for p in procs:
         p.start()
     got = dict(q.get(timeout=300) for _ in range(world))
@@ -214,11 +219,23 @@ def test_peer_blocks_overflow_falls_back_and_grows():
 
 
 @pytest.mark.gpu
-def test_peer_exchange_between_two_processes_sharing_one_gpu():
-    """CUDA IPC mapping + the flag protocol with two ranks even on a one-GPU box (gloo carries
-    the handles; the kernels of the two processes time-slice the device)."""
-    got, want = _run_peer_growth(2, "gloo", (600, 333, 40))
-    for r in range(2):
-        assert [f for _, f, _ in got[r]] == [0, 0, 0]
+@pytest.mark.parametrize("world,image_exchange", [(2, True), (2, False), (3, True), (5, True)])
+def test_peer_exchange_between_processes_sharing_one_gpu(world, image_exchange):
+    """CUDA IPC mapping + the flag protocol with several ranks even on a one-GPU box (gloo carries
+    the handles; the kernels of the processes time-slice the device).  image_exchange: records go from
+    the update batches straight to their owners (yh_exchange_images) -- or compacted first
+    (yh_compact_records + yh_exchange_records); both must equal the single-process result bit for bit."""
+    got, want = _run_peer_growth(world, "gloo", (600, 333, 40, 7), image_exchange)
+    for r in range(world):
+        assert [f for _, f, _ in got[r]] == [0, 0, 0, 0]
         for (res, _, _), w in zip(got[r], want):
             assert res == w
+
+
+@pytest.mark.gpu
+def test_a_late_rank_does_not_time_the_peer_exchange_out():
+    """One rank reaches compute() 5.5 s after the other; the exchange's flag waits last 4 s.  The eager
+    compute() orders the ranks on the stream first, so the early rank waits there (as it would in NCCL)."""
+    got, want = _run_peer_growth(2, "gloo", (300,), True, late_rank=1)
+    for r in range(2):
+        assert got[r][0][0] == want[0] and got[r][0][1] == 0

@@ -45,6 +45,7 @@ SIGNATURES = {
     "yh_peer_sum": (_i, [_vp, _i, _i, _i, _i, _vp, C.c_uint, _vp]),
     "yh_peer_alloc": (_i, [_sz, _vp, _vp]),
     "yh_peer_open": (_i, [_vp, _vp]),
+    "yh_peer_set_wait_ms": (_i, [_vp, C.c_uint]),
     "yh_peer_close": (_i, [_vp]),
     "yh_peer_free": (_i, [_vp]),
     "yh_peer_block_bytes": (_sz, [_i64]),
@@ -53,6 +54,9 @@ SIGNATURES = {
     "yh_exchange_workspace_bytes": (_sz, [_i64]),
     "yh_exchange_records": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _i, _i, _vp, _i64, C.c_uint, _vp, _i64, _vp, _vp,
                                  _vp, _sz, _vp]),
+    "yh_exchange_images_workspace_bytes": (_sz, [_i64, _i]),
+    "yh_exchange_images": (_i, [_i, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp, _i64, C.c_uint, _vp, _vp, _vp, _vp, _sz,
+                                _vp]),
     "yh_encode_targets": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "yh_iou_pairs": (_i, [_vp, _vp, _i64, _i, _vp, _vp]),
     "yh_nms_lists": (_i, [_vp, _i, _vp, _vp, _vp, _d, _i, _i, _vp, _vp, _i, _vp]),

@@ -37,6 +37,22 @@ int check_launch(const char *what, int kernels_launched = 1);
 
 inline bool shape_ok(int S, int B, int C) { return S == kS && B == kB && C == kC; }
 
+// Every other head shape runs the one-thread-per-image kernels of generic.cu (same results, no tuning).
+// with_classes_in_flags: the metric / inference entry points (C <= 32); the loss takes any C.
+bool generic_shape_ok(int S, int B, int C, bool with_classes_in_flags);
+int generic_decode_nms(const float *pred, int N, int S, int B, int C, double conf_thr, double nms_thr, int iou_mode,
+                       int order, int32_t *n_keep, uint8_t *keep_k, uint8_t *keep_cls, double *keep_conf,
+                       double *keep_box, int32_t *n_cand, uint8_t *bad_range, cudaStream_t st);
+int generic_map_update(const float *pred, const float *tgt, int N, int S, int B, int C, double conf_thr, double nms_thr,
+                       const double *thresholds_host, int T, int32_t *n_keep, uint64_t *rec_key, uint64_t *rec_flags,
+                       uint8_t *rec_k, void *rec_box, int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls, float *gt_raw,
+                       int32_t *gt_count, cudaStream_t st);
+int generic_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t *n_gt, uint8_t *gt_cls, double *gt_box,
+                     cudaStream_t st);
+size_t generic_loss_workspace_bytes(int N, int S);
+int generic_loss(const void *pred, int pred_dtype, const float *tgt, int N, int S, int B, int C, float lambda_coord,
+                 float lambda_noobj, float *parts, void *grad, void *workspace, cudaStream_t st);
+
 // ---- Python float semantics -------------------------------------------------
 // builtin max(a, b) / min(a, b): first argument unless the second is strictly
 // greater / smaller (so a NaN second argument never wins).

@@ -13,7 +13,7 @@
 // over tiles, and the scatter (each record read twice, written once).
 #include <string.h>
 
-#include "common.cuh"
+#include "peer.cuh"
 
 namespace yh {
 
@@ -22,20 +22,6 @@ constexpr int kPartWarps = kPartThreads / 32;
 constexpr int kPartRounds = 4;
 constexpr int kPartSpan = 32 * kPartRounds;         // consecutive records one warp owns
 constexpr int kPartTile = kPartWarps * kPartSpan;   // 1024 records per CTA
-constexpr int kMaxParts = 32;
-
-struct OwnerTable {
-    uint8_t of_class[256];
-};
-
-__device__ __forceinline__ int64_t part_count_of(int64_t cap, const int64_t *dev) {
-    if (dev == nullptr) return cap;
-    const int64_t m = *dev;
-    return m < cap ? m : cap;
-}
-
-__device__ __forceinline__ int owner_of(const OwnerTable &tab, uint64_t flags) { return tab.of_class[flags >> 56]; }
-
 // tile_cnt[tile][p] = records of the tile that go to part p
 __global__ void __launch_bounds__(kPartThreads)
 part_tile_counts(const uint64_t *__restrict__ flags, int64_t Mcap, const int64_t *__restrict__ Mdev,
@@ -187,66 +173,6 @@ part_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
 // falls back to the NCCL exchange and grows the buffers.  Waits give up after a few
 // seconds (info[3]) instead of hanging the GPU.
 
-constexpr int kGtWords = 4 * 32 + 2;  // 4 subsets x (C <= 32) counts + image count (2 words)
-
-constexpr int kResWords = 4 * 32 * YH_MAX_THRESHOLDS + 4;  // AP table + totals + error flag of one rank
-
-struct PeerCtl {
-    unsigned ready[kMaxParts];
-    unsigned done[kMaxParts];
-    unsigned res_ready[kMaxParts];
-    unsigned calls;              // exchanges this rank has started: the epoch when the caller passes 0
-    unsigned pad[kMaxParts - 1];
-    long long row[kMaxParts][kMaxParts];
-    int gt[kMaxParts][kGtWords];
-    double res[kMaxParts][kResWords];
-};
-
-struct PeerTable {
-    PeerCtl *ctl[kMaxParts];
-    uint64_t *key[kMaxParts];
-    uint64_t *flags[kMaxParts];
-};
-
-struct ExchangeLocal {        // head of the workspace, zeroed per call
-    unsigned finished_ctas;
-    unsigned timed_out;
-    unsigned overflow;
-    unsigned pad;
-};
-
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
-    unsigned v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long now_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-constexpr unsigned long long kWaitLimitNs = 4000000000ull;
-
-// epoch 0 = "the library's own call counter" (kept in the rank's block, advanced by peer_begin):
-// what a CUDA-graph replay needs, where kernel arguments are frozen
-__device__ __forceinline__ unsigned epoch_of(unsigned epoch, const PeerCtl *mine) {
-    return epoch ? epoch : *reinterpret_cast<const volatile unsigned *>(&mine->calls);
-}
-
-// true once *flag == epoch; false if the limit ran out
-__device__ __forceinline__ bool wait_flag(const unsigned *flag, unsigned epoch) {
-    if (ld_acquire_sys(flag) == epoch) return true;
-    const unsigned long long t0 = now_ns();
-    while (ld_acquire_sys(flag) != epoch) {
-        __nanosleep(200);
-        if (now_ns() - t0 > kWaitLimitNs) return false;
-    }
-    return true;
-}
-
 // first kernel of an exchange: clears the per-call words and advances the call counter
 __global__ void peer_begin(ExchangeLocal *__restrict__ loc, PeerCtl *__restrict__ mine) {
     if (threadIdx.x == 0) {
@@ -364,7 +290,7 @@ peer_scatter(const uint64_t *__restrict__ key, const uint64_t *__restrict__ flag
     if (tid == 0) s_state = 0;
     __syncthreads();
     // persistent CTAs: one wait for the peers' rows per CTA, one system fence at the end
-    if (tid < world && !wait_flag(&mine->ready[tid], epoch)) s_state = 1;
+    if (tid < world && !wait_flag(&mine->ready[tid], epoch, mine->wait_ms)) s_state = 1;
     __syncthreads();
     if (s_state) {
         if (tid == 0) loc->timed_out = 1;
@@ -484,7 +410,7 @@ peer_finish(const __grid_constant__ PeerTable peers, int world, int me, unsigned
     epoch = epoch_of(epoch, mine);
     if (tid == 0) s_bad = 0;
     __syncthreads();
-    if (tid < world && !wait_flag(&mine->done[tid], epoch)) s_bad = 1;
+    if (tid < world && !wait_flag(&mine->done[tid], epoch, mine->wait_ms)) s_bad = 1;
     __syncthreads();
     const bool bad = s_bad || loc->timed_out;
     const bool overflow = loc->overflow != 0;
@@ -584,7 +510,7 @@ peer_sum_results(const __grid_constant__ PeerTable peers, int world, int me, uns
     __syncthreads();
     if (tid < world) {
         st_release_sys(&peers.ctl[tid]->res_ready[me], epoch);
-        if (!wait_flag(&mine->res_ready[tid], epoch)) s_bad = 1;
+        if (!wait_flag(&mine->res_ready[tid], epoch, mine->wait_ms)) s_bad = 1;
     }
     __syncthreads();
     for (int i = tid; i < n; i += blockDim.x) {
@@ -639,6 +565,21 @@ extern "C" int yh_peer_alloc(size_t bytes, void **ptr, void *handle64) {
     }
     memcpy(handle64, &h, 64);
     *ptr = p;
+    return 0;
+}
+
+// how long this rank's kernels wait for a peer's flag before they give up (info[3] / the error word of yh_peer_sum)
+extern "C" int yh_peer_set_wait_ms(void *own_block, unsigned wait_ms) {
+    if (!own_block) {
+        set_error("yh_peer_set_wait_ms: bad argument");
+        return YH_ERR_BAD_ARG;
+    }
+    const cudaError_t e = cudaMemcpy(&((yh::PeerCtl *)own_block)->wait_ms, &wait_ms, sizeof(unsigned), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        set_error("yh_peer_set_wait_ms: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        return (int)e;
+    }
     return 0;
 }
 
@@ -757,3 +698,4 @@ extern "C" int yh_exchange_records(const uint64_t *key, const uint64_t *flags, i
     peer_finish<<<1, 256, 0, st>>>(peers, world, rank, epoch, 4 * C, loc, gt_count_global, info);
     return check_launch("yh_exchange_records", 5);
 }
+#include "exchange_images.cuh"

@@ -157,7 +157,7 @@ class PeerExchange:
     anything back, and the epoch of the flag protocol is the library's own call counter on the
     device (epoch argument 0), so an exchange can sit inside a captured CUDA graph."""
 
-    def __init__(self, capacity: int, device: torch.device, group=None):
+    def __init__(self, capacity: int, device: torch.device, group=None, wait_ms: int = 0):
         lib = _lib.lib()
         self.group, self.device = group, device
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
@@ -198,6 +198,9 @@ class PeerExchange:
         elif problem:
             raise PeerUnavailable(problem)
         self._blocks = (_lib.C.c_void_p * self.world)(*blocks)
+        if wait_ms:
+            with _lib.on_device(device):
+                _lib.check(lib.yh_peer_set_wait_ms(self._own, int(wait_ms)), "yh_peer_set_wait_ms")
         raw = torch.as_tensor(_DeviceBlock(self._own.value, self.nbytes), device=device)
         ko, fo = int(lib.yh_peer_key_offset(self.capacity)), int(lib.yh_peer_flags_offset(self.capacity))
         self.recv_key = raw[ko:ko + 8 * self.capacity].view(torch.int64)
@@ -218,6 +221,29 @@ class PeerExchange:
                                          gt_glob.data_ptr(), info.data_ptr(), ws.data_ptr(),
                                          ws.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "yh_exchange_records")
+        return self.recv_key, self.recv_flags, gt_glob, info
+
+    def exchange_images(self, chunks, owners: List[int], gt_count: torch.Tensor):
+        """yh_exchange_images: the same result as compact + exchange(), straight from the fixed-stride records
+        of the update batches (`chunks`: head.UpdateChunk list in update order).  world <= 8."""
+        lib, dev = _lib.lib(), self.device
+        n = len(chunks)
+        VP, I = _lib.C.c_void_p, _lib.C.c_int
+        nk = (VP * max(n, 1))(*[ch.n_keep.data_ptr() for ch in chunks])
+        rk = (VP * max(n, 1))(*[ch.rec_key.data_ptr() for ch in chunks])
+        rf = (VP * max(n, 1))(*[ch.rec_flags.data_ptr() for ch in chunks])
+        ni = (I * max(n, 1))(*[int(ch.n) for ch in chunks])
+        K = int(chunks[0].rec_key.shape[1]) if n else 98
+        total = sum(int(ch.n) for ch in chunks)
+        ws = self._ws.get(dev, int(lib.yh_exchange_images_workspace_bytes(total, n)))
+        gt_glob = torch.empty_like(gt_count)
+        info = torch.empty(4, dtype=torch.int64, device=dev)
+        tab = (_lib.C.c_uint8 * len(owners))(*owners)
+        with _lib.on_device(dev):
+            rc = lib.yh_exchange_images(n, nk, rk, rf, ni, K, tab, len(owners), self.world, self.rank, self._blocks,
+                                        self.capacity, 0, gt_count.data_ptr(), gt_glob.data_ptr(), info.data_ptr(),
+                                        ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
+        _lib.check(rc, "yh_exchange_images")
         return self.recv_key, self.recv_flags, gt_glob, info
 
     def sum_results(self, vec: torch.Tensor, n: int, err_index: int) -> None:
@@ -263,14 +289,19 @@ class DistributedMAP:
     use (collective, ranks on one box); call close() (collective) to release them.
     "auto" = "peer" if that mapping works on every rank, else "class_shard"."""
 
-    def __init__(self, metric: mAPMetric, group=None, mode: str = "class_shard"):
+    def __init__(self, metric: mAPMetric, group=None, mode: str = "class_shard", peer_wait_ms: int = 0):
         if mode not in ("gather", "class_shard", "peer", "auto"):
             raise ValueError(f"unknown exchange mode {mode!r}")
+        # peer mode: how long a rank's kernels wait for a peer's flag before giving up (0 = the library's 4 s).
+        # An eager compute() lines the ranks up first (a one-element all-reduce on the stream), so ordinary skew
+        # -- a short tail shard, a model forward still queued -- never comes near it; what is left is a dead peer.
+        self.peer_wait_ms = int(peer_wait_ms)
         self.metric = metric
         self.group = group
         self.mode = mode
         self._peer: Optional[PeerExchange] = None
         self.peer_fallbacks = 0            # compute() calls that overflowed the receive blocks
+        self.image_exchange = True         # peer mode: yh_exchange_images (False: compact + yh_exchange_records)
 
     def close(self):
         if self._peer is not None:
@@ -300,7 +331,7 @@ class DistributedMAP:
             capacity = int(np.ceil(1.25 * top))
         if self._peer is not None:
             self._peer.close()
-        self._peer = PeerExchange(capacity, dev, g)
+        self._peer = PeerExchange(capacity, dev, g, self.peer_wait_ms)
         return self._peer
 
     def __getattr__(self, name):
@@ -329,14 +360,28 @@ class DistributedMAP:
         gt_count = m._gt_count.clone() if m._gt_count is not None else torch.zeros(4 * C, dtype=torch.int32, device=dev)
         return key, flg, cap, running, gt_count
 
-    def enqueue_peer(self, dev, key, flg, cap, running, gt_count, n_images) -> torch.Tensor:
+    def enqueue_peer(self, dev) -> torch.Tensor:
         """Peer-mode compute() up to, not including, the host read: exchange, sort + AP, sum over
-        the ranks.  Returns the device vector finish_peer() decodes.  Capturable in a CUDA graph."""
+        the ranks.  Returns the device vector finish_peer() decodes.  Capturable in a CUDA graph.
+
+        Up to 8 ranks the records go from the update batches straight to their owners
+        (yh_exchange_images: one pass); beyond that they are compacted first (yh_exchange_records)."""
         m = self.metric
         world = dist.get_world_size(self.group)
         T, C = len(m.iou_thresholds), m.num_classes
+        if m._lists_live or m._pred_lists:
+            raise _lib.YoloHeadError("DistributedMAP: the Python list state was touched on this rank; the sharded "
+                                     "compute() runs from the device records only")
+        cap = sum(ch.rec_key.numel() for ch in m._chunks)
         px = self._peer_blocks(dev, cap)
-        rk, rf, gt_glob, info = px.exchange(key, flg, cap, running, class_owners(C, world), gt_count, n_images)
+        owners = class_owners(C, world)
+        if world <= 8 and self.image_exchange:
+            gt_count = m._gt_count if m._gt_count is not None else torch.zeros(4 * C, dtype=torch.int32, device=dev)
+            rk, rf, gt_glob, info = px.exchange_images(m._chunks, owners, gt_count)
+        else:
+            key, flg, cap, running, gt_count = self._local_records(dev)
+            n_images = sum(ch.n for ch in m._chunks)
+            rk, rf, gt_glob, info = px.exchange(key, flg, cap, running, owners, gt_count, n_images)
         _, _, packed = head.ap_reduce(rk, rf, px.capacity, gt_glob, C, T, m_dev=info[:1])
         if world > 1:
             px.sum_results(packed, 4 * C * T + 3, 4 * C * T + 2)
@@ -348,7 +393,8 @@ class DistributedMAP:
         T, C = len(m.iou_thresholds), m.num_classes
         host = vec.cpu()
         if host[-1] != 0:
-            raise _lib.YoloHeadError("yh_exchange_records: a rank of the group did not show up within 4 s")
+            raise _lib.YoloHeadError("peer exchange: a rank of the group did not show up within the wait limit "
+                                     f"({self.peer_wait_ms or 4000} ms; DistributedMAP(peer_wait_ms=...))")
         if host[-2] != 0:
             return None
         if int(host[-3]) == 0:
@@ -361,8 +407,8 @@ class DistributedMAP:
         world = dist.get_world_size(g)
         dev = m._device if m._device is not None else torch.device("cuda", torch.cuda.current_device())
         T, C = len(m.iou_thresholds), m.num_classes
-        key, flg, cap, running, gt_count = self._local_records(dev)
         n_images = len(m._pred_lists) + sum(c.n for c in m._chunks)
+        cap = sum(ch.rec_key.numel() for ch in m._chunks)
         if self.mode == "auto":            # "peer" where the ranks can map each other's memory
             try:
                 self._peer_blocks(dev, cap)
@@ -373,10 +419,14 @@ class DistributedMAP:
                 warnings.warn(f"DistributedMAP: peer-memory exchange unavailable ({e}); using the NCCL exchange")
                 self.mode = "class_shard"
         if self.mode == "peer":
-            res = self.finish_peer(self.enqueue_peer(dev, key, flg, cap, running, gt_count, n_images))
+            if world > 1 and not torch.cuda.is_current_stream_capturing():
+                # the flag waits of the exchange are bounded; order the ranks on the stream first, as NCCL would
+                dist.all_reduce(torch.zeros(1, dtype=torch.int32, device=dev), group=g)
+            res = self.finish_peer(self.enqueue_peer(dev))
             if res is not None:
                 return res
             self.peer_fallbacks += 1           # a receive block was too small: NCCL path now, larger blocks next
+        key, flg, cap, running, gt_count = self._local_records(dev)
         # ground-truth counts and the image count travel in one all-reduce
         glob = torch.cat([gt_count.to(torch.int64),
                           torch.tensor([n_images], dtype=torch.int64, device=dev)])

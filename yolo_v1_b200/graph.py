@@ -105,10 +105,7 @@ class CapturedHeadStep:
                 self.grad = p.grad
             parts64 = parts.to(torch.float64)
         if self._dist:
-            dm, m = self.metric, self._inner()
-            key, flg, cap, running, gt_count = dm._local_records(dev)
-            n_images = sum(ch.n for ch in m._chunks)
-            vec = dm.enqueue_peer(dev, key, flg, cap, running, gt_count, n_images)
+            vec = self.metric.enqueue_peer(dev)
         else:
             vec = self.metric._enqueue_reduce()
         main.wait_stream(self._side)                     # join
