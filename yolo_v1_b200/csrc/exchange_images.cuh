@@ -9,7 +9,7 @@
 // over the images, and one copy: source = the image's run, destination = the owner's receive buffer.
 //
 //   xi_count         one warp per image: owner of every record, eight 8-bit counters per image packed into one
-//                    word; per-CTA (256 images) totals
+//                    word; per-CTA (64 images) totals
 //   xi_scan_publish  one CTA per batch: exclusive prefix of the CTA totals behind the batches before it; after
 //                    the last batch the rank's run lengths, ground-truth counts and image count go to every rank
 //                    and ready[me] is raised (as peer_scan_publish)
@@ -27,8 +27,9 @@
 namespace yh {
 
 constexpr int kXiOwners = 8;          // counters are 8 x 8 bits per image, 4 x 16 bits x 2 per CTA
-constexpr int kXiImages = 256;        // images per CTA
 constexpr int kXiThreads = 256;
+constexpr int kXiIpw = 8;             // images per warp: few, so that many warps are in flight (the copy is latency-bound)
+constexpr int kXiImages = kXiIpw * kXiThreads / 32;   // images per CTA
 
 struct XiLocal {                      // head of the workspace (after ExchangeLocal), zeroed by xi_begin
     unsigned long long run_total[kXiOwners];   // records of the batches scanned so far, per owner
@@ -58,10 +59,10 @@ xi_count(const int32_t *__restrict__ n_keep, const uint64_t *__restrict__ rec_fl
          unsigned *__restrict__ cta_tot) {
     __shared__ unsigned long long s_lo[kXiThreads / 32], s_hi[kXiThreads / 32];
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
-    const int img0 = blockIdx.x * kXiImages + wp * 32;
-    unsigned long long mine = 0;   // lane i keeps the counters of image img0 + i
-#pragma unroll 1
-    for (int i = 0; i < 32; ++i) {
+    const int img0 = blockIdx.x * kXiImages + wp * kXiIpw;
+    unsigned long long mine = 0;   // lane i < kXiIpw keeps the counters of image img0 + i
+#pragma unroll 2
+    for (int i = 0; i < kXiIpw; ++i) {
         const int img = img0 + i;
         if (img >= N) break;       // warp-uniform
         const int n = n_keep[img];
@@ -75,8 +76,8 @@ xi_count(const int32_t *__restrict__ n_keep, const uint64_t *__restrict__ rec_fl
         hi = __reduce_add_sync(0xffffffffu, hi);
         if (lane == i) mine = ((unsigned long long)hi << 32) | lo;
     }
-    if (img0 + lane < N) img_cnt[img0 + lane] = mine;
-    // CTA totals: 16-bit fields (256 images x 98 records fit)
+    if (lane < kXiIpw && img0 + lane < N) img_cnt[img0 + lane] = mine;
+    // CTA totals: 16-bit fields (64 images x 255 records fit)
     unsigned long long tl = spread_bytes((unsigned)mine), th = spread_bytes((unsigned)(mine >> 32));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -194,8 +195,8 @@ xi_scatter(const int32_t *__restrict__ n_keep, const uint64_t *__restrict__ rec_
     const bool overflow = s_state == 2;
     if (overflow && tid == 0 && blockIdx.x == 0) loc->overflow = 1;
     if (!overflow) {
-        const int img = blockIdx.x * kXiImages + wp * 32 + lane;   // lane <-> one of the warp's 32 images
-        const unsigned long long c8 = img < N ? img_cnt[img] : 0ull;
+        const int img = blockIdx.x * kXiImages + wp * kXiIpw + lane;   // lane < kXiIpw <-> one of the warp's images
+        const unsigned long long c8 = (lane < kXiIpw && img < N) ? img_cnt[img] : 0ull;
         // offsets of my image's runs inside the CTA: inclusive scan of 16-bit fields over the lanes, then the warps
         unsigned long long il = spread_bytes((unsigned)c8), ih = spread_bytes((unsigned)(c8 >> 32));
         const unsigned long long ml = il, mh = ih;
@@ -220,7 +221,7 @@ xi_scatter(const int32_t *__restrict__ n_keep, const uint64_t *__restrict__ rec_
         const unsigned long long exl = il - ml, exh = ih - mh;          // exclusive inside the warp
         // first record of every owner's run inside my image: byte-wise exclusive prefix of the counters
         const unsigned long long first8 = c8 * 0x0101010101010101ull - c8;
-        const size_t src0 = (size_t)(blockIdx.x * kXiImages + wp * 32) * K;
+        const size_t src0 = (size_t)(blockIdx.x * kXiImages + wp * kXiIpw) * K;
 #pragma unroll 1
         for (int r = 0; r < world; ++r) {
             const int sh = 16 * (r & 3);
@@ -233,14 +234,28 @@ xi_scatter(const int32_t *__restrict__ n_keep, const uint64_t *__restrict__ rec_
             __syncwarp();
             uint64_t *dk = peers.key[r] + dst_base[r] + wbase;
             uint64_t *df = peers.flags[r] + dst_base[r] + wbase;
-            for (unsigned j = lane; j < total; j += 32) {
-                int i = 0;   // the last image whose offset is <= j (empty images share an offset with their successor)
+            // four records per lane and round: the loads of one round are all in flight before the first store
+            for (unsigned j0 = lane; j0 < total; j0 += 128) {
+                uint64_t kv[4], fv[4];
 #pragma unroll
-                for (int h = 16; h > 0; h >>= 1)
-                    if (s_off[wp][i + h] <= j) i += h;
-                const size_t s = src0 + (size_t)i * K + s_first[wp][i] + (j - s_off[wp][i]);
-                dk[j] = __ldg(rec_key + s);
-                df[j] = __ldg(rec_flags + s);
+                for (int u = 0; u < 4; ++u) {
+                    const unsigned j = j0 + 32 * u;
+                    if (j >= total) break;
+                    int i = 0;   // the last image whose offset is <= j (empty images share an offset with their successor)
+#pragma unroll
+                    for (int h = 16; h > 0; h >>= 1)
+                        if (s_off[wp][i + h] <= j) i += h;
+                    const size_t s = src0 + (size_t)i * K + s_first[wp][i] + (j - s_off[wp][i]);
+                    kv[u] = __ldg(rec_key + s);
+                    fv[u] = __ldg(rec_flags + s);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const unsigned j = j0 + 32 * u;
+                    if (j >= total) break;
+                    dk[j] = kv[u];
+                    df[j] = fv[u];
+                }
             }
             __syncwarp();
         }
