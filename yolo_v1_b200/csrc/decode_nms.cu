@@ -209,13 +209,27 @@ extern "C" int yh_decode_nms(const float *pred, int N, int S, int B, int C, doub
                              double nms_thr, int iou_mode, int order, int32_t *n_keep,
                              uint8_t *keep_k, uint8_t *keep_cls, double *keep_conf,
                              double *keep_box, int32_t *n_cand, uint8_t *bad_range, void *stream) {
-    if (!shape_ok(S, B, C)) {
-        set_error("yh_decode_nms: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
+    const bool fast = shape_ok(S, B, C);
+    if (!fast && !generic_shape_ok(S, B, C, true)) {
+        set_error("yh_decode_nms: shape S=%d,B=%d,C=%d outside this build (S*S*B <= 255, B <= 8, C <= 32)", S, B, C);
         return YH_ERR_UNSUPPORTED;
     }
     if (N < 0 || !pred || !n_keep || !keep_k) {
         set_error("yh_decode_nms: bad argument");
         return YH_ERR_BAD_ARG;
+    }
+    if (!fast) {   // any other head shape: one thread per image (generic.cu)
+        if (order != YH_ORDER_CLASS_GROUPED && order != YH_ORDER_GLOBAL_CONF) {
+            set_error("yh_decode_nms: unknown order %d", order);
+            return YH_ERR_BAD_ARG;
+        }
+        if (iou_mode != YH_IOU_METRICS && iou_mode != YH_IOU_INFER) {
+            set_error("yh_decode_nms: unknown iou_mode %d", iou_mode);
+            return YH_ERR_BAD_ARG;
+        }
+        if (N == 0) return 0;
+        return generic_decode_nms(pred, N, S, B, C, conf_thr, nms_thr, iou_mode, order, n_keep, keep_k, keep_cls, keep_conf,
+                                  keep_box, n_cand, bad_range, (cudaStream_t)stream);
     }
     if ((uintptr_t)pred % 8) {
         set_error("yh_decode_nms: pred must be 8-byte aligned");

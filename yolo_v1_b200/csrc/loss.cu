@@ -388,7 +388,8 @@ static void launch_loss(const LossLaunch &L, const void *pred, void *grad) {
 }  // namespace yh
 
 extern "C" size_t yh_loss_workspace_bytes(int N, int S, int B, int C) {
-    if (N < 0 || !shape_ok(S, B, C)) return 0;
+    if (N < 0) return 0;
+    if (!shape_ok(S, B, C)) return (S >= 1 && B >= 1 && B <= 8 && C >= 1) ? generic_loss_workspace_bytes(N, S) : 0;
     size_t cells = (size_t)N * kCells;
     size_t blocks = (cells + kTile - 1) / kTile;
     return 256 + blocks * 4 * sizeof(double);
@@ -398,8 +399,9 @@ extern "C" int yh_loss_fwd_bwd(const void *pred, int pred_dtype, const float *tg
                                int B, int C, float lambda_coord, float lambda_noobj, float *parts,
                                void *grad_pred, void *workspace, size_t workspace_bytes,
                                void *stream) {
-    if (!shape_ok(S, B, C)) {
-        set_error("yh_loss_fwd_bwd: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
+    const bool fast = shape_ok(S, B, C);
+    if (!fast && !(S >= 1 && B >= 1 && B <= 8 && C >= 1)) {
+        set_error("yh_loss_fwd_bwd: shape S=%d,B=%d,C=%d outside this build (B <= 8)", S, B, C);
         return YH_ERR_UNSUPPORTED;
     }
     if (N <= 0 || !pred || !tgt || !parts || !workspace) {
@@ -409,6 +411,14 @@ extern "C" int yh_loss_fwd_bwd(const void *pred, int pred_dtype, const float *tg
     if (workspace_bytes < yh_loss_workspace_bytes(N, S, B, C)) {
         set_error("yh_loss_fwd_bwd: workspace too small");
         return YH_ERR_WORKSPACE;
+    }
+    if (!fast) {   // any other head shape: one thread per cell (generic.cu)
+        if (pred_dtype != YH_F32 && pred_dtype != YH_F16 && pred_dtype != YH_BF16) {
+            set_error("yh_loss_fwd_bwd: unknown pred_dtype %d", pred_dtype);
+            return YH_ERR_BAD_ARG;
+        }
+        return generic_loss(pred, pred_dtype, tgt, N, S, B, C, lambda_coord, lambda_noobj, parts, grad_pred, workspace,
+                            (cudaStream_t)stream);
     }
     const size_t esz = (pred_dtype == YH_F32) ? 4 : 2;
     if (((uintptr_t)pred % (2 * esz)) || ((uintptr_t)tgt % 8) || ((uintptr_t)grad_pred % (2 * esz)) ||

@@ -470,8 +470,9 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
                              int32_t *n_keep, uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k,
                              void *rec_box, int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls,
                              float *gt_raw, int32_t *gt_count, void *stream) {
-    if (!shape_ok(S, B, C)) {
-        set_error("yh_map_update: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
+    const bool fast = shape_ok(S, B, C);
+    if (!fast && !generic_shape_ok(S, B, C, true)) {
+        set_error("yh_map_update: shape S=%d,B=%d,C=%d outside this build (S*S*B <= 255, B <= 8, C <= 32)", S, B, C);
         return YH_ERR_UNSUPPORTED;
     }
     if (T < 1 || T > YH_MAX_THRESHOLDS) {
@@ -484,11 +485,15 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
         set_error("yh_map_update: bad argument");
         return YH_ERR_BAD_ARG;
     }
-    if (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8) || ((uintptr_t)rec_box % 8) || ((uintptr_t)gt_raw % 16)) {
+    if (fast ? (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8) || ((uintptr_t)rec_box % 8) || ((uintptr_t)gt_raw % 16))
+             : (((uintptr_t)pred % 4) || ((uintptr_t)tgt % 4) || ((uintptr_t)rec_box % 8) || ((uintptr_t)gt_raw % 16))) {
         set_error("yh_map_update: pred/tgt/rec_box must be 8-byte aligned, gt_raw 16-byte aligned");
         return YH_ERR_ALIGNMENT;
     }
     if (N == 0) return 0;
+    if (!fast)   // any other head shape: one thread per image (generic.cu)
+        return generic_map_update(pred, tgt, N, S, B, C, conf_thr, nms_thr, thresholds_host, T, n_keep, rec_key, rec_flags,
+                                  rec_k, rec_box, n_gt, gt_cell, gt_cls, gt_raw, gt_count, (cudaStream_t)stream);
     Thresholds th;
     th.n = T;
     for (int i = 0; i < YH_MAX_THRESHOLDS; ++i) th.t[i] = i < T ? thresholds_host[i] : 2.0;
@@ -510,8 +515,9 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
 
 extern "C" int yh_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t *n_gt,
                            uint8_t *gt_cls, double *gt_box, void *stream) {
-    if (!shape_ok(S, B, C)) {
-        set_error("yh_parse_gt: only S=7,B=2,C=20 is built (got %d,%d,%d)", S, B, C);
+    const bool fast = shape_ok(S, B, C);
+    if (!fast && !generic_shape_ok(S, B, C, true)) {
+        set_error("yh_parse_gt: shape S=%d,B=%d,C=%d outside this build (S*S*B <= 255, B <= 8, C <= 32)", S, B, C);
         return YH_ERR_UNSUPPORTED;
     }
     if (N < 0 || !tgt || !n_gt || !gt_cls || !gt_box) {
@@ -519,6 +525,7 @@ extern "C" int yh_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t
         return YH_ERR_BAD_ARG;
     }
     if (N == 0) return 0;
+    if (!fast) return generic_parse_gt(tgt, N, S, B, C, n_gt, gt_cls, gt_box, (cudaStream_t)stream);
     parse_gt_kernel<<<(N + 3) / 4, 128, 0, (cudaStream_t)stream>>>(tgt, N, n_gt, gt_cls, gt_box);
     return check_launch("yh_parse_gt");
 }

@@ -44,7 +44,7 @@ def loss_fwd_bwd(pred: torch.Tensor, tgt: torch.Tensor, S: int, B: int, C: int, 
     grad = torch.empty_like(p) if want_grad else None
     nbytes = lib.yh_loss_workspace_bytes(N, S, B, C)
     if nbytes == 0:
-        raise NotImplementedError(f"YOLOLoss kernels are built for S=7,B=2,C=20 only (got {S},{B},{C})")
+        raise NotImplementedError(f"YOLOLoss: shape S={S}, B={B}, C={C} is outside this build (B <= 8)")
     ws = _WS.get(p.device, nbytes)
     with _lib.on_device(p.device):
         rc = lib.yh_loss_fwd_bwd(p.data_ptr(), _lib.dtype_code(p), t.data_ptr(), N, S, B, C,

@@ -18,7 +18,7 @@ By default (``lists="lazy"``) update() only keeps a reference to the batch it wa
 given and the lists are rebuilt from it by yh_decode_nms + yh_parse_gt, so the
 update kernel writes nothing but the 16-byte records; ``lists="eager"`` makes the
 update kernel write the list data next to the records instead (no reference to the
-caller's tensors is kept).  Once touched the lists are authoritative: compute()
+caller's tensors is kept; S=7, B=2, C=20 only -- other head shapes always rebuild).  Once touched the lists are authoritative: compute()
 then uploads them and runs the list-form kernels (yh_match_lists), so hand-edited
 state gives the reference's answer too.
 """
@@ -194,7 +194,7 @@ class mAPMetric:
             self._device = dev
         chunk = head.map_update(predictions, targets, self.conf_threshold, self.nms_threshold,
                                 self.iou_thresholds, self._gt_count, self.S, self.B, self.num_classes,
-                                want_lists=self.lists == "eager")
+                                want_lists=self.lists == "eager" and (self.S, self.B, self.num_classes) == (7, 2, 20))
         self._chunks.append(chunk)
         if self._lists_live:
             self._materialise()
