@@ -34,12 +34,16 @@ def test_library_exports_every_declared_symbol():
 def test_workspace_queries_and_argument_errors_without_gpu():
     lib = _lib.lib()
     assert lib.yh_loss_workspace_bytes(64, 7, 2, 20) >= 256
-    assert lib.yh_loss_workspace_bytes(64, 14, 2, 20) == 0       # unsupported grid
+    assert lib.yh_loss_workspace_bytes(64, 14, 2, 20) >= 256     # other shapes: the generic kernels
+    assert lib.yh_loss_workspace_bytes(64, 7, 9, 20) == 0        # more than 8 boxes per cell: outside the build
     assert lib.yh_ap_workspace_bytes(1000, 20, 10) > 16 * 1000
     assert lib.yh_ap_workspace_bytes(1000, 20, 14) == 0          # too many thresholds
     assert lib.yh_compact_workspace_bytes(4952) >= 256
+    # S = 9 is a supported (generic) shape now: the null pointers are what is wrong; S = 14 (392 candidates) is not
     rc = lib.yh_decode_nms(None, 1, 9, 2, 20, 0.1, 0.4, 0, 0, None, None, None, None, None, None, None, None)
-    assert rc == -2 and b"S=7" in lib.yh_last_error()
+    assert rc == -1
+    rc = lib.yh_decode_nms(None, 1, 14, 2, 20, 0.1, 0.4, 0, 0, None, None, None, None, None, None, None, None)
+    assert rc == -2 and b"S=14" in lib.yh_last_error()
     rc = lib.yh_loss_fwd_bwd(None, 0, None, 1, 7, 2, 20, 5.0, 0.5, None, None, None, 0, None)
     assert rc == -1
 
