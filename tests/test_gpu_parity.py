@@ -100,8 +100,12 @@ def test_loss_rejects_cpu_and_bad_shapes():
         crit(torch.zeros(1, 7, 7, 30), torch.zeros(1, 7, 7, 30))
     with pytest.raises(ValueError):
         crit(torch.zeros(1, 7, 7, 29, device=DEV), torch.zeros(1, 7, 7, 29, device=DEV))
+    # other head shapes run the generic kernels (tests/test_generic_shapes.py): S = 14 is fine for the loss, which has
+    # no candidate limit; more than 8 boxes per cell is outside the build
+    total, parts = YOLOLoss(S=14)(torch.zeros(1, 14, 14, 30, device=DEV), torch.zeros(1, 14, 14, 30, device=DEV))
+    assert float(total) == 0.0 and parts["conf_noobj"] == 0.0
     with pytest.raises(NotImplementedError):
-        YOLOLoss(S=14)(torch.zeros(1, 14, 14, 30, device=DEV), torch.zeros(1, 14, 14, 30, device=DEV))
+        YOLOLoss(B=9)(torch.zeros(1, 7, 7, 65, device=DEV), torch.zeros(1, 7, 7, 65, device=DEV))
 
 
 # ------------------------------------------------------------------ decode + NMS
