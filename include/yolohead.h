@@ -75,6 +75,20 @@ int yh_loss_fwd_bwd(const void *pred, int pred_dtype, const float *tgt, int N, i
  * *scale == 1, so the plain fp32 training path costs no extra traffic. */
 int yh_scale_inplace(void *grad, int dtype, size_t n_elems, const float *scale, void *stream);
 
+/* yh_loss_fwd_bwd without a caller-supplied workspace.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  The kernel's scratch (ticket word + per-CTA partial sums) is a 128 KiB
+ * file-scope device array (yh_loss_static_scratch_bytes()), held by every GPU that loads the library until the
+ * process exits.  Same arguments, results and error codes as yh_loss_fwd_bwd otherwise; a batch whose
+ * yh_loss_workspace_bytes(N, S, B, C) exceeds the array is rejected with YH_ERR_WORKSPACE (S=7, B=2, C=20:
+ * at most 10,678 images per call).  Allocates nothing, frees nothing, synchronises nothing.  All calls on a
+ * device share the array: calls ordered on one stream are independent (what must start at zero is cleared on
+ * the stream by every call), calls that OVERLAP on the GPU race on it and return wrong sums. */
+size_t yh_loss_static_scratch_bytes(void);
+int yh_loss_fwd_bwd_static(const void *pred, int pred_dtype, const float *tgt, int N, int S, int B, int C,
+                           float lambda_coord, float lambda_noobj, float *parts, void *grad_pred,
+                           void *stream);
+
 /* ------------------------------------------------------- decode + NMS ----
  * Replaces mAPMetric._parse_predictions + _apply_nms (metrics.py:173-218,
  * 258-296) and YOLOInference.parse_predictions + non_max_suppression

@@ -482,3 +482,67 @@ extern "C" int yh_scale_inplace(void *grad, int dtype, size_t n_elems, const flo
     }
     return check_launch("yh_scale_inplace");
 }
+
+// ------------------------------------------------------------------ yh_loss_fwd_bwd_static
+// The same loss forward + backward for callers that cannot allocate (code under CUDA-graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc): the scratch yh_loss_fwd_bwd takes from its caller -- the ticket word
+// and the per-CTA partial sums -- lives in a file-scope device array instead.  No counterpart in the
+// reference.
+//
+//   * kStaticScratchBytes = 128 KiB per GPU that loads the library, held until the process exits.  A call whose
+//     yh_loss_workspace_bytes(N, S, B, C) exceeds it is rejected (S=7, B=2, C=20: N <= 10,678 images).
+//   * In HOST code `g_loss_scratch` is a host-side stand-in, not a device address (a kernel handed it faults, or
+//     silently uses the wrong memory where the GPU can reach host memory).  The device address comes from
+//     cudaGetSymbolAddress, looked up once per device with that device current, return code checked.
+//   * Every call on a device shares the array, and it keeps the previous call's contents: the ticket word is cleared
+//     on the stream at the start of every call and every partial that is read has been written by the same call,
+//     so calls that follow each other on one stream (or are otherwise ordered) are independent.  Calls that
+//     OVERLAP on the GPU -- two streams, or a graph replay next to an eager call -- race on it and give wrong sums.
+//   * Calls no cudaMalloc / cudaFree / allocating library routine; enqueues on the caller's stream only.
+namespace yh {
+constexpr size_t kStaticScratchBytes = 128 * 1024;
+static __device__ __align__(256) unsigned char g_loss_scratch[kStaticScratchBytes];
+static std::atomic<void *> g_loss_scratch_ptr[kMaxDevices];   // device address of the array, per device
+}  // namespace yh
+
+extern "C" size_t yh_loss_static_scratch_bytes(void) { return kStaticScratchBytes; }
+
+extern "C" int yh_loss_fwd_bwd_static(const void *pred, int pred_dtype, const float *tgt, int N, int S, int B, int C,
+                                      float lambda_coord, float lambda_noobj, float *parts, void *grad_pred,
+                                      void *stream) {
+    if (N <= 0 || !pred || !tgt || !parts) {
+        set_error("yh_loss_fwd_bwd_static: bad argument (N=%d)", N);
+        return YH_ERR_BAD_ARG;
+    }
+    const size_t need = yh_loss_workspace_bytes(N, S, B, C);
+    if (need == 0) {
+        set_error("yh_loss_fwd_bwd_static: shape S=%d,B=%d,C=%d outside this build (B <= 8)", S, B, C);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (need > kStaticScratchBytes) {
+        set_error("yh_loss_fwd_bwd_static: N=%d images of %dx%d cells need %zu bytes of scratch, the built-in array holds "
+                  "%zu (S=7: at most 10,678 images per call); split the batch or call yh_loss_fwd_bwd with a workspace",
+                  N, S, S, need, kStaticScratchBytes);
+        return YH_ERR_WORKSPACE;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        set_error("yh_loss_fwd_bwd_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        cudaGetLastError();
+        return e != cudaSuccess ? (int)e : YH_ERR_UNSUPPORTED;
+    }
+    void *scratch = g_loss_scratch_ptr[dev].load(std::memory_order_acquire);
+    if (scratch == nullptr) {   // first call on this device: this device's copy of the symbol
+        e = cudaGetSymbolAddress(&scratch, g_loss_scratch);
+        if (e != cudaSuccess || scratch == nullptr) {
+            set_error("yh_loss_fwd_bwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+            return e != cudaSuccess ? (int)e : YH_ERR_UNSUPPORTED;
+        }
+        g_loss_scratch_ptr[dev].store(scratch, std::memory_order_release);
+    }
+    // the ticket word is cleared on the stream by yh_loss_fwd_bwd itself (cudaMemsetAsync, no allocation)
+    return yh_loss_fwd_bwd(pred, pred_dtype, tgt, N, S, B, C, lambda_coord, lambda_noobj, parts, grad_pred, scratch,
+                           kStaticScratchBytes, stream);
+}
