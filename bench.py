@@ -339,11 +339,13 @@ def main():
 
             for _ in range(max(args.warmup, 3)):
                 g_out = graph_step()
-            assert g_out == (loss_total, map5095), (g_out, loss_total, map5095)   # same bits as the eager step
+            # same mAP bits as the eager step; the captured step computes the loss inside the update kernel
+            # (CapturedHeadStep(fused=True): one read of the inputs), whose five sums are added in another order
+            assert g_out[1] == map5095 and abs(g_out[0] - loss_total) <= 2e-6 * abs(loss_total), (g_out, loss_total, map5095)
             with ClockSampler(local) as clk:
                 ms, (loss_total, map5095) = timed(graph_step, args.steps)
             launches = captured.launches_per_replay
-            step_launch = "cuda_graph (CapturedHeadStep)"
+            step_launch = "cuda_graph (CapturedHeadStep" + (", loss fused into the update kernel)" if captured.fused else ")")
         else:
             step_launch += f"; graph capture unavailable ({why or 'on another rank'})"
     value = world * n / (ms * 1e-3)
@@ -371,7 +373,7 @@ def main():
         if chk_step is not None:
             g_loss, g_res = chk_step.replay()
             check["agree"]["graph_vs_eager"] = bool(inner.result_digest() == check["sha256"] and
-                                                    float(g_loss["total"]) == chk_loss)
+                                                    abs(float(g_loss["total"]) - chk_loss) <= 2e-6 * abs(chk_loss))
             del chk_step
     if world > 1:   # rank 0 repeats the step alone on the concatenated images of all ranks
         allp = [torch.empty_like(chk_pred) for _ in range(world)] if rank == 0 else None
@@ -587,6 +589,13 @@ def main():
     stages["map_update"] = {"ms": t_upd, "bytes_per_image": upd_bytes, "kept_per_image": kbar, "gt_per_image": gbar,
                             "written_bytes_per_image": 8 + 17 * kbar,
                             "gbs": upd_bytes * n / (t_upd * 1e-3) / 1e9}
+    # the loss riding on the update kernel (what CapturedHeadStep replays): pred + tgt read once, gradient written
+    t_fused = time_call(lambda: head.map_update_loss(pred_d, tgt_d, args.conf, args.nms, thr, gt_count, 5.0, 0.5, True))
+    fused_bytes = 3 * IMG_BYTES + 128 + 24 * kbar
+    stages["map_update_loss_fused"] = {"ms": t_fused, "bytes_per_image": fused_bytes, "gbs": fused_bytes * n / (t_fused * 1e-3) / 1e9,
+                                       "what": "yh_map_update_loss: loss fwd+bwd inside the update kernel + object-cell kernel + fold; "
+                                               "replaces loss_fwd_bwd + map_update (their sum: "
+                                               f"{stages['loss_fwd_bwd']['ms'] + t_upd:.3f} ms)"}
     t_dec = time_call(lambda: head.decode_nms(pred_d, args.conf, args.nms, head.IOU_INFER, head.ORDER_GLOBAL_CONF,
                                               want_boxes=False))
     stages["decode_nms_infer"] = {"ms": t_dec, "bytes_per_image": IMG_BYTES + 128,

@@ -133,6 +133,21 @@ int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int 
                   int32_t *n_gt, uint8_t *gt_cell, uint8_t *gt_cls, float *gt_raw,
                   int32_t *gt_count, void *stream);
 
+/* yh_map_update with the loss riding on it (S=7, B=2, C=20, fp32 predictions): a validation or monitoring
+ * step that wants YOLOLoss.forward (+ backward) AND mAPMetric.update of the same batch (trainer.py:87,174 next to
+ * metrics.py:709) reads the two tensors once instead of twice.  While a prediction cell is staged for decoding its
+ * loss terms are computed (loss.py:98-159, the arithmetic of yh_loss_fwd_bwd) and the cell is replaced by
+ * d loss / d prediction, which leaves as the gradient tensor (grad_pred nullable = forward only).  parts[5] as
+ * yh_loss_fwd_bwd (device, already / N; summed in a fixed order, so repeatable).  Records / counts as
+ * yh_map_update, without its optional list outputs.  workspace: yh_map_update_loss_workspace_bytes(N),
+ * zero-filled before the first use (the call leaves it ready for the next one), 256-byte aligned. */
+size_t yh_map_update_loss_workspace_bytes(int N);
+int yh_map_update_loss(const float *pred, const float *tgt, int N, int S, int B, int C, double conf_thr,
+                       double nms_thr, const double *thresholds_host, int T, int32_t *n_keep,
+                       uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k, int32_t *n_gt,
+                       int32_t *gt_count, float lambda_coord, float lambda_noobj, float *parts,
+                       float *grad_pred, void *workspace, size_t workspace_bytes, void *stream);
+
 /* The reference keeps its state as two Python lists (metrics.py:70-71, 99-100).
  * yh_list_form expands the records of yh_map_update into that form on demand:
  *   rec_pos[n*K+q]       position of record q in all_predictions[n] (class groups in

@@ -94,6 +94,33 @@ def test_loss_half_precision_predictions(golden, dt, name):
     assert err < 5 * tol
 
 
+@pytest.mark.parametrize("case", LOSS_CASES)
+def test_update_with_loss_matches_reference_golden_and_the_two_separate_kernels(golden, case):
+    """yh_map_update_loss: the loss rides on the update kernel.  Loss parts vs the reference's (rtol 1e-5), gradient
+    bit-identical to the stand-alone loss kernel's (same per-cell arithmetic), records identical to yh_map_update's."""
+    g = golden("loss")
+    pred, tgt = torch.from_numpy(g[f"{case}/pred"]).to(DEV), torch.from_numpy(g[f"{case}/tgt"]).to(DEV)
+    m = mAPMetric(num_classes=20, conf_threshold=0.05)
+    parts, grad = m.update_with_loss(pred, tgt, YOLOLoss())
+    np.testing.assert_allclose(parts.cpu().numpy().astype(np.float64), g[f"{case}/parts"], rtol=1e-5, atol=1e-9)
+    ref = g[f"{case}/grad"]
+    np.testing.assert_allclose(grad.cpu().numpy(), ref, rtol=1e-5, atol=1e-7 * max(1.0, np.abs(ref).max()))
+    p2 = pred.clone().requires_grad_(True)
+    total, _ = YOLOLoss()(p2, tgt)
+    total.backward()
+    assert torch.equal(grad, p2.grad)
+    m2 = mAPMetric(num_classes=20, conf_threshold=0.05)
+    m2.update(pred, tgt)
+    a, b = m._chunks[0], m2._chunks[0]
+    assert torch.equal(a.n_keep, b.n_keep) and torch.equal(a.n_gt, b.n_gt) and torch.equal(m._gt_count, m2._gt_count)
+    live = (torch.arange(98, device=DEV)[None, :] < a.n_keep[:, None])
+    for x, y in ((a.rec_key, b.rec_key), (a.rec_flags, b.rec_flags), (a.rec_k, b.rec_k)):
+        assert torch.equal(x[live], y[live])
+    assert m.compute() == m2.compute()
+    fwd_parts, none = mAPMetric(num_classes=20).update_with_loss(pred, tgt, YOLOLoss(), backward=False)
+    assert none is None and torch.equal(fwd_parts, parts)          # forward only: same sums, repeatable
+
+
 def test_loss_rejects_cpu_and_bad_shapes():
     crit = YOLOLoss()
     with pytest.raises(RuntimeError):

@@ -22,8 +22,9 @@ def _eager(pred, tgt, conf):
     return parts, {k: float(v) for k, v in m.compute().items()}, p.grad
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("profile,conf", [("correlated", 0.01), ("uniform", 0.3)])
-def test_replay_equals_eager_and_follows_new_data(profile, conf):
+def test_replay_equals_eager_and_follows_new_data(profile, conf, fused):
     from yolo_v1_b200 import CapturedHeadStep, YOLOLoss, mAPMetric, synth
 
     dev = torch.device("cuda")
@@ -33,14 +34,21 @@ def test_replay_equals_eager_and_follows_new_data(profile, conf):
         t = synth.make_targets(n, seed=seed, p_obj=0.055, size_mix=True)
         sets.append((synth.make_preds(n, profile, seed=seed, targets=t).to(dev), t.to(dev)))
     pred, tgt = sets[0][0].clone(), sets[0][1].clone()
-    step = CapturedHeadStep(YOLOLoss(), mAPMetric(num_classes=20, conf_threshold=conf), pred, tgt)
-    assert step.launches_per_replay >= 10
+    step = CapturedHeadStep(YOLOLoss(), mAPMetric(num_classes=20, conf_threshold=conf), pred, tgt, fused=fused)
+    assert step.launches_per_replay >= 10 and step.fused == fused
     for p_new, t_new in sets + sets[:1]:
         pred.copy_(p_new)
         tgt.copy_(t_new)
         loss, res = step.replay()
         want_loss, want_res, want_grad = _eager(p_new, t_new, conf)
-        assert loss == want_loss
+        if fused:
+            # the loss rides on the update kernel: the same per-cell arithmetic (the gradient is bit-identical),
+            # the five sums are added up in a different order than the stand-alone loss kernel's
+            assert loss.keys() == want_loss.keys()
+            for k in loss:
+                assert loss[k] == pytest.approx(want_loss[k], rel=2e-6, abs=1e-9), k
+        else:
+            assert loss == want_loss
         assert {k: float(v) for k, v in res.items()} == want_res
         assert torch.equal(step.grad, want_grad)
 
@@ -51,10 +59,13 @@ def test_forward_only_capture():
     dev = torch.device("cuda")
     t = synth.make_targets(300, seed=9, p_obj=0.055, size_mix=True)
     p = synth.make_preds(300, "correlated", seed=9, targets=t).to(dev)
-    step = CapturedHeadStep(YOLOLoss(), mAPMetric(num_classes=20), p, t.to(dev), backward=False)
-    loss, res = step.replay()
-    want_loss, want_res, _ = _eager(p, t.to(dev), 0.01)
-    assert loss == want_loss and {k: float(v) for k, v in res.items()} == want_res and step.grad is None
+    for fused in (True, False):
+        step = CapturedHeadStep(YOLOLoss(), mAPMetric(num_classes=20), p, t.to(dev), backward=False, fused=fused)
+        loss, res = step.replay()
+        want_loss, want_res, _ = _eager(p, t.to(dev), 0.01)
+        assert all(loss[k] == pytest.approx(want_loss[k], rel=2e-6, abs=1e-9) for k in want_loss)
+        assert fused or loss == want_loss
+        assert {k: float(v) for k, v in res.items()} == want_res and step.grad is None
 
 
 # ----------------------------------------------------------------------------- two ranks, peer exchange in the graph

@@ -174,10 +174,16 @@ __device__ __forceinline__ unsigned spread16(unsigned x) {
 // tgt_img / tconf0 / tconf1 (optional): the target image and the slot-0 confidences of this
 // lane's two target cells; object cells get their lines prefetched towards L2 between the
 // two halves, a good while before the caller parses them.
+// hook.after_half(w, cs, lane, cell, live, c): called once per half after the lane's cell has been decoded and
+// before the buffer is staged again -- the fused loss of map_update.cu works on the staged cell there.
+struct NoHalfHook {
+    __device__ __forceinline__ void after_half(WarpWindow &, int, int, int, bool, float *) {}
+};
+template <class Hook>
 __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__restrict__ img, int lane,
                                                 double conf_thr, bool *bad, ImageFilter &filt,
-                                                const float *__restrict__ tgt_img = nullptr,
-                                                float tconf0 = 0.f, float tconf1 = 0.f) {
+                                                const float *__restrict__ tgt_img, float tconf0, float tconf1,
+                                                Hook &hook) {
     const float *st = reinterpret_cast<const float *>(w.stage);
     Mask128 valid = {0, 0, 0, 0};
     bool any_bad = false;
@@ -186,6 +192,17 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
 #pragma unroll 1
     for (int cs = 0; cs < 2; ++cs) {
         stage_half(w, img, cs, lane);
+        if (cs == 0 && tgt_img != nullptr) {
+            // the staging loads have landed, so the target confidences issued before them have too: pull the object
+            // cells of BOTH halves towards L2 now, a decode (or more) ahead of whoever parses them
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                if (lane + 32 * h < kCells && (h ? tconf1 : tconf0) > 0.f) {
+                    const float *tc = tgt_img + (lane + 32 * h) * kD;  // 120 B: may straddle two lines
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(tc));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(tc + kD - 1));
+                }
+        }
         const int cell = lane + 32 * cs;
         const bool live = cell < kCells;
         const float *c = st + (live ? lane : 0) * kD;
@@ -227,15 +244,7 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
         const unsigned m0 = __ballot_sync(kFull, ok[0]), m1 = __ballot_sync(kFull, ok[1]);
         valid.set_word(2 * cs, spread16(m0 & 0xffffu) | (spread16(m1 & 0xffffu) << 1));
         valid.set_word(2 * cs + 1, spread16(m0 >> 16) | (spread16(m1 >> 16) << 1));
-        if (cs == 0 && tgt_img != nullptr) {
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-                if (lane + 32 * h < kCells && (h ? tconf1 : tconf0) > 0.f) {
-                    const float *c = tgt_img + (lane + 32 * h) * kD;  // 120 B: may straddle two lines
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(c));
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(c + kD - 1));
-                }
-        }
+        hook.after_half(w, cs, lane, cell, live, const_cast<float *>(c));
     }
     if (bad != nullptr) *bad = any_bad;
     // image-wide magnitude bound: non-negative floats (and NaN, whose pattern is the largest) order like
@@ -246,6 +255,13 @@ __device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__re
     filt.E = filter_margin(M);
     __syncwarp();
     return valid;
+}
+__device__ __forceinline__ Mask128 decode_image(WarpWindow &w, const float *__restrict__ img, int lane,
+                                                double conf_thr, bool *bad, ImageFilter &filt,
+                                                const float *__restrict__ tgt_img = nullptr,
+                                                float tconf0 = 0.f, float tconf1 = 0.f) {
+    NoHalfHook none;
+    return decode_image(w, img, lane, conf_thr, bad, filt, tgt_img, tconf0, tconf1, none);
 }
 
 }  // namespace yh

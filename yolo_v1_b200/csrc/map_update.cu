@@ -166,6 +166,295 @@ static __device__ __noinline__ int match_exact(const MatchOverlay &mo, const flo
     return bg;
 }
 
+// ------------------------------------------------------------------ fused loss (yh_map_update_loss)
+// A validation / monitoring step wants the loss AND the metric of the same predictions; run separately the two
+// kernels read the prediction and target tensors twice (loss.cu: 17,640 B per image on its own).  Here the loss
+// rides on the update kernel: while a lane has its prediction cell staged in shared memory (decode_image's
+// per-half hook) it adds the cell's no-object term and overwrites the cell with d loss / d prediction; the warp
+// then stores the staged half as the gradient, coalesced, before the buffer is staged again.
+// OBJECT cells (about 2.7 of an image's 49) are not handled there: their arithmetic (IoU of both boxes, square
+// roots, the gradient through the IoU) is ~800 instructions that would sit in the middle of a kernel already at
+// the edge of the instruction cache -- measured: 0.51 ms against 0.30 ms, `no_instruction` the top stall.  A second,
+// small kernel (loss_object_cells, one thread per object cell) takes them from a 49-bit mask per image that the hook
+// leaves behind, does loss.cu's arithmetic operator for operator (loss.py:98-159 in fp32, gradient through the IoU,
+// torch's maximum / minimum / clamp conventions) and overwrites their 30 gradient values.  loss_rows_fold adds the
+// per-image no-object sums and the object-cell sums up in a fixed order (deterministic) and applies the lambdas and
+// 1 / N (loss.py:162-170).
+struct LossArgs {
+    float lambda_coord, lambda_noobj, inv_n;
+    float2 *grad;        // (N, 7, 7, 30) fp32 as float2, nullable (forward only)
+    float *noobj;        // [N] per image: sum of squared confidences over its no-object cells (raw)
+    uint4 *objmask;      // [N] per image: bits 0..48 of (x, y) = cell holds an object; of (z, w) = its target box is in slot 1
+    double *obj_sums;    // [ceil(N / kObjImages)][4] raw sums (coord, conf_obj, conf_noobj, class) of the object cells
+};
+constexpr int kObjImages = 256;   // images per CTA of loss_object_cells
+
+__device__ __forceinline__ float lt_max(float a, float b) { return (a > b || a != a) ? a : b; }   // torch.maximum
+__device__ __forceinline__ float lt_min(float a, float b) { return (a < b || a != a) ? a : b; }
+__device__ __forceinline__ float lt_relu(float v) { return (v < 0.f) ? 0.f : v; }
+__device__ __forceinline__ float lt_max_mask(float self, float other) { return (self < other) ? 0.f : ((self == other) ? 0.5f : 1.f); }
+__device__ __forceinline__ float lt_min_mask(float self, float other) { return (self > other) ? 0.f : ((self == other) ? 0.5f : 1.f); }
+
+struct LtIou {
+    float iou, inter, U, iw, ih, rawx, rawy, px1, px2, py1, py2;
+};
+__device__ __forceinline__ LtIou lt_iou(float x, float y, float w, float h, float tx1, float tx2, float ty1, float ty2,
+                                        float tarea) {   // loss.py:191-212
+    LtIou c;
+    const float hw = w * 0.5f, hh = h * 0.5f;
+    c.px1 = x - hw; c.px2 = x + hw;
+    c.py1 = y - hh; c.py2 = y + hh;
+    c.rawx = lt_min(c.px2, tx2) - lt_max(c.px1, tx1);
+    c.rawy = lt_min(c.py2, ty2) - lt_max(c.py1, ty1);
+    c.iw = lt_relu(c.rawx);
+    c.ih = lt_relu(c.rawy);
+    c.inter = c.iw * c.ih;
+    c.U = ((w * h + tarea) - c.inter) + 1e-6f;
+    c.iou = c.inter / c.U;
+    return c;
+}
+
+// An object cell (rare: about one in eighteen): the full loss.cu arithmetic on the staged prediction cell `p`
+// (overwritten with the gradient when want_grad) against the target cell `t` in global memory.
+static __device__ __noinline__ void loss_object_cell(float *p, const float *__restrict__ t, int slot, float lc, float ln,
+                                                     float inv_n, bool want_grad, float &a_coord, float &a_obj,
+                                                     float &a_noobj, float &a_cls) {
+    const float tx = __ldg(t + slot * 5), ty = __ldg(t + slot * 5 + 1), tw = __ldg(t + slot * 5 + 2), th = __ldg(t + slot * 5 + 3);
+    const float thw = tw * 0.5f, thh = th * 0.5f;
+    const float tx1 = tx - thw, tx2 = tx + thw, ty1 = ty - thh, ty2 = ty + thh, tarea = tw * th;
+    const LtIou c0 = lt_iou(p[0], p[1], p[2], p[3], tx1, tx2, ty1, ty2, tarea);
+    const LtIou c1 = lt_iou(p[5], p[6], p[7], p[8], tx1, tx2, ty1, ty2, tarea);
+    const bool pick1 = (c1.iou > c0.iou) || (c1.iou != c1.iou && c0.iou == c0.iou);   // first maximum, NaN maximal
+    const LtIou c = pick1 ? c1 : c0;
+    const float x = pick1 ? p[5] : p[0], y = pick1 ? p[6] : p[1], w = pick1 ? p[7] : p[2], h = pick1 ? p[8] : p[3];
+    const float cf = pick1 ? p[9] : p[4], co = pick1 ? p[4] : p[9];
+    const float dx = x - tx, dy = y - ty;
+    const float wc = lt_max(w, 1e-6f), hc = lt_max(h, 1e-6f);
+    const float sw = sqrtf(wc), sh = sqrtf(hc);
+    const float dw = sw - sqrtf(lt_max(tw, 1e-6f)), dh = sh - sqrtf(lt_max(th, 1e-6f));
+    a_coord += (dx * dx + dy * dy) + (dw * dw + dh * dh);
+    const float dc = cf - c.iou;
+    a_obj += dc * dc;
+    a_noobj += co * co;
+    float cs = 0.f;
+    {   // the 20 class targets as ten 8-byte loads, all in flight before the first use; summed in class order
+        float2 tv[kC / 2];
+#pragma unroll
+        for (int i = 0; i < kC / 2; ++i) tv[i] = __ldg(reinterpret_cast<const float2 *>(t + kB * 5) + i);
+#pragma unroll
+        for (int i = 0; i < kC / 2; ++i) {
+            float2 *pp = reinterpret_cast<float2 *>(p + kB * 5) + i;
+            const float2 pv = *pp;
+            const float d0 = pv.x - tv[i].x, d1 = pv.y - tv[i].y;
+            cs += d0 * d0;
+            cs += d1 * d1;
+            if (want_grad) *pp = make_float2(inv_n * (2.f * d0), inv_n * (2.f * d1));
+        }
+    }
+    a_cls += cs;
+    if (!want_grad) return;
+    const float gc = inv_n * lc, gn = inv_n * ln;
+    const float g_other = gn * (2.f * co), g_resp = inv_n * (2.f * dc);
+    float gx = gc * (2.f * dx), gy = gc * (2.f * dy);
+    float gw = (w >= 1e-6f) ? (gc * (2.f * dw)) / (2.f * sw) : 0.f;
+    float gh = (h >= 1e-6f) ? (gc * (2.f * dh)) / (2.f * sh) : 0.f;
+    const float gi = -(inv_n * (2.f * dc));
+    const float g_union = -gi * c.inter / (c.U * c.U);
+    const float g_inter = gi / c.U - g_union;
+    gw += g_union * h;
+    gh += g_union * w;
+    const float g_rawx = (c.rawx >= 0.f) ? g_inter * c.ih : 0.f;
+    const float g_rawy = (c.rawy >= 0.f) ? g_inter * c.iw : 0.f;
+    const float gpx2 = g_rawx * lt_min_mask(c.px2, tx2), gpx1 = -g_rawx * lt_max_mask(c.px1, tx1);
+    const float gpy2 = g_rawy * lt_min_mask(c.py2, ty2), gpy1 = -g_rawy * lt_max_mask(c.py1, ty1);
+    gx += gpx1 + gpx2;
+    gy += gpy1 + gpy2;
+    gw += (gpx2 - gpx1) * 0.5f;
+    gh += (gpy2 - gpy1) * 0.5f;
+    p[0] = pick1 ? 0.f : gx; p[1] = pick1 ? 0.f : gy; p[2] = pick1 ? 0.f : gw; p[3] = pick1 ? 0.f : gh;
+    p[4] = pick1 ? g_other : g_resp;
+    p[5] = pick1 ? gx : 0.f; p[6] = pick1 ? gy : 0.f; p[7] = pick1 ? gw : 0.f; p[8] = pick1 ? gh : 0.f;
+    p[9] = pick1 ? g_resp : g_other;
+}
+
+struct LossHalfHook {
+    LossArgs la;
+    float2 *gimg;           // this image's gradient (nullable)
+    float tconf0, tconf1;   // slot-0 target confidences of cells lane / lane + 32
+    float tsec0, tsec1;     // slot-1 confidences of the same cells (loaded up front: no global load in the decode chain)
+    float a_noobj;          // the lane's running sum of no-object confidences squared
+    unsigned obj_lo, obj_hi, s1_lo, s1_hi;   // the image's object-cell mask and slot-1 mask (warp-uniform)
+
+    __device__ __forceinline__ void after_half(WarpWindow &w, int cs, int lane, int cell, bool live, float *c) {
+        const bool want_grad = gimg != nullptr;
+        {
+            const bool h0 = (cs ? tconf1 : tconf0) > 0.f, h1 = (cs ? tsec1 : tsec0) > 0.f;
+            const unsigned ob = __ballot_sync(kFull, live && (h0 || h1)), s1 = __ballot_sync(kFull, live && !h0 && h1);
+            if (cs) { obj_hi = ob; s1_hi = s1; } else { obj_lo = ob; s1_lo = s1; }
+        }
+        if (live) {
+            const bool has0 = (cs ? tconf1 : tconf0) > 0.f, has1 = (cs ? tsec1 : tsec0) > 0.f;   // loss.py:98-99: any slot
+            // every cell gets the no-object treatment here (both confidences are "noobj" terms, loss.py:150-153, and
+            // nothing else has a gradient); object cells are left out of the sum and their gradient cell is
+            // overwritten by loss_object_cells afterwards
+            const float2 q2 = *reinterpret_cast<const float2 *>(c + 4), q4 = *reinterpret_cast<const float2 *>(c + 8);
+            const float c0 = q2.x, c1 = q4.y;
+            if (!(has0 || has1)) a_noobj += c0 * c0 + c1 * c1;
+            if (want_grad) {
+                const float gn = la.inv_n * la.lambda_noobj;
+                float2 *c2 = reinterpret_cast<float2 *>(c);
+                const float2 z = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int i = 0; i < kD / 2; ++i) c2[i] = z;
+                c2[2] = make_float2(gn * (2.f * c0), 0.f);
+                c2[4] = make_float2(0.f, gn * (2.f * c1));
+            }
+        }
+        if (want_grad) {
+            // the staged half now holds the gradient of its cells: store it, coalesced, before the next staging
+            __syncwarp();
+            const int count = cs ? (kStagePairs - kHalfPairs) : kHalfPairs;
+            float2 *dst = gimg + cs * kHalfPairs;
+#pragma unroll
+            for (int i = 0; i < kHalfPairs / 32; ++i) {
+                const int q = lane + 32 * i;
+                if (q < count) dst[q] = w.stage[q];
+            }
+        }
+    }
+};
+
+// The object cells (loss.py:98-104: a cell with any slot filled) of kObjImages images per CTA, ONE THREAD PER OBJECT
+// CELL: the update kernel's hook left a 49-bit mask per image, from which the CTA builds the list of its object
+// cells in (image, cell) order (a prefix sum over the per-image counts); thread t then takes entries t, t + 256, ...
+// -- copies the prediction cell from global memory, runs it through loss_object_cell, and replaces the 30 gradient
+// values the hook stored for the cell.  A lane per object inside a warp per image measured 0.12 ms (a warp ran the
+// ~800 instructions for one or two active lanes); compacted, the same work is ~20 x fewer warp instructions.
+// Sums: per thread in entry order, then a fixed tree over the CTA, in doubles -> obj_sums[cta] (deterministic).
+__global__ void __launch_bounds__(256)
+loss_object_cells(const float *__restrict__ pred, const float *__restrict__ tgt, int N, const LossArgs la) {
+    __shared__ unsigned short s_list[kObjImages * kCells];   // (image in CTA) << 7 | slot << 6 | cell
+    __shared__ int s_warp[8];
+    __shared__ double s_sum[256][4];
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const int img = blockIdx.x * kObjImages + tid;
+    uint4 m = make_uint4(0u, 0u, 0u, 0u);
+    if (img < N) m = la.objmask[img];
+    const int cnt = __popc(m.x) + __popc(m.y);
+    int inc = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(kFull, inc, off);
+        if (lane >= off) inc += v;
+    }
+    if (lane == 31) s_warp[wp] = inc;
+    __syncthreads();
+    int base = inc - cnt, total = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        if (q < wp) base += s_warp[q];
+        total += s_warp[q];
+    }
+    for (unsigned long long bits = ((unsigned long long)m.y << 32) | m.x, s1 = ((unsigned long long)m.w << 32) | m.z; bits;
+         bits &= bits - 1) {
+        const int cell = __ffsll((long long)bits) - 1;
+        s_list[base++] = (unsigned short)((tid << 7) | ((int)((s1 >> cell) & 1ull) << 6) | cell);
+    }
+    __syncthreads();
+    const bool want_grad = la.grad != nullptr;
+    float a_coord = 0.f, a_obj = 0.f, a_noobj = 0.f, a_cls = 0.f;
+    double d[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 1
+    for (int e = tid; e < total; e += 256) {
+        const int ent = s_list[e], cell = ent & 63, slot = (ent >> 6) & 1;
+        const size_t im = (size_t)blockIdx.x * kObjImages + (ent >> 7);
+        const float *t = tgt + im * kImgFloats + cell * kD;
+        float p[kD];
+        const float2 *src = reinterpret_cast<const float2 *>(pred + im * kImgFloats + cell * kD);
+#pragma unroll
+        for (int i = 0; i < kD / 2; ++i) {
+            const float2 v = __ldg(src + i);
+            p[2 * i] = v.x;
+            p[2 * i + 1] = v.y;
+        }
+        a_coord = a_obj = a_noobj = a_cls = 0.f;
+        loss_object_cell(p, t, slot, la.lambda_coord, la.lambda_noobj, la.inv_n, want_grad, a_coord, a_obj, a_noobj, a_cls);
+        d[0] += (double)a_coord; d[1] += (double)a_obj; d[2] += (double)a_noobj; d[3] += (double)a_cls;
+        if (want_grad) {
+            float2 *dst = la.grad + im * kStagePairs + cell * (kD / 2);
+#pragma unroll
+            for (int i = 0; i < kD / 2; ++i) dst[i] = make_float2(p[2 * i], p[2 * i + 1]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s_sum[tid][k] = d[k];
+    __syncthreads();
+    for (int st = 128; st > 0; st >>= 1) {
+        if (tid < st)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_sum[tid][k] += s_sum[tid + st][k];
+        __syncthreads();
+    }
+    if (tid < 4) la.obj_sums[(size_t)blockIdx.x * 4 + tid] = s_sum[0][tid];
+}
+
+// noobj[N] + obj_sums[n_obj_ctas][4] -> the five loss values, summed in a fixed order: CTA b adds a contiguous slice
+// of the per-image no-object sums (doubles); the last CTA to finish adds the CTA sums and the object-cell sums in a
+// fixed order (strided per thread, then a tree) and applies the lambdas and 1 / N.
+constexpr int kFoldThreads = 256;
+__global__ void __launch_bounds__(kFoldThreads)
+loss_rows_fold(const float *__restrict__ noobj, int N, const double *__restrict__ obj_sums, int n_obj_ctas,
+               float lambda_coord, float lambda_noobj, float inv_n, double *__restrict__ partials,
+               unsigned *__restrict__ ticket, float *__restrict__ parts) {
+    __shared__ double s_sum[kFoldThreads][4];
+    __shared__ bool s_last;
+    const int tid = threadIdx.x;
+    const int per = (N + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int lo = min(N, (int)blockIdx.x * per), hi = min(N, lo + per);
+    double a = 0.0;
+    for (int i = lo + tid; i < hi; i += kFoldThreads) a += (double)__ldcg(noobj + i);   // written just before
+    s_sum[tid][0] = a;
+    __syncthreads();
+    for (int st = kFoldThreads / 2; st > 0; st >>= 1) {
+        if (tid < st) s_sum[tid][0] += s_sum[tid + st][0];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        partials[blockIdx.x] = s_sum[0][0];
+        __threadfence();
+        s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double t[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int b = tid; b < n_obj_ctas; b += kFoldThreads)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) t[k] += __ldcg(obj_sums + (size_t)b * 4 + k);
+    for (int b = tid; b < (int)gridDim.x; b += kFoldThreads) t[2] += __ldcg(partials + b);
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s_sum[tid][k] = t[k];
+    __syncthreads();
+    for (int st = kFoldThreads / 2; st > 0; st >>= 1) {
+        if (tid < st)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_sum[tid][k] += s_sum[tid + st][k];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const double coord = (double)lambda_coord * s_sum[0][0], cobj = s_sum[0][1];
+        const double noobj_t = (double)lambda_noobj * s_sum[0][2], cls = s_sum[0][3], invn = (double)inv_n;
+        parts[0] = (float)((coord + cobj + noobj_t + cls) * invn);
+        parts[1] = (float)(coord * invn);
+        parts[2] = (float)(cobj * invn);
+        parts[3] = (float)(noobj_t * invn);
+        parts[4] = (float)(cls * invn);
+        *ticket = 0u;   // ready for the next call
+    }
+}
+
+template <bool LOSS>
 __global__ void __launch_bounds__(kWarpsPerCtaM * 32, kCtasPerSmM)
 map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt, int N,
                   double conf_thr, double nms_thr, const __grid_constant__ Thresholds thr,
@@ -173,7 +462,7 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
                   uint64_t *__restrict__ rec_flags, uint8_t *__restrict__ rec_k,
                   uint64_t *__restrict__ rec_box, int32_t *__restrict__ n_gt, uint8_t *__restrict__ gt_cell,
                   uint8_t *__restrict__ gt_cls, float4 *__restrict__ gt_raw,
-                  int32_t *__restrict__ gt_count, unsigned *__restrict__ ticket) {
+                  int32_t *__restrict__ gt_count, unsigned *__restrict__ ticket, const LossArgs la) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WarpWindow *windows = reinterpret_cast<WarpWindow *>(smem_raw);
     __shared__ int gt_hist[4 * kC];
@@ -219,9 +508,34 @@ map_update_kernel(const float *__restrict__ pred, const float *__restrict__ tgt,
         // slot-0 confidence of my two target cells: in flight while the predictions are decoded
         const float tconf0 = __ldg(timg + lane * kD + 4);
         const float tconf1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 4);
+        float tsec0 = 0.f, tsec1 = 0.f;
+        if (LOSS) {   // the loss's object rule looks at every slot (loss.py:98-99)
+            tsec0 = __ldg(timg + lane * kD + 9);
+            tsec1 = __ldg(timg + (lane + 32 < kCells ? lane + 32 : lane) * kD + 9);
+        }
         // ---- predictions: decode, order, NMS
         ImageFilter filt;
-        const Mask128 valid = decode_image(w, pimg, lane, conf_thr, nullptr, filt, timg, tconf0, tconf1);
+        Mask128 valid;
+        if (LOSS) {
+            LossHalfHook hook;
+            hook.la = la;
+            hook.gimg = la.grad != nullptr ? la.grad + (size_t)img * kStagePairs : nullptr;
+            hook.tconf0 = tconf0;
+            hook.tconf1 = tconf1;
+            hook.tsec0 = tsec0;
+            hook.tsec1 = tsec1;
+            hook.a_noobj = 0.f;
+            hook.obj_lo = hook.obj_hi = hook.s1_lo = hook.s1_hi = 0u;
+            valid = decode_image(w, pimg, lane, conf_thr, nullptr, filt, timg, tconf0, tconf1, hook);
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) hook.a_noobj += __shfl_down_sync(kFull, hook.a_noobj, off);
+            if (lane == 0) {
+                la.noobj[img] = hook.a_noobj;
+                la.objmask[img] = make_uint4(hook.obj_lo, hook.obj_hi, hook.s1_lo, hook.s1_hi);
+            }
+        } else {
+            valid = decode_image(w, pimg, lane, conf_thr, nullptr, filt, timg, tconf0, tconf1);
+        }
         ImageFilter nfilt = filt;
         nfilt.ok = filt.ok && fp.thr_ok;
         int n;
@@ -500,17 +814,94 @@ extern "C" int yh_map_update(const float *pred, const float *tgt, int N, int S, 
     const size_t smem = sizeof(WarpWindow) * kWarpsPerCtaM;
     static std::atomic<bool> attr_done[kMaxDevices];
     if (first_use_on_device(attr_done)) {
-        cudaFuncSetAttribute(map_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(map_update_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     }
     int ctas = (N + kWarpsPerCtaM - 1) / kWarpsPerCtaM;
     const int cap = 148 * kCtasPerSmM;
     if (ctas > cap) ctas = cap;
     unsigned *ticket = fresh_ticket((cudaStream_t)stream);
     if (ticket == nullptr) return YH_ERR_UNSUPPORTED;
-    map_update_kernel<<<ctas, kWarpsPerCtaM * 32, smem, (cudaStream_t)stream>>>(
+    LossArgs la = {0.f, 0.f, 0.f, nullptr, nullptr, nullptr, nullptr};
+    map_update_kernel<false><<<ctas, kWarpsPerCtaM * 32, smem, (cudaStream_t)stream>>>(
         pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, (uint64_t *)rec_box, n_gt, gt_cell,
-        gt_cls, (float4 *)gt_raw, gt_count, ticket);
+        gt_cls, (float4 *)gt_raw, gt_count, ticket, la);
     return check_launch("yh_map_update");
+}
+
+constexpr int kFoldCtas = 64;
+static inline size_t mul_up256(size_t v) { return (v + 255) & ~(size_t)255; }
+// workspace: [fold ticket 256 B][fold partials][object-cell masks N x 16 B][no-object sums N x 4 B][object-cell CTA sums]
+extern "C" size_t yh_map_update_loss_workspace_bytes(int N) {
+    if (N < 0) return 0;
+    const size_t n_obj = ((size_t)N + kObjImages - 1) / kObjImages;
+    return 256 + mul_up256(sizeof(double) * kFoldCtas) + mul_up256(sizeof(uint4) * (size_t)N) +
+           mul_up256(sizeof(float) * (size_t)N) + mul_up256(sizeof(double) * 4 * n_obj);
+}
+
+extern "C" int yh_map_update_loss(const float *pred, const float *tgt, int N, int S, int B, int C,
+                                  double conf_thr, double nms_thr, const double *thresholds_host, int T,
+                                  int32_t *n_keep, uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k,
+                                  int32_t *n_gt, int32_t *gt_count, float lambda_coord, float lambda_noobj,
+                                  float *parts, float *grad_pred, void *workspace, size_t workspace_bytes,
+                                  void *stream) {
+    if (!shape_ok(S, B, C)) {
+        set_error("yh_map_update_loss: the fused loss is built for S=7,B=2,C=20 (got %d,%d,%d); call yh_loss_fwd_bwd and "
+                  "yh_map_update separately", S, B, C);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (T < 1 || T > YH_MAX_THRESHOLDS) {
+        set_error("yh_map_update_loss: T=%d thresholds; this build carries 1..%d", T, YH_MAX_THRESHOLDS);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (N <= 0 || !pred || !tgt || !thresholds_host || !n_keep || !rec_key || !rec_flags || !n_gt || !gt_count ||
+        !parts || !workspace) {
+        set_error("yh_map_update_loss: bad argument (N=%d)", N);
+        return YH_ERR_BAD_ARG;
+    }
+    if (((uintptr_t)pred % 8) || ((uintptr_t)tgt % 8) || ((uintptr_t)grad_pred % 8) || ((uintptr_t)workspace % 256)) {
+        set_error("yh_map_update_loss: pred / tgt / grad_pred must be 8-byte aligned (workspace: 256 B)");
+        return YH_ERR_ALIGNMENT;
+    }
+    if (workspace_bytes < yh_map_update_loss_workspace_bytes(N)) {
+        set_error("yh_map_update_loss: workspace too small");
+        return YH_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    Thresholds th;
+    th.n = T;
+    for (int i = 0; i < YH_MAX_THRESHOLDS; ++i) th.t[i] = i < T ? thresholds_host[i] : 2.0;
+    const size_t smem = sizeof(WarpWindow) * kWarpsPerCtaM;
+    static std::atomic<bool> attr_done[kMaxDevices];
+    if (first_use_on_device(attr_done))
+        cudaFuncSetAttribute(map_update_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int ctas = (N + kWarpsPerCtaM - 1) / kWarpsPerCtaM;
+    const int cap = 148 * kCtasPerSmM;
+    if (ctas > cap) ctas = cap;
+    unsigned *ticket = fresh_ticket(st);
+    if (ticket == nullptr) return YH_ERR_UNSUPPORTED;
+    char *ws = (char *)workspace;
+    unsigned *fold_ticket = (unsigned *)ws;                       // zero between calls (the fold resets it)
+    double *partials = (double *)(ws + 256);
+    char *q = ws + 256 + mul_up256(sizeof(double) * kFoldCtas);
+    const int n_obj = (N + kObjImages - 1) / kObjImages;
+    LossArgs la;
+    la.lambda_coord = lambda_coord;
+    la.lambda_noobj = lambda_noobj;
+    la.inv_n = 1.0f / (float)N;
+    la.grad = (float2 *)grad_pred;
+    la.objmask = (uint4 *)q;
+    q += mul_up256(sizeof(uint4) * (size_t)N);
+    la.noobj = (float *)q;
+    q += mul_up256(sizeof(float) * (size_t)N);
+    la.obj_sums = (double *)q;
+    map_update_kernel<true><<<ctas, kWarpsPerCtaM * 32, smem, st>>>(
+        pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, nullptr, n_gt, nullptr, nullptr, nullptr,
+        gt_count, ticket, la);
+    loss_object_cells<<<n_obj, 256, 0, st>>>(pred, tgt, N, la);   // after the update kernel: overwrites gradient cells
+    const int fold = N < 1024 * kFoldCtas ? (N + 1023) / 1024 : kFoldCtas;
+    loss_rows_fold<<<fold, kFoldThreads, 0, st>>>(la.noobj, N, la.obj_sums, n_obj, lambda_coord, lambda_noobj, la.inv_n, partials,
+                                                  fold_ticket, parts);
+    return check_launch("yh_map_update_loss", 3);
 }
 
 extern "C" int yh_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t *n_gt,

@@ -32,12 +32,20 @@ from .metrics import mAPMetric
 
 class CapturedHeadStep:
     def __init__(self, criterion: YOLOLoss, metric, predictions: torch.Tensor, targets: torch.Tensor,
-                 backward: bool = True, warmup: int = 2):
+                 backward: bool = True, warmup: int = 2, fused: bool | None = None):
         _lib.require_cuda(predictions, "predictions")
         _lib.require_cuda(targets, "targets")
         self.criterion, self.metric = criterion, metric
         self.predictions, self.targets = predictions, targets
         self.backward = backward
+        # fused: the loss rides on the update kernel (yh_map_update_loss: one read of the two tensors instead of two).
+        # Default: wherever that kernel exists (S=7, B=2, C=20, fp32 predictions).
+        inner = metric if isinstance(metric, mAPMetric) else metric.metric
+        can_fuse = ((inner.S, inner.B, inner.num_classes) == (7, 2, 20) and (criterion.S, criterion.B, criterion.C) == (7, 2, 20)
+                    and predictions.dtype is torch.float32)
+        if fused and not can_fuse:
+            raise _lib.YoloHeadError("CapturedHeadStep(fused=True) needs S=7, B=2, C=20 and fp32 predictions")
+        self.fused = can_fuse if fused is None else bool(fused)
         self.grad: Optional[torch.Tensor] = None        # d loss / d predictions after replay()
         self._dist = not isinstance(metric, mAPMetric)  # a DistributedMAP wrapping one
         if self._dist and metric.mode not in ("peer", "auto"):
@@ -94,6 +102,11 @@ class CapturedHeadStep:
         c = self.criterion
         dev = self.predictions.device
         main = torch.cuda.current_stream(dev)
+        if self.fused:
+            self.metric.reset()
+            parts, self.grad = self.metric.update_with_loss(self.predictions.detach(), self.targets, c, self.backward)
+            vec = self.metric.enqueue_peer(dev) if self._dist else self.metric._enqueue_reduce()
+            return torch.cat([vec, parts.to(torch.float64)])
         p = self.predictions.detach().requires_grad_(self.backward)
         self.metric.reset()
         self.metric.update(p.detach(), self.targets)

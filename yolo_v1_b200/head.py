@@ -128,6 +128,42 @@ def map_update(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: 
     return UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, rec_raw, n_gt, gt_cell, gt_cls, gt_raw, (S, B, Cn), src)
 
 
+_FUSED_WS = _lib.Workspace(zeroed=True)
+
+
+def map_update_loss(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: float, thresholds,
+                    gt_count: torch.Tensor, lambda_coord: float, lambda_noobj: float, want_grad: bool = True):
+    """yh_map_update_loss: the update kernel with the loss (forward + backward) riding on it; one read of the two
+    tensors.  S=7, B=2, C=20 and fp32 predictions.  Returns (chunk, parts (5,) fp32 device tensor, grad or None)."""
+    p = _check_pred(pred, "predictions", S_, B_, C_)
+    t = _check_pred(tgt, "targets", S_, B_, C_)
+    if p.shape != t.shape:
+        raise ValueError(f"predictions {tuple(p.shape)} and targets {tuple(t.shape)} differ in shape")
+    if p.shape[0] == 0:
+        raise ValueError("empty batch")
+    _, thr_c = _thr_array(thresholds)
+    N, K, dev = p.shape[0], S_ * S_ * B_, p.device
+    n_keep = torch.zeros(N, dtype=torch.int32, device=dev)
+    n_gt = torch.zeros(N, dtype=torch.int32, device=dev)
+    rec_key = torch.empty(N, K, dtype=torch.int64, device=dev)
+    rec_flags = torch.empty(N, K, dtype=torch.int64, device=dev)
+    rec_k = torch.empty(N, K, dtype=torch.uint8, device=dev)
+    parts = torch.empty(5, dtype=torch.float32, device=dev)
+    grad = torch.empty_like(p) if want_grad else None
+    lib = _lib.lib()
+    ws = _FUSED_WS.get(dev, int(lib.yh_map_update_loss_workspace_bytes(N)))
+    with _lib.on_device(dev):
+        rc = lib.yh_map_update_loss(p.data_ptr(), t.data_ptr(), N, S_, B_, C_, float(conf_thr), float(nms_thr), thr_c,
+                                    len(thr_c), n_keep.data_ptr(), rec_key.data_ptr(), rec_flags.data_ptr(),
+                                    rec_k.data_ptr(), n_gt.data_ptr(), gt_count.data_ptr(), float(lambda_coord),
+                                    float(lambda_noobj), parts.data_ptr(), _lib.ptr(grad), ws.data_ptr(), ws.numel(),
+                                    _lib.stream_ptr(dev))
+    _lib.check(rc, "yh_map_update_loss")
+    chunk = UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, None, n_gt, None, None, None, (S_, B_, C_),
+                        (p, t, p._version, t._version))
+    return chunk, parts, grad
+
+
 def parse_gt(tgt: torch.Tensor, S: int = S_, B: int = B_, Cn: int = C_):
     """yh_parse_gt over a batch: (n_gt int32 (N,), gt_cls uint8 (N,S*S), gt_box float64 (N,S*S,4))."""
     t = _check_pred(tgt, "targets", S, B, Cn)

@@ -199,6 +199,34 @@ class mAPMetric:
         if self._lists_live:
             self._materialise()
 
+    def update_with_loss(self, predictions: torch.Tensor, targets: torch.Tensor, criterion, backward: bool = True):
+        """Extension: update() and `criterion(predictions, targets)` (+ backward) of the same batch in ONE pass over
+        the two tensors (yh_map_update_loss) -- what a validation step that wants both the loss and the metric
+        does.  Returns (parts, grad): the five loss values as a (5,) fp32 device tensor in the order of the
+        reference's loss_dict (total, coord, conf_obj, conf_noobj, class; loss.py:164-170) and d total / d
+        predictions (None without `backward`).  Needs S=7, B=2, C=20, fp32 CUDA predictions; anything else raises
+        and the caller runs the two calls separately."""
+        if (self.S, self.B, self.num_classes) != (7, 2, 20) or (criterion.S, criterion.B, criterion.C) != (7, 2, 20):
+            raise NotImplementedError("update_with_loss: the fused kernel is built for S=7, B=2, C=20")
+        _lib.require_cuda(predictions, "predictions")
+        if predictions.dtype is not torch.float32:
+            raise NotImplementedError("update_with_loss: fp32 predictions only (the loss alone takes fp16 / bf16)")
+        dev = predictions.device
+        targets = targets.to(dev)
+        if self._gt_count is None or self._device != dev:
+            if self._chunks and self._device != dev:
+                self._materialise()
+                self._lists_live = True
+            self._gt_count = torch.zeros(4 * self.num_classes, dtype=torch.int32, device=dev)
+            self._device = dev
+        chunk, parts, grad = head.map_update_loss(predictions, targets, self.conf_threshold, self.nms_threshold,
+                                                  self.iou_thresholds, self._gt_count, criterion.lambda_coord,
+                                                  criterion.lambda_noobj, want_grad=backward)
+        self._chunks.append(chunk)
+        if self._lists_live:
+            self._materialise()
+        return parts, grad
+
     # ------------------------------------------------------------------ compute
     def compute(self) -> Dict[str, float]:
         """mAP50:95 / mAP50 / mAP75, per-class APs, overall precision / recall, size-bucketed mAPs."""
