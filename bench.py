@@ -633,7 +633,7 @@ def main():
 
     # dominant kernel = the longest single launch of the step (the sort's passes are ~0.07 ms each)
     dom = max(("loss_fwd_bwd", "map_update"), key=lambda k: stages[k]["ms"])
-    kernel_name = {"loss_fwd_bwd": "loss_kernel<float, 0>", "map_update": "map_update_kernel"}[dom]
+    kernel_name = {"loss_fwd_bwd": "loss_kernel<float, 0>", "map_update": "map_update_kernel<0>"}[dom]
     traffic = None
     try:  # DRAM bytes per launch from the committed ncu --set full capture of the same workload
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))

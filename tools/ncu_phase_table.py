@@ -57,11 +57,12 @@ if "map_update" in open(sys.argv[1]).read(4000):
     phases += [
         ("target parse", "map_update.cu", L(mu, "int parse_targets("), L(mu, "int match_exact(")),
         ("image loop head", "map_update.cu", L(mu, "for (int img = blockIdx.x"), L(mu, "// ---- targets: parse into the overlay")),
-        ("items", "map_update.cu", L(mu, "// ---- items:"), L(mu, "// ---- best ground truth and threshold mask")),
+        ("records + items", "map_update.cu", L(mu, "// ---- records, in sorted order among the kept"), L(mu, "// ---- IoU intervals of all")),
+        ("pair intervals", "map_update.cu", L(mu, "// ---- IoU intervals of all"), L(mu, "// ---- best ground truth and threshold mask")),
         ("best GT + masks", "map_update.cu", L(mu, "// ---- best ground truth and threshold mask"), L(mu, "// ---- greedy TP/FP")),
-        ("best GT: interval", "iou_filter.cuh", L(fi, "YH_HD int iou_interval("), 10 ** 6),
-        ("TP/FP", "map_update.cu", L(mu, "// ---- greedy TP/FP"), L(mu, "// ---- records, in sorted order")),
-        ("records + next ticket", "map_update.cu", L(mu, "// ---- records, in sorted order"), 10 ** 6),
+        ("interval arithmetic (pairs)", "iou_filter.cuh", L(fi, "YH_HD int iou_interval("), 10 ** 6),
+        ("TP/FP + patch records", "map_update.cu", L(mu, "// ---- greedy TP/FP"), L(mu, "// keep the (slow) ticket read down here")),
+        ("next ticket + tail", "map_update.cu", L(mu, "// keep the (slow) ticket read down here"), 10 ** 6),
     ]
 ts, tn, tw = (sum(v[j] for v in agg.values()) or 1 for j in (0, 1, 3))
 used = set()

@@ -68,8 +68,15 @@ def main():
     x = torch.randn(a.batch, 3, 448, 448, generator=g).to(dev).contiguous(memory_format=torch.channels_last)
     t = synth.make_targets(a.batch, seed=1234 + rank, p_obj=0.055, size_mix=True).to(dev)
 
-    def step(use_kernel):
+    import contextlib
+
+    def step(use_kernel, sync=True):
         opt.zero_grad(set_to_none=True)
+        ctx = model.no_sync() if (world > 1 and not sync) else contextlib.nullcontext()
+        with ctx:
+            return _step(use_kernel)
+
+    def _step(use_kernel):
         with torch.autocast("cuda", dtype=amp, enabled=amp is not None):
             pred = model(x)
             if use_kernel:
@@ -107,6 +114,10 @@ def main():
         step(False)
     full_ms, (loss, parts, pred) = timed(lambda: step(True), a.steps)
     bare_ms, _ = timed(lambda: step(False), a.steps)
+    nosync_ms = None
+    if world > 1:   # the same step without DDP's gradient all-reduce: the difference is what NCCL adds to the step
+        step(True, sync=False)
+        nosync_ms, _ = timed(lambda: step(True, sync=False), a.steps)
     head_out = pred.detach()
 
     def loss_only():
@@ -122,7 +133,10 @@ def main():
             "step_ms": full_ms, "images_per_s": world * a.batch / (full_ms * 1e-3),
             "step_ms_with_trivial_loss": bare_ms, "loss_share_of_step_ms": full_ms - bare_ms,
             "loss_fwd_bwd_alone_ms": lk_ms - clone_ms, "head_output_dtype": str(head_out.dtype),
-            "loss_total": float(parts["total"]),
+            "loss_total": float(parts["total"]), "n_gpus": world, "global_batch": world * a.batch,
+            "step_ms_without_gradient_allreduce": nosync_ms,
+            "exposed_allreduce_ms": (full_ms - nosync_ms) if nosync_ms is not None else None,
+            "gradient_bytes": sum(p.numel() * p.element_size() for p in model.parameters()),
         }))
     if world > 1:
         dist.destroy_process_group()

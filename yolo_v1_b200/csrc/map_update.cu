@@ -187,7 +187,7 @@ struct LossArgs {
     uint4 *objmask;      // [N] per image: bits 0..48 of (x, y) = cell holds an object; of (z, w) = its target box is in slot 1
     double *obj_sums;    // [ceil(N / kObjImages)][4] raw sums (coord, conf_obj, conf_noobj, class) of the object cells
 };
-constexpr int kObjImages = 256;   // images per CTA of loss_object_cells
+constexpr int kObjImages = 64;    // images per CTA of loss_object_cells: ~170 object cells, at most one per thread as a rule
 
 __device__ __forceinline__ float lt_max(float a, float b) { return (a > b || a != a) ? a : b; }   // torch.maximum
 __device__ __forceinline__ float lt_min(float a, float b) { return (a < b || a != a) ? a : b; }
@@ -339,7 +339,7 @@ loss_object_cells(const float *__restrict__ pred, const float *__restrict__ tgt,
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     const int img = blockIdx.x * kObjImages + tid;
     uint4 m = make_uint4(0u, 0u, 0u, 0u);
-    if (img < N) m = la.objmask[img];
+    if (tid < kObjImages && img < N) m = la.objmask[img];
     const int cnt = __popc(m.x) + __popc(m.y);
     int inc = cnt;
 #pragma unroll
