@@ -318,6 +318,7 @@ def main():
         ms, (loss_total, map5095) = timed(lambda: step(pred_d.detach(), tgt_d), args.steps)
     launches = (_lib.lib().yh_launch_count() - l0) // args.steps
     eager_ms, step_launch = ms, "eager (one Python call per stage)"
+    graph_serial = None
     # The same step captured once as a CUDA graph (yolo_v1_b200.CapturedHeadStep: same kernels, same
     # results, one launch + one read-back per step).  It is the `value` when it is available -- with
     # N > 1 that needs the peer-memory exchange -- and the eager figure stays in the line beside it.
@@ -326,7 +327,7 @@ def main():
 
         captured, why = None, ""
         try:
-            captured = CapturedHeadStep(crit, metric, pred_d, tgt_d)
+            captured = CapturedHeadStep(crit, metric, pred_d, tgt_d, pipelined=True)
         except Exception as e:  # noqa: BLE001 - the eager figure above stands, and says why
             why = f"{type(e).__name__}: {e}"
         ok = torch.tensor([1 if captured is not None else 0], device=dev)
@@ -342,10 +343,30 @@ def main():
             # same mAP bits as the eager step; the captured step computes the loss inside the update kernel
             # (CapturedHeadStep(fused=True): one read of the inputs), whose five sums are added in another order
             assert g_out[1] == map5095 and abs(g_out[0] - loss_total) <= 2e-6 * abs(loss_total), (g_out, loss_total, map5095)
+            serial_ms, serial_out = timed(graph_step, args.steps)     # submit, wait, decode -- one step at a time
+
+            def pipelined_steps(k):
+                """k steps, step i + 1 submitted before step i's results are decoded; EVERY step's loss and mAP are
+                read back (one step later than in the strict form)."""
+                out = None
+                captured.submit()
+                for i in range(k):
+                    if i + 1 < k:
+                        captured.submit()
+                    loss, res = captured.collect()
+                    out = (float(loss["total"]), float(res["mAP50:95"]))
+                return out
+
+            assert pipelined_steps(3) == serial_out
             with ClockSampler(local) as clk:
-                ms, (loss_total, map5095) = timed(graph_step, args.steps)
+                total_ms, (loss_total, map5095) = timed(lambda: pipelined_steps(args.steps), 1)
+            ms = total_ms / args.steps
+            graph_serial = {"ms_per_step": serial_ms, "value": world * n / (serial_ms * 1e-3),
+                            "what": "the same graph, strictly one step at a time: replay() = submit, wait, decode"}
             launches = captured.launches_per_replay
-            step_launch = "cuda_graph (CapturedHeadStep" + (", loss fused into the update kernel)" if captured.fused else ")")
+            step_launch = ("cuda_graph (CapturedHeadStep" + (", loss fused into the update kernel" if captured.fused else "") +
+                           "; two alternating graphs, step k+1 submitted before step k's results are decoded, every "
+                           "step's loss and mAP read back)")
         else:
             step_launch += f"; graph capture unavailable ({why or 'on another rank'})"
     value = world * n / (ms * 1e-3)
@@ -631,9 +652,15 @@ def main():
     t_cmp = time_call(lambda: head.compact_records(chunk))
     stages["compact_records"] = {"ms": t_cmp, "bytes": M * 32 + n * 4, "gbs": (M * 32 + n * 4) / (t_cmp * 1e-3) / 1e9}
 
-    # dominant kernel = the longest single launch of the step (the sort's passes are ~0.07 ms each)
-    dom = max(("loss_fwd_bwd", "map_update"), key=lambda k: stages[k]["ms"])
-    kernel_name = {"loss_fwd_bwd": "loss_kernel<float, 0>", "map_update": "map_update_kernel<0>"}[dom]
+    # dominant kernel = the longest single launch of the step `value` times (the sort's passes are ~0.05 ms each): with the
+    # captured step the loss rides on the update kernel, otherwise the update kernel or the loss kernel
+    fused_step = step_launch.startswith("cuda_graph") and "fused" in step_launch
+    if fused_step:
+        dom = "map_update_loss_fused"
+    else:
+        dom = max(("loss_fwd_bwd", "map_update"), key=lambda k: stages[k]["ms"])
+    kernel_name = {"loss_fwd_bwd": "loss_kernel<float, 0>", "map_update": "map_update_kernel<0>",
+                   "map_update_loss_fused": "map_update_kernel<1>"}[dom]
     traffic = None
     try:  # DRAM bytes per launch from the committed ncu --set full capture of the same workload
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
@@ -641,14 +668,21 @@ def main():
             traffic = tj["kernels"].get(kernel_name)
     except Exception:
         pass
-    step_kernel_ms = stages["loss_fwd_bwd"]["ms"] + stages["map_update"]["ms"] + stages["compact_records"]["ms"] + \
-        stages["ap_reduce"]["ms"]
+    if fused_step:
+        step_kernel_ms = stages["map_update_loss_fused"]["ms"] + stages["compact_records"]["ms"] + stages["ap_reduce"]["ms"]
+    else:
+        step_kernel_ms = stages["loss_fwd_bwd"]["ms"] + stages["map_update"]["ms"] + stages["compact_records"]["ms"] + \
+            stages["ap_reduce"]["ms"]
     roof = {"bound": "hbm", "kernel": kernel_name,
             "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": stages[dom]["gbs"] / peak,
             "traffic": traffic, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": stages[dom]["bytes_per_image"] * n,
             "algorithmic_bytes": "SURVEY.md 8(d): 11,888 B per image + 24 B per kept detection (map_update); "
-                                 "17,640 B per image (loss fwd+bwd); 6,008 B per image (decode + NMS)",
+                                 "17,640 B per image (loss fwd+bwd); 6,008 B per image (decode + NMS); the fused loss + "
+                                 "update kernel: pred + tgt read once + gradient written + 128 B + 24 B per kept = "
+                                 "17,768 B per image + 24 B per kept",
+            "launch_includes": ("map_update_kernel<1> + loss_object_cells + loss_rows_fold (timed together; traffic is "
+                                "map_update_kernel<1> alone)") if fused_step else None,
             "launch_ms": stages[dom]["ms"], "share_of_step_kernel_time": stages[dom]["ms"] / step_kernel_ms,
             "all": {k: {"gbs": v.get("gbs"), "frac": (v["gbs"] / peak) if v.get("gbs") else None, "ms": v["ms"]}
                     for k, v in stages.items()}}
@@ -686,6 +720,7 @@ def main():
         }
         line["step_launch"] = step_launch
         line["eager"] = {"value": world * n / (eager_ms * 1e-3), "ms_per_step": eager_ms}
+        line["graph_serial"] = graph_serial
         if world > 1:
             line["exchange"] = {"mode": metric.mode, "overflow_fallbacks": metric.peer_fallbacks}
         print(json.dumps(line))

@@ -140,13 +140,17 @@ int yh_map_update(const float *pred, const float *tgt, int N, int S, int B, int 
  * d loss / d prediction, which leaves as the gradient tensor (grad_pred nullable = forward only).  parts[5] as
  * yh_loss_fwd_bwd (device, already / N; summed in a fixed order, so repeatable).  Records / counts as
  * yh_map_update, without its optional list outputs.  workspace: yh_map_update_loss_workspace_bytes(N),
- * zero-filled before the first use (the call leaves it ready for the next one), 256-byte aligned. */
+ * zero-filled before the first use (the call leaves it ready for the next one), 256-byte aligned.
+ * phases: 3 = everything on `stream`; 1 = the update kernel only (records, counts, gradient of the no-object
+ * cells); 2 = the loss tail only (object cells -> their gradient cells, then parts[5]) -- a caller that wants the
+ * record pipeline (compaction, exchange, sort) to start right behind the update kernel issues phase 2 with the same
+ * arguments on another stream, ordered after phase 1 by an event. */
 size_t yh_map_update_loss_workspace_bytes(int N);
 int yh_map_update_loss(const float *pred, const float *tgt, int N, int S, int B, int C, double conf_thr,
                        double nms_thr, const double *thresholds_host, int T, int32_t *n_keep,
                        uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k, int32_t *n_gt,
                        int32_t *gt_count, float lambda_coord, float lambda_noobj, float *parts,
-                       float *grad_pred, void *workspace, size_t workspace_bytes, void *stream);
+                       float *grad_pred, void *workspace, size_t workspace_bytes, int phases, void *stream);
 
 /* The reference keeps its state as two Python lists (metrics.py:70-71, 99-100).
  * yh_list_form expands the records of yh_map_update into that form on demand:

@@ -36,7 +36,7 @@ SIGNATURES = {
     "yh_map_update": (_i, [_vp, _vp, _i, _i, _i, _i, _d, _d, _vp, _i] + [_vp] * 11),
     "yh_map_update_loss_workspace_bytes": (_sz, [_i]),
     "yh_map_update_loss": (_i, [_vp, _vp, _i, _i, _i, _i, _d, _d, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp,
-                                _vp, _sz, _vp]),
+                                _vp, _sz, _i, _vp]),
     "yh_list_form": (_i, [_vp] * 8 + [_i, _i, _i, _i] + [_vp] * 4),
     "yh_parse_gt": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "yh_compact_workspace_bytes": (_sz, [_i]),

@@ -843,7 +843,11 @@ extern "C" int yh_map_update_loss(const float *pred, const float *tgt, int N, in
                                   int32_t *n_keep, uint64_t *rec_key, uint64_t *rec_flags, uint8_t *rec_k,
                                   int32_t *n_gt, int32_t *gt_count, float lambda_coord, float lambda_noobj,
                                   float *parts, float *grad_pred, void *workspace, size_t workspace_bytes,
-                                  void *stream) {
+                                  int phases, void *stream) {
+    if (phases < 1 || phases > 3) {
+        set_error("yh_map_update_loss: phases must be 1 (update kernel), 2 (loss tail) or 3 (both), got %d", phases);
+        return YH_ERR_BAD_ARG;
+    }
     if (!shape_ok(S, B, C)) {
         set_error("yh_map_update_loss: the fused loss is built for S=7,B=2,C=20 (got %d,%d,%d); call yh_loss_fwd_bwd and "
                   "yh_map_update separately", S, B, C);
@@ -877,8 +881,11 @@ extern "C" int yh_map_update_loss(const float *pred, const float *tgt, int N, in
     int ctas = (N + kWarpsPerCtaM - 1) / kWarpsPerCtaM;
     const int cap = 148 * kCtasPerSmM;
     if (ctas > cap) ctas = cap;
-    unsigned *ticket = fresh_ticket(st);
-    if (ticket == nullptr) return YH_ERR_UNSUPPORTED;
+    unsigned *ticket = nullptr;
+    if (phases & 1) {
+        ticket = fresh_ticket(st);
+        if (ticket == nullptr) return YH_ERR_UNSUPPORTED;
+    }
     char *ws = (char *)workspace;
     unsigned *fold_ticket = (unsigned *)ws;                       // zero between calls (the fold resets it)
     double *partials = (double *)(ws + 256);
@@ -894,14 +901,21 @@ extern "C" int yh_map_update_loss(const float *pred, const float *tgt, int N, in
     la.noobj = (float *)q;
     q += mul_up256(sizeof(float) * (size_t)N);
     la.obj_sums = (double *)q;
-    map_update_kernel<true><<<ctas, kWarpsPerCtaM * 32, smem, st>>>(
-        pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, nullptr, n_gt, nullptr, nullptr, nullptr,
-        gt_count, ticket, la);
-    loss_object_cells<<<n_obj, 256, 0, st>>>(pred, tgt, N, la);   // after the update kernel: overwrites gradient cells
-    const int fold = N < 1024 * kFoldCtas ? (N + 1023) / 1024 : kFoldCtas;
-    loss_rows_fold<<<fold, kFoldThreads, 0, st>>>(la.noobj, N, la.obj_sums, n_obj, lambda_coord, lambda_noobj, la.inv_n, partials,
-                                                  fold_ticket, parts);
-    return check_launch("yh_map_update_loss", 3);
+    int launches = 0;
+    if (phases & 1) {
+        map_update_kernel<true><<<ctas, kWarpsPerCtaM * 32, smem, st>>>(
+            pred, tgt, N, conf_thr, nms_thr, th, n_keep, rec_key, rec_flags, rec_k, nullptr, n_gt, nullptr, nullptr, nullptr,
+            gt_count, ticket, la);
+        ++launches;
+    }
+    if (phases & 2) {   // after the update kernel (stream order, or the caller's event): overwrites gradient cells
+        loss_object_cells<<<n_obj, 256, 0, st>>>(pred, tgt, N, la);
+        const int fold = N < 1024 * kFoldCtas ? (N + 1023) / 1024 : kFoldCtas;
+        loss_rows_fold<<<fold, kFoldThreads, 0, st>>>(la.noobj, N, la.obj_sums, n_obj, lambda_coord, lambda_noobj, la.inv_n,
+                                                      partials, fold_ticket, parts);
+        launches += 2;
+    }
+    return check_launch("yh_map_update_loss", launches);
 }
 
 extern "C" int yh_parse_gt(const float *tgt, int N, int S, int B, int C, int32_t *n_gt,

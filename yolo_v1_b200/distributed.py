@@ -343,8 +343,9 @@ class DistributedMAP:
     def update(self, predictions: torch.Tensor, targets: torch.Tensor):
         self.metric.update(predictions, targets)
 
-    def update_with_loss(self, predictions: torch.Tensor, targets: torch.Tensor, criterion, backward: bool = True):
-        return self.metric.update_with_loss(predictions, targets, criterion, backward)
+    def update_with_loss(self, predictions: torch.Tensor, targets: torch.Tensor, criterion, backward: bool = True,
+                         tail_stream=None):
+        return self.metric.update_with_loss(predictions, targets, criterion, backward, tail_stream)
 
     def _local_records(self, dev):
         """(key, flags, capacity, count) of this rank: all batches compacted into one buffer behind

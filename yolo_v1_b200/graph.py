@@ -32,7 +32,7 @@ from .metrics import mAPMetric
 
 class CapturedHeadStep:
     def __init__(self, criterion: YOLOLoss, metric, predictions: torch.Tensor, targets: torch.Tensor,
-                 backward: bool = True, warmup: int = 2, fused: bool | None = None):
+                 backward: bool = True, warmup: int = 2, fused: bool | None = None, pipelined: bool = False):
         _lib.require_cuda(predictions, "predictions")
         _lib.require_cuda(targets, "targets")
         self.criterion, self.metric = criterion, metric
@@ -52,7 +52,13 @@ class CapturedHeadStep:
             raise _lib.YoloHeadError("CapturedHeadStep needs the peer-memory exchange (mode 'peer' or 'auto'): the "
                                      "NCCL exchange reads its split sizes on the host")
         self.recaptures = 0
-        self._host: Optional[torch.Tensor] = None       # pinned landing buffer of the packed results
+        # pipelined: TWO graphs of the same step (own record / result buffers each) replayed in turn, so that
+        # submit() can queue step k + 1 before collect() has decoded step k: the GPU never waits for Python between
+        # steps.  Both run on the same private streams, hence strictly one after the other on the device.
+        self._slots = 2 if pipelined else 1
+        self._queue: list = []                          # submitted, not yet collected slots (oldest first)
+        self._next = 0
+        self._host: Optional[torch.Tensor] = None       # pinned landing buffer of the packed results (eager runs)
         dev = predictions.device
         # Two branches: the metric chain is captured on a high-priority stream, the loss on a normal
         # one.  The loss kernel's 25,088 short CTAs would otherwise sit in front of every kernel of
@@ -78,16 +84,26 @@ class CapturedHeadStep:
 
     def _capture(self):
         lib = _lib.lib()
-        self.graph = torch.cuda.CUDAGraph()
-        before = lib.yh_launch_count()
-        # every workspace handed out during the capture has its address baked into the graph: hold them
+        # every workspace handed out during a capture has its address baked into the graph: hold them
         # (the caches in _lib.Workspace are per stream, and these two streams are private to this object,
         # so nothing else regrows them; the references make that independent of the caches' lifetime)
         self._held: list = []
-        with _lib.Workspace.holding(self._held), torch.cuda.graph(self.graph, stream=self._main):
-            self._out = self._enqueue()
-            self._host.copy_(self._out, non_blocking=True)   # the read-back is a node of the graph too
-        self.launches_per_replay = int(lib.yh_launch_count() - before)   # this library's kernels in the graph
+        self._graphs, self._outs, self._hosts, self._grads, self._done = [], [], [], [], []
+        for _ in range(self._slots):
+            graph = torch.cuda.CUDAGraph()
+            host = torch.empty(self._host.numel(), dtype=torch.float64, pin_memory=True)
+            before = lib.yh_launch_count()
+            with _lib.Workspace.holding(self._held), torch.cuda.graph(graph, stream=self._main):
+                out = self._enqueue()
+                host.copy_(out, non_blocking=True)   # the read-back is a node of the graph too
+            self.launches_per_replay = int(lib.yh_launch_count() - before)   # this library's kernels in one graph
+            self._graphs.append(graph)
+            self._outs.append(out)
+            self._hosts.append(host)
+            self._grads.append(self.grad)
+            self._done.append(torch.cuda.Event())
+        self.graph = self._graphs[0]
+        self._queue, self._next = [], 0
 
     # ---------------------------------------------------------------- the step, enqueue only
     def _inner(self) -> mAPMetric:
@@ -103,9 +119,13 @@ class CapturedHeadStep:
         dev = self.predictions.device
         main = torch.cuda.current_stream(dev)
         if self.fused:
+            # the loss rides on the update kernel; its tail (object cells, fold) is forked to the side stream so that
+            # compaction / exchange / sort start right behind the update kernel
             self.metric.reset()
-            parts, self.grad = self.metric.update_with_loss(self.predictions.detach(), self.targets, c, self.backward)
+            parts, self.grad = self.metric.update_with_loss(self.predictions.detach(), self.targets, c, self.backward,
+                                                            tail_stream=self._side)
             vec = self.metric.enqueue_peer(dev) if self._dist else self.metric._enqueue_reduce()
+            main.wait_stream(self._side)                 # join
             return torch.cat([vec, parts.to(torch.float64)])
         p = self.predictions.detach().requires_grad_(self.backward)
         self.metric.reset()
@@ -140,19 +160,47 @@ class CapturedHeadStep:
         return loss, res
 
     # ---------------------------------------------------------------- public
-    def replay(self) -> Tuple[Dict[str, float], Dict[str, float]]:
-        """Run the captured step on whatever `predictions` / `targets` hold now.
-        Returns (loss_dict, metric results), as criterion(...)[1] and metric.compute() would."""
-        self.graph.replay()
-        torch.cuda.current_stream(self.predictions.device).synchronize()
-        loss, res = self._decode(self._host)
+    def submit(self) -> None:
+        """Queue one step on whatever `predictions` / `targets` hold when the GPU gets to it (stream order: data
+        written into them on the current stream before this call is what the step sees).  Returns at once."""
+        if len(self._queue) >= self._slots:
+            raise _lib.YoloHeadError(f"CapturedHeadStep: {len(self._queue)} step(s) in flight and not collected; "
+                                     "call collect() first" + ("" if self._slots > 1 else " (or pipelined=True)"))
+        i = self._next
+        self._next = (i + 1) % self._slots
+        self._graphs[i].replay()
+        self._done[i].record(torch.cuda.current_stream(self.predictions.device))
+        self._queue.append(i)
+
+    def collect(self) -> Tuple[Dict[str, float], Dict[str, float]]:
+        """Wait for the oldest submitted step and return its (loss_dict, metric results), as criterion(...)[1] and
+        metric.compute() would.  `grad` is then that step's d loss / d predictions."""
+        if not self._queue:
+            raise _lib.YoloHeadError("CapturedHeadStep.collect(): nothing was submitted")
+        i = self._queue.pop(0)
+        self._done[i].synchronize()
+        self.grad = self._grads[i]
+        loss, res = self._decode(self._hosts[i])
         if res is None:
-            # A skewed class mix overflowed the peer receive blocks (every rank sees it, nothing was
-            # moved).  The metric's chunks are the graph's own tensors, so the eager compute() sees this
-            # step's data: it takes the NCCL exchange and re-creates larger blocks (collective), and the
-            # step is captured again against them.
-            res = self.metric.compute()
-            torch.cuda.synchronize(self.predictions.device)
+            # A skewed class mix overflowed the peer receive blocks (every rank sees it, nothing was moved).  Drain
+            # what is in flight, redo the step eagerly on the tensors' current contents -- the eager compute() takes
+            # the NCCL exchange and re-creates larger blocks (collective) -- and capture again against them.
+            while self._queue:
+                self._done[self._queue.pop(0)].synchronize()
+            dev = self.predictions.device
+            self._main.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(self._main):
+                loss, res = self._eager()
+            torch.cuda.current_stream(dev).wait_stream(self._main)
+            torch.cuda.synchronize(dev)
             self._capture()
             self.recaptures += 1
         return loss, res
+
+    def replay(self) -> Tuple[Dict[str, float], Dict[str, float]]:
+        """Run the captured step on whatever `predictions` / `targets` hold now and wait for it:
+        submit() + collect().  Returns (loss_dict, metric results)."""
+        if self._queue:
+            raise _lib.YoloHeadError("CapturedHeadStep.replay(): steps submitted earlier are still uncollected")
+        self.submit()
+        return self.collect()

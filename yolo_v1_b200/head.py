@@ -132,9 +132,13 @@ _FUSED_WS = _lib.Workspace(zeroed=True)
 
 
 def map_update_loss(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: float, thresholds,
-                    gt_count: torch.Tensor, lambda_coord: float, lambda_noobj: float, want_grad: bool = True):
+                    gt_count: torch.Tensor, lambda_coord: float, lambda_noobj: float, want_grad: bool = True,
+                    tail_stream: "torch.cuda.Stream | None" = None):
     """yh_map_update_loss: the update kernel with the loss (forward + backward) riding on it; one read of the two
-    tensors.  S=7, B=2, C=20 and fp32 predictions.  Returns (chunk, parts (5,) fp32 device tensor, grad or None)."""
+    tensors.  S=7, B=2, C=20 and fp32 predictions.  Returns (chunk, parts (5,) fp32 device tensor, grad or None).
+    tail_stream: run the loss tail (object cells, fold) there, forked behind the update kernel, so that whatever the
+    caller enqueues next on the current stream (compaction, exchange, sort) starts right away; `parts` and the object
+    cells of `grad` are then ready on tail_stream, which the caller joins."""
     p = _check_pred(pred, "predictions", S_, B_, C_)
     t = _check_pred(tgt, "targets", S_, B_, C_)
     if p.shape != t.shape:
@@ -152,13 +156,22 @@ def map_update_loss(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_
     grad = torch.empty_like(p) if want_grad else None
     lib = _lib.lib()
     ws = _FUSED_WS.get(dev, int(lib.yh_map_update_loss_workspace_bytes(N)))
-    with _lib.on_device(dev):
+
+    def call(phases, stream_handle):
         rc = lib.yh_map_update_loss(p.data_ptr(), t.data_ptr(), N, S_, B_, C_, float(conf_thr), float(nms_thr), thr_c,
                                     len(thr_c), n_keep.data_ptr(), rec_key.data_ptr(), rec_flags.data_ptr(),
                                     rec_k.data_ptr(), n_gt.data_ptr(), gt_count.data_ptr(), float(lambda_coord),
                                     float(lambda_noobj), parts.data_ptr(), _lib.ptr(grad), ws.data_ptr(), ws.numel(),
-                                    _lib.stream_ptr(dev))
-    _lib.check(rc, "yh_map_update_loss")
+                                    phases, stream_handle)
+        _lib.check(rc, "yh_map_update_loss")
+
+    with _lib.on_device(dev):
+        if tail_stream is None:
+            call(3, _lib.stream_ptr(dev))
+        else:
+            call(1, _lib.stream_ptr(dev))
+            tail_stream.wait_stream(torch.cuda.current_stream(dev))
+            call(2, tail_stream.cuda_stream)
     chunk = UpdateChunk(N, n_keep, rec_key, rec_flags, rec_k, None, n_gt, None, None, None, (S_, B_, C_),
                         (p, t, p._version, t._version))
     return chunk, parts, grad

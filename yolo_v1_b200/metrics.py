@@ -199,13 +199,14 @@ class mAPMetric:
         if self._lists_live:
             self._materialise()
 
-    def update_with_loss(self, predictions: torch.Tensor, targets: torch.Tensor, criterion, backward: bool = True):
+    def update_with_loss(self, predictions: torch.Tensor, targets: torch.Tensor, criterion, backward: bool = True,
+                         tail_stream=None):
         """Extension: update() and `criterion(predictions, targets)` (+ backward) of the same batch in ONE pass over
         the two tensors (yh_map_update_loss) -- what a validation step that wants both the loss and the metric
         does.  Returns (parts, grad): the five loss values as a (5,) fp32 device tensor in the order of the
         reference's loss_dict (total, coord, conf_obj, conf_noobj, class; loss.py:164-170) and d total / d
         predictions (None without `backward`).  Needs S=7, B=2, C=20, fp32 CUDA predictions; anything else raises
-        and the caller runs the two calls separately."""
+        and the caller runs the two calls separately.  tail_stream: see head.map_update_loss."""
         if (self.S, self.B, self.num_classes) != (7, 2, 20) or (criterion.S, criterion.B, criterion.C) != (7, 2, 20):
             raise NotImplementedError("update_with_loss: the fused kernel is built for S=7, B=2, C=20")
         _lib.require_cuda(predictions, "predictions")
@@ -221,7 +222,7 @@ class mAPMetric:
             self._device = dev
         chunk, parts, grad = head.map_update_loss(predictions, targets, self.conf_threshold, self.nms_threshold,
                                                   self.iou_thresholds, self._gt_count, criterion.lambda_coord,
-                                                  criterion.lambda_noobj, want_grad=backward)
+                                                  criterion.lambda_noobj, want_grad=backward, tail_stream=tail_stream)
         self._chunks.append(chunk)
         if self._lists_live:
             self._materialise()
