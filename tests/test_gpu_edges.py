@@ -394,18 +394,32 @@ def test_concurrent_streams_do_not_share_scratch():
             assert torch.equal(a_parts, b_parts) and torch.equal(a_packed, b_packed)
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
-def test_one_process_two_devices():
+def test_one_process_every_visible_device():
     """The ticket array is a __device__ symbol with one address per device, and kernel attributes are per
-    device: a process that uses cuda:0 and then cuda:1 must get the same answer on both."""
+    device: a process that uses cuda:0, then cuda:1, then cuda:0 again must get the same answer everywhere
+    (also the static-scratch loss, whose array address is looked up per device).  On a one-GPU box the three
+    passes all run on cuda:0 -- still a repeatability check; the two-device form ran on a 2-GPU box in round 2."""
+    from yolo_v1_b200 import _lib
+
+    last = torch.cuda.device_count() - 1
+    devices = ["cuda:0", f"cuda:{min(1, last)}", "cuda:0"]
     tgt = synth.make_targets(3000, seed=21, p_obj=0.055, size_mix=True)
     pred = synth.make_preds(3000, "correlated", seed=21, targets=tgt)
     res = []
-    for d in ("cuda:0", "cuda:1", "cuda:0"):
+    for d in devices:
         m = mAPMetric(num_classes=20, conf_threshold=0.05)
         m.update(pred.to(d), tgt.to(d))
         res.append(m.compute())
         r = head.decode_nms(pred.to(d), 0.3, 0.4, head.IOU_INFER, head.ORDER_GLOBAL_CONF, want_boxes=False)
-        res.append(r.keep_k.cpu())
-    assert res[0] == res[2] == res[4]
-    assert torch.equal(res[1], res[3]) and torch.equal(res[1], res[5])
+        live = torch.arange(98, device=d)[None, :] < r.n_keep[:, None]      # entries past n_keep are uninitialised
+        res.append(torch.where(live, r.keep_k, torch.zeros_like(r.keep_k)).cpu())
+        p_d, t_d = pred.to(d), tgt.to(d)
+        parts = torch.empty(5, dtype=torch.float32, device=d)
+        with torch.cuda.device(d):
+            rc = _lib.lib().yh_loss_fwd_bwd_static(p_d.data_ptr(), 0, t_d.data_ptr(), 3000, 7, 2, 20, 5.0, 0.5,
+                                                   parts.data_ptr(), None, _lib.stream_ptr(torch.device(d)))
+        assert rc == 0
+        res.append(parts.cpu())
+    assert res[0] == res[3] == res[6]
+    assert torch.equal(res[1], res[4]) and torch.equal(res[1], res[7])
+    assert torch.equal(res[2], res[5]) and torch.equal(res[2], res[8])
