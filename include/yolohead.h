@@ -332,6 +332,29 @@ int yh_match_lists(const int64_t *det_off, const int32_t *det_cls, const double 
                    uint64_t *rec_key, uint64_t *rec_flags, int32_t *gt_count, int max_dets,
                    void *stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * The head's last layer fused with the loss.  Replaces, for S=7, B=2, C=20, in_features=4096 and
+ * fp16 / bf16 operands (what autocast makes of the layer: src/yolo/training/trainer.py:70, 165):
+ *     x = nn.Linear(4096, S*S*(B*5+C))(x); x = x.view(-1, S, S, B*5+C)      src/yolo/models.py:326-331, 345-348
+ *     loss, loss_dict = YOLOLoss(...)(x, targets); d loss / d x               src/yolo/loss.py:55-172 + autograd
+ * by ONE tcgen05 / TMEM / TMA kernel whose epilogue evaluates the loss on the accumulator tile: the [M, 1470]
+ * prediction tensor is not written to memory unless pred_out asks for it.
+ *   x [M, 4096], weight [1470, 4096] (nn.Linear's own layout), both `dtype` (YH_F16 / YH_BF16), 16-byte aligned;
+ *   bias [1470] fp32 or NULL; tgt [M, 7, 7, 30] fp32, or NULL = plain Linear (pred_out required, parts / grad unused);
+ *   round_pred != 0: the prediction is rounded to `dtype` before the loss sees it, as the autocast Linear's output is;
+ *   parts[5] fp32 = total, coord, conf_obj, conf_noobj, class (loss.py:164-170);
+ *   grad [M, 1470] = grad_scale * d total / d prediction in `grad_dtype` (= dtype, or YH_F32), or NULL -- grad_scale is
+ *   the GradScaler factor: fp16 cannot hold 2 d / M for a large M;
+ *   pred_out [M, 1470] fp32 or NULL (feeds yh_map_update / yh_decode_nms directly).
+ * The caller finishes the layer's backward with two library GEMMs (d x = grad @ weight, d weight = grad^T @ x).
+ * Accumulation is fp32; the loss arithmetic is yh_loss_fwd_bwd's on the same predictions, bit for bit; the five sums are
+ * folded in a fixed order for a given GPU (one partial per SM).  Other shapes / dtypes: YH_ERR_UNSUPPORTED. */
+size_t yh_head_linear_loss_workspace_bytes(void);
+int yh_head_linear_loss(const void *x, const void *weight, const float *bias, int dtype, const float *tgt, int M,
+                        int S, int B, int C, int in_features, float lambda_coord, float lambda_noobj,
+                        float grad_scale, int round_pred, float *parts, void *grad, int grad_dtype,
+                        float *pred_out, void *workspace, size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

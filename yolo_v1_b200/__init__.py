@@ -6,6 +6,7 @@ hand-written CUDA kernels behind a C ABI (include/yolohead.h, libyolohead.so).
 The conv backbone stays stock PyTorch/cuDNN and is not part of this package.
 """
 from .graph import CapturedHeadStep
+from .head_linear import FusedHeadLoss, head_linear
 from .inference import YOLOInference
 from .loss import YOLOLoss
 from .metrics import evaluate_model, mAPMetric
@@ -15,5 +16,5 @@ from .targets import encode_target, encode_targets, encode_targets_csr
 
 __version__ = "0.1.0"
 
-__all__ = ["BoundingBox", "CapturedHeadStep", "Detection", "YOLOInference", "YOLOLoss", "encode_target", "encode_targets",
-           "encode_targets_csr", "evaluate_model", "format_evaluation_report", "mAPMetric", "write_results_file"]
+__all__ = ["BoundingBox", "CapturedHeadStep", "Detection", "FusedHeadLoss", "YOLOInference", "YOLOLoss", "encode_target", "encode_targets",
+           "encode_targets_csr", "evaluate_model", "format_evaluation_report", "head_linear", "mAPMetric", "write_results_file"]

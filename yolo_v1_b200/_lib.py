@@ -32,6 +32,8 @@ SIGNATURES = {
     "yh_scale_inplace": (_i, [_vp, _i, _sz, _vp, _vp]),
     "yh_loss_static_scratch_bytes": (_sz, []),
     "yh_loss_fwd_bwd_static": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
+    "yh_head_linear_loss_workspace_bytes": (_sz, []),
+    "yh_head_linear_loss": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _f, _f, _i, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
     "yh_decode_nms": (_i, [_vp, _i, _i, _i, _i, _d, _d, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "yh_map_update": (_i, [_vp, _vp, _i, _i, _i, _i, _d, _d, _vp, _i] + [_vp] * 11),
     "yh_map_update_loss_workspace_bytes": (_sz, [_i]),

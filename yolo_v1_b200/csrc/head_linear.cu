@@ -1,0 +1,560 @@
+// head_linear.cu -- the detection head's last Linear(4096 -> S*S*(B*5+C)) + view, fused with the YOLOv1 loss
+// forward + backward (sm_100a: tcgen05.mma with TMEM accumulators, operands brought in by TMA).
+//
+// Replaces, for S=7, B=2, C=20 and fp16 / bf16 operands (what `autocast("cuda")` makes of the layer,
+// reference src/yolo/training/trainer.py:70, 165):
+//     x = self.fc_layers[-1](x); x = x.view(-1, S, S, B*5 + C)          (src/yolo/models.py:326-331, 345-348)
+//     loss, loss_dict = criterion(x, targets); loss.backward() as far as d loss / d x   (src/yolo/loss.py:55-172)
+// in ONE kernel: the [M, 1470] prediction tensor never goes to HBM (optionally it is also written out, for the
+// metric).  SURVEY 8(f) row 4.
+//
+// Shape of the kernel (one persistent CTA per SM, 192 threads, roles per warp):
+//   warp 0      TMA producer: A = activations [M, 4096] and B = weight [1470, 4096], both K-major, 128-byte
+//               swizzled boxes of 64 K-elements into a 4-stage shared-memory ring (mbarrier full / empty).
+//   warp 1      allocates TMEM; one elected thread issues tcgen05.mma (M=128, N=224, K=16 per instruction) into
+//               one of two 224-column fp32 accumulators, committing each stage back to the producer and the
+//               finished accumulator to the epilogue.
+//   warps 2-5   epilogue: a thread owns one image row of the 128 x 224 tile.  An N tile is 210 useful columns =
+//               7 whole cells (7 tiles x 7 cells = 49 cells); the thread reads a cell's 30 accumulators with one
+//               tcgen05.ld, adds the bias, evaluates the cell's loss terms and gradient in registers (the same
+//               arithmetic as loss.cu), writes the 30 gradient values and adds to its running sums.  The MMA
+//               of the next tile runs meanwhile in the other accumulator.
+// Tiles: (m_blk, n_blk) = (t / 7, t % 7), t = blockIdx.x + i * gridDim.x -- the 7 N tiles of an M block run at the
+// same time on neighbouring SMs and share its A tile in L2; the weight (12 MB) stays L2-resident.
+//
+// Roofline: tensor.  Useful flops 2 * M * 4096 * 1470; issued 2 * M * 4096 * 1568 (224 / 210: 14 columns of the
+// next cell are computed and dropped so that cells never straddle tiles).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace yh {
+namespace hl {
+
+constexpr int kK = 4096;              // in_features
+constexpr int kNOut = kCells * kD;    // 1470 out_features
+constexpr int kBM = 128, kBN = 224, kBK = 64;
+constexpr int kCellsPerTile = 7;      // 210 useful columns
+constexpr int kNUse = kCellsPerTile * kD;
+constexpr int kNTiles = kCells / kCellsPerTile;  // 7
+constexpr int kStages = 4;
+constexpr int kKBlocks = kK / kBK;    // 64
+constexpr int kABytes = kBM * kBK * 2, kBBytes = kBN * kBK * 2;   // 16,384 + 28,672
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kAccStride = 256;       // TMEM columns between the two accumulators
+constexpr int kTmemCols = 512;
+constexpr int kThreads = 192;
+constexpr int kEpiWarps = 4;
+static_assert(kNTiles * kCellsPerTile == kCells, "cells per tile");
+
+struct Smem {
+    alignas(1024) unsigned char tiles[kStages][kStageBytes];
+    alignas(8) unsigned long long full[kStages], empty[kStages], acc_full[2], acc_empty[2];
+    unsigned tmem_base;
+    float bias[kNTiles * kBN];        // bias of every N tile, padded to 224 (zeros)
+    double red[kEpiWarps][4];
+    bool last;
+};
+
+// ------------------------------------------------------------------ PTX
+__device__ __forceinline__ unsigned s32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bar_init(unsigned long long *b, unsigned n) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(b)), "r"(n) : "memory");
+}
+__device__ __forceinline__ void bar_expect(unsigned long long *b, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(unsigned long long *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(b)) : "memory");
+}
+__device__ __forceinline__ void bar_wait(unsigned long long *b, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "W_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra D_%=;\n"
+        "bra W_%=;\n"
+        "D_%=:\n"
+        "}\n" ::"r"(s32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c_inner, int c_outer, unsigned long long *b) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+                     s32(dst)),
+                 "l"(map), "r"(s32(b)), "r"(c_inner), "r"(c_outer)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+// tcgen05.commit: the mbarrier gets one arrival once every MMA issued so far by this thread has finished
+__device__ __forceinline__ void mma_commit(unsigned long long *b) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(b)) : "memory");
+}
+__device__ __forceinline__ void mma_f16(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc, unsigned idesc,
+                                        unsigned accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Shared-memory matrix descriptor of a K-major tile whose rows are 128 bytes (64 fp16 / bf16), 128-byte swizzle:
+// start address / 16 in bits [0,14), stride between 8-row groups (1,024 B) / 16 in bits [32,46), descriptor version 1
+// in bits [46,48), layout type 2 (SWIZZLE_128B) in bits [61,64).  The leading-dimension offset is not used by this layout.
+__device__ __forceinline__ unsigned long long smem_desc(unsigned addr) {
+    return (unsigned long long)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((unsigned long long)(1024 >> 4) << 32) | (1ull << 46) |
+           (2ull << 61);
+}
+// Instruction descriptor, kind::f16: D = fp32 (bits [4,6) = 1), A / B format in bits [7,10) / [10,13) (0 = fp16, 1 = bf16),
+// both K-major (bits 15, 16 = 0), N / 8 in bits [17,23), M / 16 in bits [24,29).
+__host__ __device__ constexpr unsigned instr_desc(int fmt) {
+    return (1u << 4) | ((unsigned)fmt << 7) | ((unsigned)fmt << 10) | ((unsigned)(kBN >> 3) << 17) | ((unsigned)(kBM >> 4) << 24);
+}
+// 32 consecutive fp32 columns of this thread's TMEM lane (the warp reads its own 32-lane quarter)
+__device__ __forceinline__ void tmem_ld32(unsigned taddr, float (&v)[32]) {
+    unsigned r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        "tcgen05.wait::ld.sync.aligned;\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ------------------------------------------------------------------ element types
+template <typename T> struct Elem;
+template <> struct Elem<__half> {
+    static constexpr int fmt = 0;
+    static __device__ __forceinline__ float round(float v) { return __half2float(__float2half_rn(v)); }
+    static __device__ __forceinline__ unsigned pack(float a, float b) {
+        __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<unsigned *>(&h);
+    }
+};
+template <> struct Elem<__nv_bfloat16> {
+    static constexpr int fmt = 1;
+    static __device__ __forceinline__ float round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+    static __device__ __forceinline__ unsigned pack(float a, float b) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<unsigned *>(&h);
+    }
+};
+
+// ------------------------------------------------------------------ the loss of one cell, in registers
+// torch.maximum / torch.minimum / clamp(min=0): NaN propagates (as in loss.cu).
+__device__ __forceinline__ float t_max(float a, float b) { return (a > b || a != a) ? a : b; }
+__device__ __forceinline__ float t_min(float a, float b) { return (a < b || a != a) ? a : b; }
+__device__ __forceinline__ float max_mask(float self, float other) { return (self < other) ? 0.f : ((self == other) ? 0.5f : 1.f); }
+__device__ __forceinline__ float min_mask(float self, float other) { return (self > other) ? 0.f : ((self == other) ? 0.5f : 1.f); }
+
+struct Iou {   // loss.py:191-212 in fp32, one rounding per operator, with what the backward needs
+    float iou, inter, U, iw, ih, rawx, rawy, px1, px2, py1, py2;
+};
+__device__ __forceinline__ Iou iou_fwd(float x, float y, float w, float h, float tx1, float tx2, float ty1, float ty2, float tarea) {
+    Iou c;
+    const float hw = w * 0.5f, hh = h * 0.5f;
+    c.px1 = x - hw; c.px2 = x + hw;
+    c.py1 = y - hh; c.py2 = y + hh;
+    c.rawx = t_min(c.px2, tx2) - t_max(c.px1, tx1);
+    c.rawy = t_min(c.py2, ty2) - t_max(c.py1, ty1);
+    c.iw = c.rawx < 0.f ? 0.f : c.rawx;
+    c.ih = c.rawy < 0.f ? 0.f : c.rawy;
+    c.inter = c.iw * c.ih;
+    const float uni = (w * h + tarea) - c.inter;
+    c.U = uni + 1e-6f;
+    c.iou = c.inter / c.U;
+    return c;
+}
+
+struct LossSums {   // fp64: a thread adds up to a few hundred cells, and the order of the tiles must not show in the result
+    double coord, obj, noobj, cls;
+};
+
+// p[0..29]: the cell's predictions; tg: its 30 target floats (8-byte aligned).  Writes d total / d p into g[0..29]
+// (not yet multiplied by the caller's gradient scale) and adds the cell's four raw sums (loss.py:126-157).
+__device__ __forceinline__ void cell_loss(const float (&p)[32], const float2 *__restrict__ tg, float inv_n, float lambda_coord,
+                                          float lambda_noobj, float (&g)[30], LossSums &acc) {
+#pragma unroll
+    for (int i = 0; i < 30; ++i) g[i] = 0.f;
+    const float2 t45 = __ldg(tg + 2), t89 = __ldg(tg + 4);    // (t[4], t[5]), (t[8], t[9])
+    const bool has0 = t45.x > 0.f, has1 = t89.y > 0.f;
+    const float gn = inv_n * lambda_noobj;
+    if (!(has0 || has1)) {                                  // loss.py:150-153: both confidences are no-object terms
+        acc.noobj += (double)(p[4] * p[4] + p[9] * p[9]);
+        g[4] = gn * (2.f * p[4]);
+        g[9] = gn * (2.f * p[9]);
+        return;
+    }
+    float t[30];
+#pragma unroll
+    for (int i = 0; i < 15; ++i) {
+        const float2 v = __ldg(tg + i);
+        t[2 * i] = v.x;
+        t[2 * i + 1] = v.y;
+    }
+    const int slot = (!has0 && has1) ? 1 : 0;              // loss.py:102: the first filled slot
+    const float tx = slot ? t[5] : t[0], ty = slot ? t[6] : t[1], tw = slot ? t[7] : t[2], th = slot ? t[8] : t[3];
+    const float thw = tw * 0.5f, thh = th * 0.5f;
+    const float tx1 = tx - thw, tx2 = tx + thw, ty1 = ty - thh, ty2 = ty + thh, tarea = tw * th;
+    const Iou c0 = iou_fwd(p[0], p[1], p[2], p[3], tx1, tx2, ty1, ty2, tarea);
+    const Iou c1 = iou_fwd(p[5], p[6], p[7], p[8], tx1, tx2, ty1, ty2, tarea);
+    const bool pick1 = (c1.iou > c0.iou) || (c1.iou != c1.iou && c0.iou == c0.iou);   // first maximum, NaN maximal
+    const Iou c = pick1 ? c1 : c0;
+    const float x = pick1 ? p[5] : p[0], y = pick1 ? p[6] : p[1], w = pick1 ? p[7] : p[2], h = pick1 ? p[8] : p[3];
+    const float cf = pick1 ? p[9] : p[4], co = pick1 ? p[4] : p[9];
+    const float dx = x - tx, dy = y - ty;
+    const float wc = t_max(w, 1e-6f), hc = t_max(h, 1e-6f);
+    const float sw = sqrtf(wc), sh = sqrtf(hc);
+    const float dw = sw - sqrtf(t_max(tw, 1e-6f)), dh = sh - sqrtf(t_max(th, 1e-6f));
+    acc.coord += (double)((dx * dx + dy * dy) + (dw * dw + dh * dh));
+    const float dc = cf - c.iou;                            // the IoU target is not detached (loss.py:142-147)
+    acc.obj += (double)(dc * dc);
+    acc.noobj += (double)(co * co);
+    const float gc = inv_n * lambda_coord;
+    const float g_other = gn * (2.f * co), g_resp = inv_n * (2.f * dc);
+    float gx = gc * (2.f * dx), gy = gc * (2.f * dy);
+    float gw = (w >= 1e-6f) ? (gc * (2.f * dw)) / (2.f * sw) : 0.f;
+    float gh = (h >= 1e-6f) ? (gc * (2.f * dh)) / (2.f * sh) : 0.f;
+    const float gi = -(inv_n * (2.f * dc));
+    const float g_union = -gi * c.inter / (c.U * c.U);
+    const float g_inter = gi / c.U - g_union;
+    gw += g_union * h;
+    gh += g_union * w;
+    const float g_rawx = (c.rawx >= 0.f) ? g_inter * c.ih : 0.f;
+    const float g_rawy = (c.rawy >= 0.f) ? g_inter * c.iw : 0.f;
+    const float gpx2 = g_rawx * min_mask(c.px2, tx2), gpx1 = -g_rawx * max_mask(c.px1, tx1);
+    const float gpy2 = g_rawy * min_mask(c.py2, ty2), gpy1 = -g_rawy * max_mask(c.py1, ty1);
+    gx += gpx1 + gpx2;
+    gy += gpy1 + gpy2;
+    gw += (gpx2 - gpx1) * 0.5f;
+    gh += (gpy2 - gpy1) * 0.5f;
+    g[0] = pick1 ? 0.f : gx; g[1] = pick1 ? 0.f : gy; g[2] = pick1 ? 0.f : gw; g[3] = pick1 ? 0.f : gh;
+    g[4] = pick1 ? g_other : g_resp;
+    g[5] = pick1 ? gx : 0.f; g[6] = pick1 ? gy : 0.f; g[7] = pick1 ? gw : 0.f; g[8] = pick1 ? gh : 0.f;
+    g[9] = pick1 ? g_resp : g_other;
+    float cs = 0.f;                                         // loss.py:156-157, summed in class order
+#pragma unroll
+    for (int i = 10; i < 30; ++i) {
+        const float d = p[i] - t[i];
+        cs += d * d;
+        g[i] = inv_n * (2.f * d);
+    }
+    acc.cls += (double)cs;
+}
+
+// ------------------------------------------------------------------ the kernel
+struct Args {
+    const float *bias;        // [1470] or nullptr
+    const float2 *tgt;        // [M, 7, 7, 30] fp32, or nullptr: plain Linear (pred_out only)
+    int M;
+    int round_pred;           // round the prediction to the operand type first, as the autocast Linear's output is
+    float lambda_coord, lambda_noobj, inv_n, grad_scale;
+    void *grad;               // [M, 1470] in GT, or nullptr
+    float *pred_out;          // [M, 1470] fp32, or nullptr
+    double *partials;         // [gridDim.x][4]
+    unsigned *ticket;
+    float *parts;             // total, coord, conf_obj, conf_noobj, class
+};
+
+template <typename T, typename GT>
+__global__ void __launch_bounds__(kThreads, 1)
+head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Args a) {
+    extern __shared__ unsigned char smem_raw[];
+    Smem &sm = *reinterpret_cast<Smem *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tiles = (a.M + kBM - 1) / kBM;
+    const int total = m_tiles * kNTiles;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            bar_init(&sm.full[s], 1);
+            bar_init(&sm.empty[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            bar_init(&sm.acc_full[s], 1);
+            bar_init(&sm.acc_empty[s], kEpiWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    for (int i = threadIdx.x; i < kNTiles * kBN; i += kThreads) {
+        const int nb = i / kBN, j = i - nb * kBN;
+        sm.bias[i] = (a.bias != nullptr && j < kNUse) ? __ldg(a.bias + nb * kNUse + j) : 0.f;
+    }
+    if (warp == 1) {   // the warp that allocates TMEM also frees it
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&sm.tmem_base)), "n"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const unsigned tmem = sm.tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {                       // ---- TMA producer
+            int s = 0, ph = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int m_blk = t / kNTiles, n_blk = t - m_blk * kNTiles;
+                for (int kb = 0; kb < kKBlocks; ++kb) {
+                    bar_wait(&sm.empty[s], ph ^ 1);
+                    bar_expect(&sm.full[s], kStageBytes);
+                    tma_load_2d(sm.tiles[s], &map_a, kb * kBK, m_blk * kBM, &sm.full[s]);
+                    tma_load_2d(sm.tiles[s] + kABytes, &map_b, kb * kBK, n_blk * kNUse, &sm.full[s]);
+                    if (++s == kStages) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {                       // ---- MMA issuer
+            const unsigned idesc = instr_desc(Elem<T>::fmt);
+            int s = 0, ph = 0, as = 0, aph = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                bar_wait(&sm.acc_empty[as], aph ^ 1);          // the epilogue has drained this accumulator
+                fence_after();
+                const unsigned d = tmem + as * kAccStride;
+                for (int kb = 0; kb < kKBlocks; ++kb) {
+                    bar_wait(&sm.full[s], ph);
+                    fence_after();
+                    const unsigned long long ad = smem_desc(s32(sm.tiles[s])), bd = smem_desc(s32(sm.tiles[s] + kABytes));
+#pragma unroll
+                    for (int k = 0; k < kBK / 16; ++k)        // 32 bytes along K per instruction: + 2 in the address field
+                        mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                    mma_commit(&sm.empty[s]);                  // frees the stage once these MMAs have read it
+                    if (++s == kStages) { s = 0; ph ^= 1; }
+                }
+                mma_commit(&sm.acc_full[as]);
+                as ^= 1;
+                if (as == 0) aph ^= 1;
+            }
+        }
+        __syncwarp();
+    } else {                                   // ---- epilogue: warps 2..5 own TMEM lanes 32 * (warp % 4) ..
+        const int q = warp & 3, row = q * 32 + lane;
+        LossSums acc = {0.0, 0.0, 0.0, 0.0};
+        int as = 0, aph = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int m_blk = t / kNTiles, n_blk = t - m_blk * kNTiles;
+            const int img = m_blk * kBM + row;
+            const bool live = img < a.M;
+            bar_wait(&sm.acc_full[as], aph);
+            fence_after();
+            const unsigned taddr = tmem + ((unsigned)(q * 32) << 16) + as * kAccStride;
+#pragma unroll 1
+            for (int c = 0; c < kCellsPerTile; ++c) {
+                float v[32];
+                __syncwarp();                  // tcgen05.ld is warp-wide: lanes that left the previous cell early wait here
+                tmem_ld32(taddr + c * kD, v);
+                const float *b = sm.bias + n_blk * kBN + c * kD;
+#pragma unroll
+                for (int j = 0; j < kD; ++j) {
+                    v[j] += b[j];
+                    if (a.round_pred) v[j] = Elem<T>::round(v[j]);
+                }
+                if (!live) continue;
+                const size_t cell = (size_t)img * kCells + n_blk * kCellsPerTile + c;
+                if (a.pred_out != nullptr) {
+                    float2 *o = reinterpret_cast<float2 *>(a.pred_out + cell * kD);
+#pragma unroll
+                    for (int j = 0; j < kD / 2; ++j) o[j] = make_float2(v[2 * j], v[2 * j + 1]);
+                }
+                if (a.tgt != nullptr) {
+                    float g[30];
+                    cell_loss(v, a.tgt + cell * (kD / 2), a.inv_n, a.lambda_coord, a.lambda_noobj, g, acc);
+                    if (a.grad != nullptr) {
+                        if (sizeof(GT) == 4) {
+                            float2 *o = reinterpret_cast<float2 *>(a.grad) + cell * (kD / 2);
+#pragma unroll
+                            for (int j = 0; j < kD / 2; ++j) o[j] = make_float2(g[2 * j] * a.grad_scale, g[2 * j + 1] * a.grad_scale);
+                        } else {
+                            unsigned *o = reinterpret_cast<unsigned *>(a.grad) + cell * (kD / 2);
+#pragma unroll
+                            for (int j = 0; j < kD / 2; ++j) o[j] = Elem<T>::pack(g[2 * j] * a.grad_scale, g[2 * j + 1] * a.grad_scale);
+                        }
+                    }
+                }
+            }
+            fence_before();
+            __syncwarp();
+            if (lane == 0) bar_arrive(&sm.acc_empty[as]);
+            as ^= 1;
+            if (as == 0) aph ^= 1;
+        }
+        // the warp's four sums (fp64 from here on)
+        double s4[4] = {acc.coord, acc.obj, acc.noobj, acc.cls};
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) s4[k] += __shfl_down_sync(0xffffffffu, s4[k], off);
+        if (lane == 0)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) sm.red[warp - 2][k] = s4[k];
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols) : "memory");
+    }
+    if (a.tgt == nullptr) return;
+
+    // per-CTA partials in a fixed place, folded in a fixed order by the last CTA to finish: deterministic for a grid size
+    if (threadIdx.x < 4) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kEpiWarps; ++w) s += sm.red[w][threadIdx.x];
+        a.partials[(size_t)blockIdx.x * 4 + threadIdx.x] = s;
+        __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) sm.last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (!sm.last) return;
+    __threadfence();
+    if (threadIdx.x < 4) {
+        double s = 0.0;
+        for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(a.partials + (size_t)b * 4 + threadIdx.x);
+        sm.red[0][threadIdx.x] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const double invn = (double)a.inv_n;
+        const double coord = (double)a.lambda_coord * sm.red[0][0], cobj = sm.red[0][1];
+        const double noobj = (double)a.lambda_noobj * sm.red[0][2], cls = sm.red[0][3];
+        a.parts[0] = (float)((coord + cobj + noobj + cls) * invn);
+        a.parts[1] = (float)(coord * invn);
+        a.parts[2] = (float)(cobj * invn);
+        a.parts[3] = (float)(noobj * invn);
+        a.parts[4] = (float)(cls * invn);
+        *a.ticket = 0u;
+    }
+}
+
+}  // namespace hl
+}  // namespace yh
+
+using namespace yh;
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+    static std::atomic<EncodeTiledFn> cached{nullptr};
+    EncodeTiledFn fn = cached.load();
+    if (fn != nullptr) return fn;
+    void *sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) != cudaSuccess || sym == nullptr ||
+        q != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = (EncodeTiledFn)sym;
+    cached.store(fn);
+    return fn;
+}
+
+// rows x 4096 K-major fp16 / bf16 matrix, boxes of 64 K-elements x box_rows rows, 128-byte swizzle, zero fill outside
+bool make_map(CUtensorMap *map, const void *base, int dtype, long long rows, int box_rows) {
+    EncodeTiledFn fn = encode_tiled();
+    if (fn == nullptr) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)hl::kK, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)hl::kK * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)hl::kBK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUtensorMapDataType dt = dtype == YH_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    return fn(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+constexpr int kMaxCtas = 256;   // partials are sized for this many CTAs (one per SM)
+
+template <typename T, typename GT>
+int launch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int ctas, cudaStream_t st) {
+    static std::atomic<bool> attr_done[kMaxDevices];
+    const int smem = (int)sizeof(hl::Smem) + 1024;
+    if (first_use_on_device(attr_done))
+        cudaFuncSetAttribute(hl::head_linear_loss_kernel<T, GT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    hl::head_linear_loss_kernel<T, GT><<<ctas, hl::kThreads, smem, st>>>(ma, mb, a);
+    return check_launch("yh_head_linear_loss");
+}
+
+}  // namespace
+
+extern "C" size_t yh_head_linear_loss_workspace_bytes(void) { return 256 + sizeof(double) * 4 * kMaxCtas; }
+
+extern "C" int yh_head_linear_loss(const void *x, const void *weight, const float *bias, int dtype, const float *tgt, int M,
+                                   int S, int B, int C, int in_features, float lambda_coord, float lambda_noobj,
+                                   float grad_scale, int round_pred, float *parts, void *grad, int grad_dtype,
+                                   float *pred_out, void *workspace, size_t workspace_bytes, void *stream) {
+    if (!shape_ok(S, B, C) || in_features != hl::kK) {
+        set_error("yh_head_linear_loss: built for Linear(4096 -> 7*7*30), got in_features=%d S=%d B=%d C=%d", in_features, S, B, C);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (dtype != YH_F16 && dtype != YH_BF16) {
+        set_error("yh_head_linear_loss: operands must be fp16 or bf16 (dtype %d)", dtype);
+        return YH_ERR_UNSUPPORTED;
+    }
+    if (grad != nullptr && grad_dtype != dtype && grad_dtype != YH_F32) {
+        set_error("yh_head_linear_loss: the gradient is written in the operand type or in fp32 (grad_dtype %d)", grad_dtype);
+        return YH_ERR_BAD_ARG;
+    }
+    if (M < 0 || !x || !weight || (tgt != nullptr && (!parts || !workspace)) || (tgt == nullptr && pred_out == nullptr)) {
+        set_error("yh_head_linear_loss: bad argument");
+        return YH_ERR_BAD_ARG;
+    }
+    if (tgt != nullptr && workspace_bytes < yh_head_linear_loss_workspace_bytes()) {
+        set_error("yh_head_linear_loss: workspace too small");
+        return YH_ERR_WORKSPACE;
+    }
+    if (((uintptr_t)x | (uintptr_t)weight) & 15u) {
+        set_error("yh_head_linear_loss: activations and weight must be 16-byte aligned (TMA)");
+        return YH_ERR_ALIGNMENT;
+    }
+    if ((((uintptr_t)tgt | (uintptr_t)pred_out) & 7u) || ((uintptr_t)grad & 7u)) {
+        set_error("yh_head_linear_loss: targets, predictions and gradient must be 8-byte aligned");
+        return YH_ERR_ALIGNMENT;
+    }
+    if (M == 0) return 0;
+    CUtensorMap ma, mb;
+    if (!make_map(&ma, x, dtype, M, hl::kBM) || !make_map(&mb, weight, dtype, hl::kNOut, hl::kBN)) {
+        set_error("yh_head_linear_loss: cuTensorMapEncodeTiled failed");
+        return YH_ERR_UNSUPPORTED;
+    }
+    int dev = current_device(), sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int tiles = ((M + hl::kBM - 1) / hl::kBM) * hl::kNTiles;
+    int ctas = tiles < sms ? tiles : sms;
+    if (ctas > kMaxCtas) ctas = kMaxCtas;
+    hl::Args a;
+    a.bias = bias;
+    a.tgt = (const float2 *)tgt;
+    a.M = M;
+    a.round_pred = round_pred;
+    a.lambda_coord = lambda_coord;
+    a.lambda_noobj = lambda_noobj;
+    a.inv_n = 1.0f / (float)M;
+    a.grad_scale = grad_scale;
+    a.grad = grad;
+    a.pred_out = pred_out;
+    a.ticket = (unsigned *)workspace;
+    a.partials = workspace ? (double *)((char *)workspace + 256) : nullptr;
+    a.parts = parts;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool g32 = grad == nullptr || grad_dtype == YH_F32;
+    if (dtype == YH_F16) return g32 ? launch<__half, float>(ma, mb, a, ctas, st) : launch<__half, __half>(ma, mb, a, ctas, st);
+    return g32 ? launch<__nv_bfloat16, float>(ma, mb, a, ctas, st) : launch<__nv_bfloat16, __nv_bfloat16>(ma, mb, a, ctas, st);
+}

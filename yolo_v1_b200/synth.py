@@ -191,3 +191,18 @@ def make_exact(n: int, seed: int = 1234, S: int = 7, B: int = 2, C: int = 20, p_
     p[..., 4] = np.where(obj, conf, p[..., 4])
     p[..., B * 5:] = np.where(hit[..., None], sharp, p[..., B * 5:])
     return torch.from_numpy(np.ascontiguousarray(p)), torch.from_numpy(np.ascontiguousarray(t))
+
+
+def head_linear_inputs(M: int, seed: int):
+    """x [M, 4096], w [1470, 4096], b [1470], targets [M, 7, 7, 30] as fp32 numpy arrays for the fused head Linear + loss
+    (tests/golden/make_head_linear_golden.py): x and w have 8 significant bits, i.e. are exact in bf16 AND fp16."""
+    import numpy as np
+
+    def q(a):
+        return np.round(a * 128.0) / 128.0          # multiples of 2^-7 below 1
+
+    x = q(exact_uniform((M, 4096), seed, 11) - 0.5).astype(np.float32)
+    w = (q(exact_uniform((1470, 4096), seed, 12) - 0.5) * 2.0 ** -5).astype(np.float32)
+    b = (0.15 + 0.5 * exact_uniform((1470,), seed, 13)).astype(np.float32)
+    _, tgt = make_exact(M, seed=seed, p_obj=0.12)
+    return x, w, b, tgt.numpy()
