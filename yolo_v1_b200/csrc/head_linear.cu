@@ -8,13 +8,14 @@
 // in ONE kernel: the [M, 1470] prediction tensor never goes to HBM (optionally it is also written out, for the
 // metric).  SURVEY 8(f) row 4.
 //
-// Shape of the kernel (one persistent CTA per SM, 192 threads, roles per warp):
+// Shape of the kernel (one persistent CTA per SM, 320 threads, roles per warp):
 //   warp 0      TMA producer: A = activations [M, 4096] and B = weight [1470, 4096], both K-major, 128-byte
 //               swizzled boxes of 64 K-elements into a 4-stage shared-memory ring (mbarrier full / empty).
 //   warp 1      allocates TMEM; one elected thread issues tcgen05.mma (M=128, N=224, K=16 per instruction) into
 //               one of two 224-column fp32 accumulators, committing each stage back to the producer and the
 //               finished accumulator to the epilogue.
-//   warps 2-5   epilogue: a thread owns one image row of the 128 x 224 tile.  An N tile is 210 useful columns =
+//   warps 2-9   epilogue, two warps per TMEM lane quarter (a lone warp on a scheduler cannot hide its own instruction
+//               latency), each taking half of the tile's cells: a thread owns one image row of the 128 x 224 tile.  An N tile is 210 useful columns =
 //               7 whole cells (7 tiles x 7 cells = 49 cells); the thread reads a cell's 30 accumulators with one
 //               tcgen05.ld, adds the bias, evaluates the cell's loss terms and gradient in registers (the same
 //               arithmetic as loss.cu), writes the 30 gradient values and adds to its running sums.  The MMA
@@ -25,6 +26,7 @@
 // Roofline: tensor.  Useful flops 2 * M * 4096 * 1470; issued 2 * M * 4096 * 1568 (224 / 210: 14 columns of the
 // next cell are computed and dropped so that cells never straddle tiles).
 #include <cuda.h>
+#include <stdlib.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -39,24 +41,14 @@ constexpr int kBM = 128, kBN = 224, kBK = 64;
 constexpr int kCellsPerTile = 7;      // 210 useful columns
 constexpr int kNUse = kCellsPerTile * kD;
 constexpr int kNTiles = kCells / kCellsPerTile;  // 7
-constexpr int kStages = 4;
 constexpr int kKBlocks = kK / kBK;    // 64
-constexpr int kABytes = kBM * kBK * 2, kBBytes = kBN * kBK * 2;   // 16,384 + 28,672
-constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kABytes = kBM * kBK * 2;   // 16,384
 constexpr int kAccStride = 256;       // TMEM columns between the two accumulators
 constexpr int kTmemCols = 512;
-constexpr int kThreads = 192;
-constexpr int kEpiWarps = 4;
+constexpr int kEpiGroups = 2;          // epilogue warps per TMEM lane quarter: each takes a share of the tile's 7 cells
+constexpr int kEpiWarps = 4 * kEpiGroups;
+constexpr int kThreads = 64 + 32 * kEpiWarps;   // TMA warp, MMA warp, epilogue warps
 static_assert(kNTiles * kCellsPerTile == kCells, "cells per tile");
-
-struct Smem {
-    alignas(1024) unsigned char tiles[kStages][kStageBytes];
-    alignas(8) unsigned long long full[kStages], empty[kStages], acc_full[2], acc_empty[2];
-    unsigned tmem_base;
-    float bias[kNTiles * kBN];        // bias of every N tile, padded to 224 (zeros)
-    double red[kEpiWarps][4];
-    bool last;
-};
 
 // ------------------------------------------------------------------ PTX
 __device__ __forceinline__ unsigned s32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -111,8 +103,8 @@ __device__ __forceinline__ unsigned long long smem_desc(unsigned addr) {
 }
 // Instruction descriptor, kind::f16: D = fp32 (bits [4,6) = 1), A / B format in bits [7,10) / [10,13) (0 = fp16, 1 = bf16),
 // both K-major (bits 15, 16 = 0), N / 8 in bits [17,23), M / 16 in bits [24,29).
-__host__ __device__ constexpr unsigned instr_desc(int fmt) {
-    return (1u << 4) | ((unsigned)fmt << 7) | ((unsigned)fmt << 10) | ((unsigned)(kBN >> 3) << 17) | ((unsigned)(kBM >> 4) << 24);
+__host__ __device__ constexpr unsigned instr_desc(int fmt, int m) {
+    return (1u << 4) | ((unsigned)fmt << 7) | ((unsigned)fmt << 10) | ((unsigned)(kBN >> 3) << 17) | ((unsigned)(m >> 4) << 24);
 }
 // 32 consecutive fp32 columns of this thread's TMEM lane (the warp reads its own 32-lane quarter)
 __device__ __forceinline__ void tmem_ld32(unsigned taddr, float (&v)[32]) {
@@ -177,21 +169,19 @@ __device__ __forceinline__ Iou iou_fwd(float x, float y, float w, float h, float
     return c;
 }
 
-struct LossSums {   // fp64: a thread adds up to a few hundred cells, and the order of the tiles must not show in the result
-    double coord, obj, noobj, cls;
+struct LossSums {   // one tile's share (at most 4 cells) in fp32; the thread's running sums over all its tiles are fp64
+    float coord, obj, noobj, cls;
 };
 
 // p[0..29]: the cell's predictions; tg: its 30 target floats (8-byte aligned).  Writes d total / d p into g[0..29]
 // (not yet multiplied by the caller's gradient scale) and adds the cell's four raw sums (loss.py:126-157).
-__device__ __forceinline__ void cell_loss(const float (&p)[32], const float2 *__restrict__ tg, float inv_n, float lambda_coord,
-                                          float lambda_noobj, float (&g)[30], LossSums &acc) {
+__device__ __forceinline__ void cell_loss(const float (&p)[32], const float2 *__restrict__ tg, bool has0, bool has1, float inv_n,
+                                          float lambda_coord, float lambda_noobj, float (&g)[30], LossSums &acc) {
 #pragma unroll
     for (int i = 0; i < 30; ++i) g[i] = 0.f;
-    const float2 t45 = __ldg(tg + 2), t89 = __ldg(tg + 4);    // (t[4], t[5]), (t[8], t[9])
-    const bool has0 = t45.x > 0.f, has1 = t89.y > 0.f;
     const float gn = inv_n * lambda_noobj;
     if (!(has0 || has1)) {                                  // loss.py:150-153: both confidences are no-object terms
-        acc.noobj += (double)(p[4] * p[4] + p[9] * p[9]);
+        acc.noobj += p[4] * p[4] + p[9] * p[9];
         g[4] = gn * (2.f * p[4]);
         g[9] = gn * (2.f * p[9]);
         return;
@@ -217,10 +207,10 @@ __device__ __forceinline__ void cell_loss(const float (&p)[32], const float2 *__
     const float wc = t_max(w, 1e-6f), hc = t_max(h, 1e-6f);
     const float sw = sqrtf(wc), sh = sqrtf(hc);
     const float dw = sw - sqrtf(t_max(tw, 1e-6f)), dh = sh - sqrtf(t_max(th, 1e-6f));
-    acc.coord += (double)((dx * dx + dy * dy) + (dw * dw + dh * dh));
+    acc.coord += (dx * dx + dy * dy) + (dw * dw + dh * dh);
     const float dc = cf - c.iou;                            // the IoU target is not detached (loss.py:142-147)
-    acc.obj += (double)(dc * dc);
-    acc.noobj += (double)(co * co);
+    acc.obj += dc * dc;
+    acc.noobj += co * co;
     const float gc = inv_n * lambda_coord;
     const float g_other = gn * (2.f * co), g_resp = inv_n * (2.f * dc);
     float gx = gc * (2.f * dx), gy = gc * (2.f * dy);
@@ -250,7 +240,7 @@ __device__ __forceinline__ void cell_loss(const float (&p)[32], const float2 *__
         cs += d * d;
         g[i] = inv_n * (2.f * d);
     }
-    acc.cls += (double)cs;
+    acc.cls += cs;
 }
 
 // ------------------------------------------------------------------ the kernel
@@ -267,23 +257,94 @@ struct Args {
     float *parts;             // total, coord, conf_obj, conf_noobj, class
 };
 
-template <typename T, typename GT>
-__global__ void __launch_bounds__(kThreads, 1)
+// CTAS = 2: two CTAs of a cluster (one SM pair) share a 256 x 224 tile.  Each loads its own 128 rows of A and HALF of
+// the B tile (112 rows); the leader's thread issues tcgen05.mma.cta_group::2 (M = 256), which reads A from each CTA's
+// own shared memory and the two halves of B from both, and accumulates into each CTA's own TMEM.  Per SM that is
+// 7.5 KB of shared-memory reads per K = 16 step instead of 11 KB, and 30 KB of TMA writes per stage instead of 44 KB --
+// the single-CTA form needs ~200 B / clk of a 128 B / clk shared memory to keep the tensor core busy.
+template <int CTAS>
+struct Cfg {
+    static constexpr int kBRows = kBN / CTAS;                    // rows of the B tile one CTA holds
+    static constexpr int kBBytes1 = kBRows * kBK * 2;
+    static constexpr int kStageBytes1 = kABytes + kBBytes1;      // 45,056 / 30,720
+    static constexpr int kStages1 = CTAS == 1 ? 4 : 6;
+};
+template <int CTAS>
+struct SmemT {
+    alignas(1024) unsigned char tiles[Cfg<CTAS>::kStages1][Cfg<CTAS>::kStageBytes1];
+    alignas(8) unsigned long long full[Cfg<CTAS>::kStages1], empty[Cfg<CTAS>::kStages1], acc_full[2], acc_empty[2];
+    unsigned tmem_base;
+    float bias[kNTiles * kBN];        // bias of every N tile, padded to 224 (zeros)
+    float2 out[kEpiWarps][32 * (kD / 2)];   // one cell of a warp's 32 rows on its way out (3,840 B per warp)
+    double red[kEpiWarps][4];
+    bool last;
+};
+
+__device__ __forceinline__ unsigned cluster_rank() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// the address, in the cluster's shared window, of `local` in CTA `rank`
+__device__ __forceinline__ unsigned map_to_rank(unsigned local, unsigned rank) {
+    unsigned r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void bar_arrive_cluster(unsigned cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(void *dst, const CUtensorMap *map, int c_inner, int c_outer, unsigned bar_cluster_addr) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            s32(dst)),
+        "l"(map), "r"(bar_cluster_addr), "r"(c_inner), "r"(c_outer)
+        : "memory");
+}
+__device__ __forceinline__ void mma_commit_pair(unsigned long long *b) {   // arrives at this offset in both CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(s32(b)),
+                 "h"((unsigned short)3)
+                 : "memory");
+}
+__device__ __forceinline__ void mma_f16_pair(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc, unsigned idesc,
+                                             unsigned accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+template <typename T, typename GT, int CTAS>
+__global__ void __launch_bounds__(kThreads, 1)   // 10 warps are allocated as 12: 168 registers per thread
 head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Args a) {
-    extern __shared__ unsigned char smem_raw[];
-    Smem &sm = *reinterpret_cast<Smem *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    using C = Cfg<CTAS>;
+    constexpr int kSt = C::kStages1;
+    // No static shared memory in this kernel: the dynamic window starts at offset 0 of the CTA's shared memory, which is
+    // what gives the tiles the 1,024-byte alignment the 128-byte swizzle needs (checked below).  Used in place, so that
+    // the compiler keeps the shared address space (an integer round-up of the pointer turns every access generic).
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    SmemT<CTAS> &sm = *reinterpret_cast<SmemT<CTAS> *>(smem_raw);
+    if ((s32(smem_raw) & 1023u) != 0u) __trap();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m_tiles = (a.M + kBM - 1) / kBM;
-    const int total = m_tiles * kNTiles;
+    const unsigned rank = CTAS == 2 ? cluster_rank() : 0u;       // 0 = the leader: issues the MMAs, owns full / acc_empty
+    const int unit = blockIdx.x / CTAS, units = gridDim.x / CTAS;
+    const int m_units = (a.M + kBM * CTAS - 1) / (kBM * CTAS);
+    const int total = m_units * kNTiles;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < kSt; ++s) {
             bar_init(&sm.full[s], 1);
             bar_init(&sm.empty[s], 1);
         }
         for (int s = 0; s < 2; ++s) {
             bar_init(&sm.acc_full[s], 1);
-            bar_init(&sm.acc_empty[s], kEpiWarps);
+            bar_init(&sm.acc_empty[s], kEpiWarps * CTAS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -292,37 +353,52 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         const int nb = i / kBN, j = i - nb * kBN;
         sm.bias[i] = (a.bias != nullptr && j < kNUse) ? __ldg(a.bias + nb * kNUse + j) : 0.f;
     }
-    if (warp == 1) {   // the warp that allocates TMEM also frees it
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&sm.tmem_base)), "n"(kTmemCols)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (warp == 1) {   // the warp that allocates TMEM also frees it (the same warp in both CTAs of a pair)
+        if (CTAS == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&sm.tmem_base)), "n"(kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&sm.tmem_base)), "n"(kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     fence_before();
-    __syncthreads();
+    if (CTAS == 2) cluster_sync(); else __syncthreads();          // barriers of both CTAs initialised before anyone signals them
     fence_after();
     const unsigned tmem = sm.tmem_base;
 
     if (warp == 0) {
-        if (lane == 0) {                       // ---- TMA producer
+        if (lane == 0) {                       // ---- TMA producer (in every CTA: its A rows, its share of the B rows)
             int s = 0, ph = 0;
-            for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                const int m_blk = t / kNTiles, n_blk = t - m_blk * kNTiles;
+            for (int t = unit; t < total; t += units) {
+                const int m_unit = t / kNTiles, n_blk = t - m_unit * kNTiles;
+                const int a_row = (m_unit * CTAS + (int)rank) * kBM, b_row = n_blk * kNUse + (int)rank * C::kBRows;
                 for (int kb = 0; kb < kKBlocks; ++kb) {
                     bar_wait(&sm.empty[s], ph ^ 1);
-                    bar_expect(&sm.full[s], kStageBytes);
-                    tma_load_2d(sm.tiles[s], &map_a, kb * kBK, m_blk * kBM, &sm.full[s]);
-                    tma_load_2d(sm.tiles[s] + kABytes, &map_b, kb * kBK, n_blk * kNUse, &sm.full[s]);
-                    if (++s == kStages) { s = 0; ph ^= 1; }
+                    if (CTAS == 2) {
+                        // all bytes of both CTAs complete on the leader's barrier; the leader arms it for the pair
+                        const unsigned full0 = map_to_rank(s32(&sm.full[s]), 0);
+                        if (rank == 0) bar_expect(&sm.full[s], 2 * C::kStageBytes1);
+                        tma_load_2d_pair(sm.tiles[s], &map_a, kb * kBK, a_row, full0);
+                        tma_load_2d_pair(sm.tiles[s] + kABytes, &map_b, kb * kBK, b_row, full0);
+                    } else {
+                        bar_expect(&sm.full[s], C::kStageBytes1);
+                        tma_load_2d(sm.tiles[s], &map_a, kb * kBK, a_row, &sm.full[s]);
+                        tma_load_2d(sm.tiles[s] + kABytes, &map_b, kb * kBK, b_row, &sm.full[s]);
+                    }
+                    if (++s == kSt) { s = 0; ph ^= 1; }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 1) {
-        if (lane == 0) {                       // ---- MMA issuer
-            const unsigned idesc = instr_desc(Elem<T>::fmt);
+        if (lane == 0 && rank == 0) {          // ---- MMA issuer (the leader's, for the pair)
+            const unsigned idesc = instr_desc(Elem<T>::fmt, kBM * CTAS);
             int s = 0, ph = 0, as = 0, aph = 0;
-            for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                bar_wait(&sm.acc_empty[as], aph ^ 1);          // the epilogue has drained this accumulator
+            for (int t = unit; t < total; t += units) {
+                bar_wait(&sm.acc_empty[as], aph ^ 1);          // the epilogue (of both CTAs) has drained this accumulator
                 fence_after();
                 const unsigned d = tmem + as * kAccStride;
                 for (int kb = 0; kb < kKBlocks; ++kb) {
@@ -330,30 +406,49 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                     fence_after();
                     const unsigned long long ad = smem_desc(s32(sm.tiles[s])), bd = smem_desc(s32(sm.tiles[s] + kABytes));
 #pragma unroll
-                    for (int k = 0; k < kBK / 16; ++k)        // 32 bytes along K per instruction: + 2 in the address field
-                        mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
-                    mma_commit(&sm.empty[s]);                  // frees the stage once these MMAs have read it
-                    if (++s == kStages) { s = 0; ph ^= 1; }
+                    for (int k = 0; k < kBK / 16; ++k) {      // 32 bytes along K per instruction: + 2 in the address field
+                        if (CTAS == 2) mma_f16_pair(d, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                        else mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                    }
+                    if (CTAS == 2) mma_commit_pair(&sm.empty[s]); else mma_commit(&sm.empty[s]);   // frees the stage
+                    if (++s == kSt) { s = 0; ph ^= 1; }
                 }
-                mma_commit(&sm.acc_full[as]);
+                if (CTAS == 2) mma_commit_pair(&sm.acc_full[as]); else mma_commit(&sm.acc_full[as]);
                 as ^= 1;
                 if (as == 0) aph ^= 1;
             }
         }
         __syncwarp();
     } else {                                   // ---- epilogue: warps 2..5 own TMEM lanes 32 * (warp % 4) ..
-        const int q = warp & 3, row = q * 32 + lane;
-        LossSums acc = {0.0, 0.0, 0.0, 0.0};
+        const int q = warp & 3, grp = (warp - 2) >> 2;
+        const int c_lo = (grp * kCellsPerTile + kEpiGroups - 1) / kEpiGroups, c_hi = ((grp + 1) * kCellsPerTile + kEpiGroups - 1) / kEpiGroups;
+        double sum_coord = 0.0, sum_obj = 0.0, sum_noobj = 0.0, sum_cls = 0.0;
         int as = 0, aph = 0;
-        for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            const int m_blk = t / kNTiles, n_blk = t - m_blk * kNTiles;
-            const int img = m_blk * kBM + row;
+        for (int t = unit; t < total; t += units) {
+            const int m_unit = t / kNTiles, n_blk = t - m_unit * kNTiles;
+            const int img0 = (m_unit * CTAS + (int)rank) * kBM + q * 32;    // the warp's first row
+            const int img = img0 + lane;
             const bool live = img < a.M;
+            const size_t cell0 = (size_t)img * kCells + n_blk * kCellsPerTile;
+            // the two object flags (t[4] > 0, t[9] > 0) of the row's cells, in flight while the accumulator is still being made
+            unsigned has0 = 0u, has1 = 0u;
+            if (live && a.tgt != nullptr) {
+#pragma unroll
+                for (int c = 0; c < kCellsPerTile; ++c) {
+                    if (c < c_lo || c >= c_hi) continue;
+                    const float *tc = reinterpret_cast<const float *>(a.tgt + (cell0 + c) * (kD / 2));
+                    has0 |= (unsigned)(__ldg(tc + 4) > 0.f) << c;
+                    has1 |= (unsigned)(__ldg(tc + 9) > 0.f) << c;
+                }
+            }
             bar_wait(&sm.acc_full[as], aph);
             fence_after();
             const unsigned taddr = tmem + ((unsigned)(q * 32) << 16) + as * kAccStride;
+            float2 *stage = sm.out[warp - 2];
+            LossSums acc = {0.f, 0.f, 0.f, 0.f};
+            const int rows_live = a.M - img0 < 32 ? (a.M - img0 < 0 ? 0 : a.M - img0) : 32;
 #pragma unroll 1
-            for (int c = 0; c < kCellsPerTile; ++c) {
+            for (int c = c_lo; c < c_hi; ++c) {
                 float v[32];
                 __syncwarp();                  // tcgen05.ld is warp-wide: lanes that left the previous cell early wait here
                 tmem_ld32(taddr + c * kD, v);
@@ -363,37 +458,70 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                     v[j] += b[j];
                     if (a.round_pred) v[j] = Elem<T>::round(v[j]);
                 }
-                if (!live) continue;
-                const size_t cell = (size_t)img * kCells + n_blk * kCellsPerTile + c;
+                // A cell of the warp's 32 rows leaves through shared memory: a lane puts its row's 30 values down (row
+                // stride 15 x 8 B, odd: conflict-free), then the warp writes row after row with neighbouring lanes on
+                // neighbouring words -- 60 / 120 contiguous bytes per row instead of 32 scattered words per instruction.
+                const size_t out0 = ((size_t)img0 * kCells + n_blk * kCellsPerTile + c) * (kD / 2);   // word index, row 0
                 if (a.pred_out != nullptr) {
-                    float2 *o = reinterpret_cast<float2 *>(a.pred_out + cell * kD);
 #pragma unroll
-                    for (int j = 0; j < kD / 2; ++j) o[j] = make_float2(v[2 * j], v[2 * j + 1]);
+                    for (int j = 0; j < kD / 2; ++j) stage[lane * (kD / 2) + j] = make_float2(v[2 * j], v[2 * j + 1]);
+                    __syncwarp();
+                    float2 *o = reinterpret_cast<float2 *>(a.pred_out);
+#pragma unroll
+                    for (int k = 0; k < kD / 2; ++k) {
+                        const int w = k * 32 + lane, r = w / (kD / 2), j = w - r * (kD / 2);
+                        if (r < rows_live) o[out0 + (size_t)r * (kCells * kD / 2) + j] = stage[w];
+                    }
+                    __syncwarp();
                 }
                 if (a.tgt != nullptr) {
                     float g[30];
-                    cell_loss(v, a.tgt + cell * (kD / 2), a.inv_n, a.lambda_coord, a.lambda_noobj, g, acc);
+                    if (live) cell_loss(v, a.tgt + (cell0 + c) * (kD / 2), (has0 >> c) & 1u, (has1 >> c) & 1u, a.inv_n, a.lambda_coord, a.lambda_noobj, g, acc);
                     if (a.grad != nullptr) {
+                        __syncwarp();
                         if (sizeof(GT) == 4) {
-                            float2 *o = reinterpret_cast<float2 *>(a.grad) + cell * (kD / 2);
 #pragma unroll
-                            for (int j = 0; j < kD / 2; ++j) o[j] = make_float2(g[2 * j] * a.grad_scale, g[2 * j + 1] * a.grad_scale);
+                            for (int j = 0; j < kD / 2; ++j)
+                                stage[lane * (kD / 2) + j] = make_float2(g[2 * j] * a.grad_scale, g[2 * j + 1] * a.grad_scale);
+                            __syncwarp();
+                            float2 *o = reinterpret_cast<float2 *>(a.grad);
+#pragma unroll
+                            for (int k = 0; k < kD / 2; ++k) {
+                                const int w = k * 32 + lane, r = w / (kD / 2), j = w - r * (kD / 2);
+                                if (r < rows_live) o[out0 + (size_t)r * (kCells * kD / 2) + j] = stage[w];
+                            }
                         } else {
-                            unsigned *o = reinterpret_cast<unsigned *>(a.grad) + cell * (kD / 2);
+                            unsigned *st32 = reinterpret_cast<unsigned *>(stage);
 #pragma unroll
-                            for (int j = 0; j < kD / 2; ++j) o[j] = Elem<T>::pack(g[2 * j] * a.grad_scale, g[2 * j + 1] * a.grad_scale);
+                            for (int j = 0; j < kD / 2; ++j)
+                                st32[lane * (kD / 2) + j] = Elem<T>::pack(g[2 * j] * a.grad_scale, g[2 * j + 1] * a.grad_scale);
+                            __syncwarp();
+                            unsigned *o = reinterpret_cast<unsigned *>(a.grad);
+#pragma unroll
+                            for (int k = 0; k < kD / 2; ++k) {
+                                const int w = k * 32 + lane, r = w / (kD / 2), j = w - r * (kD / 2);
+                                if (r < rows_live) o[out0 + (size_t)r * (kCells * kD / 2) + j] = st32[w];
+                            }
                         }
+                        __syncwarp();
                     }
                 }
             }
+            sum_coord += (double)acc.coord;
+            sum_obj += (double)acc.obj;
+            sum_noobj += (double)acc.noobj;
+            sum_cls += (double)acc.cls;
             fence_before();
             __syncwarp();
-            if (lane == 0) bar_arrive(&sm.acc_empty[as]);
+            if (lane == 0) {
+                if (CTAS == 2) bar_arrive_cluster(map_to_rank(s32(&sm.acc_empty[as]), 0));
+                else bar_arrive(&sm.acc_empty[as]);
+            }
             as ^= 1;
             if (as == 0) aph ^= 1;
         }
         // the warp's four sums (fp64 from here on)
-        double s4[4] = {acc.coord, acc.obj, acc.noobj, acc.cls};
+        double s4[4] = {sum_coord, sum_obj, sum_noobj, sum_cls};
 #pragma unroll
         for (int k = 0; k < 4; ++k)
 #pragma unroll
@@ -403,10 +531,11 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
             for (int k = 0; k < 4; ++k) sm.red[warp - 2][k] = s4[k];
     }
     fence_before();
-    __syncthreads();
+    if (CTAS == 2) cluster_sync(); else __syncthreads();          // nobody leaves while its partner may still signal it
     if (warp == 1) {
         fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols) : "memory");
+        if (CTAS == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols) : "memory");
     }
     if (a.tgt == nullptr) return;
 
@@ -482,14 +611,47 @@ bool make_map(CUtensorMap *map, const void *base, int dtype, long long rows, int
 
 constexpr int kMaxCtas = 256;   // partials are sized for this many CTAs (one per SM)
 
-template <typename T, typename GT>
+// CTAs that share a tile: 2 (an SM pair, tcgen05 cta_group::2) unless YH_HL_CTAS=1 asks for the single-CTA form
+int ctas_per_tile() {
+    static int cached = 0;
+    if (cached == 0) {
+        const char *e = getenv("YH_HL_CTAS");
+        cached = (e != nullptr && e[0] == '1') ? 1 : 2;
+    }
+    return cached;
+}
+
+template <typename T, typename GT, int CTAS>
 int launch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int ctas, cudaStream_t st) {
     static std::atomic<bool> attr_done[kMaxDevices];
-    const int smem = (int)sizeof(hl::Smem) + 1024;
-    if (first_use_on_device(attr_done))
-        cudaFuncSetAttribute(hl::head_linear_loss_kernel<T, GT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    hl::head_linear_loss_kernel<T, GT><<<ctas, hl::kThreads, smem, st>>>(ma, mb, a);
+    const int smem = (int)sizeof(hl::SmemT<CTAS>);
+    auto kern = hl::head_linear_loss_kernel<T, GT, CTAS>;
+    if (first_use_on_device(attr_done)) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)ctas);
+    cfg.blockDim = dim3(hl::kThreads);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CTAS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, mb, a);
+    if (e != cudaSuccess) {
+        set_error("yh_head_linear_loss: launch failed: %s", cudaGetErrorString(e));
+        return (int)e;
+    }
     return check_launch("yh_head_linear_loss");
+}
+
+template <int CTAS>
+int dispatch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int ctas, int dtype, bool g32, cudaStream_t st) {
+    if (dtype == YH_F16)
+        return g32 ? launch<__half, float, CTAS>(ma, mb, a, ctas, st) : launch<__half, __half, CTAS>(ma, mb, a, ctas, st);
+    return g32 ? launch<__nv_bfloat16, float, CTAS>(ma, mb, a, ctas, st) : launch<__nv_bfloat16, __nv_bfloat16, CTAS>(ma, mb, a, ctas, st);
 }
 
 }  // namespace
@@ -529,15 +691,16 @@ extern "C" int yh_head_linear_loss(const void *x, const void *weight, const floa
         return YH_ERR_ALIGNMENT;
     }
     if (M == 0) return 0;
+    const int per = ctas_per_tile();
     CUtensorMap ma, mb;
-    if (!make_map(&ma, x, dtype, M, hl::kBM) || !make_map(&mb, weight, dtype, hl::kNOut, hl::kBN)) {
+    if (!make_map(&ma, x, dtype, M, hl::kBM) || !make_map(&mb, weight, dtype, hl::kNOut, hl::kBN / per)) {
         set_error("yh_head_linear_loss: cuTensorMapEncodeTiled failed");
         return YH_ERR_UNSUPPORTED;
     }
     int dev = current_device(), sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int tiles = ((M + hl::kBM - 1) / hl::kBM) * hl::kNTiles;
-    int ctas = tiles < sms ? tiles : sms;
+    const int units = ((M + hl::kBM * per - 1) / (hl::kBM * per)) * hl::kNTiles;   // tiles of one CTA / one SM pair
+    int ctas = units * per < sms ? units * per : sms - sms % per;
     if (ctas > kMaxCtas) ctas = kMaxCtas;
     hl::Args a;
     a.bias = bias;
@@ -555,6 +718,5 @@ extern "C" int yh_head_linear_loss(const void *x, const void *weight, const floa
     a.parts = parts;
     cudaStream_t st = (cudaStream_t)stream;
     const bool g32 = grad == nullptr || grad_dtype == YH_F32;
-    if (dtype == YH_F16) return g32 ? launch<__half, float>(ma, mb, a, ctas, st) : launch<__half, __half>(ma, mb, a, ctas, st);
-    return g32 ? launch<__nv_bfloat16, float>(ma, mb, a, ctas, st) : launch<__nv_bfloat16, __nv_bfloat16>(ma, mb, a, ctas, st);
+    return per == 2 ? dispatch<2>(ma, mb, a, ctas, dtype, g32, st) : dispatch<1>(ma, mb, a, ctas, dtype, g32, st);
 }
