@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--e2e-chunks", type=int, default=8, help="mini-batches the e2e step streams from the host")
     ap.add_argument("--no-graph", action="store_true", help="time the eager step only (no CapturedHeadStep)")
     ap.add_argument("--no-other-configs", action="store_true", help="skip the BASELINE.json configs[2] / [4] records")
+    ap.add_argument("--no-head-linear", action="store_true", help="skip the fused head Linear + loss record (SURVEY 8(f) row 4)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "class_shard", "gather"],
                     help="N>1: how compute() makes the per-class order global (yolo_v1_b200/distributed.py)")
     return ap.parse_args()
@@ -164,6 +165,60 @@ def run_reference(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+def head_linear_record(n, tgt_d, peaks, time_call):
+    """SURVEY 8(f) row 4 beside the headline: the head's last Linear(4096 -> 1470) + view fused with the loss forward +
+    backward (yh_head_linear_loss, tcgen05 / TMEM / TMA) on n rows of bf16 activations, against what the reference's
+    autocast step runs -- torch's Linear (cuBLAS, out_features = 1470) followed by the loss (here this package's loss
+    kernel, itself ~100x the reference's) -- and against the same with the layer padded to 1472 outputs.  Tensor roofline:
+    useful flops 2 * n * 4096 * 1470 over the measured cuBLAS bf16 peak (burst: the kernel is timed alone)."""
+    import torch.nn.functional as F
+
+    from yolo_v1_b200.head_linear import linear_loss
+    from yolo_v1_b200.loss import loss_fwd_bwd
+
+    dev = tgt_d.device
+    g = torch.Generator(device=dev).manual_seed(7)
+    x = (torch.randn(n, 4096, device=dev, generator=g) * 0.1).to(torch.bfloat16)
+    w = (torch.randn(1470, 4096, device=dev, generator=g) * 0.02).to(torch.bfloat16)
+    b = torch.rand(1470, device=dev, generator=g) * 0.6
+    b16 = b.to(torch.bfloat16)
+    w_pad = torch.zeros(1472, 4096, device=dev, dtype=torch.bfloat16)
+    w_pad[:1470] = w
+    b_pad = torch.zeros(1472, device=dev, dtype=torch.bfloat16)
+    b_pad[:1470] = b16
+
+    def two_calls():
+        pred = F.linear(x, w, b16)
+        return loss_fwd_bwd(pred.view(n, 7, 7, 30), tgt_d, 7, 2, 20, 5.0, 0.5, True)
+
+    def two_calls_padded():
+        pred = F.linear(x, w_pad, b_pad)[:, :1470].contiguous()
+        return loss_fwd_bwd(pred.view(n, 7, 7, 30), tgt_d, 7, 2, 20, 5.0, 0.5, True)
+
+    parts_f = linear_loss(x, w, b, tgt_d)[0]
+    parts_2 = two_calls()[0]
+    agree = bool(torch.allclose(parts_f, parts_2, rtol=2e-2))     # bf16 predictions on both sides, a few round the other way
+    t_f = time_call(lambda: linear_loss(x, w, b, tgt_d))
+    t_fp = time_call(lambda: linear_loss(x, w, b, tgt_d, want_pred=True))
+    t_2 = time_call(two_calls)
+    t_2p = time_call(two_calls_padded)
+    t_mm = time_call(lambda: F.linear(x, w_pad, b_pad))
+    flops = 2.0 * n * 4096 * 1470
+    peak = float(peaks.get("bf16_tflops", 1590.0))
+    tf = flops / (t_f * 1e-3) / 1e12
+    return {"what": "Linear(4096 -> 1470) + view + loss fwd + d loss / d prediction in one kernel, bf16 operands, fp32 accumulate",
+            "rows": n, "ms": t_f, "ms_with_fp32_predictions_written": t_fp,
+            "roofline": {"bound": "tensor", "kernel": "head_linear_loss_kernel<bf16, bf16, 2>", "achieved": tf, "peak": peak,
+                         "unit": "TFLOP/s", "frac": tf / peak, "useful_flops_per_launch": flops,
+                         "issued_flops_per_launch": 2.0 * n * 4096 * 1568,
+                         "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops, cuBLAS 8192^3 burst)" if "bf16_tflops" in peaks
+                         else "of fallback 1.59 PFLOP/s"},
+            "torch_linear_plus_loss_kernel_ms": t_2, "torch_linear_padded_1472_plus_loss_kernel_ms": t_2p,
+            "cublas_linear_padded_1472_alone_ms": t_mm, "speedup_vs_two_calls": t_2 / t_f,
+            "speedup_vs_two_calls_padded": t_2p / t_f, "loss_parts_agree_with_two_calls": agree,
+            "loss_total": float(parts_f[0])}
 
 
 def workload_config(args, images_per_gpu):
@@ -697,6 +752,13 @@ def main():
                       "frac": map_bytes / (map_ms * 1e-3) / 1e9 / peak},
     }
 
+    head_linear_rec = None
+    if not args.no_head_linear and rank == 0 and (S, B, C) == (7, 2, 20):
+        try:
+            head_linear_rec = head_linear_record(n, tgt_d, peaks, time_call)
+        except Exception as exc:  # noqa: BLE001 - the headline line must still print
+            head_linear_rec = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+
     # ---- the other BASELINE.json configs, after the timed region (records, not the headline)
     other = {}
     if not args.no_other_configs:
@@ -718,6 +780,7 @@ def main():
             "result_check": {"loss_total": loss_total, "mAP50:95": map5095, "sensitive": check},
             "value_loss": halves["value_loss"], "value_map": halves["value_map"], "other_configs": other,
         }
+        line["head_linear_loss"] = head_linear_rec
         line["step_launch"] = step_launch
         line["eager"] = {"value": world * n / (eager_ms * 1e-3), "ms_per_step": eager_ms}
         line["graph_serial"] = graph_serial

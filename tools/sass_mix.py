@@ -5,7 +5,9 @@
 Readable without a GPU: how much of each kernel is fp64 (DADD / DMUL / DFMA / DSETP), shared-memory traffic
 (LDS / STS / ATOMS), warp collectives (SHFL / VOTE / REDUX / MATCH), and which opcodes dominate.  No tensor-core
 (UTC*MMA / HMMA), TMEM (LDTM) or TMA (UTMALDG) opcode is expected in the per-image kernels: nothing there is a
-contraction and an image start is only 8-byte aligned; they would show up here if they were used."""
+contraction and an image start is only 8-byte aligned.  They are what the fused head Linear + loss kernel (the last
+entry, the one contraction next to this path) is made of: UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = TMA tensor
+load, UTCBAR = tcgen05.commit, SYNCS = mbarrier operations."""
 import collections
 import os
 import re
@@ -15,7 +17,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "yolo_v1_b200", "libyolohead.so")
 WANT = [("N2yh17map_update_kernel", "yh::map_update_kernel"), ("decode_nms_kernelILi1E", "yh::decode_nms_kernel<YH_IOU_INFER>"),
         ("loss_kernelIfLb0E", "yh::loss_kernel<float, staged>"), ("radix_pass", "yh::radix_pass"),
-        ("xi_scatter", "yh::xi_scatter"), ("emit_precisions", "yh::emit_precisions")]
+        ("xi_scatter", "yh::xi_scatter"), ("emit_precisions", "yh::emit_precisions"),
+        ("head_linear_loss_kernelI13__nv_bfloat16S2_Li2E", "yh::hl::head_linear_loss_kernel<bf16, bf16, 2> (SM pair)")]
 GROUPS = {
     "fp64 (DADD DMUL DFMA DSETP)": r"^(DADD|DMUL|DFMA|DSETP|DMNMX)",
     "fp32 (FADD FMUL FFMA FSETP FMNMX FSEL MUFU)": r"^(FADD|FMUL|FFMA|FSETP|FMNMX|FMNMX3|FSEL|MUFU|FCHK)",
@@ -55,6 +58,17 @@ for needle, title in WANT:
         print(f"| {name} | {c} | {100 * c / total:.1f} % |")
     print(f"| other ({' '.join(sorted(left)[:8])}) | {total - seen} | {100 * (total - seen) / total:.1f} % |\n")
     print("top opcodes: " + ", ".join(f"{k} {v}" for k, v in cnt.most_common(18)) + "\n")
+    tc = {k: v for k, v in cnt.items() if re.match(GROUPS["tensor core / TMEM / TMA (HMMA UTC*MMA LDTM UTMALDG ...)"], k)}
+    if tc:
+        print("tensor core / TMEM / TMA opcodes: " + ", ".join(f"{k} {v}" for k, v in sorted(tc.items(), key=lambda kv: -kv[1])) + "\n")
+        ex = [t for o, t in ops if o in ("UTCHMMA", "LDTM", "UTMALDG", "UTCBAR")]
+        seen_op, keep = set(), []
+        for t in ex:
+            op = t.split()[0]
+            if op not in seen_op:
+                seen_op.add(op)
+                keep.append(re.sub(r"\s*/\*.*", "", t).strip())
+        print("excerpt: `" + "`, `".join(keep) + "`\n")
     f64 = [t for o, t in ops if re.match(r"^(DADD|DMUL|DFMA|DSETP)", o)]
     if f64:
         print("fp64 excerpt (first 6): `" + "`, `".join(re.sub(r"\s*/\*.*", "", t).strip() for t in f64[:6]) + "`\n")
