@@ -88,7 +88,7 @@ def test_rounded_prediction_matches_reference_on_rounded_prediction(gold, name):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("M", [1, 127, 128, 129, 1000, 4097])
+@pytest.mark.parametrize("M", [1, 127, 128, 129, 1000, 4097, 20001])
 def test_loss_is_the_loss_kernel_on_the_same_predictions(M, dtype):
     """The epilogue's loss arithmetic is yh_loss_fwd_bwd's: same parts, same gradient bits, on the predictions the kernel
     itself reports; the plain layer (targets=None) reports the same predictions; they match torch's fp32 Linear."""
@@ -175,3 +175,26 @@ def test_unsupported_shapes_and_dtypes_raise():
         FusedHeadLoss(torch.nn.Linear(4096, 7 * 7 * 13), YOLOLoss(C=3))
     parts, grad, pred = linear_loss(x[:0], w, None, tgt[:0])     # empty batch: nothing launched
     assert grad.shape == (0, 1470)
+
+
+def test_capturable_in_a_cuda_graph():
+    """The call only enqueues work (tensor maps travel as kernel arguments): captured once, replayed on new data."""
+    from yolo_v1_b200 import synth
+    from yolo_v1_b200.head_linear import linear_loss
+
+    M = 700
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = (torch.randn(M, 4096, device="cuda", generator=g) * 0.1).to(torch.bfloat16)
+    w = (torch.randn(1470, 4096, device="cuda", generator=g) * 0.02).to(torch.bfloat16)
+    b = torch.rand(1470, device="cuda", generator=g) * 0.6
+    tgt = synth.make_targets(M, seed=2, p_obj=0.1, size_mix=True).cuda()
+    linear_loss(x, w, b, tgt)                       # workspace exists before the capture
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        parts, grad, _ = linear_loss(x, w, b, tgt)
+    for seed in (21, 22):
+        x.copy_((torch.randn(M, 4096, device="cuda", generator=g.manual_seed(seed)) * 0.1).to(torch.bfloat16))
+        graph.replay()
+        want_parts, want_grad, _ = linear_loss(x, w, b, tgt)
+        assert torch.equal(parts, want_parts) and torch.equal(grad, want_grad)
