@@ -198,3 +198,22 @@ def test_capturable_in_a_cuda_graph():
         graph.replay()
         want_parts, want_grad, _ = linear_loss(x, w, b, tgt)
         assert torch.equal(parts, want_parts) and torch.equal(grad, want_grad)
+
+
+def test_every_visible_device_in_one_process():
+    """Per-device state (function attributes, workspaces, tensor maps): the same call on every GPU this process sees."""
+    from yolo_v1_b200 import synth
+    from yolo_v1_b200.head_linear import linear_loss
+
+    M = 300
+    x, w, b, tgt = synth.head_linear_inputs(M, 9)
+    outs = []
+    for d in range(torch.cuda.device_count()):
+        dev = torch.device("cuda", d)
+        args = (torch.from_numpy(x).to(dev, torch.bfloat16), torch.from_numpy(w).to(dev, torch.bfloat16),
+                torch.from_numpy(b).to(dev), torch.from_numpy(tgt).to(dev))
+        parts, grad, pred = linear_loss(*args, want_pred=True)
+        assert parts.device == dev
+        outs.append((parts.cpu(), grad.cpu(), pred.cpu()))
+    for o in outs[1:]:
+        assert all(torch.equal(a, b_) for a, b_ in zip(o, outs[0]))
