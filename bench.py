@@ -205,6 +205,20 @@ def head_linear_record(n, tgt_d, peaks, time_call):
     t_2 = time_call(two_calls)
     t_2p = time_call(two_calls_padded)
     t_mm = time_call(lambda: F.linear(x, w_pad, b_pad))
+    # the reference's default (non-AMP) step: fp32 operands through three TF32 passes against torch's fp32 Linear + the loss kernel
+    del w_pad, b_pad
+    x32, w32 = x.float(), w.float()
+
+    def two_calls_fp32():
+        pred = F.linear(x32, w32, b)
+        return loss_fwd_bwd(pred.view(n, 7, 7, 30), tgt_d, 7, 2, 20, 5.0, 0.5, True)
+
+    parts_3x = linear_loss(x32, w32, b, tgt_d)[0]
+    parts_32 = two_calls_fp32()[0]
+    agree32 = bool(torch.allclose(parts_3x, parts_32, rtol=1e-5))
+    t_3x = time_call(lambda: linear_loss(x32, w32, b, tgt_d), reps=5)
+    t_32 = time_call(two_calls_fp32, reps=3)
+    del x32, w32
     flops = 2.0 * n * 4096 * 1470
     peak = float(peaks.get("bf16_tflops", 1590.0))
     tf = flops / (t_f * 1e-3) / 1e12
@@ -218,7 +232,11 @@ def head_linear_record(n, tgt_d, peaks, time_call):
             "torch_linear_plus_loss_kernel_ms": t_2, "torch_linear_padded_1472_plus_loss_kernel_ms": t_2p,
             "cublas_linear_padded_1472_alone_ms": t_mm, "speedup_vs_two_calls": t_2 / t_f,
             "speedup_vs_two_calls_padded": t_2p / t_f, "loss_parts_agree_with_two_calls": agree,
-            "loss_total": float(parts_f[0])}
+            "loss_total": float(parts_f[0]),
+            "fp32_operands": {"what": "the reference's default (non-AMP) step: fp32 operands, 3xTF32 (three tensor-core passes, fp32's "
+                                      "accuracy) against torch's fp32 Linear (allow_tf32 off) + the loss kernel",
+                              "ms": t_3x, "torch_fp32_linear_plus_loss_kernel_ms": t_32, "speedup_vs_two_calls": t_32 / t_3x,
+                              "loss_parts_agree_with_two_calls_rtol_1e-5": agree32}}
 
 
 def workload_config(args, images_per_gpu):

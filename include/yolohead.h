@@ -42,6 +42,7 @@ extern "C" {
 #define YH_F32 0
 #define YH_F16 1
 #define YH_BF16 2
+#define YH_TF32 3 /* yh_head_linear_loss only: fp32 operands read by the tensor core as TF32, one pass (torch's allow_tf32) */
 
 /* iou_mode: which of the reference's IoU definitions NMS uses */
 #define YH_IOU_METRICS 0 /* metrics.py:298-341: inter/union, union == 0 -> 0            */
@@ -339,7 +340,10 @@ int yh_match_lists(const int64_t *det_off, const int32_t *det_cls, const double 
  *     loss, loss_dict = YOLOLoss(...)(x, targets); d loss / d x               src/yolo/loss.py:55-172 + autograd
  * by ONE tcgen05 / TMEM / TMA kernel whose epilogue evaluates the loss on the accumulator tile: the [M, 1470]
  * prediction tensor is not written to memory unless pred_out asks for it.
- *   x [M, 4096], weight [1470, 4096] (nn.Linear's own layout), both `dtype` (YH_F16 / YH_BF16), 16-byte aligned;
+ *   x [M, 4096], weight [1470, 4096] (nn.Linear's own layout), both `dtype`, 16-byte aligned: YH_F16 / YH_BF16, or fp32
+ *   operands for the reference's default (non-AMP) step -- YH_F32 = 3xTF32 (each operand split into the 19 bits TF32
+ *   keeps and the rest, three tensor-core passes: fp32's accuracy), YH_TF32 = one TF32 pass (what torch does under
+ *   allow_tf32); fp32 operands take an fp32 gradient and ignore round_pred;
  *   bias [1470] fp32 or NULL; tgt [M, 7, 7, 30] fp32, or NULL = plain Linear (pred_out required, parts / grad unused);
  *   round_pred != 0: the prediction is rounded to `dtype` before the loss sees it, as the autocast Linear's output is;
  *   parts[5] fp32 = total, coord, conf_obj, conf_noobj, class (loss.py:164-170);

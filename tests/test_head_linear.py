@@ -164,7 +164,9 @@ def test_unsupported_shapes_and_dtypes_raise():
     w = torch.zeros(1470, 4096, device="cuda", dtype=torch.bfloat16)
     tgt = torch.zeros(4, 7, 7, 30, device="cuda")
     with pytest.raises(NotImplementedError):
-        linear_loss(x.float(), w.float(), None, tgt)
+        linear_loss(x.double(), w.double(), None, tgt)
+    with pytest.raises(NotImplementedError):
+        linear_loss(x.float(), w, None, tgt)                      # operands of two types
     with pytest.raises(NotImplementedError):
         linear_loss(x[:, :2048].contiguous(), w[:, :2048].contiguous(), None, tgt)
     with pytest.raises(_lib.YoloHeadError):
@@ -217,3 +219,73 @@ def test_every_visible_device_in_one_process():
         outs.append((parts.cpu(), grad.cpu(), pred.cpu()))
     for o in outs[1:]:
         assert all(torch.equal(a, b_) for a, b_ in zip(o, outs[0]))
+
+
+# ----------------------------------------------------------------------------- fp32 operands (the reference's default step)
+@pytest.mark.parametrize("precision", ["3xtf32", "tf32"])
+@pytest.mark.parametrize("name", ["m64", "m333"])
+def test_fp32_operands_match_reference_fixture(gold, name, precision):
+    """The fixtures' operands have 8 significant bits: exact in TF32 too, so both precisions must reproduce the reference."""
+    from yolo_v1_b200.head_linear import linear_loss
+
+    x, w, b, tgt = _inputs(gold, name, torch.float32)
+    parts, grad, pred = linear_loss(x, w, b, tgt, want_pred=True, precision=precision)
+    assert grad.dtype is torch.float32
+    np.testing.assert_allclose(parts.cpu().numpy().astype(np.float64), gold[f"{name}/parts"], rtol=RTOL_FP32)
+    np.testing.assert_allclose(pred[:4].cpu().numpy(), gold[f"{name}/pred_head"], rtol=1e-5, atol=2e-6)
+    M = x.shape[0]
+    np.testing.assert_allclose(grad.view(M, 7, 7, 30)[:4].cpu().numpy(), gold[f"{name}/dpred_head"], rtol=2e-4, atol=1e-7)
+
+
+@pytest.mark.parametrize("M", [300, 4096])
+def test_3xtf32_has_fp32_accuracy_on_arbitrary_operands(M):
+    """Random fp32 operands (24 significant bits) against an fp64 Linear: 3xTF32 keeps the prediction within 2e-5 absolute
+    (torch's own fp32 Linear: 2e-6; what is left is the tensor core's truncating accumulate over 512 steps) and the loss
+    within 1e-5 relative -- north_star's tolerance; one TF32 pass is ~5e-4 / 4e-4, what torch's allow_tf32 gives."""
+    from yolo_v1_b200 import synth
+    from yolo_v1_b200.head_linear import linear_loss
+    from yolo_v1_b200.loss import loss_fwd_bwd
+
+    g = torch.Generator(device="cuda").manual_seed(M)
+    x = torch.randn(M, 4096, device="cuda", generator=g) * 0.1
+    w = torch.randn(1470, 4096, device="cuda", generator=g) * 0.02
+    b = torch.rand(1470, device="cuda", generator=g) * 0.6
+    tgt = synth.make_targets(M, seed=M, p_obj=0.2, size_mix=True).cuda()
+    ref = (x.double() @ w.double().T + b.double()).view(M, 7, 7, 30)
+    want_parts = loss_fwd_bwd(ref.float(), tgt, 7, 2, 20, 5.0, 0.5, False)[0].cpu().numpy()
+    parts, grad, pred = linear_loss(x, w, b, tgt, want_pred=True)                 # precision="3xtf32" is the default
+    assert (pred.double() - ref).abs().max().item() < 2e-5
+    np.testing.assert_allclose(parts.cpu().numpy(), want_parts, rtol=1e-5)
+    # the loss arithmetic is the loss kernel's on the predictions the kernel reports
+    same_parts, same_grad = loss_fwd_bwd(pred, tgt, 7, 2, 20, 5.0, 0.5, True)
+    assert torch.equal(grad.view_as(same_grad), same_grad)
+    np.testing.assert_allclose(parts.cpu().numpy(), same_parts.cpu().numpy(), rtol=2e-6)
+    parts1, _, pred1 = linear_loss(x, w, b, tgt, want_pred=True, precision="tf32")
+    err1 = (pred1.double() - ref).abs().max().item()
+    assert 5e-5 < err1 < 2e-3
+    np.testing.assert_allclose(parts1.cpu().numpy(), want_parts, rtol=2e-3)
+
+
+def test_module_with_fp32_operands_matches_reference_fixture(gold):
+    """FusedHeadLoss(operand_dtype=torch.float32): the reference's non-AMP step, gradients for activations, weight, bias."""
+    from yolo_v1_b200 import FusedHeadLoss, YOLOLoss, _lib
+    from yolo_v1_b200.head_linear import linear_loss
+
+    name = "m200"
+    x, w, b, tgt = _inputs(gold, name, torch.float32)
+    lin = torch.nn.Linear(4096, 1470).cuda()
+    with torch.no_grad():
+        lin.weight.copy_(w)
+        lin.bias.copy_(b)
+    fused = FusedHeadLoss(lin, YOLOLoss(), operand_dtype=torch.float32)
+    xr = x.clone().requires_grad_(True)
+    loss, d = fused(xr, tgt)
+    loss.backward()
+    np.testing.assert_allclose([d[k] for k in KEYS], gold[f"{name}/parts"], rtol=RTOL_FP32)
+    np.testing.assert_allclose(lin.bias.grad.cpu().numpy(), gold[f"{name}/db"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(xr.grad[:8, :256].cpu().numpy(), gold[f"{name}/dx_head"], rtol=1e-3, atol=1e-7)
+    np.testing.assert_allclose(lin.weight.grad[:64, :128].cpu().numpy(), gold[f"{name}/dw_head"], rtol=1e-3, atol=1e-7)
+    with pytest.raises(_lib.YoloHeadError):
+        linear_loss(x, w, b, tgt, grad_dtype=torch.bfloat16)      # fp32 operands take an fp32 gradient
+    with pytest.raises(ValueError):
+        linear_loss(x, w, b, tgt, precision="fp32")

@@ -1,7 +1,7 @@
 """The head's last Linear fused with the loss (yh_head_linear_loss) against torch's Linear (cuBLAS) + this package's loss
 kernel, CUDA events.
 
-    python tools/time_head_linear.py [--rows 65536] [--dtype bf16|fp16] [--reps 10]
+    python tools/time_head_linear.py [--rows 65536] [--dtype bf16|fp16|fp32] [--reps 10]
 
 Prints one JSON line: ms and useful TFLOP/s (2 * M * 4096 * 1470) of the fused kernel (loss + narrow gradient, no
 prediction written), of the plain layer (fp32 predictions written), of torch.nn.functional.linear with the layer's own
@@ -24,6 +24,41 @@ ap.add_argument("--rows", type=int, default=65536)
 ap.add_argument("--dtype", default="bf16")
 ap.add_argument("--reps", type=int, default=10)
 args = ap.parse_args()
+if args.dtype == "fp32":
+    # the reference's default (non-AMP) step: fp32 operands; 3xTF32 (fp32's accuracy) and one TF32 pass against torch's fp32 Linear
+    # with and without allow_tf32
+    M = args.rows
+    g = torch.Generator(device="cuda").manual_seed(0)
+    x = torch.randn(M, 4096, device="cuda", generator=g) * 0.1
+    w = torch.randn(1470, 4096, device="cuda", generator=g) * 0.02
+    b = torch.rand(1470, device="cuda", generator=g) * 0.6
+    tgt = synth.make_targets(M, seed=1, p_obj=0.055, size_mix=True).cuda()
+
+    def timeit32(fn):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / args.reps
+
+    def two():
+        pred = torch.nn.functional.linear(x, w, b)
+        return loss_fwd_bwd(pred.view(M, 7, 7, 30), tgt, 7, 2, 20, 5.0, 0.5, True)
+
+    rows = {"fused_3xtf32": timeit32(lambda: linear_loss(x, w, b, tgt, precision="3xtf32")),
+            "fused_tf32": timeit32(lambda: linear_loss(x, w, b, tgt, precision="tf32"))}
+    torch.backends.cuda.matmul.allow_tf32 = False
+    rows["torch_fp32_linear_plus_loss_kernel"] = timeit32(two)
+    torch.backends.cuda.matmul.allow_tf32 = True
+    rows["torch_allow_tf32_linear_plus_loss_kernel"] = timeit32(two)
+    flops = 2.0 * M * 4096 * 1470
+    print(json.dumps({"rows": M, "dtype": "fp32", "useful_flops": flops, "ms": {k: round(v, 4) for k, v in rows.items()},
+                      "tflops_useful": {k: round(flops / v * 1e-9, 1) for k, v in rows.items()}}))
+    sys.exit(0)
 dt = {"bf16": torch.bfloat16, "fp16": torch.float16}[args.dtype]
 M = args.rows
 

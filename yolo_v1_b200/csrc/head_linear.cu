@@ -37,17 +37,21 @@ namespace hl {
 
 constexpr int kK = 4096;              // in_features
 constexpr int kNOut = kCells * kD;    // 1470 out_features
-constexpr int kBM = 128, kBN = 224, kBK = 64;
+constexpr int kBM = 128, kBN = 224;
+constexpr int kRowBytes = 128;        // one K block of a tile row: 64 fp16 / bf16 or 32 fp32 (the 128-byte swizzle span)
 constexpr int kCellsPerTile = 7;      // 210 useful columns
 constexpr int kNUse = kCellsPerTile * kD;
 constexpr int kNTiles = kCells / kCellsPerTile;  // 7
-constexpr int kKBlocks = kK / kBK;    // 64
-constexpr int kABytes = kBM * kBK * 2;   // 16,384
+constexpr int kABytes = kBM * kRowBytes;   // 16,384
 constexpr int kAccStride = 256;       // TMEM columns between the two accumulators
 constexpr int kTmemCols = 512;
 constexpr int kEpiGroups = 2;          // epilogue warps per TMEM lane quarter: each takes a share of the tile's 7 cells
 constexpr int kEpiWarps = 4 * kEpiGroups;
 constexpr int kThreads = 64 + 32 * kEpiWarps;   // TMA warp, MMA warp, epilogue warps
+#ifndef YH_HL_CONV_WARPS
+#define YH_HL_CONV_WARPS 6   // 2 / 4 / 6 warps: 4.57 / 4.13 / 3.99 ms at 65,536 rows (16 warps in all; they cost no registers over 14)
+#endif
+constexpr int kConvWarps = YH_HL_CONV_WARPS;   // 3xTF32 only: warps that split a landed fp32 stage into its hi and lo parts
 static_assert(kNTiles * kCellsPerTile == kCells, "cells per tile");
 
 // ------------------------------------------------------------------ PTX
@@ -141,6 +145,12 @@ template <> struct Elem<__nv_bfloat16> {
         __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
         return *reinterpret_cast<unsigned *>(&h);
     }
+};
+
+template <> struct Elem<float> {   // fp32 operands: the tensor core reads them as TF32 (kind::tf32); nothing to round, fp32 gradient
+    static constexpr int fmt = 2;
+    static __device__ __forceinline__ float round(float v) { return v; }
+    static __device__ __forceinline__ unsigned pack(float a, float) { return __float_as_uint(a); }
 };
 
 // ------------------------------------------------------------------ the loss of one cell, in registers
@@ -262,17 +272,23 @@ struct Args {
 // own shared memory and the two halves of B from both, and accumulates into each CTA's own TMEM.  Per SM that is
 // 7.5 KB of shared-memory reads per K = 16 step instead of 11 KB, and 30 KB of TMA writes per stage instead of 44 KB --
 // the single-CTA form needs ~200 B / clk of a 128 B / clk shared memory to keep the tensor core busy.
-template <int CTAS>
+// PASSES = 3 (fp32 operands only): 3xTF32.  a = hi + lo with hi = a's top 19 bits (what TF32 keeps) and lo = a - hi (exact in
+// fp32); x.w ~ hi.hi + hi.lo + lo.hi leaves a relative error of ~2^-21 per product, fp32's own.  Two converter warps
+// turn every landed stage into (hi in place, lo in a second tile) before the MMA warp may read it.
+template <int CTAS, int PASSES>
 struct Cfg {
     static constexpr int kBRows = kBN / CTAS;                    // rows of the B tile one CTA holds
-    static constexpr int kBBytes1 = kBRows * kBK * 2;
+    static constexpr int kBBytes1 = kBRows * kRowBytes;
     static constexpr int kStageBytes1 = kABytes + kBBytes1;      // 45,056 / 30,720
-    static constexpr int kStages1 = CTAS == 1 ? 4 : 6;
+    static constexpr int kStages1 = PASSES == 3 ? 3 : (CTAS == 1 ? 4 : 6);
+    static constexpr int kThreads1 = kThreads + (PASSES == 3 ? 32 * kConvWarps : 0);
 };
-template <int CTAS>
+template <int CTAS, int PASSES>
 struct SmemT {
-    alignas(1024) unsigned char tiles[Cfg<CTAS>::kStages1][Cfg<CTAS>::kStageBytes1];
-    alignas(8) unsigned long long full[Cfg<CTAS>::kStages1], empty[Cfg<CTAS>::kStages1], acc_full[2], acc_empty[2];
+    alignas(1024) unsigned char tiles[Cfg<CTAS, PASSES>::kStages1][Cfg<CTAS, PASSES>::kStageBytes1];
+    alignas(1024) unsigned char lo[PASSES == 3 ? Cfg<CTAS, PASSES>::kStages1 : 1][PASSES == 3 ? Cfg<CTAS, PASSES>::kStageBytes1 : 16];
+    alignas(8) unsigned long long full[Cfg<CTAS, PASSES>::kStages1], empty[Cfg<CTAS, PASSES>::kStages1],
+        conv[Cfg<CTAS, PASSES>::kStages1], acc_full[2], acc_empty[2];
     unsigned tmem_base;
     float bias[kNTiles * kBN];        // bias of every N tile, padded to 224 (zeros)
     float2 out[kEpiWarps][32 * (kD / 2)];   // one cell of a warp's 32 rows on its way out (3,840 B per warp)
@@ -320,16 +336,64 @@ __device__ __forceinline__ void mma_f16_pair(unsigned tmem_d, unsigned long long
         : "memory");
 }
 
-template <typename T, typename GT, int CTAS>
-__global__ void __launch_bounds__(kThreads, 1)   // 10 warps are allocated as 12: 168 registers per thread
+__device__ __forceinline__ void mma_tf32(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc, unsigned idesc,
+                                         unsigned accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mma_tf32_pair(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc, unsigned idesc,
+                                              unsigned accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+template <typename T, int CTAS>
+__device__ __forceinline__ void mma_any(unsigned d, unsigned long long ad, unsigned long long bd, unsigned idesc, unsigned acc) {
+    if (sizeof(T) == 4) {
+        if (CTAS == 2) mma_tf32_pair(d, ad, bd, idesc, acc); else mma_tf32(d, ad, bd, idesc, acc);
+    } else {
+        if (CTAS == 2) mma_f16_pair(d, ad, bd, idesc, acc); else mma_f16(d, ad, bd, idesc, acc);
+    }
+}
+// arrival that publishes this thread's earlier writes to a waiter in another CTA of the cluster
+__device__ __forceinline__ void bar_arrive_cluster_release(unsigned cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void bar_wait_cluster_acquire(unsigned long long *b, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "W_%=:\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra D_%=;\n"
+        "bra W_%=;\n"
+        "D_%=:\n"
+        "}\n" ::"r"(s32(b)), "r"(parity) : "memory");
+}
+
+template <typename T, typename GT, int CTAS, int PASSES>
+__global__ void __launch_bounds__(Cfg<CTAS, PASSES>::kThreads1, 1)   // 10 (12) warps are allocated as 12: 168 registers per thread
 head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Args a) {
-    using C = Cfg<CTAS>;
+    using C = Cfg<CTAS, PASSES>;
     constexpr int kSt = C::kStages1;
+    constexpr int kBKe = kRowBytes / (int)sizeof(T);            // K elements per block: 64 (fp16 / bf16) or 32 (fp32)
+    constexpr int kKBlocks = kK / kBKe;
+    constexpr int kNThreads = C::kThreads1;
+    constexpr bool kOwnFull = CTAS == 1 || PASSES == 3;          // every CTA waits for its own loads (the converter needs to)
     // No static shared memory in this kernel: the dynamic window starts at offset 0 of the CTA's shared memory, which is
     // what gives the tiles the 1,024-byte alignment the 128-byte swizzle needs (checked below).  Used in place, so that
     // the compiler keeps the shared address space (an integer round-up of the pointer turns every access generic).
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    SmemT<CTAS> &sm = *reinterpret_cast<SmemT<CTAS> *>(smem_raw);
+    SmemT<CTAS, PASSES> &sm = *reinterpret_cast<SmemT<CTAS, PASSES> *>(smem_raw);
     if ((s32(smem_raw) & 1023u) != 0u) __trap();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned rank = CTAS == 2 ? cluster_rank() : 0u;       // 0 = the leader: issues the MMAs, owns full / acc_empty
@@ -341,6 +405,7 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         for (int s = 0; s < kSt; ++s) {
             bar_init(&sm.full[s], 1);
             bar_init(&sm.empty[s], 1);
+            bar_init(&sm.conv[s], kConvWarps * CTAS);
         }
         for (int s = 0; s < 2; ++s) {
             bar_init(&sm.acc_full[s], 1);
@@ -349,7 +414,7 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    for (int i = threadIdx.x; i < kNTiles * kBN; i += kThreads) {
+    for (int i = threadIdx.x; i < kNTiles * kBN; i += kNThreads) {
         const int nb = i / kBN, j = i - nb * kBN;
         sm.bias[i] = (a.bias != nullptr && j < kNUse) ? __ldg(a.bias + nb * kNUse + j) : 0.f;
     }
@@ -377,16 +442,16 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                 const int a_row = (m_unit * CTAS + (int)rank) * kBM, b_row = n_blk * kNUse + (int)rank * C::kBRows;
                 for (int kb = 0; kb < kKBlocks; ++kb) {
                     bar_wait(&sm.empty[s], ph ^ 1);
-                    if (CTAS == 2) {
+                    if (!kOwnFull) {
                         // all bytes of both CTAs complete on the leader's barrier; the leader arms it for the pair
                         const unsigned full0 = map_to_rank(s32(&sm.full[s]), 0);
                         if (rank == 0) bar_expect(&sm.full[s], 2 * C::kStageBytes1);
-                        tma_load_2d_pair(sm.tiles[s], &map_a, kb * kBK, a_row, full0);
-                        tma_load_2d_pair(sm.tiles[s] + kABytes, &map_b, kb * kBK, b_row, full0);
+                        tma_load_2d_pair(sm.tiles[s], &map_a, kb * kBKe, a_row, full0);
+                        tma_load_2d_pair(sm.tiles[s] + kABytes, &map_b, kb * kBKe, b_row, full0);
                     } else {
                         bar_expect(&sm.full[s], C::kStageBytes1);
-                        tma_load_2d(sm.tiles[s], &map_a, kb * kBK, a_row, &sm.full[s]);
-                        tma_load_2d(sm.tiles[s] + kABytes, &map_b, kb * kBK, b_row, &sm.full[s]);
+                        tma_load_2d(sm.tiles[s], &map_a, kb * kBKe, a_row, &sm.full[s]);
+                        tma_load_2d(sm.tiles[s] + kABytes, &map_b, kb * kBKe, b_row, &sm.full[s]);
                     }
                     if (++s == kSt) { s = 0; ph ^= 1; }
                 }
@@ -401,25 +466,65 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                 bar_wait(&sm.acc_empty[as], aph ^ 1);          // the epilogue (of both CTAs) has drained this accumulator
                 fence_after();
                 const unsigned d = tmem + as * kAccStride;
+                // 3xTF32: the two small cross terms get an accumulator of their own.  The tensor core truncates on every
+                // accumulate (~2^-24 of the accumulator per MMA): in one accumulator the 1,024 extra steps of the cross terms
+                // would cost more accuracy (2e-5 absolute on a prediction) than the terms add; apart, they cost nothing.
+                const unsigned d_small = tmem + kAccStride;
                 for (int kb = 0; kb < kKBlocks; ++kb) {
-                    bar_wait(&sm.full[s], ph);
+                    if (PASSES == 3) bar_wait_cluster_acquire(&sm.conv[s], ph);   // both CTAs' stages are split into hi and lo
+                    else bar_wait(&sm.full[s], ph);
                     fence_after();
                     const unsigned long long ad = smem_desc(s32(sm.tiles[s])), bd = smem_desc(s32(sm.tiles[s] + kABytes));
 #pragma unroll
-                    for (int k = 0; k < kBK / 16; ++k) {      // 32 bytes along K per instruction: + 2 in the address field
-                        if (CTAS == 2) mma_f16_pair(d, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
-                        else mma_f16(d, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                    for (int k = 0; k < kRowBytes / 32; ++k) {      // 32 bytes along K per instruction: + 2 in the address field
+                        mma_any<T, CTAS>(d, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                        if constexpr (PASSES == 3) {
+                            const unsigned long long al = smem_desc(s32(sm.lo[s])), bl = smem_desc(s32(sm.lo[s] + kABytes));
+                            mma_any<T, CTAS>(d_small, ad + 2 * k, bl + 2 * k, idesc, (kb | k) != 0);     // hi . lo
+                            mma_any<T, CTAS>(d_small, al + 2 * k, bd + 2 * k, idesc, 1u);                // lo . hi
+                        }
                     }
                     if (CTAS == 2) mma_commit_pair(&sm.empty[s]); else mma_commit(&sm.empty[s]);   // frees the stage
                     if (++s == kSt) { s = 0; ph ^= 1; }
                 }
                 if (CTAS == 2) mma_commit_pair(&sm.acc_full[as]); else mma_commit(&sm.acc_full[as]);
-                as ^= 1;
-                if (as == 0) aph ^= 1;
+                if (PASSES == 3) aph ^= 1;                      // one accumulator pair: the next tile waits for the epilogue
+                else { as ^= 1; if (as == 0) aph ^= 1; }
             }
         }
         __syncwarp();
-    } else {                                   // ---- epilogue: warps 2..5 own TMEM lanes 32 * (warp % 4) ..
+    } else if (PASSES == 3 && warp >= 2 + kEpiWarps) {
+      if constexpr (PASSES == 3) {
+        // ---- converters (3xTF32): hi = the top 19 bits in place, lo = value - hi in the second tile; elementwise, so the
+        // swizzled layout does not matter.  Then the writes are made visible to the tensor core (async proxy) and the
+        // leader's MMA warp is told, across the cluster.
+        const int ct = (warp - 2 - kEpiWarps) * 32 + lane;
+        int s = 0, ph = 0;
+        const unsigned conv0 = CTAS == 2 ? map_to_rank(s32(&sm.conv[0]), 0) : s32(&sm.conv[0]);
+        for (int t = unit; t < total; t += units) {
+            for (int kb = 0; kb < kKBlocks; ++kb) {
+                bar_wait(&sm.full[s], ph);
+                uint4 *hi4 = reinterpret_cast<uint4 *>(sm.tiles[s]);
+                float4 *lo4 = reinterpret_cast<float4 *>(sm.lo[s]);
+#pragma unroll 6
+                for (int i = ct; i < C::kStageBytes1 / 16; i += 32 * kConvWarps) {
+                    const uint4 v = hi4[i];
+                    const uint4 h = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u);
+#ifdef YH_HL_HI_MASK   // not needed: the tensor core ignores the low 13 bits of a TF32 operand (same results bit for bit, 4 % faster)
+                    hi4[i] = h;
+#endif
+                    lo4[i] = make_float4(__uint_as_float(v.x) - __uint_as_float(h.x), __uint_as_float(v.y) - __uint_as_float(h.y),
+                                         __uint_as_float(v.z) - __uint_as_float(h.z), __uint_as_float(v.w) - __uint_as_float(h.w));
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) bar_arrive_cluster_release(conv0 + (unsigned)(s * sizeof(unsigned long long)));
+                if (++s == kSt) { s = 0; ph ^= 1; }
+            }
+        }
+        __syncwarp();
+      }
+    } else {                                   // ---- epilogue: warps 2..9 own TMEM lanes 32 * (warp % 4) ..
         const int q = warp & 3, grp = (warp - 2) >> 2;
         const int c_lo = (grp * kCellsPerTile + kEpiGroups - 1) / kEpiGroups, c_hi = ((grp + 1) * kCellsPerTile + kEpiGroups - 1) / kEpiGroups;
         double sum_coord = 0.0, sum_obj = 0.0, sum_noobj = 0.0, sum_cls = 0.0;
@@ -452,6 +557,12 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                 float v[32];
                 __syncwarp();                  // tcgen05.ld is warp-wide: lanes that left the previous cell early wait here
                 tmem_ld32(taddr + c * kD, v);
+                if constexpr (PASSES == 3) {   // + the cross terms' accumulator
+                    float u[32];
+                    tmem_ld32(taddr + kAccStride + c * kD, u);
+#pragma unroll
+                    for (int j = 0; j < kD; ++j) v[j] += u[j];
+                }
                 const float *b = sm.bias + n_blk * kBN + c * kD;
 #pragma unroll
                 for (int j = 0; j < kD; ++j) {
@@ -517,8 +628,8 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                 if (CTAS == 2) bar_arrive_cluster(map_to_rank(s32(&sm.acc_empty[as]), 0));
                 else bar_arrive(&sm.acc_empty[as]);
             }
-            as ^= 1;
-            if (as == 0) aph ^= 1;
+            if (PASSES == 3) aph ^= 1;
+            else { as ^= 1; if (as == 0) aph ^= 1; }
         }
         // the warp's four sums (fp64 from here on)
         double s4[4] = {sum_coord, sum_obj, sum_noobj, sum_cls};
@@ -596,15 +707,17 @@ EncodeTiledFn encode_tiled() {
     return fn;
 }
 
-// rows x 4096 K-major fp16 / bf16 matrix, boxes of 64 K-elements x box_rows rows, 128-byte swizzle, zero fill outside
+// rows x 4096 K-major matrix (fp16 / bf16 / fp32), boxes of one 128-byte K block x box_rows rows, 128-byte swizzle, zero fill outside
 bool make_map(CUtensorMap *map, const void *base, int dtype, long long rows, int box_rows) {
     EncodeTiledFn fn = encode_tiled();
     if (fn == nullptr) return false;
+    const int esize = (dtype == YH_F16 || dtype == YH_BF16) ? 2 : 4;
     const cuuint64_t dims[2] = {(cuuint64_t)hl::kK, (cuuint64_t)rows};
-    const cuuint64_t strides[1] = {(cuuint64_t)hl::kK * 2};
-    const cuuint32_t box[2] = {(cuuint32_t)hl::kBK, (cuuint32_t)box_rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)hl::kK * esize};
+    const cuuint32_t box[2] = {(cuuint32_t)(hl::kRowBytes / esize), (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    const CUtensorMapDataType dt = dtype == YH_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const CUtensorMapDataType dt = dtype == YH_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                   : dtype == YH_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     return fn(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
@@ -621,15 +734,15 @@ int ctas_per_tile() {
     return cached;
 }
 
-template <typename T, typename GT, int CTAS>
+template <typename T, typename GT, int CTAS, int PASSES = 1>
 int launch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int ctas, cudaStream_t st) {
     static std::atomic<bool> attr_done[kMaxDevices];
-    const int smem = (int)sizeof(hl::SmemT<CTAS>);
-    auto kern = hl::head_linear_loss_kernel<T, GT, CTAS>;
+    const int smem = (int)sizeof(hl::SmemT<CTAS, PASSES>);
+    auto kern = hl::head_linear_loss_kernel<T, GT, CTAS, PASSES>;
     if (first_use_on_device(attr_done)) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas);
-    cfg.blockDim = dim3(hl::kThreads);
+    cfg.blockDim = dim3(hl::Cfg<CTAS, PASSES>::kThreads1);
     cfg.dynamicSmemBytes = (size_t)smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -649,6 +762,8 @@ int launch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int 
 
 template <int CTAS>
 int dispatch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int ctas, int dtype, bool g32, cudaStream_t st) {
+    if (dtype == YH_F32) return launch<float, float, CTAS, 3>(ma, mb, a, ctas, st);     // fp32 operands, 3xTF32: fp32's accuracy
+    if (dtype == YH_TF32) return launch<float, float, CTAS, 1>(ma, mb, a, ctas, st);    // fp32 operands, one TF32 pass
     if (dtype == YH_F16)
         return g32 ? launch<__half, float, CTAS>(ma, mb, a, ctas, st) : launch<__half, __half, CTAS>(ma, mb, a, ctas, st);
     return g32 ? launch<__nv_bfloat16, float, CTAS>(ma, mb, a, ctas, st) : launch<__nv_bfloat16, __nv_bfloat16, CTAS>(ma, mb, a, ctas, st);
@@ -666,11 +781,12 @@ extern "C" int yh_head_linear_loss(const void *x, const void *weight, const floa
         set_error("yh_head_linear_loss: built for Linear(4096 -> 7*7*30), got in_features=%d S=%d B=%d C=%d", in_features, S, B, C);
         return YH_ERR_UNSUPPORTED;
     }
-    if (dtype != YH_F16 && dtype != YH_BF16) {
-        set_error("yh_head_linear_loss: operands must be fp16 or bf16 (dtype %d)", dtype);
+    if (dtype != YH_F16 && dtype != YH_BF16 && dtype != YH_F32 && dtype != YH_TF32) {
+        set_error("yh_head_linear_loss: operands must be fp16, bf16 or fp32 (dtype %d)", dtype);
         return YH_ERR_UNSUPPORTED;
     }
-    if (grad != nullptr && grad_dtype != dtype && grad_dtype != YH_F32) {
+    const bool narrow = dtype == YH_F16 || dtype == YH_BF16;
+    if (grad != nullptr && grad_dtype != YH_F32 && !(narrow && grad_dtype == dtype)) {
         set_error("yh_head_linear_loss: the gradient is written in the operand type or in fp32 (grad_dtype %d)", grad_dtype);
         return YH_ERR_BAD_ARG;
     }
