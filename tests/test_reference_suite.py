@@ -302,6 +302,43 @@ def test_predict_validates_every_candidate_before_nms(golden, tmp_path, case):
             assert got == want["kept"]
 
 
+def test_lazy_detections_equal_the_eager_lists_and_build_on_demand(golden):
+    """predict_batch(lazy=True): SURVEY 8(f) row 2 -- Detection objects are built when read, not when the batch returns;
+    the out-of-range check still happens up front."""
+    import time
+
+    from pydantic import ValidationError
+
+    from yolo_v1_b200 import synth
+    from yolo_v1_b200.inference import LazyDetections
+
+    n = 600
+    tgt = synth.make_targets(n, seed=31, p_obj=0.1, size_mix=True)
+    pred = synth.make_preds(n, "correlated", seed=31, targets=tgt)
+    eng = YOLOInference(_Fixed(pred[0]), device="cuda")
+    names = [f"c{i}" for i in range(20)]
+    t0 = time.perf_counter()
+    eager = eng.predict_batch(pred, 0.05, 0.4, names)
+    t1 = time.perf_counter()
+    lazy = eng.predict_batch(pred, 0.05, 0.4, names, lazy=True)
+    t2 = time.perf_counter()
+    assert all(isinstance(d, LazyDetections) for d in lazy) and sum(d.built for d in lazy) == 0
+    assert [len(d) for d in lazy] == [len(d) for d in eager] and sum(len(d) for d in eager) > 1000
+    i = max(range(n), key=lambda j: len(eager[j]))
+    assert lazy[i][0] == eager[i][0] and lazy[i].built == 1 and lazy[i][-1] == eager[i][-1] and lazy[i].built == 2
+    assert lazy[i][1:3] == eager[i][1:3] and isinstance(lazy[i][0], Detection) and lazy[i][0].class_name.startswith("c")
+    assert (lazy[i].class_ids.tolist(), lazy[i].confidences.tolist()) == ([d.class_id for d in eager[i]], [d.confidence for d in eager[i]])
+    with pytest.raises(IndexError):
+        lazy[i][len(lazy[i])]
+    assert all(a == b for a, b in zip(lazy, eager)) and lazy[i] == eager[i] and not (lazy[i] == eager[i][:-1])
+    assert sum(d.built for d in lazy) == sum(len(d) for d in eager)
+    assert (t2 - t1) < (t1 - t0)          # nothing was built in the lazy call
+    g = golden("validation")
+    bad = torch.from_numpy(g["suppressed_x_gt_1/pred"])
+    with pytest.raises(ValidationError):
+        eng.predict_batch(torch.stack([pred[0], bad]), 0.5, 0.4, lazy=True)
+
+
 # ------------------------------------------------------------------ evaluate_model (metrics.py:654-714)
 def test_evaluate_model_over_a_dataloader_equals_the_metric_fed_the_same_batches():
     """model + DataLoader of HOST tensors + device string in, compute() dict out: the same dict as an mAPMetric

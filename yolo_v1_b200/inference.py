@@ -9,6 +9,7 @@ batched form the kernel is built for.
 from __future__ import annotations
 
 import warnings
+from collections.abc import Sequence
 
 import torch
 import torch.nn as nn
@@ -23,6 +24,67 @@ def _default_device() -> str:
     if torch.cuda.is_available():
         return "cuda"
     raise _lib.YoloHeadError("no CUDA device: YOLOInference post-processing has no CPU fallback")
+
+
+class LazyDetections(Sequence):
+    """The detections of one image as a read-only sequence: `Detection` objects (pydantic-validated, as the reference
+    builds them at inference.py:197-208) are constructed when an element is first read and kept.  len(), indexing,
+    slicing, iteration and == against a list of Detections behave like the eager list predict_batch() returns."""
+
+    __slots__ = ("_cls", "_conf", "_box", "_names", "_items", "built")
+
+    def __init__(self, cls, conf, box, class_names):
+        self._cls, self._conf, self._box, self._names = cls, conf, box, class_names
+        self._items: list = [None] * len(cls)
+        self.built = 0                       # Detections constructed so far
+
+    def __len__(self) -> int:
+        return len(self._items)
+
+    def _at(self, q: int) -> Detection:
+        d = self._items[q]
+        if d is None:
+            cid = int(self._cls[q])
+            b = self._box[q]
+            d = Detection(class_id=cid, class_name=self._names[cid] if self._names else f"class_{cid}",
+                          confidence=float(self._conf[q]),
+                          bbox=BoundingBox(x=float(b[0]), y=float(b[1]), width=float(b[2]), height=float(b[3])))
+            self._items[q] = d
+            self.built += 1
+        return d
+
+    def __getitem__(self, q):
+        if isinstance(q, slice):
+            return [self._at(i) for i in range(*q.indices(len(self._items)))]
+        n = len(self._items)
+        if q < -n or q >= n:
+            raise IndexError("LazyDetections index out of range")
+        return self._at(q % n)
+
+    def __iter__(self):
+        return (self._at(i) for i in range(len(self._items)))
+
+    def __eq__(self, other):
+        if isinstance(other, (list, tuple, LazyDetections)):
+            return len(other) == len(self) and all(a == b for a, b in zip(self, other))
+        return NotImplemented
+
+    def __repr__(self) -> str:
+        return f"LazyDetections({len(self)} detections, {self.built} built)"
+
+    # what a caller can ask without building anything
+    @property
+    def class_ids(self):
+        return self._cls.astype("int64")
+
+    @property
+    def confidences(self):
+        return self._conf
+
+    @property
+    def boxes(self):
+        """(n, 4) float64 array of (x, y, width, height), normalised to the image."""
+        return self._box
 
 
 class YOLOInference:
@@ -66,7 +128,7 @@ class YOLOInference:
         return self.predict_batch(out[:1], conf_threshold, nms_threshold, class_names)[0]
 
     def predict_images(self, image_paths, conf_threshold: float = 0.5, nms_threshold: float = 0.4,
-                       class_names: list[str] | None = None, batch_size: int = 64) -> list[list[Detection]]:
+                       class_names: list[str] | None = None, batch_size: int = 64, lazy: bool = False) -> list[list[Detection]]:
         """predict() for many images (the loop of predict.py:128-185): every image is preprocessed to the
         same (3, 448, 448) tensor, `batch_size` of them go through the model in one forward, and decode + NMS
         of the whole batch is one launch.  Per image the same result as predict(path)."""
@@ -76,11 +138,11 @@ class YOLOInference:
             batch = torch.cat([self.preprocess_image(self.load_image(p)) for p in paths[lo:lo + batch_size]])
             with torch.no_grad():
                 pred = self.model(batch)
-            out.extend(self.predict_batch(pred, conf_threshold, nms_threshold, class_names))
+            out.extend(self.predict_batch(pred, conf_threshold, nms_threshold, class_names, lazy=lazy))
         return out
 
     def predict_batch(self, predictions: torch.Tensor, conf_threshold: float = 0.5, nms_threshold: float = 0.4,
-                      class_names: list[str] | None = None) -> list[list[Detection]]:
+                      class_names: list[str] | None = None, lazy: bool = False) -> list[list[Detection]]:
         """Decode + NMS for a whole (N,S,S,B*5+C) batch in one launch; one list per image.
 
         Same result per image as parse_predictions() followed by non_max_suppression() -- including
@@ -88,7 +150,11 @@ class YOLOInference:
         threshold before NMS runs (inference.py:133-136, 197-208), so a candidate outside [0, 1] raises
         pydantic's ValidationError even when NMS would have suppressed it.  The kernel flags such
         images (`bad_range`); the first flagged image is then decoded without NMS, which builds its
-        Detections in the reference's cell / box order and raises at the same candidate."""
+        Detections in the reference's cell / box order and raises at the same candidate.
+
+        lazy=True (extension): each image's result is a LazyDetections -- a read-only sequence over the kernel's
+        arrays that builds a validated `Detection` only when an element is first read (pydantic construction, ~10 us
+        per object, is the host bottleneck of a large batch).  Compares equal to the eager list."""
         S, B = self.model.S, self.model.B
         Cn = predictions.shape[-1] - B * 5
         predictions = self._on_cuda(predictions)
@@ -100,7 +166,7 @@ class YOLOInference:
             one = predictions[first] if predictions.dim() == 4 else predictions
             self.parse_predictions(one, conf_threshold, class_names)   # raises ValidationError
             raise _lib.YoloHeadError("yh_decode_nms flagged an out-of-range candidate that the schema accepted")
-        return self._build(r, class_names)
+        return self._build_lazy(r, class_names) if lazy else self._build(r, class_names)
 
     def parse_predictions(self, pred: torch.Tensor, conf_threshold: float,
                           class_names: list[str] | None = None) -> list[Detection]:
@@ -151,6 +217,13 @@ class YOLOInference:
 
     def _on_cuda(self, t: torch.Tensor) -> torch.Tensor:
         return t if t.is_cuda else t.to(self._cuda_device())
+
+    @staticmethod
+    def _build_lazy(r: head.DecodeResult, class_names) -> "list[LazyDetections]":
+        """One LazyDetections per image over host copies of the kernel's outputs (four device->host copies per batch)."""
+        n_keep = r.n_keep.cpu().numpy()
+        cls, conf, box = r.keep_cls.cpu().numpy(), r.keep_conf.cpu().numpy(), r.keep_box.cpu().numpy()
+        return [LazyDetections(cls[i, :n], conf[i, :n], box[i, :n], class_names) for i, n in enumerate(n_keep.tolist())]
 
     @staticmethod
     def _build(r: head.DecodeResult, class_names, sort_by_candidate: bool = False) -> list[list[Detection]]:
