@@ -770,13 +770,6 @@ def main():
                       "frac": map_bytes / (map_ms * 1e-3) / 1e9 / peak},
     }
 
-    head_linear_rec = None
-    if not args.no_head_linear and rank == 0 and (S, B, C) == (7, 2, 20):
-        try:
-            head_linear_rec = head_linear_record(n, tgt_d, peaks, time_call)
-        except Exception as exc:  # noqa: BLE001 - the headline line must still print
-            head_linear_rec = {"error": f"{type(exc).__name__}: {exc}"[:300]}
-
     # ---- the other BASELINE.json configs, after the timed region (records, not the headline)
     other = {}
     if not args.no_other_configs:
@@ -784,6 +777,16 @@ def main():
             other = other_configs(args, world, rank, dev, timed, barrier)
         except Exception as exc:  # noqa: BLE001 - the headline line must still print
             other = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+
+    # rank 0 alone, after every collective of this run (the other ranks wait at the barrier below)
+    head_linear_rec = None
+    if not args.no_head_linear and rank == 0 and (S, B, C) == (7, 2, 20):
+        try:
+            head_linear_rec = head_linear_record(n, tgt_d, peaks, time_call)
+        except Exception as exc:  # noqa: BLE001 - the headline line must still print
+            head_linear_rec = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+
+    barrier()
 
     if rank == 0:
         cpu = None
