@@ -133,12 +133,13 @@ _FUSED_WS = _lib.Workspace(zeroed=True)
 
 def map_update_loss(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_thr: float, thresholds,
                     gt_count: torch.Tensor, lambda_coord: float, lambda_noobj: float, want_grad: bool = True,
-                    tail_stream: "torch.cuda.Stream | None" = None):
+                    tail_stream: "torch.cuda.Stream | None" = None, phases: int = 3):
     """yh_map_update_loss: the update kernel with the loss (forward + backward) riding on it; one read of the two
     tensors.  S=7, B=2, C=20 and fp32 predictions.  Returns (chunk, parts (5,) fp32 device tensor, grad or None).
     tail_stream: run the loss tail (object cells, fold) there, forked behind the update kernel, so that whatever the
     caller enqueues next on the current stream (compaction, exchange, sort) starts right away; `parts` and the object
-    cells of `grad` are then ready on tail_stream, which the caller joins."""
+    cells of `grad` are then ready on tail_stream, which the caller joins.  phases (measurement only): 1 = the update
+    kernel alone, 2 = the loss tail alone (on what the last phase-1 call left in the workspace), 3 = both."""
     p = _check_pred(pred, "predictions", S_, B_, C_)
     t = _check_pred(tgt, "targets", S_, B_, C_)
     if p.shape != t.shape:
@@ -167,7 +168,7 @@ def map_update_loss(pred: torch.Tensor, tgt: torch.Tensor, conf_thr: float, nms_
 
     with _lib.on_device(dev):
         if tail_stream is None:
-            call(3, _lib.stream_ptr(dev))
+            call(int(phases), _lib.stream_ptr(dev))
         else:
             call(1, _lib.stream_ptr(dev))
             tail_stream.wait_stream(torch.cuda.current_stream(dev))
