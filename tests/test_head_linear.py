@@ -289,3 +289,27 @@ def test_module_with_fp32_operands_matches_reference_fixture(gold):
         linear_loss(x, w, b, tgt, grad_dtype=torch.bfloat16)      # fp32 operands take an fp32 gradient
     with pytest.raises(ValueError):
         linear_loss(x, w, b, tgt, precision="fp32")
+
+
+def test_non_finite_activations_stay_in_their_row():
+    """A NaN / inf in one image's activations makes that image's predictions (hence the total) non-finite, as torch's Linear
+    + the reference's criterion would; every other image's gradient is what it was."""
+    from yolo_v1_b200 import synth
+    from yolo_v1_b200.head_linear import linear_loss
+
+    M = 260
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = (torch.randn(M, 4096, device="cuda", generator=g) * 0.1).to(torch.bfloat16)
+    w = (torch.randn(1470, 4096, device="cuda", generator=g) * 0.02).to(torch.bfloat16)
+    b = torch.rand(1470, device="cuda", generator=g) * 0.6
+    tgt = synth.make_targets(M, seed=5, p_obj=0.2, size_mix=True).cuda()
+    _, clean, _ = linear_loss(x, w, b, tgt, grad_dtype=torch.float32)
+    for bad, row in ((float("nan"), 3), (float("inf"), 200)):
+        xb = x.clone()
+        xb[row, 77] = bad
+        parts, grad, pred = linear_loss(xb, w, b, tgt, grad_dtype=torch.float32, want_pred=True)
+        assert not torch.isfinite(parts[0])
+        assert not torch.isfinite(pred[row]).all()
+        keep = torch.ones(M, dtype=torch.bool, device="cuda")
+        keep[row] = False
+        assert torch.isfinite(pred[keep]).all() and torch.equal(grad[keep], clean[keep])
