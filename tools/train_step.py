@@ -39,8 +39,12 @@ class ResNetYolo(nn.Module):
         self.fc = nn.Sequential(nn.Flatten(), nn.Linear(1024 * S * S, 4096), act(), nn.Dropout(0.5),
                                 nn.Linear(4096, S * S * (B * 5 + C)))
 
-    def forward(self, x):
-        return self.fc(self.convs(self.backbone(x))).view(-1, self.S, self.S, self.B * 5 + self.C)
+    def forward(self, x, targets=None, fused=None, loss_scale=1.0):
+        if fused is None:
+            return self.fc(self.convs(self.backbone(x))).view(-1, self.S, self.S, self.B * 5 + self.C)
+        # --fused-head: everything up to the last Linear here, the layer + view + loss in yolo_v1_b200.FusedHeadLoss
+        # (inside forward so that DDP sees the layer's parameters being used)
+        return fused(self.fc[:-1](self.convs(self.backbone(x))), targets, loss_scale=loss_scale)
 
 
 def main():
@@ -49,6 +53,8 @@ def main():
     ap.add_argument("--batch", type=int, default=32, help="images per GPU")
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--fused-head", action="store_true",
+                    help="the head's last Linear + view + loss as one kernel (yolo_v1_b200.FusedHeadLoss) instead of Linear, then YOLOLoss")
     a = ap.parse_args()
     world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -63,6 +69,11 @@ def main():
     opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, weight_decay=5e-4)
     crit = YOLOLoss(defer_loss_dict=True)
     amp = {"none": None, "bf16": torch.bfloat16, "fp16": torch.float16}[a.amp]
+    fused = None
+    if a.fused_head:
+        from yolo_v1_b200 import FusedHeadLoss
+        inner = model.module if world > 1 else model
+        fused = FusedHeadLoss(inner.fc[-1], crit, operand_dtype=amp if amp is not None else torch.float32)
     scaler = torch.amp.GradScaler("cuda") if amp == torch.float16 else None
     g = torch.Generator().manual_seed(1234 + rank)
     x = torch.randn(a.batch, 3, 448, 448, generator=g).to(dev).contiguous(memory_format=torch.channels_last)
@@ -78,11 +89,15 @@ def main():
 
     def _step(use_kernel):
         with torch.autocast("cuda", dtype=amp, enabled=amp is not None):
-            pred = model(x)
-            if use_kernel:
-                loss, parts = crit(pred, t)
+            if use_kernel and fused is not None:
+                loss, parts = model(x, t, fused, scaler.get_scale() if scaler is not None else 1.0)
+                pred = None
             else:
-                loss, parts = pred.float().square().mean(), None
+                pred = model(x)
+                if use_kernel:
+                    loss, parts = crit(pred, t)
+                else:
+                    loss, parts = pred.float().square().mean(), None
         if scaler is not None:
             scaler.scale(loss).backward()
             scaler.step(opt)
@@ -118,6 +133,9 @@ def main():
     if world > 1:   # the same step without DDP's gradient all-reduce: the difference is what NCCL adds to the step
         step(True, sync=False)
         nosync_ms, _ = timed(lambda: step(True, sync=False), a.steps)
+    if pred is None:   # --fused-head: the loss-alone timing below still wants a head output
+        with torch.no_grad(), torch.autocast("cuda", dtype=amp, enabled=amp is not None):
+            pred = model(x)
     head_out = pred.detach()
 
     def loss_only():
@@ -128,6 +146,7 @@ def main():
     lk_ms, _ = timed(loss_only, 50)
     if rank == 0:
         print(json.dumps({
+            "fused_head": bool(a.fused_head),
             "config": f"ResNet50-YOLOv1 training step, random init, {a.batch} x 448x448 per GPU, amp={a.amp}, "
                       f"{world} GPU(s){', DDP/NCCL' if world > 1 else ''}, SGD momentum",
             "step_ms": full_ms, "images_per_s": world * a.batch / (full_ms * 1e-3),
