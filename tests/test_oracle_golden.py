@@ -139,3 +139,20 @@ def test_encode_oracle_matches_reference(golden):
     for name in [str(n) for n in g["names"]]:
         got = encode_oracle.encode_target(g[f"{name}/boxes"].tolist(), g[f"{name}/cls"].tolist())
         assert got.tobytes() == g[f"{name}/target"].tobytes(), name
+
+
+@pytest.mark.parametrize("name", ["m64", "m200", "m333"])
+def test_head_linear_oracle_matches_reference(golden, name):
+    """tests/golden/head_linear.npz (the reference's nn.Linear + view + YOLOLoss + backward): the checker smoke() uses for
+    the fused kernel -- an fp32 CPU Linear over synth.head_linear_inputs followed by loss_oracle -- reproduces it."""
+    from yolo_v1_b200 import synth
+
+    g = golden("head_linear")
+    M, seed = int(g[f"{name}/M"]), int(g[f"{name}/seed"])
+    x, w, b, tgt = (torch.from_numpy(a) for a in synth.head_linear_inputs(M, seed))
+    pred = torch.nn.functional.linear(x, w, b).view(M, 7, 7, 30)
+    parts, grad = loss_oracle.yolo_loss_and_grad(pred, tgt)
+    np.testing.assert_allclose(parts.double().numpy(), g[f"{name}/parts"], rtol=1e-6)
+    np.testing.assert_allclose(pred[:4].numpy(), g[f"{name}/pred_head"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(grad[:4].numpy(), g[f"{name}/dpred_head"], rtol=1e-5, atol=1e-8)
+    np.testing.assert_allclose(grad.reshape(M, 1470).double().sum(0).numpy(), g[f"{name}/db"], rtol=1e-4, atol=1e-6)
