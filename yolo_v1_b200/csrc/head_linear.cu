@@ -382,7 +382,8 @@ __device__ __forceinline__ void bar_wait_cluster_acquire(unsigned long long *b, 
 
 template <typename T, typename GT, int CTAS, int PASSES>
 __global__ void __launch_bounds__(Cfg<CTAS, PASSES>::kThreads1, 1)   // 10 (12) warps are allocated as 12: 168 registers per thread
-head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Args a) {
+head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                        const __grid_constant__ CUtensorMap map_blo, const Args a) {
     using C = Cfg<CTAS, PASSES>;
     constexpr int kSt = C::kStages1;
     constexpr int kBKe = kRowBytes / (int)sizeof(T);            // K elements per block: 64 (fp16 / bf16) or 32 (fp32)
@@ -449,9 +450,11 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                         tma_load_2d_pair(sm.tiles[s], &map_a, kb * kBKe, a_row, full0);
                         tma_load_2d_pair(sm.tiles[s] + kABytes, &map_b, kb * kBKe, b_row, full0);
                     } else {
-                        bar_expect(&sm.full[s], C::kStageBytes1);
+                        // 3xTF32: the weight's lo part was split off once per call (split_lo_kernel) and arrives by TMA as well
+                        bar_expect(&sm.full[s], C::kStageBytes1 + (PASSES == 3 ? C::kBBytes1 : 0));
                         tma_load_2d(sm.tiles[s], &map_a, kb * kBKe, a_row, &sm.full[s]);
                         tma_load_2d(sm.tiles[s] + kABytes, &map_b, kb * kBKe, b_row, &sm.full[s]);
+                        if constexpr (PASSES == 3) tma_load_2d(sm.lo[s] + kABytes, &map_blo, kb * kBKe, b_row, &sm.full[s]);
                     }
                     if (++s == kSt) { s = 0; ph ^= 1; }
                 }
@@ -506,8 +509,8 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
                 bar_wait(&sm.full[s], ph);
                 uint4 *hi4 = reinterpret_cast<uint4 *>(sm.tiles[s]);
                 float4 *lo4 = reinterpret_cast<float4 *>(sm.lo[s]);
-#pragma unroll 6
-                for (int i = ct; i < C::kStageBytes1 / 16; i += 32 * kConvWarps) {
+#pragma unroll
+                for (int i = ct; i < kABytes / 16; i += 32 * kConvWarps) {      // the activations' rows; the weight's lo came by TMA
                     const uint4 v = hi4[i];
                     const uint4 h = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u);
 #ifdef YH_HL_HI_MASK   // not needed: the tensor core ignores the low 13 bits of a TF32 operand (same results bit for bit, 4 % faster)
@@ -682,6 +685,15 @@ head_linear_loss_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     }
 }
 
+// lo = w - (w with its low 13 bits cleared): the part of an fp32 weight that TF32 drops (exact in fp32)
+__global__ void __launch_bounds__(256) split_lo_kernel(const uint4 *__restrict__ w, float4 *__restrict__ lo, size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+        const uint4 v = __ldg(w + i);
+        lo[i] = make_float4(__uint_as_float(v.x) - __uint_as_float(v.x & 0xFFFFE000u), __uint_as_float(v.y) - __uint_as_float(v.y & 0xFFFFE000u),
+                            __uint_as_float(v.z) - __uint_as_float(v.z & 0xFFFFE000u), __uint_as_float(v.w) - __uint_as_float(v.w & 0xFFFFE000u));
+    }
+}
+
 }  // namespace hl
 }  // namespace yh
 
@@ -735,7 +747,7 @@ int ctas_per_tile() {
 }
 
 template <typename T, typename GT, int CTAS, int PASSES = 1>
-int launch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int ctas, cudaStream_t st) {
+int launch(const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mblo, const hl::Args &a, int ctas, cudaStream_t st) {
     static std::atomic<bool> attr_done[kMaxDevices];
     const int smem = (int)sizeof(hl::SmemT<CTAS, PASSES>);
     auto kern = hl::head_linear_loss_kernel<T, GT, CTAS, PASSES>;
@@ -752,7 +764,7 @@ int launch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int 
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, mb, a);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, mb, mblo, a);
     if (e != cudaSuccess) {
         set_error("yh_head_linear_loss: launch failed: %s", cudaGetErrorString(e));
         return (int)e;
@@ -761,17 +773,23 @@ int launch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int 
 }
 
 template <int CTAS>
-int dispatch(const CUtensorMap &ma, const CUtensorMap &mb, const hl::Args &a, int ctas, int dtype, bool g32, cudaStream_t st) {
-    if (dtype == YH_F32) return launch<float, float, CTAS, 3>(ma, mb, a, ctas, st);     // fp32 operands, 3xTF32: fp32's accuracy
-    if (dtype == YH_TF32) return launch<float, float, CTAS, 1>(ma, mb, a, ctas, st);    // fp32 operands, one TF32 pass
+int dispatch(const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &ml, const hl::Args &a, int ctas, int dtype, bool g32,
+             cudaStream_t st) {
+    if (dtype == YH_F32) return launch<float, float, CTAS, 3>(ma, mb, ml, a, ctas, st);     // fp32 operands, 3xTF32: fp32's accuracy
+    if (dtype == YH_TF32) return launch<float, float, CTAS, 1>(ma, mb, ml, a, ctas, st);    // fp32 operands, one TF32 pass
     if (dtype == YH_F16)
-        return g32 ? launch<__half, float, CTAS>(ma, mb, a, ctas, st) : launch<__half, __half, CTAS>(ma, mb, a, ctas, st);
-    return g32 ? launch<__nv_bfloat16, float, CTAS>(ma, mb, a, ctas, st) : launch<__nv_bfloat16, __nv_bfloat16, CTAS>(ma, mb, a, ctas, st);
+        return g32 ? launch<__half, float, CTAS>(ma, mb, ml, a, ctas, st) : launch<__half, __half, CTAS>(ma, mb, ml, a, ctas, st);
+    return g32 ? launch<__nv_bfloat16, float, CTAS>(ma, mb, ml, a, ctas, st)
+               : launch<__nv_bfloat16, __nv_bfloat16, CTAS>(ma, mb, ml, a, ctas, st);
 }
 
 }  // namespace
 
-extern "C" size_t yh_head_linear_loss_workspace_bytes(void) { return 256 + sizeof(double) * 4 * kMaxCtas; }
+// ticket + per-CTA partial sums + (3xTF32) the lo part of the weight, split off once per call
+static const size_t kWeightLoOffset = 256 + ((sizeof(double) * 4 * kMaxCtas + 255) & ~(size_t)255);
+extern "C" size_t yh_head_linear_loss_workspace_bytes(void) {
+    return kWeightLoOffset + sizeof(float) * (size_t)hl::kNOut * hl::kK;
+}
 
 extern "C" int yh_head_linear_loss(const void *x, const void *weight, const float *bias, int dtype, const float *tgt, int M,
                                    int S, int B, int C, int in_features, float lambda_coord, float lambda_noobj,
@@ -794,8 +812,8 @@ extern "C" int yh_head_linear_loss(const void *x, const void *weight, const floa
         set_error("yh_head_linear_loss: bad argument");
         return YH_ERR_BAD_ARG;
     }
-    if (tgt != nullptr && workspace_bytes < yh_head_linear_loss_workspace_bytes()) {
-        set_error("yh_head_linear_loss: workspace too small");
+    if ((tgt != nullptr || dtype == YH_F32) && (workspace == nullptr || workspace_bytes < yh_head_linear_loss_workspace_bytes())) {
+        set_error("yh_head_linear_loss: workspace too small (or missing)");
         return YH_ERR_WORKSPACE;
     }
     if (((uintptr_t)x | (uintptr_t)weight) & 15u) {
@@ -834,5 +852,17 @@ extern "C" int yh_head_linear_loss(const void *x, const void *weight, const floa
     a.parts = parts;
     cudaStream_t st = (cudaStream_t)stream;
     const bool g32 = grad == nullptr || grad_dtype == YH_F32;
-    return per == 2 ? dispatch<2>(ma, mb, a, ctas, dtype, g32, st) : dispatch<1>(ma, mb, a, ctas, dtype, g32, st);
+    CUtensorMap ml = mb;
+    if (dtype == YH_F32) {
+        float *wlo = (float *)((char *)workspace + kWeightLoOffset);
+        const size_t n4 = (size_t)hl::kNOut * hl::kK / 4;
+        hl::split_lo_kernel<<<148 * 8, 256, 0, st>>>((const uint4 *)weight, (float4 *)wlo, n4);
+        const int rc = check_launch("yh_head_linear_loss (weight split)");
+        if (rc != 0) return rc;
+        if (!make_map(&ml, wlo, dtype, hl::kNOut, hl::kBN / per)) {
+            set_error("yh_head_linear_loss: cuTensorMapEncodeTiled failed");
+            return YH_ERR_UNSUPPORTED;
+        }
+    }
+    return per == 2 ? dispatch<2>(ma, mb, ml, a, ctas, dtype, g32, st) : dispatch<1>(ma, mb, ml, a, ctas, dtype, g32, st);
 }
