@@ -350,6 +350,8 @@ int yh_match_lists(const int64_t *det_off, const int32_t *det_cls, const double 
  *   grad [M, 1470] = grad_scale * d total / d prediction in `grad_dtype` (= dtype, or YH_F32), or NULL -- grad_scale is
  *   the GradScaler factor: fp16 cannot hold 2 d / M for a large M;
  *   pred_out [M, 1470] fp32 or NULL (feeds yh_map_update / yh_decode_nms directly).
+ *   workspace: yh_head_linear_loss_workspace_bytes() = a ticket word, one partial sum set per SM and 24 MB in which a YH_F32 call
+ *   keeps the part of the weight that TF32 drops (split off once per call); needed when tgt != NULL or dtype == YH_F32.
  * The caller finishes the layer's backward with two library GEMMs (d x = grad @ weight, d weight = grad^T @ x).
  * Accumulation is fp32; the loss arithmetic is yh_loss_fwd_bwd's on the same predictions, bit for bit; the five sums are
  * folded in a fixed order for a given GPU (one partial per SM).  Other shapes / dtypes: YH_ERR_UNSUPPORTED. */
