@@ -49,7 +49,7 @@ constexpr int kEpiGroups = 2;          // epilogue warps per TMEM lane quarter: 
 constexpr int kEpiWarps = 4 * kEpiGroups;
 constexpr int kThreads = 64 + 32 * kEpiWarps;   // TMA warp, MMA warp, epilogue warps
 #ifndef YH_HL_CONV_WARPS
-#define YH_HL_CONV_WARPS 6   // 2 / 4 / 6 warps: 4.57 / 4.13 / 3.99 ms at 65,536 rows (16 warps in all; they cost no registers over 14)
+#define YH_HL_CONV_WARPS 2   // 2 / 4 / 6 warps: 3.61 / 3.63 / 3.74 ms at 65,536 rows (12 warps keep 168 registers per thread; 14 - 16 leave 128)
 #endif
 constexpr int kConvWarps = YH_HL_CONV_WARPS;   // 3xTF32 only: warps that split a landed fp32 stage into its hi and lo parts
 static_assert(kNTiles * kCellsPerTile == kCells, "cells per tile");
