@@ -313,3 +313,29 @@ def test_non_finite_activations_stay_in_their_row():
         keep = torch.ones(M, dtype=torch.bool, device="cuda")
         keep[row] = False
         assert torch.isfinite(pred[keep]).all() and torch.equal(grad[keep], clean[keep])
+
+
+def test_second_backward_and_changing_upstream_gradient():
+    """The gradient buffer is rescaled in place by upstream / loss_scale; a second backward over a retained graph, with
+    another upstream factor, must not compound the first."""
+    from yolo_v1_b200 import FusedHeadLoss, YOLOLoss, synth
+
+    M = 200
+    g = torch.Generator(device="cuda").manual_seed(8)
+    x = torch.randn(M, 4096, device="cuda", generator=g) * 0.1
+    tgt = synth.make_targets(M, seed=8, p_obj=0.1, size_mix=True).cuda()
+    lin = torch.nn.Linear(4096, 1470).cuda()
+    with torch.no_grad():
+        lin.bias.add_(0.4)
+    fused = FusedHeadLoss(lin, YOLOLoss(), operand_dtype=torch.bfloat16, backward_dtype=torch.float32)
+    xr = x.clone().requires_grad_(True)
+    loss, _ = fused(xr, tgt)
+    loss.backward(retain_graph=True)
+    g1 = xr.grad.clone()
+    xr.grad = None
+    (loss * 3.0).backward(retain_graph=True)
+    g3 = xr.grad.clone()
+    xr.grad = None
+    loss.backward()
+    torch.testing.assert_close(g3, 3.0 * g1, rtol=1e-4, atol=1e-7)   # fp32 GEMMs of g and of 3 g: sums round differently
+    torch.testing.assert_close(xr.grad, g1, rtol=1e-4, atol=1e-7)

@@ -107,6 +107,8 @@ class _FusedFn(torch.autograd.Function):
                                         want_grad=need, grad_dtype=backward_dtype, want_pred=want_pred, precision=precision)
         ctx.save_for_backward(xo, wo, grad)
         ctx.grad_scale = grad_scale
+        # what `grad` has been multiplied by since the kernel wrote it (a device scalar: no host read in backward)
+        ctx.applied = torch.ones(1, dtype=torch.float32, device=xo.device) if grad is not None else None
         ctx.in_dtypes = (x.dtype, weight.dtype, None if bias is None else bias.dtype)
         ctx.mark_non_differentiable(parts)
         if pred is not None:
@@ -118,8 +120,17 @@ class _FusedFn(torch.autograd.Function):
         xo, wo, grad = ctx.saved_tensors
         if grad is None:
             return (None,) * 12
-        # grad already carries grad_scale; what arrives here is the scaler's factor again (or 1): apply the ratio
-        g = grad * (g_total.to(torch.float32) / ctx.grad_scale).to(grad.dtype)
+        # grad already carries grad_scale; what arrives here is the scaler's factor again (or 1): bring the buffer to
+        # upstream / grad_scale IN PLACE (yh_scale_inplace returns at once when the factor is exactly 1, the usual case;
+        # a second backward over a retained graph finds what the first one applied in ctx.applied)
+        want = (g_total.detach().to(torch.float32) / ctx.grad_scale).reshape(1)
+        factor = (want / ctx.applied).contiguous()
+        with _lib.on_device(grad.device):
+            rc = _lib.lib().yh_scale_inplace(grad.data_ptr(), _lib.dtype_code(grad), grad.numel(), factor.data_ptr(),
+                                             _lib.stream_ptr(grad.device))
+        _lib.check(rc, "yh_scale_inplace")
+        ctx.applied.copy_(want)
+        g = grad
         dx, dw, db = ctx.in_dtypes
         gx = gw = gb = None
         if ctx.needs_input_grad[0]:
